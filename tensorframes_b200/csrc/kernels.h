@@ -1,0 +1,38 @@
+// Launch wrappers for the hand-written sm_100a kernels. All launches are
+// asynchronous on `stream`; the callers own error checking of the stream.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "common.h"
+#include "graph.h"
+#include "program.h"
+
+namespace tfs {
+
+inline void cuda_check(cudaError_t e, const char* what) {
+  if (e != cudaSuccess)
+    fail(TFS_ERR_CUDA, std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")");
+}
+#define TFS_CUDA(call) ::tfs::cuda_check((call), #call)
+
+struct DeviceInfo {
+  int device = 0;
+  int sm_count = 148;
+};
+
+// K1: fused element-wise group over n elements. `wide` = the program touches a
+// 64-bit dtype. Returns the number of kernels launched.
+int launch_eltwise(const EltProgram& prog, int64_t n, bool wide, const DeviceInfo& dev, cudaStream_t stream);
+
+// K2: reduction of in[outer, inner] along axis 0 into out[inner].
+// `scratch` must hold reduce_scratch_bytes(...) bytes; its first 256 bytes are a
+// counter block that must be zero before the first launch (kernels re-zero it).
+size_t reduce_scratch_bytes(int dtype, int64_t outer, int64_t inner, const DeviceInfo& dev);
+int launch_reduce_axis0(int dtype, int red_op, const void* in, int64_t outer, int64_t inner, void* out,
+                        void* scratch, const DeviceInfo& dev, cudaStream_t stream);
+
+// Row reduction: in[outer, inner] along axis 1 into out[outer].
+int launch_reduce_rows(int dtype, int red_op, const void* in, int64_t outer, int64_t inner, void* out,
+                       const DeviceInfo& dev, cudaStream_t stream);
+
+}  // namespace tfs

@@ -1,0 +1,667 @@
+// Session: planning and execution. See session.h.
+#include "session.h"
+
+#include <algorithm>
+#include <map>
+#include <set>
+
+namespace tfs {
+namespace {
+
+constexpr size_t kAlign = 256;
+size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
+
+bool is_elt(const Node& n) {
+  return n.cls == OpClass::Unary || n.cls == OpClass::Binary || n.cls == OpClass::Fill;
+}
+bool is_compute_barrier(const Node& n) { return n.cls == OpClass::Reduce || n.cls == OpClass::MatMul; }
+
+// data operands of an element-wise node (Fill's dims input is a static attribute, not data)
+std::vector<int> elt_operands(const Node& n) {
+  if (n.cls == OpClass::Fill) return {n.in[1]};
+  return n.in;
+}
+
+bool is_device_pointer(const void* p) {
+  if (p == nullptr) return false;
+  cudaPointerAttributes a{};
+  cudaError_t e = cudaPointerGetAttributes(&a, p);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+struct Step {
+  enum Kind { ELT, REDUCE_AXIS0, REDUCE_ROWS, COPY, MATMUL } kind = ELT;
+  std::vector<int> nodes;   // ELT: the group (topological order); others: one node
+  Shape shape;              // ELT: iteration shape
+  int64_t outer = 0, inner = 0;  // reductions
+};
+
+}  // namespace
+
+struct Session::Plan {
+  std::vector<int> needed;            // topological
+  std::vector<Shape> shape;           // by node index
+  std::vector<int> feed_of;           // by node index: feed position or -1
+  std::vector<int> fetch_nodes;
+  std::vector<Step> steps;            // execution order
+  std::vector<int> step_of;           // by node index, -1 = not computed by a step
+  std::vector<char> materialize;      // by node index: output needs a device buffer
+};
+
+Session::Session(const Graph& g, int device) : g_(g) { dev_.device = device; }
+
+Session::~Session() {
+  if (!device_ready_) return;
+  cudaSetDevice(dev_.device);
+  cudaStreamSynchronize(stream_);
+  if (stream_ != own_stream_) cudaStreamSynchronize(own_stream_);
+  for (auto& kv : const_dev_) cudaFree(kv.second);
+  if (ws_) cudaFree(ws_);
+  if (red_scratch_) cudaFree(red_scratch_);
+  if (err_flag_) cudaFree(err_flag_);
+  if (err_host_) cudaFreeHost(err_host_);
+  if (own_stream_) cudaStreamDestroy(own_stream_);
+}
+
+void Session::ensure_device() {
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    cudaGetLastError();
+    fail(TFS_ERR_CUDA, "no CUDA device is available: libtfsb200 has no CPU execution path");
+  }
+  TFS_CHECK(dev_.device >= 0 && dev_.device < count, TFS_ERR_INVALID,
+            "device ordinal " + std::to_string(dev_.device) + " out of range (" + std::to_string(count) + " devices)");
+  TFS_CUDA(cudaSetDevice(dev_.device));
+  if (device_ready_) return;
+  cudaDeviceProp prop{};
+  TFS_CUDA(cudaGetDeviceProperties(&prop, dev_.device));
+  TFS_CHECK(prop.major >= 10, TFS_ERR_CUDA,
+            std::string("device '") + prop.name + "' is sm_" + std::to_string(prop.major) + std::to_string(prop.minor) +
+                "; this library is built for sm_100a (B200) only");
+  dev_.sm_count = prop.multiProcessorCount;
+  TFS_CUDA(cudaStreamCreateWithFlags(&own_stream_, cudaStreamNonBlocking));
+  if (!stream_) stream_ = own_stream_;
+  TFS_CUDA(cudaMalloc(reinterpret_cast<void**>(&err_flag_), kAlign));
+  TFS_CUDA(cudaMemset(err_flag_, 0, kAlign));
+  TFS_CUDA(cudaMallocHost(reinterpret_cast<void**>(&err_host_), sizeof(int32_t)));
+  *err_host_ = 0;
+  device_ready_ = true;
+}
+
+void Session::sync() {
+  if (!device_ready_) return;
+  TFS_CUDA(cudaSetDevice(dev_.device));
+  check_device_error();
+}
+
+void Session::check_device_error() {
+  TFS_CUDA(cudaMemcpyAsync(err_host_, err_flag_, sizeof(int32_t), cudaMemcpyDeviceToHost, stream_));
+  TFS_CUDA(cudaStreamSynchronize(stream_));
+  if (*err_host_ != 0) {
+    *err_host_ = 0;
+    TFS_CUDA(cudaMemsetAsync(err_flag_, 0, sizeof(int32_t), stream_));
+    TFS_CUDA(cudaStreamSynchronize(stream_));
+    fail(TFS_ERR_RUNTIME, "Integer division by zero");
+  }
+}
+
+void Session::reserve_workspace(size_t bytes) {
+  if (bytes <= ws_cap_) return;
+  TFS_CUDA(cudaStreamSynchronize(stream_));
+  if (ws_) TFS_CUDA(cudaFree(ws_));
+  ws_ = nullptr;
+  ws_cap_ = 0;
+  size_t cap = align_up(bytes + bytes / 8);
+  TFS_CUDA(cudaMalloc(reinterpret_cast<void**>(&ws_), cap));
+  ws_cap_ = cap;
+}
+
+void* Session::const_device(int node) {
+  auto it = const_dev_.find(node);
+  if (it != const_dev_.end()) return it->second;
+  const TensorValue& v = g_.nodes[size_t(node)].value;
+  void* p = nullptr;
+  size_t bytes = std::max<size_t>(v.bytes.size(), 16);
+  TFS_CUDA(cudaMalloc(&p, bytes));
+  if (!v.bytes.empty())
+    TFS_CUDA(cudaMemcpyAsync(p, v.bytes.data(), v.bytes.size(), cudaMemcpyHostToDevice, stream_));
+  // v.bytes is pageable: the copy above has been staged when the call returns.
+  const_dev_[node] = p;
+  return p;
+}
+
+// ---------------------------------------------------------------------------
+// Planning
+// ---------------------------------------------------------------------------
+void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<std::string>& fetch_names,
+                         Plan& plan) {
+  const size_t N = g_.nodes.size();
+  plan.shape.assign(N, Shape());
+  plan.feed_of.assign(N, -1);
+  plan.step_of.assign(N, -1);
+  plan.materialize.assign(N, 0);
+
+  for (size_t i = 0; i < feeds.size(); ++i) {
+    int idx = g_.find(feeds[i].name);
+    TFS_CHECK(idx >= 0, TFS_ERR_INVALID, "feed '" + feeds[i].name + "' is not a node of the graph");
+    const Node& n = g_.nodes[size_t(idx)];
+    TFS_CHECK(n.cls == OpClass::Placeholder, TFS_ERR_INVALID,
+              "Invalid type for input node " + n.name + ". It has to be a placeholder");
+    TFS_CHECK(plan.feed_of[size_t(idx)] < 0, TFS_ERR_INVALID, "placeholder '" + n.name + "' is fed twice");
+    // No implicit casting (reference: impl/DebugRowOps.scala:328-333).
+    TFS_CHECK(feeds[i].dtype == n.dtype, TFS_ERR_INVALID,
+              "The type of node '" + n.name + "' (" + dtype_name(n.dtype) +
+                  ") is not compatible with the data type of the feed (" + dtype_name(feeds[i].dtype) + ")");
+    const Shape& fs = feeds[i].shape;
+    TFS_CHECK(fs.fully_known(), TFS_ERR_INVALID, "feed '" + n.name + "' has unknown dimensions: " + fs.str());
+    // Shape.checkMorePreciseThan (reference: Shape.scala:54-59)
+    if (n.sshape.known_rank()) {
+      bool ok = n.sshape.rank == fs.rank;
+      for (int d = 0; ok && d < fs.rank; ++d) ok = n.sshape.d[d] < 0 || n.sshape.d[d] == fs.d[d];
+      TFS_CHECK(ok, TFS_ERR_INVALID,
+                "The data fed to '" + n.name + "' has shape " + fs.str() + " (not compatible) with shape " +
+                    n.sshape.str() + " requested by the TF graph");
+    }
+    plan.feed_of[size_t(idx)] = int(i);
+  }
+
+  for (const std::string& f : fetch_names) {
+    int idx = g_.find(f);
+    TFS_CHECK(idx >= 0, TFS_ERR_INVALID, "fetch '" + f + "' is not a node of the graph");
+    plan.fetch_nodes.push_back(idx);
+  }
+  TFS_CHECK(!plan.fetch_nodes.empty(), TFS_ERR_INVALID, "Output cannot be empty: no fetch requested");
+
+  // needed nodes, topological
+  std::vector<char> state(N, 0);
+  for (int root : plan.fetch_nodes) {
+    if (state[size_t(root)]) continue;
+    std::vector<std::pair<int, size_t>> stack{{root, 0}};
+    state[size_t(root)] = 1;
+    while (!stack.empty()) {
+      auto& [u, k] = stack.back();
+      const Node& nu = g_.nodes[size_t(u)];
+      if (k < nu.in.size()) {
+        int v = nu.in[k++];
+        if (!state[size_t(v)]) { state[size_t(v)] = 1; stack.push_back({v, 0}); }
+      } else {
+        plan.needed.push_back(u);
+        stack.pop_back();
+      }
+    }
+  }
+
+  // concrete shapes
+  for (int idx : plan.needed) {
+    const Node& n = g_.nodes[size_t(idx)];
+    if (n.cls == OpClass::Placeholder) {
+      int f = plan.feed_of[size_t(idx)];
+      TFS_CHECK(f >= 0, TFS_ERR_INVALID, "placeholder '" + n.name + "' is needed by the fetches but was not fed");
+      plan.shape[size_t(idx)] = feeds[size_t(f)].shape;
+    } else {
+      std::vector<Shape> in;
+      for (int k : n.in) in.push_back(plan.shape[size_t(k)]);
+      Shape s = infer_shape(g_, n, in);
+      TFS_CHECK(s.fully_known(), TFS_ERR_INVALID, "could not resolve the shape of node '" + n.name + "': " + s.str());
+      plan.shape[size_t(idx)] = s;
+    }
+  }
+
+  // levels: number of reduce/matmul nodes on the longest path below a node
+  std::vector<int> level(N, 0);
+  for (int idx : plan.needed) {
+    const Node& n = g_.nodes[size_t(idx)];
+    int l = 0;
+    for (int k : n.in) l = std::max(l, level[size_t(k)] + (is_compute_barrier(g_.nodes[size_t(k)]) ? 1 : 0));
+    level[size_t(idx)] = l;
+  }
+
+  // steps: element-wise nodes of equal (level, shape) fuse into one group
+  std::map<std::string, int> group_of_key;
+  for (int idx : plan.needed) {
+    const Node& n = g_.nodes[size_t(idx)];
+    if (is_elt(n)) {
+      std::string key = std::to_string(level[size_t(idx)]) + "|" + plan.shape[size_t(idx)].str();
+      auto it = group_of_key.find(key);
+      if (it == group_of_key.end()) {
+        Step s;
+        s.kind = Step::ELT;
+        s.shape = plan.shape[size_t(idx)];
+        plan.steps.push_back(s);
+        it = group_of_key.emplace(key, int(plan.steps.size()) - 1).first;
+      }
+      plan.steps[size_t(it->second)].nodes.push_back(idx);
+      plan.step_of[size_t(idx)] = it->second;
+    } else if (n.cls == OpClass::Reduce) {
+      Step s;
+      s.nodes = {idx};
+      const Shape& xs = plan.shape[size_t(n.in[0])];
+      std::vector<int> axes = normalize_axes(n, xs.rank);
+      const int k = int(axes.size());
+      bool leading = true, trailing = true;
+      for (int i = 0; i < k; ++i) {
+        leading = leading && axes[size_t(i)] == i;
+        trailing = trailing && axes[size_t(i)] == xs.rank - k + i;
+      }
+      if (k == 0) {
+        s.kind = Step::COPY;
+      } else if (leading) {
+        s.kind = Step::REDUCE_AXIS0;
+        s.outer = s.inner = 1;
+        for (int i = 0; i < xs.rank; ++i) (i < k ? s.outer : s.inner) *= xs.d[i];
+      } else if (trailing) {
+        s.kind = Step::REDUCE_ROWS;
+        s.outer = s.inner = 1;
+        for (int i = 0; i < xs.rank; ++i) (i < xs.rank - k ? s.outer : s.inner) *= xs.d[i];
+      } else {
+        fail(TFS_ERR_UNSUPPORTED, "node '" + n.name + "' (" + n.op +
+                                      "): only reductions over leading or trailing axes are supported, input shape " +
+                                      xs.str());
+      }
+      plan.steps.push_back(s);
+      plan.step_of[size_t(idx)] = int(plan.steps.size()) - 1;
+    } else if (n.cls == OpClass::MatMul) {
+      Step s;
+      s.kind = Step::MATMUL;
+      s.nodes = {idx};
+      plan.steps.push_back(s);
+      plan.step_of[size_t(idx)] = int(plan.steps.size()) - 1;
+    }
+  }
+
+  // order steps (Kahn) and mark which node outputs cross a step boundary
+  const size_t S = plan.steps.size();
+  std::vector<std::set<int>> deps(S);
+  for (int idx : plan.needed) {
+    int st = plan.step_of[size_t(idx)];
+    if (st < 0) continue;
+    const Node& n = g_.nodes[size_t(idx)];
+    std::vector<int> operands = is_elt(n) ? elt_operands(n) : std::vector<int>{n.in[0]};
+    if (n.cls == OpClass::MatMul) operands = n.in;
+    for (int k : operands) {
+      int sk = plan.step_of[size_t(k)];
+      if (sk != st) plan.materialize[size_t(k)] = 1;
+      if (sk >= 0 && sk != st) deps[size_t(st)].insert(sk);
+    }
+  }
+  for (int f : plan.fetch_nodes) plan.materialize[size_t(f)] = 1;
+  std::vector<int> order;
+  std::vector<char> placed(S, 0);
+  while (order.size() < S) {
+    bool progress = false;
+    for (size_t s = 0; s < S; ++s) {
+      if (placed[s]) continue;
+      bool ready = true;
+      for (int d : deps[s]) ready = ready && placed[size_t(d)];
+      if (ready) { placed[s] = 1; order.push_back(int(s)); progress = true; }
+    }
+    TFS_CHECK(progress, TFS_ERR_UNSUPPORTED, "internal: cyclic dependency between fused groups");
+  }
+  std::vector<Step> sorted;
+  std::vector<int> remap(S, 0);
+  for (size_t i = 0; i < S; ++i) { remap[size_t(order[i])] = int(i); sorted.push_back(plan.steps[size_t(order[i])]); }
+  plan.steps.swap(sorted);
+  for (int idx : plan.needed)
+    if (plan.step_of[size_t(idx)] >= 0) plan.step_of[size_t(idx)] = remap[size_t(plan.step_of[size_t(idx)])];
+}
+
+void Session::resolve(const std::vector<TensorArg>& feeds, std::vector<TensorArg>& fetches) {
+  Plan plan;
+  std::vector<std::string> names;
+  for (auto& f : fetches) names.push_back(f.name);
+  build_plan(feeds, names, plan);
+  for (size_t i = 0; i < fetches.size(); ++i) {
+    int idx = plan.fetch_nodes[i];
+    fetches[i].dtype = g_.nodes[size_t(idx)].dtype;
+    fetches[i].shape = plan.shape[size_t(idx)];
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Element-wise group -> accumulator-machine program
+// ---------------------------------------------------------------------------
+namespace {
+
+struct GroupCompiler {
+  const Graph& g;
+  const std::vector<Shape>& shape;
+  const std::vector<void*>& dev_ptr;
+  const std::vector<char>& materialize;
+  const Step& step;
+  EltProgram prog{};
+  bool wide = false;
+  std::set<int> members;
+  std::map<int, int> uses;        // remaining internal uses per member
+  std::map<int, int> tmp_of;      // member -> persistent tmp slot
+  std::set<int> done;
+  bool tmp_busy[kMaxTmp] = {false, false, false, false};
+
+  GroupCompiler(const Graph& g_, const std::vector<Shape>& sh, const std::vector<void*>& dp,
+                const std::vector<char>& mat, const Step& st)
+      : g(g_), shape(sh), dev_ptr(dp), materialize(mat), step(st) {
+    for (int n : step.nodes) members.insert(n);
+    for (int n : step.nodes) {
+      std::vector<int> ops = elt_operands(g.nodes[size_t(n)]);
+      if (ops.size() == 2 && ops[0] == ops[1]) ops.pop_back();
+      for (int o : ops)
+        if (members.count(o)) uses[o]++;
+      if (dtype_size(g.nodes[size_t(n)].dtype) == 8) wide = true;
+      for (int o : ops)
+        if (dtype_size(g.nodes[size_t(o)].dtype) == 8) wide = true;
+    }
+  }
+
+  const Node& node(int i) const { return g.nodes[size_t(i)]; }
+  uint8_t di(int n) const { return uint8_t(dtype_index(node(n).dtype)); }
+
+  Instr& emit(uint8_t op) {
+    TFS_CHECK(prog.n_instr < kMaxInstr, TFS_ERR_UNSUPPORTED,
+              "element-wise group too large for one kernel (" + std::to_string(kMaxInstr) + " instructions)");
+    Instr& in = prog.ins[prog.n_instr++];
+    in = Instr{};
+    in.op = op;
+    return in;
+  }
+  int alloc_tmp() {
+    for (int t = 0; t < kMaxTmp; ++t)
+      if (!tmp_busy[t]) { tmp_busy[t] = true; return t; }
+    fail(TFS_ERR_UNSUPPORTED, "element-wise expression needs more than " + std::to_string(kMaxTmp) + " live temporaries");
+  }
+  int buffer(int n, int64_t period) {
+    void* p = dev_ptr[size_t(n)];
+    TFS_CHECK(p != nullptr, TFS_ERR_INVALID, "internal: no device buffer for node '" + node(n).name + "'");
+    for (int i = 0; i < prog.n_bufs; ++i)
+      if (prog.bufs[i].ptr == p && prog.bufs[i].period == period) return i;
+    TFS_CHECK(prog.n_bufs < kMaxBufs, TFS_ERR_UNSUPPORTED,
+              "element-wise group touches more than " + std::to_string(kMaxBufs) + " tensors");
+    BufRef& b = prog.bufs[prog.n_bufs];
+    b.ptr = p;
+    b.period = period;
+    b.dt = di(n);
+    b.pad = 0;
+    return prog.n_bufs++;
+  }
+
+  // Fills src/arg/imm of `in` for operand `o` (an external tensor or a member held in a tmp).
+  void set_source(Instr& in, int o) {
+    if (members.count(o)) {
+      auto it = tmp_of.find(o);
+      TFS_CHECK(it != tmp_of.end(), TFS_ERR_INVALID, "internal: member operand without a temporary");
+      in.src = S_TMP;
+      in.arg = uint16_t(it->second);
+      if (--uses[o] == 0) { tmp_busy[it->second] = false; tmp_of.erase(it); }
+      return;
+    }
+    const Shape& os = shape[size_t(o)];
+    const Shape& it = step.shape;
+    const int64_t on = os.numel(), n = it.numel();
+    const Node& no = node(o);
+    if (on == 1 && no.cls == OpClass::Const) {
+      in.src = S_IMM;
+      uint64_t bits = 0;
+      memcpy(&bits, no.value.bytes.data(), size_t(dtype_size(no.dtype)));
+      in.imm = bits;
+      return;
+    }
+    if (on == n) {
+      in.src = S_BUF;
+      in.arg = uint16_t(buffer(o, 0));
+      return;
+    }
+    // row broadcast: operand dims (leading 1s dropped) must equal the trailing dims of the block
+    int lead = 0;
+    while (lead < os.rank && os.d[lead] == 1) ++lead;
+    const int k = os.rank - lead;
+    bool ok = k <= it.rank;
+    for (int i = 0; ok && i < k; ++i) ok = os.d[lead + i] == it.d[it.rank - k + i];
+    TFS_CHECK(ok, TFS_ERR_UNSUPPORTED,
+              "broadcasting " + os.str() + " against " + it.str() + " (operand '" + no.name +
+                  "') is not supported: only scalars and trailing-dimension broadcasts are");
+    in.src = S_PERIODIC;
+    in.arg = uint16_t(buffer(o, on));
+  }
+
+  bool needs_compute(int o) const { return members.count(o) && !tmp_of.count(o); }
+
+  void into_acc(int o) {
+    if (needs_compute(o)) {
+      compute(o, true);
+    } else {
+      Instr& in = emit(M_LOAD);
+      in.dt = di(o);
+      set_source(in, o);
+    }
+  }
+
+  // Leaves the value of member n in the accumulator.
+  void compute(int n, bool consumer_takes_acc) {
+    TFS_CHECK(!done.count(n), TFS_ERR_INVALID, "internal: element-wise node computed twice");
+    const Node& nd = node(n);
+    std::vector<int> ops = elt_operands(nd);
+    if (nd.cls == OpClass::Fill || nd.cls == OpClass::Unary) {
+      into_acc(ops[0]);
+      if (nd.cls == OpClass::Unary && nd.elt_op == E_CAST) {
+        Instr& in = emit(M_CAST);
+        in.dt = di(ops[0]);
+        in.dt2 = di(n);
+      } else if (nd.cls == OpClass::Unary && nd.elt_op != E_IDENTITY) {
+        Instr& in = emit(M_UNARY);
+        in.sub = uint8_t(nd.elt_op);
+        in.dt = di(n);
+      }
+    } else {
+      const int a = ops[0], b = ops[1];
+      auto bin = [&](int operand, bool swap) -> Instr& {
+        Instr& in = emit(M_BINARY);
+        in.sub = uint8_t(nd.elt_op);
+        in.dt = di(n);
+        in.flags = swap ? F_SWAP : 0;
+        (void)operand;
+        return in;
+      };
+      if (a == b) {
+        into_acc(a);
+        bin(a, false).src = S_ACC;
+      } else if (needs_compute(a) && needs_compute(b)) {
+        compute(a, true);
+        int t = alloc_tmp();
+        Instr& st = emit(M_STTMP);
+        st.arg = uint16_t(t);
+        compute(b, true);
+        Instr& in = bin(a, true);   // acc holds b, tmp holds a: result = op(tmp, acc)
+        in.src = S_TMP;
+        in.arg = uint16_t(t);
+        tmp_busy[t] = false;
+      } else if (needs_compute(b)) {
+        compute(b, true);
+        set_source(bin(a, true), a);
+      } else {
+        into_acc(a);
+        set_source(bin(b, false), b);
+      }
+    }
+    done.insert(n);
+    if (materialize[size_t(n)]) {
+      Instr& in = emit(M_STORE);
+      in.dt = di(n);
+      in.arg = uint16_t(buffer(n, 0));
+    }
+    int remaining = uses.count(n) ? uses[n] : 0;
+    if (consumer_takes_acc) remaining -= 1;
+    uses[n] = remaining;
+    if (remaining > 0) {
+      int t = alloc_tmp();
+      Instr& in = emit(M_STTMP);
+      in.arg = uint16_t(t);
+      tmp_of[n] = t;
+    }
+  }
+
+  void build(int32_t* err) {
+    prog.err = err;
+    for (int n : step.nodes)
+      if (materialize[size_t(n)] && !done.count(n)) compute(n, false);
+  }
+};
+
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// Execution
+// ---------------------------------------------------------------------------
+void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorArg>& fetches) {
+  Plan plan;
+  std::vector<std::string> names;
+  for (auto& f : fetches) names.push_back(f.name);
+  build_plan(feeds, names, plan);
+  for (size_t i = 0; i < fetches.size(); ++i) {
+    int idx = plan.fetch_nodes[i];
+    const Node& n = g_.nodes[size_t(idx)];
+    TFS_CHECK(fetches[i].data != nullptr || plan.shape[size_t(idx)].numel() == 0, TFS_ERR_INVALID,
+              "fetch '" + n.name + "' has no output buffer");
+    TFS_CHECK(fetches[i].dtype == 0 || fetches[i].dtype == n.dtype, TFS_ERR_INVALID,
+              "fetch '" + n.name + "' produces " + dtype_name(n.dtype) + " but the output buffer is declared " +
+                  dtype_name(fetches[i].dtype));
+    if (fetches[i].shape.known_rank())
+      TFS_CHECK(fetches[i].shape.fully_known() && fetches[i].shape.numel() == plan.shape[size_t(idx)].numel(),
+                TFS_ERR_INVALID,
+                "fetch '" + n.name + "' has shape " + plan.shape[size_t(idx)].str() + " but the output buffer is declared " +
+                    fetches[i].shape.str());
+  }
+  for (const Step& s : plan.steps)
+    TFS_CHECK(s.kind != Step::MATMUL, TFS_ERR_UNSUPPORTED, "MatMul execution is not available in this build");
+
+  ensure_device();
+  const size_t N = g_.nodes.size();
+  std::vector<void*> dev_ptr(N, nullptr);
+  auto nbytes = [&](int idx) { return size_t(plan.shape[size_t(idx)].numel()) * size_t(dtype_size(g_.nodes[size_t(idx)].dtype)); };
+
+  // classify caller pointers
+  bool any_host = false;
+  std::vector<char> feed_dev(feeds.size(), 0), fetch_dev(fetches.size(), 0);
+  for (size_t i = 0; i < feeds.size(); ++i) {
+    TFS_CHECK(feeds[i].data != nullptr || feeds[i].shape.numel() == 0, TFS_ERR_INVALID,
+              "feed '" + feeds[i].name + "' has a null data pointer");
+    feed_dev[i] = is_device_pointer(feeds[i].data);
+    if (!feed_dev[i]) any_host = true;
+  }
+  for (size_t i = 0; i < fetches.size(); ++i) {
+    fetch_dev[i] = is_device_pointer(fetches[i].data);
+    if (!fetch_dev[i]) any_host = true;
+  }
+
+  // workspace layout: staged host feeds, then every materialised node not bound to a caller buffer
+  size_t ws_bytes = 0;
+  std::vector<size_t> ws_off(N, SIZE_MAX);
+  bool needs_reduce_scratch = false;
+  size_t red_bytes = 0;
+  for (int idx : plan.needed) {
+    const Node& n = g_.nodes[size_t(idx)];
+    if (n.cls == OpClass::Placeholder) {
+      int f = plan.feed_of[size_t(idx)];
+      if (feed_dev[size_t(f)]) dev_ptr[size_t(idx)] = feeds[size_t(f)].data;
+      else { ws_off[size_t(idx)] = ws_bytes; ws_bytes += align_up(nbytes(idx)); }
+    } else if (n.cls == OpClass::Const) {
+      // uploaded lazily below
+    } else if (plan.materialize[size_t(idx)]) {
+      for (size_t i = 0; i < fetches.size() && !dev_ptr[size_t(idx)]; ++i)
+        if (plan.fetch_nodes[i] == idx && fetch_dev[i]) dev_ptr[size_t(idx)] = fetches[i].data;
+      if (!dev_ptr[size_t(idx)]) { ws_off[size_t(idx)] = ws_bytes; ws_bytes += align_up(std::max<size_t>(nbytes(idx), 16)); }
+    }
+  }
+  for (const Step& s : plan.steps) {
+    if (s.kind == Step::REDUCE_AXIS0) {
+      needs_reduce_scratch = true;
+      red_bytes = std::max(red_bytes, reduce_scratch_bytes(g_.nodes[size_t(s.nodes[0])].dtype, s.outer, s.inner, dev_));
+    }
+  }
+  reserve_workspace(ws_bytes);
+  for (int idx : plan.needed)
+    if (ws_off[size_t(idx)] != SIZE_MAX) dev_ptr[size_t(idx)] = ws_ + ws_off[size_t(idx)];
+  if (needs_reduce_scratch && red_bytes > red_scratch_cap_) {
+    TFS_CUDA(cudaStreamSynchronize(stream_));
+    if (red_scratch_) TFS_CUDA(cudaFree(red_scratch_));
+    red_scratch_ = nullptr;
+    red_scratch_cap_ = 0;
+    TFS_CUDA(cudaMalloc(&red_scratch_, red_bytes));
+    TFS_CUDA(cudaMemsetAsync(red_scratch_, 0, 256, stream_));
+    red_scratch_cap_ = red_bytes;
+  }
+  // constants that are read as tensors (anything but scalar immediates inside a group)
+  for (int idx : plan.needed) {
+    const Node& n = g_.nodes[size_t(idx)];
+    if (n.cls == OpClass::Const && plan.materialize[size_t(idx)]) dev_ptr[size_t(idx)] = const_device(idx);
+  }
+
+  // host -> device
+  for (int idx : plan.needed) {
+    const Node& n = g_.nodes[size_t(idx)];
+    if (n.cls != OpClass::Placeholder) continue;
+    int f = plan.feed_of[size_t(idx)];
+    if (!feed_dev[size_t(f)] && nbytes(idx) > 0)
+      TFS_CUDA(cudaMemcpyAsync(dev_ptr[size_t(idx)], feeds[size_t(f)].data, nbytes(idx), cudaMemcpyHostToDevice, stream_));
+  }
+
+  // steps
+  for (const Step& s : plan.steps) {
+    switch (s.kind) {
+      case Step::ELT: {
+        if (s.shape.numel() == 0) break;
+        GroupCompiler gc(g_, plan.shape, dev_ptr, plan.materialize, s);
+        gc.build(err_flag_);
+        launches_ += launch_eltwise(gc.prog, s.shape.numel(), gc.wide, dev_, stream_);
+        break;
+      }
+      case Step::REDUCE_AXIS0: {
+        const Node& n = g_.nodes[size_t(s.nodes[0])];
+        if (s.inner > 0)
+          launches_ += launch_reduce_axis0(n.dtype, n.red_op, dev_ptr[size_t(n.in[0])], s.outer, s.inner,
+                                           dev_ptr[size_t(s.nodes[0])], red_scratch_, dev_, stream_);
+        break;
+      }
+      case Step::REDUCE_ROWS: {
+        const Node& n = g_.nodes[size_t(s.nodes[0])];
+        launches_ += launch_reduce_rows(n.dtype, n.red_op, dev_ptr[size_t(n.in[0])], s.outer, s.inner,
+                                        dev_ptr[size_t(s.nodes[0])], dev_, stream_);
+        break;
+      }
+      case Step::COPY: {
+        const Node& n = g_.nodes[size_t(s.nodes[0])];
+        if (nbytes(s.nodes[0]) > 0)
+          TFS_CUDA(cudaMemcpyAsync(dev_ptr[size_t(s.nodes[0])], dev_ptr[size_t(n.in[0])], nbytes(s.nodes[0]),
+                                   cudaMemcpyDeviceToDevice, stream_));
+        break;
+      }
+      case Step::MATMUL:
+        break;
+    }
+  }
+
+  // results
+  for (size_t i = 0; i < fetches.size(); ++i) {
+    int idx = plan.fetch_nodes[i];
+    size_t bytes = nbytes(idx);
+    if (bytes == 0) continue;
+    void* src = dev_ptr[size_t(idx)];
+    TFS_CHECK(src != nullptr, TFS_ERR_INVALID, "internal: fetch '" + g_.nodes[size_t(idx)].name + "' was not produced");
+    if (fetch_dev[i]) {
+      if (src != fetches[i].data)
+        TFS_CUDA(cudaMemcpyAsync(fetches[i].data, src, bytes, cudaMemcpyDeviceToDevice, stream_));
+    } else {
+      TFS_CUDA(cudaMemcpyAsync(fetches[i].data, src, bytes, cudaMemcpyDeviceToHost, stream_));
+    }
+  }
+  if (any_host) check_device_error();
+}
+
+void Session::aggregate(int64_t, const int64_t*, const std::vector<TensorArg>&, const std::vector<TensorArg>&,
+                        int64_t, int64_t*, int64_t*) {
+  fail(TFS_ERR_UNSUPPORTED, "aggregate is not available in this build");
+}
+
+}  // namespace tfs

@@ -1,0 +1,65 @@
+// Session: one imported graph bound to one CUDA device.  It plans a run for the
+// concrete feed shapes (fused element-wise groups, reductions, matmul), owns the
+// stream / workspace / uploaded constants, and executes the steps.
+//
+// Stand-in for TF-Java's Session + Runner as the reference uses them
+// (impl/TensorFlowOps.scala:76-85, impl/DebugRowOps.scala:783-802, 900-917).
+#pragma once
+#include <memory>
+#include <unordered_map>
+#include <vector>
+
+#include "graph.h"
+#include "kernels.h"
+
+namespace tfs {
+
+struct TensorArg {
+  std::string name;
+  int dtype = 0;
+  Shape shape;
+  void* data = nullptr;
+};
+
+class Session {
+ public:
+  Session(const Graph& g, int device);
+  ~Session();
+  Session(const Session&) = delete;
+  Session& operator=(const Session&) = delete;
+
+  void set_stream(cudaStream_t s) { stream_ = s ? s : own_stream_; }
+  void sync();
+  int64_t launches() const { return launches_; }
+
+  // Fills fetches[i].dtype / .shape for the given feed shapes. No CUDA work.
+  void resolve(const std::vector<TensorArg>& feeds, std::vector<TensorArg>& fetches);
+  void run(const std::vector<TensorArg>& feeds, const std::vector<TensorArg>& fetches);
+  void aggregate(int64_t n_rows, const int64_t* keys, const std::vector<TensorArg>& feeds,
+                 const std::vector<TensorArg>& fetches, int64_t max_groups, int64_t* out_keys,
+                 int64_t* n_groups);
+
+ private:
+  struct Plan;
+  void ensure_device();
+  void build_plan(const std::vector<TensorArg>& feeds, const std::vector<std::string>& fetch_names, Plan& plan);
+  void* const_device(int node);
+  void reserve_workspace(size_t bytes);
+  void check_device_error();
+
+  Graph g_;
+  DeviceInfo dev_;
+  bool device_ready_ = false;
+  cudaStream_t own_stream_ = nullptr;
+  cudaStream_t stream_ = nullptr;
+  char* ws_ = nullptr;
+  size_t ws_cap_ = 0;
+  void* red_scratch_ = nullptr;
+  size_t red_scratch_cap_ = 0;
+  int32_t* err_flag_ = nullptr;       // device
+  int32_t* err_host_ = nullptr;       // pinned
+  std::unordered_map<int, void*> const_dev_;
+  int64_t launches_ = 0;
+};
+
+}  // namespace tfs

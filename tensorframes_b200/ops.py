@@ -1,0 +1,393 @@
+"""Block executors over the C ABI: the counterpart of the reference's DebugRowOps.
+
+Reference: src/main/scala/org/tensorframes/Operations.scala:20-135 (the operator
+interface), src/main/scala/org/tensorframes/impl/DebugRowOps.scala (schema
+validation :80-170 and :305-372, mapBlocks :290-393, reduceBlocks :503-526,
+aggregate :547-592, performMap :766-803, performReduceBlock :872-895),
+impl/TensorFlowOps.scala:101-141 (analyzeGraphTF), impl/TFDataOps.scala:27-59
+and :128-169 (block packing / unpacking rules), impl/DataOps.scala:105-144
+(inferPhysicalShape).
+
+What stays on the host is what the reference does on the Spark driver: name and
+type validation with the reference's error messages, output schema, per-partition
+bookkeeping.  Every tensor operation goes through tfs_session_run /
+tfs_session_aggregate on the device; nothing in this module computes on data.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import _native, dsl
+from .frame import (ColumnInformation, GroupedData, Row, SparkTFColInfo, StructField, StructType, TensorFrame,
+                    analyze as _analyze, explain as _explain, _to_python)
+from .shape import ScalarType, Shape, ShapeDescription, Unknown
+
+
+@dataclass(frozen=True)
+class GraphNodeSummary:
+    """impl/TensorFlowOps.scala:163-169"""
+    isPlaceholder: bool
+    isInput: bool
+    isOutput: bool
+    scalarType: ScalarType
+    shape: Shape
+    name: str
+
+
+def _strip0(name: str) -> str:
+    return name[:-2] if name.endswith(":0") else name
+
+
+def analyze_graph(graph: _native.Graph, hints: ShapeDescription) -> List[GraphNodeSummary]:
+    """Inputs = zero-input Placeholders; outputs = requested fetches; dtype and shape from the
+    library's static analysis, the hinted shape winning (impl/TensorFlowOps.scala:101-141)."""
+    outputs = {_strip0(f) for f in hints.requestedFetches}
+    res = []
+    for name, op in graph.nodes():
+        dtype, shape, is_ph, n_in = graph.node_info(name)
+        is_input = is_ph and n_in == 0
+        is_output = name in outputs
+        if not (is_input or is_output):
+            continue
+        hinted = hints.out.get(name, hints.out.get(name + ":0"))
+        s = hinted if hinted is not None else shape
+        if s is None:
+            raise Exception(f"The shape of node '{name}' is unknown and no shape hint was given for it")
+        res.append(GraphNodeSummary(is_input, is_input, is_output, dtype, s, name))
+    missing = outputs - {r.name for r in res}
+    if missing:
+        raise Exception(f"Requested fetches are not in the graph: {', '.join(sorted(missing))}")
+    return res
+
+
+def infer_physical_shape(num_scalars: int, cell: Shape, expected_rows: Optional[int]) -> Tuple[int, Shape]:
+    """Row count and cell shape of an output block from its element count (impl/DataOps.scala:105-144)."""
+    if sum(1 for d in cell.dims if d == Unknown) > 1:
+        raise ValueError(f"Shape has too many unkown values to perform inference: {cell}")
+    h = []
+    for d in cell.dims:
+        if d < 0:
+            break
+        h.append(d)
+    t = list(cell.dims[len(h) + 1:]) if len(h) < len(cell.dims) else []
+    p = int(np.prod(h, dtype=np.int64)) * int(np.prod(t, dtype=np.int64))
+    if expected_rows is None and cell.hasUnknown:
+        raise ValueError(f"Cannot infer the final cell shape: {cell}")
+    if expected_rows is not None and not cell.hasUnknown:
+        if num_scalars != p * expected_rows:
+            raise ValueError(f"Expected {p * expected_rows} elements in the final buffer,"
+                             f"but got {num_scalars} instead. shape={cell}, numRows={expected_rows}")
+        return expected_rows, cell
+    if expected_rows is not None:
+        inferred = num_scalars // (p * expected_rows) if p * expected_rows else 0
+        shape = Shape(h + [inferred] + t)
+        assert shape.numElements * expected_rows == num_scalars, \
+            f"Incompatible values: shape={cell} numRows={expected_rows} numScalars={num_scalars}"
+        return expected_rows, shape
+    rows = num_scalars // p if p else 0
+    assert (cell.numElements or 0) * rows == num_scalars, \
+        f"Incompatible values: shape={cell} numRows={rows} numScalars={num_scalars}"
+    return rows, cell
+
+
+def _as_graph(fetches) -> Tuple[bytes, ShapeDescription]:
+    nodes: List[dsl.Node] = []
+    for f in fetches:
+        nodes.extend(f if isinstance(f, (list, tuple)) else [f])
+    g = dsl.build_graph(*nodes)
+    return g, dsl.hints(nodes)
+
+
+@dataclass(frozen=True)
+class ReduceBlockSchema:
+    """impl/DebugRowOps.scala:36-40"""
+    mapInput: StructType
+    mapTFCols: Tuple[int, ...]
+    output: StructType
+    reduceInput: StructType
+
+
+def _widen_lead(f: StructField) -> StructField:
+    ci = ColumnInformation.of(f)
+    if ci.stf is not None and ci.stf.shape.numDims >= 1:
+        s = ci.stf.shape.tail.prepend(Unknown)
+        return ColumnInformation(f, SparkTFColInfo(s, ci.stf.dataType)).merged
+    return f
+
+
+def reduce_blocks_schema(schema: StructType, graph: _native.Graph, hints: ShapeDescription) -> ReduceBlockSchema:
+    """The X / X_input naming contract and its checks (impl/DebugRowOps.scala:80-170)."""
+    from dataclasses import replace
+    summary = {s.name: s for s in analyze_graph(graph, hints)}
+    fields_by_name = {f.name: f for f in schema.fields}
+    field_names = ", ".join(sorted(fields_by_name))
+    outputs = {k: v for k, v in summary.items() if v.isOutput}
+    output_names = ", ".join(sorted(outputs))
+    suffix = "_input"
+
+    missing_cols = sorted(set(outputs) - set(fields_by_name))
+    if missing_cols:
+        raise Exception(f"Based on the TF graph, some inputs are missing: {', '.join(missing_cols)}. "
+                        f"Dataframe columns: {field_names}; Outputs: {output_names}")
+    inputs = {k: v for k, v in summary.items() if v.isInput}
+    expected = {o + suffix for o in outputs}
+    extra = sorted(set(inputs) - expected)
+    if extra:
+        raise Exception(f"Extra graph inputs have been found: {', '.join(extra)}. Dataframe columns: {field_names}")
+    missing = sorted(expected - set(inputs))
+    if missing:
+        raise Exception(f"Some inputs are missing in the graph: {', '.join(missing)}. Dataframe columns: {field_names}")
+
+    out_fields = []
+    for f in schema.fields:  # keep the DataFrame's column order
+        if f.name not in outputs:
+            continue
+        stf = ColumnInformation.of(f).stf
+        if stf is None:
+            raise Exception(f"Data column '{f.name}' has not been analyzed yet, cannot run TF on this dataframe")
+        out = summary[f.name]
+        if stf.dataType != out.scalarType:
+            raise Exception(f"Output '{f.name}' has type {out.scalarType} but the column type is {stf.dataType}")
+        cell = stf.shape.tail
+        if not out.shape.checkMorePreciseThan(cell):
+            raise Exception(f"Output '{f.name}' has shape {out.shape}, not compatible with the shape "
+                            f"of field elements {cell}")
+        in_shape = cell.prepend(Unknown)
+        in_name = f.name + suffix
+        inp = summary.get(in_name)
+        if inp is None:
+            raise Exception(f"The graph needs to have a placeholder input called {in_name}.")
+        assert inp.isPlaceholder, f"Node {in_name} should be a placeholder"
+        if not in_shape.checkMorePreciseThan(inp.shape):
+            raise Exception(f"The data column '{f.name}' has shape {in_shape}, not compatible with shape"
+                            f" {inp.shape} requested by the TF graph")
+        if stf.dataType != inp.scalarType:
+            raise Exception(f"The type of node '{inp.name}' ({stf.dataType}) is not compatible with the data"
+                            f" type of the column ({inp.scalarType})")
+        out_fields.append(ColumnInformation(f, SparkTFColInfo(in_shape, stf.dataType)).merged)
+    output_schema = StructType(tuple(out_fields))
+    map_input = StructType(tuple(_widen_lead(replace(f, name=f.name + suffix)) if f.name in outputs else f
+                                 for f in schema.fields))
+    reduce_input = StructType(tuple(_widen_lead(replace(f, name=f.name + suffix))
+                                    for f in schema.fields if f.name in outputs))
+    idx = tuple(i for i, f in enumerate(schema.fields) if f.name in outputs)
+    return ReduceBlockSchema(map_input, idx, output_schema, reduce_input)
+
+
+class B200Ops:
+    """OperationsInterface (Operations.scala:20-135) executed on a B200 through libtfsb200."""
+
+    def __init__(self, device: int = 0):
+        self.device = device
+
+    def __repr__(self) -> str:
+        return f"B200Ops(device={self.device})"
+
+    # ---- helpers -------------------------------------------------------------------
+    @staticmethod
+    def _graph_args(args) -> Tuple[bytes, ShapeDescription]:
+        """(graph_bytes, hints) given either DSL nodes or an explicit (bytes, ShapeDescription)."""
+        if len(args) == 2 and isinstance(args[0], (bytes, bytearray)) and isinstance(args[1], ShapeDescription):
+            return bytes(args[0]), args[1]
+        return _as_graph(args)
+
+    @staticmethod
+    def _dense_block(df: TensorFrame, part: Dict[str, object], name: str, n_rows: int) -> np.ndarray:
+        """The [n_rows, cell...] block of a column, with the checks of TFDataOps.convert
+        (impl/TFDataOps.scala:36-52) and TensorConverter (impl/datatypes.scala:80-83)."""
+        f = df.schema[name]
+        ci = ColumnInformation.of(f).stf
+        if ci is None:
+            raise Exception(f"Could not column information for column {f}")
+        if ci.shape.numDims < 1:
+            raise Exception(f"Column {f} found to be scalar, but its dimensions should be >= 1")
+        lead = ci.shape.dims[0]
+        if lead != Unknown and lead != n_rows:
+            raise Exception(f"Lead dimension for column {f} (found to be {lead}) is not compatible with a block of "
+                            f"size {n_rows}. Expected block structure: {df.schema}, meta info = {ci}")
+        cell = ci.shape.tail
+        if cell.hasUnknown:
+            raise AssertionError(f"Shape {cell} has unknown values.")
+        col = part[name]
+        if not isinstance(col, np.ndarray):
+            raise Exception(f"Column '{name}' holds ragged or non-numeric cells and cannot be packed as a block")
+        if tuple(col.shape[1:]) != cell.dims:
+            raise Exception(f"Column '{name}' cells have shape {Shape(col.shape[1:])} but the metadata says {cell}")
+        if cell.numDims > 2:
+            raise Exception(f"Higher order dimension {cell.numDims} from shape {cell} is not supported")
+        return col
+
+    # ---- mapBlocks (impl/DebugRowOps.scala:290-393, 766-803) ---------------------------
+    def mapBlocks(self, df: TensorFrame, *fetches) -> TensorFrame:
+        g, h = self._graph_args(fetches)
+        return self._map_blocks(df, g, h, append_input=True)
+
+    def mapBlocksTrimmed(self, df: TensorFrame, *fetches) -> TensorFrame:
+        g, h = self._graph_args(fetches)
+        return self._map_blocks(df, g, h, append_input=False)
+
+    def _map_blocks(self, df: TensorFrame, graph_bytes: bytes, hints: ShapeDescription, append_input: bool) -> TensorFrame:
+        with _native.Graph(graph_bytes) as graph:
+            summary = {s.name: s for s in analyze_graph(graph, hints)}
+            inputs = {k: v for k, v in summary.items() if v.isInput}
+            outputs = {k: v for k, v in summary.items() if v.isOutput}
+            fields_by_name = {f.name: f for f in df.schema.fields}
+            cols = ", ".join(df.schema.fieldNames)
+            for inp in inputs.values():
+                f = fields_by_name.get(inp.name)
+                if f is None:
+                    raise Exception(f"Graph input {inp.name} found, but no column to match it. Dataframe columns: {cols}")
+                stf = ColumnInformation.of(f).stf
+                if stf is None:
+                    raise Exception(f"Data column {f.name} has not been analyzed yet, cannot run TF on this dataframe")
+                if stf.dataType != inp.scalarType:
+                    raise Exception(f"The type of node '{inp.name}' ({stf.dataType}) is not compatible with the data type "
+                                    f"of the column ({inp.scalarType})")
+                if not stf.shape.checkMorePreciseThan(inp.shape):
+                    raise Exception(f"The data column '{f.name}' has shape {stf.shape} (not compatible) with shape"
+                                    f" {inp.shape} requested by the TF graph")
+                if not inp.isPlaceholder:
+                    raise Exception(f"Invalid type for input node {inp.name}. It has to be a placeholder")
+            out_fields = []
+            for out in sorted(outputs.values(), key=lambda o: o.name):
+                if out.name in fields_by_name:
+                    raise Exception(f"TF graph has an output node called '{out.name}', but this column already exists. "
+                                    f"Input columns: {cols}")
+                out_fields.append(ColumnInformation.structField(out.name, out.scalarType, out.shape))
+            tf_schema = StructType(tuple(out_fields))
+            out_schema = StructType(tf_schema.fields + (df.schema.fields if append_input else ()))
+            fetch_names = [f.name for f in tf_schema.fields]
+            input_names = list(inputs.keys())
+
+            parts = []
+            with _native.Session(graph, self.device) as session:
+                for part in df.partitions:
+                    n = df._part_len(part)
+                    if n == 0:          # empty partitions never reach the runtime (:380-390, :777-779)
+                        continue
+                    feeds = {name: self._dense_block(df, part, name, n) for name in input_names}
+                    outs = session.run(feeds, fetch_names)
+                    new_part: Dict[str, object] = {}
+                    rows_seen = []
+                    for f, arr in zip(tf_schema.fields, outs):
+                        info = ColumnInformation.of(f).stf
+                        n_rows, cell = infer_physical_shape(int(arr.size), info.shape.tail, n if append_input else None)
+                        rows_seen.append(n_rows)
+                        if cell.numDims > 2:
+                            raise ValueError(f"Operations for tensors of order {cell.numDims + 1} are not supported")
+                        new_part[f.name] = arr.reshape((n_rows,) + cell.dims)
+                    if len(set(rows_seen)) != 1:
+                        raise Exception(f"Multiple number of rows detected. tf_struct={tf_schema}, tfSizes = {rows_seen}")
+                    assert (not append_input) or rows_seen[0] == n, \
+                        f"Incompatible sizes detected: appendInput={append_input}, tf num rows = {rows_seen[0]}, " \
+                        f"input num rows = {n}"
+                    if append_input:
+                        for name in df.schema.fieldNames:
+                            new_part[name] = part[name]
+                    parts.append(new_part)
+        return TensorFrame(out_schema, parts)
+
+    # ---- reduceBlocks (impl/DebugRowOps.scala:503-526, 872-895) -----------------------
+    def reduceBlocks(self, df: TensorFrame, *fetches) -> Row:
+        g, h = self._graph_args(fetches)
+        with _native.Graph(g) as graph:
+            schemas = reduce_blocks_schema(df.schema, graph, h)
+            out_names = [f.name for f in schemas.output.fields]
+            partials: List[List[np.ndarray]] = []
+            with _native.Session(graph, self.device) as session:
+                for part in df.partitions:
+                    n = df._part_len(part)
+                    if n == 0:
+                        continue
+                    feeds = {name + "_input": self._dense_block(df, part, name, n) for name in out_names}
+                    partials.append(session.run(feeds, out_names))
+                if not partials:
+                    raise ValueError("empty collection")  # RDD.reduce on an empty RDD (:524)
+                result = partials[0]
+                if len(partials) > 1:
+                    # The reference merges partition results pairwise by running the same graph on
+                    # 2-row blocks (:741-750); one run over the stacked [P, cell...] block is the same
+                    # merge for the associative reducers the contract allows.
+                    feeds = {name + "_input": np.stack([p[i] for p in partials]) for i, name in enumerate(out_names)}
+                    result = session.run(feeds, out_names)
+        for f, arr in zip(schemas.output.fields, result):
+            cell = ColumnInformation.of(f).stf.shape.tail
+            if cell.numElements is not None and int(arr.size) != cell.numElements:
+                raise ValueError(f"Expected {cell.numElements} elements in the final buffer,but got {arr.size} instead. "
+                                 f"shape={cell}, numRows=1")
+        return Row.of(out_names, [_to_python(a) for a in result])
+
+    # ---- aggregate (impl/DebugRowOps.scala:547-592, TensorFlowUDAF :601-695) ------------
+    def aggregate(self, grouped: GroupedData, *fetches) -> TensorFrame:
+        g, h = self._graph_args(fetches)
+        df = grouped.df
+        with _native.Graph(g) as graph:
+            schemas = reduce_blocks_schema(df.schema, graph, h)
+            out_names = [f.name for f in schemas.output.fields]
+            key_names = list(grouped.keys)
+            # key columns -> dense int64 ids (the grouping itself is Spark's job in the reference);
+            # a single integer key column is used as is, bit for bit.
+            key_cols = {k: [] for k in key_names}
+            blocks = {n: [] for n in out_names}
+            for part in df.partitions:
+                n = df._part_len(part)
+                if n == 0:
+                    continue
+                for k in key_names:
+                    c = part[k]
+                    key_cols[k].extend(c.tolist() if isinstance(c, np.ndarray) else list(c))
+                for name in out_names:
+                    blocks[name].append(self._dense_block(df, part, name, n))
+            total = len(key_cols[key_names[0]]) if key_names else 0
+            if total == 0:
+                return TensorFrame(StructType(tuple(df.schema[k] for k in key_names) + schemas.output.fields), [])
+            single_int = len(key_names) == 1 and all(isinstance(v, int) and not isinstance(v, bool)
+                                                      for v in key_cols[key_names[0]])
+            if single_int:
+                ids = np.asarray(key_cols[key_names[0]], dtype=np.int64)
+                decode = None
+            else:
+                tuples = list(zip(*[key_cols[k] for k in key_names]))
+                table: Dict[tuple, int] = {}
+                ids = np.empty(total, dtype=np.int64)
+                for i, t in enumerate(tuples):
+                    ids[i] = table.setdefault(t, len(table))
+                decode = list(table.keys())
+            feeds = {name + "_input": np.concatenate(blocks[name]) for name in out_names}
+            with _native.Session(graph, self.device) as session:
+                # output capacity: every row its own group at worst; for big blocks size it exactly
+                max_groups = total if total <= (1 << 20) else int(np.unique(ids).size)
+                keys_out, outs = session.aggregate(ids, feeds, out_names, max_groups)
+        part: Dict[str, object] = {}
+        if decode is None:
+            kf = df.schema[key_names[0]]
+            part[key_names[0]] = keys_out.astype(kf.dataType.np_dtype) if isinstance(kf.dataType, ScalarType) else keys_out
+        else:
+            for ki, k in enumerate(key_names):
+                vals = [decode[int(i)][ki] for i in keys_out]
+                kf = df.schema[k]
+                part[k] = np.asarray(vals, dtype=kf.dataType.np_dtype) if isinstance(kf.dataType, ScalarType) else vals
+        for f, arr in zip(schemas.output.fields, outs):
+            part[f.name] = arr
+        schema = StructType(tuple(df.schema[k] for k in key_names) + schemas.output.fields)
+        return TensorFrame(schema, [part])
+
+    # ---- analysis --------------------------------------------------------------------
+    def analyze(self, df: TensorFrame) -> TensorFrame:
+        return _analyze(df)
+
+    def explain(self, df: TensorFrame) -> str:
+        return _explain(df)
+
+
+_default: Optional[B200Ops] = None
+
+
+def default_ops() -> B200Ops:
+    global _default
+    if _default is None:
+        _default = B200Ops(0)
+    return _default
