@@ -1,0 +1,422 @@
+#!/usr/bin/env python
+"""bench.py -- throughput of the TensorFrames block path on B200.
+
+    python bench.py --gpus N --steps K --warmup W            (N > 1: launched under torchrun)
+    python bench.py --impl reference --gpus N --steps K --warmup W
+
+Headline workload (BASELINE.json configs[1], name in config.workload): reduce_blocks with
+y = reduce_sum(y_input, [0]) and z = reduce_min(z_input, [0]) over two analysed
+DoubleType[?,2] columns of 100M synthetic rows per GPU.  A "step" is one pass of that block
+through the reducer graph (N > 1: one partition per GPU, weak scaling, plus the exchange of the
+cell-sized partial rows and the merge run).
+
+  value      rows/s, whole job, inputs resident in HBM, timed with CUDA events on the launch stream
+  e2e        the same metric through the C ABI with HOST (pinned) column buffers: H2D of the block
+             and D2H of the result row are inside the timed region
+  roofline   the dominant kernel (reduce_axis0_flat_kernel) against the measured HBM peak
+  cpu_baseline / --impl reference   oracle/cpu_ref.c, the restatement of the reference's
+             per-block algorithm, on the host cores (the real Spark + TF-CPU stack is not installable here)
+
+--workload c3 measures map_blocks on the fused chain of BASELINE config 3 instead.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+ROWS_C2 = 100_000_000
+ROWS_C3 = 1_000_000_000
+ALG_BYTES_PER_ROW = {"c2": 32, "c3": 12}
+FALLBACK_HBM_GBS = 6650.0                   # /opt/skills/guides/B200_PROFILING.md
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+def hbm_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return FALLBACK_HBM_GBS, "fallback"
+
+
+def ncu_traffic(workload):
+    """Per-launch DRAM bytes of the dominant kernel from the committed ncu capture, if any."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(workload)
+    except Exception:
+        return None
+
+
+class ClockSampler:
+    """SM clock + throttle reasons during the timed region (NVML)."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _loop(self):
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def __enter__(self):
+        if self.nv:
+            self._thread = threading.Thread(target=self._loop, daemon=True)
+            self._thread.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._thread:
+            self._thread.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+# ---------------------------------------------------------------------------------------------
+def build_graph(workload):
+    import tensorframes_b200 as tfs
+    from tensorframes_b200 import dsl
+    with dsl.withGraph():
+        if workload == "c2":
+            y = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("y_input")
+            z = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("z_input")
+            return dsl.build_graph(dsl.reduce_sum(y, [0]).named("y"), dsl.reduce_min(z, [0]).named("z"))
+        x = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x")
+        return dsl.build_graph(dsl.cast(dsl.maximum(x * 1.5 + 0.25, 0.0), tfs.FloatType).named("z"))
+
+
+def make_inputs(torch, workload, rows, seed, device):
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    if workload == "c2":
+        u = torch.rand(rows, generator=g, device=device, dtype=torch.float64)
+        y = torch.stack([u, -u], dim=1).contiguous()
+        u = torch.rand(rows, generator=g, device=device, dtype=torch.float64)
+        z = torch.stack([u, -u], dim=1).contiguous()
+        return {"y_input": y, "z_input": z}
+    x = torch.rand(rows, generator=g, device=device, dtype=torch.float64) * 2.0 - 1.0
+    return {"x": x}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from tensorframes_b200 import _native
+    from tensorframes_b200.distributed import combine_reduce_blocks
+
+    world = env_int("WORLD_SIZE", 1)
+    rank = env_int("RANK", 0)
+    local = env_int("LOCAL_RANK", 0)
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run --nproc-per-node N")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    wl = args.workload
+    rows = args.rows or (ROWS_C2 if wl == "c2" else ROWS_C3)
+    DA = _native.DeviceArray.from_torch
+
+    graph_bytes = build_graph(wl)
+    graph = _native.Graph(graph_bytes)
+    sess = _native.Session(graph, local)
+    stream = torch.cuda.current_stream()
+    sess.set_stream(stream.cuda_stream)
+    feeds_t = make_inputs(torch, wl, rows, seed=(2 if wl == "c2" else 3) + 1000 * rank, device=device)
+    feeds = {k: DA(v) for k, v in feeds_t.items()}
+    if wl == "c2":
+        outs_t = {"y": torch.empty(2, dtype=torch.float64, device=device),
+                  "z": torch.empty(2, dtype=torch.float64, device=device)}
+        merged_t = {k: torch.empty_like(v) for k, v in outs_t.items()}
+    else:
+        outs_t = {"z": torch.empty(rows, dtype=torch.float32, device=device)}
+        merged_t = {}
+    outs = {k: DA(v) for k, v in outs_t.items()}
+    names = list(outs_t)
+
+    def merge(feeds_stacked):
+        sess.run_into({k: DA(v) for k, v in feeds_stacked.items()}, {k: DA(v) for k, v in merged_t.items()})
+        return [merged_t[n] for n in names]
+
+    kernel_events = []
+
+    def step(timed):
+        if timed:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+        sess.run_into(feeds, outs)
+        if timed:
+            e1.record(stream)
+            kernel_events.append((e0, e1))
+        if wl == "c2" and world > 1:
+            combine_reduce_blocks([outs_t[n] for n in names], names, merge)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step(False)
+    barrier()
+    launches0 = sess.launch_count
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clocks:
+        barrier()
+        start.record(stream)
+        for _ in range(args.steps):
+            step(True)
+        end.record(stream)
+        barrier()
+    elapsed_ms = start.elapsed_time(end)
+    launches = sess.launch_count - launches0
+    big_launches = args.steps * (2 if wl == "c2" else 1)
+    kernel_ms = sum(a.elapsed_time(b) for a, b in kernel_events)
+    t = torch.tensor([elapsed_ms], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    elapsed_ms = float(t.item())
+
+    # parity spot check on the device (the tests hold the real parity checks)
+    if wl == "c2":
+        res = merged_t if world > 1 else outs_t
+        if world == 1:
+            y = feeds_t["y_input"]
+            ref_sum = y.sum(dim=0)
+            assert torch.all((res["y"] - ref_sum).abs() <= 1e-12 * y.abs().sum(dim=0)), (res["y"], ref_sum)
+            assert torch.equal(res["z"], feeds_t["z_input"].min(dim=0).values)
+    else:
+        n_chk = min(rows, 1 << 24)
+        x = feeds_t["x"][:n_chk]
+        assert torch.equal(outs_t["z"][:n_chk], torch.clamp_min(x * 1.5 + 0.25, 0.0).to(torch.float32))
+
+    # ---- end to end: host (pinned) column buffers through the same C-ABI call -----------------
+    e2e = None
+    host_in = {}
+    pinned = []
+    h2d = sum(v.numel() * v.element_size() for v in feeds_t.values())
+    d2h = sum(v.numel() * v.element_size() for v in outs_t.values())
+    if not args.no_e2e:
+        try:
+            for k, v in feeds_t.items():
+                pb = _native.PinnedBuffer(tuple(v.shape), np.float64)
+                pinned.append(pb)
+                torch.from_numpy(pb.array).copy_(v)       # fill the pinned block once, outside the timing
+                host_in[k] = pb.array
+            host_out = {}
+            for k, v in outs_t.items():
+                pb = _native.PinnedBuffer(tuple(v.shape), np.float64 if v.dtype == torch.float64 else np.float32)
+                pinned.append(pb)
+                host_out[k] = pb.array
+            torch.cuda.synchronize()
+            k_e2e = max(1, min(args.steps, 5))
+
+            def e2e_step():
+                sess.run_into(host_in, host_out)      # H2D + kernels + D2H + sync inside
+                if wl == "c2" and world > 1:
+                    parts = [torch.from_numpy(host_out[n]).to(device) for n in names]
+                    combine_reduce_blocks(parts, names, merge)
+                    torch.cuda.synchronize()
+
+            e2e_step()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(k_e2e):
+                e2e_step()
+            barrier()
+            dt = time.perf_counter() - t0
+            tt = torch.tensor([dt], dtype=torch.float64, device=device)
+            if world > 1:
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            e2e = {"value": world * rows * k_e2e / float(tt.item()), "unit": "rows/s", "steps": k_e2e,
+                   "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)}
+            if wl == "c2" and world == 1:
+                assert np.array_equal(host_out["z"], outs_t["z"].cpu().numpy())
+        except Exception as exc:   # e.g. not enough pinnable host memory on this box
+            e2e = {"value": None, "unit": "rows/s", "error": str(exc)[:200],
+                   "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)}
+
+    # ---- CPU baseline beside it (rank 0, N = 1 only): the oracle's restatement of the reference ----
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        have_host = len(host_in) == len(feeds_t)
+        cpu = cpu_baseline_leg(wl, host_in if have_host else {k: v.cpu().numpy() for k, v in feeds_t.items()}, rows)
+    host_in = {}
+    for pb in pinned:
+        pb.free()
+
+    if rank == 0:
+        peak, peak_src = hbm_peak()
+        alg = ALG_BYTES_PER_ROW[wl]
+        bytes_per_launch = rows * alg / (2 if wl == "c2" else 1)
+        avg_launch_s = kernel_ms / 1e3 / big_launches
+        achieved = bytes_per_launch / avg_launch_s / 1e9
+        line = {
+            "metric": "rows/s for reduceBlocks (reduce_sum + reduce_min over DoubleType[?,2])" if wl == "c2"
+                      else "rows/s for mapBlocks (fused x*a+b, max(.,0), cast f32 on a float64 column)",
+            "value": world * rows * args.steps / (elapsed_ms / 1e3),
+            "unit": "rows/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": elapsed_ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": ("BASELINE configs[1]: reduce_blocks reduce_sum+reduce_min, DoubleType[?,2], "
+                                    if wl == "c2" else
+                                    "BASELINE configs[2]: map_blocks fused chain cast_f32(max(x*1.5+0.25,0)), float64 column, ")
+                                   + f"{rows} rows per GPU", "rows_per_gpu": rows, "partitions": world,
+                       "l2": "inputs larger than L2 (no flush needed)",
+                       "exchange": "all_gather of partial rows + merge run" if (wl == "c2" and world > 1) else "none"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": ncu_traffic(wl), "peak_source": peak_src,
+                         "kernel": "reduce_axis0_flat_kernel" if wl == "c2" else "eltwise_kernel",
+                         "algorithmic_bytes_per_launch": bytes_per_launch,
+                         "avg_launch_ms": avg_launch_s * 1e3, "frac_of_nominal_8000": achieved / 8000.0},
+            "e2e": e2e,
+            "gpu_launches": int(launches),
+            "clocks": clocks.summary(),
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_baseline_leg(wl, host_feeds, rows, budget_s=12.0):
+    """oracle/cpu_ref.c on a bounded sample: the whole block if it finishes within the budget,
+    else a prefix sized from a calibration run."""
+    from oracle import cpu_baseline as cb
+    cores = cb.cores()
+    if wl == "c2":
+        y, z = host_feeds["y_input"], host_feeds["z_input"]
+        probe = min(rows, 2_000_000)
+        t, _ = cb.timed(cb.reduce_blocks_sum_min, y[:probe], z[:probe], cores, cores)
+        sample = int(min(rows, max(probe, budget_s / max(t, 1e-6) * probe / 3)))
+        t, (s, m) = cb.timed(cb.reduce_blocks_sum_min, y[:sample], z[:sample], cores, cores, repeat=3)
+    else:
+        x = host_feeds["x"]
+        probe = min(rows, 4_000_000)
+        t, _ = cb.timed(cb.map_blocks_chain, x[:probe], 1.5, 0.25, cores, cores)
+        sample = int(min(rows, max(probe, budget_s / max(t, 1e-6) * probe / 3)))
+        t, _ = cb.timed(cb.map_blocks_chain, x[:sample], 1.5, 0.25, cores, cores, repeat=3)
+    return {"value": sample / t, "unit": "rows/s", "cores": cores, "kind": "port",
+            "sample": f"first {sample} rows of the same block, {cores} partitions on {cores} threads, best of 3; "
+                      "columnar unboxed input, so an upper bound on the JVM reference"}
+
+
+def run_reference(args):
+    """The reference arm: the restatement of the reference's own CPU algorithm (oracle/cpu_ref.c),
+    all host threads, same workload / metric / unit. Rank 0 only."""
+    rank = env_int("RANK", 0)
+    if rank != 0:
+        return
+    from oracle import cpu_baseline as cb
+    wl = args.workload
+    cores = cb.cores()
+    rows_full = args.rows or (ROWS_C2 if wl == "c2" else ROWS_C3)
+    rng = np.random.default_rng(2 if wl == "c2" else 3)
+    # bounded sample: sized so that warmup + steps stay within a few minutes
+    sample = min(rows_full, 20_000_000 if wl == "c2" else 50_000_000)
+    if wl == "c2":
+        u = rng.random(sample)
+        y = np.stack([u, -u], axis=1)
+        u = rng.random(sample)
+        z = np.stack([u, -u], axis=1)
+        fn = lambda: cb.reduce_blocks_sum_min(y, z, cores, cores)
+    else:
+        x = rng.random(sample) * 2.0 - 1.0
+        fn = lambda: cb.map_blocks_chain(x, 1.5, 0.25, cores, cores)
+    for _ in range(args.warmup):
+        fn()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        fn()
+    dt = time.perf_counter() - t0
+    value = sample * args.steps / dt
+    desc = (f"{sample} rows per step (bounded sample of the {rows_full}-row block), {cores} partitions on "
+            f"{cores} threads; oracle/cpu_ref.c restates the reference's per-block algorithm on columnar input "
+            "(Spark + TF-Java are not installable here)")
+    line = {
+        "impl": "reference",
+        "metric": "rows/s for reduceBlocks (reduce_sum + reduce_min over DoubleType[?,2])" if wl == "c2"
+                  else "rows/s for mapBlocks (fused x*a+b, max(.,0), cast f32 on a float64 column)",
+        "value": value, "unit": "rows/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": ("BASELINE configs[1]: reduce_blocks reduce_sum+reduce_min, DoubleType[?,2], "
+                                if wl == "c2" else "BASELINE configs[2]: map_blocks fused chain, float64 column, ")
+                               + f"{rows_full} rows per GPU", "rows_per_gpu": rows_full},
+        "cpu_baseline": {"value": value, "unit": "rows/s", "cores": cores, "kind": "port", "sample": desc},
+        "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3"])
+    ap.add_argument("--rows", type=int, default=0, help="rows per GPU (default: the BASELINE config's)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    import __graft_entry__ as entry
+    if not os.path.exists(entry.LIB_PATH) or not os.path.exists(entry.ORACLE_LIB):
+        if env_int("LOCAL_RANK", 0) == 0:
+            entry.build()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

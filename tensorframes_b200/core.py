@@ -86,11 +86,7 @@ def print_schema(dframe: TensorFrame) -> None:
 def block(df: TensorFrame, col_name: str, tf_name: str = None):
     """Placeholder for a block of a column; the lead dimension is always left unknown, as the
     python reference does (core.py:338-351, 386-390)."""
-    ph = dsl.block(df, col_name, tf_name)
-    shape = list(ph.shape.dims)
-    if shape:
-        shape[0] = dsl.Unknown
-    return dsl.placeholder(ph.scalarType, *shape).named(tf_name if tf_name is not None else col_name)
+    return dsl._extract_placeholder(df, col_name, tf_name, True, unknown_lead=True)
 
 
 def row(df: TensorFrame, col_name: str, tf_name: str = None):

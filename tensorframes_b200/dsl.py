@@ -363,7 +363,8 @@ def matmul(a: Node, b: Node, transpose_a: bool = False, transpose_b: bool = Fals
                                "transpose_b": AttrValue.of_bool(transpose_b)})
 
 
-def _extract_placeholder(df, col_name: str, tf_name: Optional[str], block_: bool) -> Node:
+def _extract_placeholder(df, col_name: str, tf_name: Optional[str], block_: bool,
+                         unknown_lead: bool = False) -> Node:
     """Placeholder typed and shaped from a column's metadata (dsl/DslImpl.scala:90-107)."""
     from .frame import ColumnInformation
     field = next((f for f in df.schema.fields if f.name == col_name), None)
@@ -373,6 +374,8 @@ def _extract_placeholder(df, col_name: str, tf_name: Optional[str], block_: bool
     if stf is None:
         raise Exception(f"The datatype of column '{col_name}' could not be understood by tensorframes: {field}")
     shape = stf.shape if block_ else stf.shape.tail
+    if block_ and unknown_lead and shape.numDims > 0:
+        shape = shape.tail.prepend(Unknown)
     return placeholder(stf.dataType, *shape.dims).named(tf_name if tf_name is not None else col_name)
 
 

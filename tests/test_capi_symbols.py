@@ -1,0 +1,63 @@
+"""The C-ABI library loads and exports exactly what include/tfs_b200.h declares. No compute."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+import tensorframes_b200 as tfs
+from tensorframes_b200 import _native, dsl
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    text = open(os.path.join(ROOT, "include", "tfs_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(tfs_[a-z_0-9]+)\s*\(", text)))
+
+
+def test_header_and_binding_agree():
+    assert _declared() == sorted(_native.SYMBOLS)
+
+
+def test_library_exports_every_declared_symbol():
+    lib = ctypes.CDLL(_native.LIB_PATH)
+    for name in _declared():
+        assert hasattr(lib, name), name
+
+
+def test_version_and_error_string():
+    lib = _native.lib()
+    assert lib.tfs_version() >= 100
+    h = ctypes.c_void_p()
+    assert lib.tfs_graph_import(b"\xff\xff", 2, ctypes.byref(h)) == _native.TFS_ERR_INVALID
+    assert b"GraphDef" in lib.tfs_last_error()
+    assert not h
+
+
+def test_resolve_needs_no_device():
+    with dsl.withGraph():
+        x = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("x_input")
+        g = dsl.build_graph(dsl.reduce_sum(x, [0]).named("x"), dsl.cast(x, tfs.FloatType).named("c"))
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        metas = s.resolve({"x_input": np.zeros((7, 2))}, ["x", "c"])
+        assert metas == [(tfs.DoubleType, (2,)), (tfs.FloatType, (7, 2))]
+        with pytest.raises(_native.NativeError, match="not compatible with the data type"):
+            s.resolve({"x_input": np.zeros((7, 2), np.float32)}, ["x"])
+        with pytest.raises(_native.NativeError, match="not compatible\\) with shape"):
+            s.resolve({"x_input": np.zeros((7, 3))}, ["x"])
+        with pytest.raises(_native.NativeError, match="was not fed"):
+            s.resolve({}, ["x"])
+
+
+@pytest.mark.skipif(_native.device_count() > 0, reason="checks the no-GPU failure mode")
+def test_run_without_gpu_fails_loudly():
+    with dsl.withGraph():
+        x = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x")
+        g = dsl.build_graph((x + 3.0).named("z"))
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        with pytest.raises(_native.NativeError) as e:
+            s.run({"x": np.arange(10.0)}, ["z"])
+        assert e.value.code == _native.TFS_ERR_CUDA and "no CPU execution path" in str(e.value)

@@ -1,0 +1,401 @@
+"""Parity tests proper: the CUDA path (through the C ABI, and through the python operators that
+sit on it) against the oracle and the reference's golden vectors.  Needs a B200.
+
+Bars: integer, index and key results bit-exact; element-wise floating point bit-exact (same IEEE
+operations in the same order as TF-CPU, no FMA contraction); floating-point reductions within
+1e-12 (f64) / 1e-5 (f32) of the exact sum, measured normwise (|gpu - exact| <= tol * sum|x|):
+reduction order is the only permitted difference.
+"""
+import numpy as np
+import pytest
+
+import _golden
+import tensorframes_b200 as tfs
+from oracle import tf_ops
+from tensorframes_b200 import _native, dsl
+from tensorframes_b200.frame import TensorFrame
+
+pytestmark = pytest.mark.gpu
+
+G = _golden.load()
+T = {"f32": tfs.FloatType, "f64": tfs.DoubleType, "i32": tfs.IntegerType, "i64": tfs.LongType}
+TOL = {np.dtype("float64"): 1e-12, np.dtype("float32"): 1e-5}
+
+
+def run_native(graph_bytes, feeds, fetches):
+    with _native.Graph(graph_bytes) as g, _native.Session(g, 0) as s:
+        return s.run(feeds, fetches)
+
+
+def rand(rng, st, shape, lo=-100, hi=100, nonzero=False):
+    if st.np_dtype.kind == "f":
+        a = rng.uniform(lo, hi, shape).astype(st.np_dtype)
+        if nonzero:
+            a = np.where(np.abs(a) < 0.5, a + np.sign(a + 0.1) * 1.0, a).astype(st.np_dtype)
+    else:
+        a = rng.integers(lo, hi, shape).astype(st.np_dtype)
+        if nonzero:
+            a = np.where(a == 0, 7, a).astype(st.np_dtype)
+    return a
+
+
+def assert_same(got, want):
+    assert got.dtype == want.dtype and got.shape == want.shape, (got.dtype, want.dtype, got.shape, want.shape)
+    assert got.tobytes() == want.tobytes(), np.argwhere(got != want)[:5]
+
+
+# ---- the reference's golden vectors through the product's operators --------------------------------
+@pytest.mark.parametrize("case", G["cases"], ids=[c["id"] for c in G["cases"]])
+def test_golden_through_operators(case):
+    df = _golden.build_frame(case)
+    kind = case["kind"]
+    with dsl.withGraph():
+        fetches = _golden.build_fetches(case, df)
+        if kind == "map_blocks":
+            out = tfs.map_blocks(fetches, df)
+        elif kind == "map_blocks_trimmed":
+            out = tfs.map_blocks(fetches, df, trim=True)
+        elif kind == "reduce_blocks":
+            res = tfs.reduce_blocks(fetches, df)
+            res = res if isinstance(res, list) else [res]
+            got = [r.tolist() if isinstance(r, np.ndarray) else r for r in res]
+            assert got == case["expected"]
+            return
+        elif kind == "aggregate":
+            out = tfs.aggregate(fetches, df.groupBy(*case["keys"]))
+    if case.get("expected_columns"):
+        assert out.columns == case["expected_columns"]
+    if kind == "map_blocks" and not case.get("select"):
+        # direct executor test of the reference: TF columns first, then the inputs
+        assert out.columns[0] == case["graph"]["fetches"][0]
+    sel = out.select(*case["select"]) if case.get("select") else out
+    assert _golden.normalize(sel.collect()) == _golden.normalize(case["expected"])
+
+
+# ---- element-wise: every op x dtype x ragged sizes, bit-exact --------------------------------------
+SIZES = [1, 2, 3, 5, 1023, 1024, 1025, 4099, 100003]
+
+
+@pytest.mark.parametrize("dt", list(T))
+@pytest.mark.parametrize("n", SIZES)
+def test_binary_ops_bit_exact(dt, n):
+    st = T[dt]
+    rng = np.random.default_rng(n)
+    a, b = rand(rng, st, n), rand(rng, st, n, nonzero=True)
+    with dsl.withGraph():
+        pa = dsl.placeholder(st, dsl.Unknown).named("a")
+        pb = dsl.placeholder(st, dsl.Unknown).named("b")
+        outs = [dsl.add(pa, pb).named("o_add"), dsl.sub(pa, pb).named("o_sub"), dsl.mul(pa, pb).named("o_mul"),
+                dsl.div(pa, pb).named("o_div"), dsl.minimum(pa, pb).named("o_min"), dsl.maximum(pa, pb).named("o_max")]
+        g = dsl.build_graph(*outs)
+    names = [o.name for o in outs]
+    got = run_native(g, {"a": a, "b": b}, names)
+    want = tf_ops.evaluate(g, {"a": a, "b": b}, names)
+    for gg, ww in zip(got, want):
+        assert_same(gg, ww)
+
+
+@pytest.mark.parametrize("dt", list(T))
+@pytest.mark.parametrize("n", [1, 7, 1025, 100003])
+def test_unary_and_cast_bit_exact(dt, n):
+    st = T[dt]
+    rng = np.random.default_rng(n + 1)
+    a = rand(rng, st, n, nonzero=True)
+    with dsl.withGraph():
+        p = dsl.placeholder(st, dsl.Unknown).named("a")
+        outs = [dsl.neg(p).named("o_neg"), dsl.relu(p).named("o_relu"), dsl.identity(p).named("o_id"),
+                dsl._build("Square", parents=[p]).named("o_sq"), dsl._build("Abs", parents=[p]).named("o_abs")]
+        if st.np_dtype.kind == "f":
+            outs += [dsl._build("Sqrt", parents=[dsl._build("Abs", parents=[p])]).named("o_sqrt"),
+                     dsl._build("Reciprocal", parents=[p]).named("o_rcp")]
+        for k, dst in T.items():
+            outs.append(dsl.cast(p, dst).named("o_cast_" + k))
+        g = dsl.build_graph(*outs)
+    names = [o.name for o in outs]
+    got = run_native(g, {"a": a}, names)
+    want = tf_ops.evaluate(g, {"a": a}, names)
+    for name, gg, ww in zip(names, got, want):
+        assert_same(gg, ww)
+
+
+def test_config3_chain_bit_exact():
+    """BASELINE config 3 at a size the oracle finishes in seconds: cast_f32(max(x*a+b, 0))."""
+    rng = np.random.default_rng(3)
+    x = rng.uniform(-1, 1, 3_000_001)
+    with dsl.withGraph():
+        p = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x")
+        z = dsl.cast(dsl.maximum(p * 1.5 + 0.25, 0.0), tfs.FloatType).named("z")
+        g = dsl.build_graph(z)
+    (got,) = run_native(g, {"x": x}, ["z"])
+    (want,) = tf_ops.evaluate(g, {"x": x}, ["z"])
+    assert_same(got, want)
+    # no FMA contraction: x*a+b must round twice
+    assert_same(got, np.maximum((x * 1.5) + 0.25, 0.0).astype(np.float32))
+
+
+def test_dag_programs():
+    """Shared sub-expressions, both operands computed, x+x, several fetches, row broadcast."""
+    rng = np.random.default_rng(11)
+    n = 5003
+    x, y = rng.uniform(-4, 4, (n, 3)), rng.uniform(1, 2, (n, 3))
+    w = np.asarray([0.5, -2.0, 3.0])
+    with dsl.withGraph():
+        px = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 3).named("x")
+        py = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 3).named("y")
+        s = (px + py)                       # used three times
+        d = (px - py) * (px + px)           # both sides computed; x + x
+        o1 = (s * s).named("o1")
+        o2 = ((s / py) - d).named("o2")
+        o3 = (dsl.constant(w) * px + dsl.constant(w)).named("o3")   # [3] against [n,3]
+        o4 = dsl.cast(dsl.minimum(d, s), tfs.LongType).named("o4")
+        o5 = (2.0 - px).named("o5")         # constant on the left of a non-commutative op
+        o6 = (py / (px * px + 1.0)).named("o6")
+        g = dsl.build_graph(o1, o2, o3, o4, o5, o6)
+    names = ["o1", "o2", "o3", "o4", "o5", "o6"]
+    got = run_native(g, {"x": x, "y": y}, names)
+    want = tf_ops.evaluate(g, {"x": x, "y": y}, names)
+    for gg, ww in zip(got, want):
+        assert_same(gg, ww)
+
+
+def test_mixed_width_program():
+    rng = np.random.default_rng(12)
+    n = 70001
+    a = rng.integers(-1000, 1000, n).astype(np.int32)
+    b = rng.uniform(-10, 10, n).astype(np.float32)
+    with dsl.withGraph():
+        pa = dsl.placeholder(tfs.IntegerType, dsl.Unknown).named("a")
+        pb = dsl.placeholder(tfs.FloatType, dsl.Unknown).named("b")
+        o1 = (dsl.cast(pa, tfs.DoubleType) * dsl.cast(pb, tfs.DoubleType)).named("o1")
+        o2 = dsl.cast(dsl.cast(pa, tfs.LongType) * dsl.constant(np.int64(1 << 33)), tfs.FloatType).named("o2")
+        o3 = (pa * pa).named("o3")
+        g = dsl.build_graph(o1, o2, o3)
+    got = run_native(g, {"a": a, "b": b}, ["o1", "o2", "o3"])
+    want = tf_ops.evaluate(g, {"a": a, "b": b}, ["o1", "o2", "o3"])
+    for gg, ww in zip(got, want):
+        assert_same(gg, ww)
+
+
+def test_integer_wraparound_and_division():
+    a = np.array([2**31 - 1, -2**31, 7, -7, 7, -7], dtype=np.int32)
+    b = np.array([1, -1, 2, 2, -2, -2], dtype=np.int32)
+    with dsl.withGraph():
+        pa = dsl.placeholder(tfs.IntegerType, dsl.Unknown).named("a")
+        pb = dsl.placeholder(tfs.IntegerType, dsl.Unknown).named("b")
+        g = dsl.build_graph((pa + pb).named("s"), (pa * pb).named("m"), dsl.div(pa, pb).named("q"))
+    s, m, q = run_native(g, {"a": a, "b": b}, ["s", "m", "q"])
+    assert s.tolist() == [-2**31, 2**31 - 1, 9, -5, 5, -9]
+    assert q.tolist()[2:] == [3, -3, -3, 3]
+    want = tf_ops.evaluate(g, {"a": a[2:], "b": b[2:]}, ["s", "m", "q"])
+    assert m[2:].tolist() == want[1].tolist()
+
+
+def test_integer_division_by_zero_is_an_error():
+    with dsl.withGraph():
+        pa = dsl.placeholder(tfs.LongType, dsl.Unknown).named("a")
+        pb = dsl.placeholder(tfs.LongType, dsl.Unknown).named("b")
+        g = dsl.build_graph(dsl.div(pa, pb).named("q"))
+    a = np.arange(1, 1001, dtype=np.int64)
+    b = np.ones(1000, dtype=np.int64)
+    bad = b.copy()
+    bad[777] = 0
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        with pytest.raises(_native.NativeError) as e:
+            s.run({"a": a, "b": bad}, ["q"])
+        assert e.value.code == _native.TFS_ERR_RUNTIME and "Integer division by zero" in str(e.value)
+        (q,) = s.run({"a": a, "b": b}, ["q"])       # the session stays usable
+        assert q.tolist() == a.tolist()
+
+
+# ---- block reductions ----------------------------------------------------------------------------
+RED = {"sum": dsl.reduce_sum, "min": dsl.reduce_min, "max": dsl.reduce_max}
+
+
+def check_reduction(got, want, x, axis):
+    if x.dtype.kind == "f" and want.dtype.kind == "f":
+        scale = np.abs(x.astype(np.float64)).sum(axis=axis)
+        assert got.dtype == want.dtype and got.shape == want.shape
+        err = np.abs(got.astype(np.float64) - want.astype(np.float64))
+        assert np.all(err <= TOL[x.dtype] * np.maximum(scale, 1e-300)), float((err / np.maximum(scale, 1e-300)).max())
+    else:
+        assert_same(got, want)
+
+
+@pytest.mark.parametrize("dt", list(T))
+@pytest.mark.parametrize("op", list(RED))
+@pytest.mark.parametrize("shape", [(1,), (2,), (1000,), (100003,), (7, 2), (100003, 2), (1001, 3), (4097, 5),
+                                   (3001, 64), (501, 100), (37, 1000), (1, 2), (300001, 1), (129, 4, 2)])
+def test_axis0_reductions(dt, op, shape):
+    st = T[dt]
+    rng = np.random.default_rng(sum(shape))
+    x = rand(rng, st, shape)
+    with dsl.withGraph():
+        p = dsl.placeholder(st, dsl.Unknown, *shape[1:]).named("x_input")
+        g = dsl.build_graph(RED[op](p, [0]).named("x"))
+    (got,) = run_native(g, {"x_input": x}, ["x"])
+    (want,) = tf_ops.evaluate(g, {"x_input": x}, ["x"])
+    if op == "sum":
+        check_reduction(got, want, x, 0)
+    else:
+        assert_same(got, want)
+
+
+@pytest.mark.parametrize("dt", ["f64", "i32"])
+def test_all_axes_and_trailing_axis_reductions(dt):
+    st = T[dt]
+    rng = np.random.default_rng(5)
+    x = rand(rng, st, (1031, 7))
+    with dsl.withGraph():
+        p = dsl.placeholder(st, dsl.Unknown, 7).named("x")
+        outs = [dsl.reduce_sum(p, None).named("all"), dsl.reduce_max(p, [1]).named("rows"),
+                dsl.reduce_sum(p, [1]).named("rowsum"), dsl.reduce_min(p, [0, 1]).named("allmin")]
+        g = dsl.build_graph(*outs)
+    names = ["all", "rows", "rowsum", "allmin"]
+    got = run_native(g, {"x": x}, names)
+    want = tf_ops.evaluate(g, {"x": x}, names)
+    check_reduction(got[0], want[0], x, None)
+    assert_same(got[1], want[1])
+    check_reduction(got[2], want[2], x, 1)
+    assert_same(got[3], want[3])
+
+
+def test_exact_sum_reference_f64():
+    """The f64 block sum against math.fsum (the correctly rounded sum), config-2 shape."""
+    rng = np.random.default_rng(2)
+    u = rng.uniform(0, 1, 200_000)
+    y = np.stack([u, -u], axis=1)
+    with dsl.withGraph():
+        p = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("y_input")
+        g = dsl.build_graph(dsl.reduce_sum(p, [0]).named("y"), dsl.reduce_min(p, [0]).named("z"))
+    s, m = run_native(g, {"y_input": y}, ["y", "z"])
+    exact = tf_ops.exact_sum_f64(y, 0)
+    assert np.all(np.abs(s - exact) <= 1e-12 * np.abs(y).sum(axis=0))
+    assert m.tolist() == y.min(axis=0).tolist()
+
+
+def test_reduction_is_deterministic():
+    rng = np.random.default_rng(9)
+    x = rng.normal(size=(1_000_003, 2))
+    with dsl.withGraph():
+        p = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("x_input")
+        g = dsl.build_graph(dsl.reduce_sum(p, [0]).named("x"))
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        first = s.run({"x_input": x}, ["x"])[0]
+        for _ in range(5):
+            assert s.run({"x_input": x}, ["x"])[0].tobytes() == first.tobytes()
+
+
+def test_reduce_then_map_in_one_graph():
+    """A fetch computed from a reduction (scalar operand produced on the device, second fused group)."""
+    rng = np.random.default_rng(21)
+    x = rng.uniform(1, 2, (4001, 2))
+    with dsl.withGraph():
+        p = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("x")
+        centered = (p - dsl.reduce_min(p, [0])).named("centered")
+        frac = (p / dsl.reduce_max(p, None)).named("frac")
+        g = dsl.build_graph(centered, frac)
+    got = run_native(g, {"x": x}, ["centered", "frac"])
+    want = tf_ops.evaluate(g, {"x": x}, ["centered", "frac"])
+    for gg, ww in zip(got, want):
+        assert_same(gg, ww)
+
+
+def test_constants_fill_and_zero_rows():
+    with dsl.withGraph():
+        p = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x")
+        g = dsl.build_graph(dsl.fill([5], 2.5).named("f"), dsl.constant([[1.0, 2.0]]).named("c"),
+                            dsl.reduce_sum(dsl.constant([1.0, 1.0]), [0]).named("s"), (p + 1.0).named("y"),
+                            dsl.reduce_sum(p, [0]).named("e"))
+    f, c, s, y, e = run_native(g, {"x": np.zeros(0)}, ["f", "c", "s", "y", "e"])
+    assert f.tolist() == [2.5] * 5 and c.tolist() == [[1.0, 2.0]] and s.item() == 2.0
+    assert y.shape == (0,) and e.item() == 0.0
+
+
+# ---- device-resident buffers (no host copies), unaligned pointers ---------------------------------
+def test_device_pointer_path_matches_host_path():
+    torch = pytest.importorskip("torch")
+    rng = np.random.default_rng(31)
+    n = 1_000_001
+    x = rng.uniform(-1, 1, n + 1)
+    y = rng.uniform(0, 1, (n, 2))
+    with dsl.withGraph():
+        px = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x")
+        py = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("y_input")
+        g = dsl.build_graph(dsl.cast(dsl.maximum(px * 1.5 + 0.25, 0.0), tfs.FloatType).named("z"),
+                            dsl.reduce_sum(py, [0]).named("y"))
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        host = s.run({"x": x[1:], "y_input": y}, ["z", "y"])
+        dx = torch.from_numpy(x).cuda()[1:]        # 8-byte aligned only: exercises the scalar variant
+        dy = torch.from_numpy(y).cuda()
+        dz = torch.empty(n, dtype=torch.float32, device="cuda")
+        ds = torch.empty(2, dtype=torch.float64, device="cuda")
+        s.set_stream(torch.cuda.current_stream().cuda_stream)
+        s.run_into({"x": _native.DeviceArray.from_torch(dx.contiguous()) if dx.data_ptr() % 16 == 0 else
+                    _native.DeviceArray(dx.data_ptr(), tfs.DoubleType, (n,), owner=dx),
+                    "y_input": _native.DeviceArray.from_torch(dy)},
+                   {"z": _native.DeviceArray.from_torch(dz), "y": _native.DeviceArray.from_torch(ds)})
+        s.sync()
+        assert dx.data_ptr() % 16 == 8
+        assert dz.cpu().numpy().tobytes() == host[0].tobytes()
+        assert ds.cpu().numpy().tobytes() == host[1].tobytes()
+
+
+def test_full_size_properties_on_device():
+    """BASELINE-scale blocks (1e8 rows) checked through closed forms that need no CPU pass."""
+    torch = pytest.importorskip("torch")
+    n = 100_000_000
+    i = torch.arange(n, dtype=torch.float64, device="cuda")
+    u = (i % 1024.0)
+    y = torch.stack([u, -u], dim=1).contiguous()
+    del i
+    with dsl.withGraph():
+        py = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("y_input")
+        pz = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("z_input")
+        g = dsl.build_graph(dsl.reduce_sum(py, [0]).named("y"), dsl.reduce_min(pz, [0]).named("z"))
+    ds = torch.empty(2, dtype=torch.float64, device="cuda")
+    dm = torch.empty(2, dtype=torch.float64, device="cuda")
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        s.set_stream(torch.cuda.current_stream().cuda_stream)
+        s.run_into({"y_input": _native.DeviceArray.from_torch(y), "z_input": _native.DeviceArray.from_torch(y)},
+                   {"y": _native.DeviceArray.from_torch(ds), "z": _native.DeviceArray.from_torch(dm)})
+        s.sync()
+    full, rem = divmod(n, 1024)
+    exact = full * (1023 * 1024 // 2) + (rem - 1) * rem // 2     # integers: every partial sum is exact in f64
+    assert ds.tolist() == [float(exact), float(-exact)]
+    assert dm.tolist() == [0.0, -1023.0]
+    # map chain: linear in x, so z(x) on a known ramp has a closed form per element
+    x = u * (1.0 / 512.0) - 1.0
+    dz = torch.empty(n, dtype=torch.float32, device="cuda")
+    with dsl.withGraph():
+        px = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x")
+        g = dsl.build_graph(dsl.cast(dsl.maximum(px * 1.5 + 0.25, 0.0), tfs.FloatType).named("z"))
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        s.set_stream(torch.cuda.current_stream().cuda_stream)
+        s.run_into({"x": _native.DeviceArray.from_torch(x)}, {"z": _native.DeviceArray.from_torch(dz)})
+        s.sync()
+    want = torch.clamp_min(x * 1.5 + 0.25, 0.0).to(torch.float32)
+    assert torch.equal(dz, want)
+
+
+# ---- operators: partitions, empties, trimming -------------------------------------------------------
+def test_map_blocks_partitions_and_empty_partition():
+    df = TensorFrame.from_columns({"x": np.arange(10, dtype=np.float64)}, num_partitions=3)
+    df.partitions.insert(1, {"x": np.zeros(0)})            # an empty partition never reaches the device
+    with dsl.withGraph():
+        z = (tfs.block(df, "x") + 3.0).named("z")
+        out = tfs.map_blocks(z, df)
+    assert out.columns == ["z", "x"]
+    assert [r.z for r in out.collect()] == [float(i) + 3.0 for i in range(10)]
+    assert len(out.partitions) == 3
+
+
+def test_reduce_blocks_over_partitions_matches_oracle():
+    rng = np.random.default_rng(41)
+    y = rng.uniform(0, 1, (10007, 2))
+    df = tfs.analyze(TensorFrame.from_columns({"y": y, "pad": np.arange(10007)}, num_partitions=4))
+    df = df.withColumn("z", "y")
+    with dsl.withGraph():
+        yi, zi = tfs.block(df, "y", "y_input"), tfs.block(df, "z", "z_input")
+        s, m = tfs.reduce_blocks([dsl.reduce_sum(yi, [0]).named("y"), dsl.reduce_min(zi, [0]).named("z")], df)
+    assert np.all(np.abs(s - tf_ops.exact_sum_f64(y, 0)) <= 1e-12 * np.abs(y).sum(axis=0))
+    assert m.tolist() == y.min(axis=0).tolist()
