@@ -164,7 +164,9 @@ def run_ours(args):
     graph_bytes = build_graph(wl)
     graph = _native.Graph(graph_bytes)
     sess = _native.Session(graph, local)
-    stream = torch.cuda.current_stream()
+    # a real (non-default) stream: the C ABI treats a NULL stream handle as "use the session's own"
+    stream = torch.cuda.Stream(device=device)
+    torch.cuda.set_stream(stream)
     sess.set_stream(stream.cuda_stream)
     feeds_t = make_inputs(torch, wl, rows, seed=(2 if wl == "c2" else 3) + 1000 * rank, device=device)
     feeds = {k: DA(v) for k, v in feeds_t.items()}

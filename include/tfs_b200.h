@@ -119,8 +119,10 @@ int tfs_graph_node_info(const tfs_graph* g, const char* name, tfs_node_info* out
  * tensors.  `device` is a CUDA ordinal. */
 int tfs_session_create(const tfs_graph* g, int device, tfs_session** out);
 void tfs_session_free(tfs_session* s);
-/* Run on a caller-provided cudaStream_t instead of the session's own stream
- * (NULL restores the own stream).  Lets a caller time with events on its stream. */
+/* Run on a caller-provided cudaStream_t instead of the session's own stream.
+ * NULL restores the own stream -- so the legacy default stream (handle 0) cannot be
+ * selected; pass a created stream, cudaStreamLegacy or cudaStreamPerThread.  Lets a
+ * caller time with events on the stream the kernels run on. */
 int tfs_session_set_stream(tfs_session* s, void* cuda_stream);
 /* Wait for everything enqueued by this session; reports deferred device-side
  * errors (TFS_ERR_RUNTIME) of asynchronous runs. */

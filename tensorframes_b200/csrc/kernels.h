@@ -35,4 +35,22 @@ int launch_reduce_axis0(int dtype, int red_op, const void* in, int64_t outer, in
 int launch_reduce_rows(int dtype, int red_op, const void* in, int64_t outer, int64_t inner, void* out,
                        const DeviceInfo& dev, cudaStream_t stream);
 
+// K3: keyed block reduction. Scratch layout for n_rows rows and at most max_groups groups.
+struct AggLayout {
+  uint64_t table_slots;
+  size_t off_header, off_slot_key, off_slot_gid, off_row_gid, off_counts, off_offsets, off_tile_sums, off_perm;
+  size_t bytes;
+};
+AggLayout agg_layout(int64_t n_rows, int64_t max_groups);
+// pass 1: hash-insert the keys, assign dense group ids, write out_keys[gid]. header (first 16 bytes of
+// scratch): [0] = number of groups, [1] = overflow flag (more than max_groups distinct keys).
+int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, char* scratch, const AggLayout& L,
+                     int64_t* out_keys_dev, const DeviceInfo& dev, cudaStream_t stream);
+// passes 2-4: group id per row, segment offsets, row permutation.
+int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, char* scratch, const AggLayout& L,
+                        const DeviceInfo& dev, cudaStream_t stream);
+// pass 5: out[g, :] = reduce over the rows of group g of payload[row, :].
+int launch_agg_reduce(int dtype, int red_op, const void* payload, int64_t cell, int64_t n_groups, char* scratch,
+                      const AggLayout& L, void* out, const DeviceInfo& dev, cudaStream_t stream);
+
 }  // namespace tfs

@@ -1,0 +1,425 @@
+// K3 -- keyed block reduction for `groupBy(key).aggregate(reduce_*(x_input, [0]))` (sm_100a).
+//
+// Stands in for the whole TensorFlowUDAF machinery of the reference
+// (impl/DebugRowOps.scala:601-695): there, Spark hashes rows to per-key buffers of <= 11 rows
+// and block-reduces each buffer through a fresh TF session.  Here one block is reduced in
+// five passes, all HBM-bound:
+//
+//   1. insert    every key into an open-addressing table (64-bit CAS on the key slot); the
+//                thread that claims a slot assigns the next dense group id      8 B/row read
+//   2. lookup    group id per row + per-group row count                          8 B read, 4 B write
+//   3. scan      exclusive prefix sum of the counts -> segment offsets           (groups only)
+//   4. scatter   row index into its group's segment (perm)                       4 B read, 4 B write
+//   5. gather-reduce  one warp per group walks its segment and gathers the payload rows --
+//                each a contiguous cell, read with coalesced vector loads -- accumulating in
+//                registers; one coalesced store per group.          cell bytes/row read
+//
+// The payload (the dominant traffic: 256 B/row at BASELINE config 4) is read exactly once
+// and no accumulator table is read-modify-written, unlike a scatter-add formulation.
+// Keys are compared bit-exactly.  Group order and the order of rows inside a group follow
+// atomic arrival order, so float sums may differ between runs by summation order (the
+// north-star tolerance); integer sums, Min and Max are exact.
+#include "kernels.h"
+
+namespace tfs {
+namespace {
+
+constexpr int kThreads = 256;
+constexpr unsigned long long kEmpty = 0x8000000000000000ULL;
+
+__device__ __forceinline__ unsigned long long mix64(unsigned long long x) {
+  x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ULL;
+  x ^= x >> 27; x *= 0x94d049bb133111ebULL;
+  x ^= x >> 31;
+  return x;
+}
+
+// header[0] = number of groups, header[1] = overflow flag, header[2] = sentinel state, header[3] = sentinel gid
+__global__ void __launch_bounds__(kThreads)
+agg_insert_kernel(const long long* __restrict__ keys, const int64_t n, unsigned long long* __restrict__ slot_key,
+                  unsigned int* __restrict__ slot_gid, const unsigned long long mask, unsigned int* __restrict__ header,
+                  long long* __restrict__ out_keys, const unsigned int max_groups) {
+  const int64_t stride = int64_t(gridDim.x) * blockDim.x;
+  for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const unsigned long long k = (unsigned long long)__ldcs(keys + i);
+    if (k == kEmpty) {  // the one key value that collides with the empty marker
+      if (atomicCAS(header + 2, 0u, 1u) == 0u) {
+        unsigned int g = atomicAdd(header, 1u);
+        if (g < max_groups) out_keys[g] = (long long)k; else header[1] = 1u;
+        header[3] = g;
+      }
+      continue;
+    }
+    unsigned long long h = mix64(k) & mask;
+    while (true) {
+      unsigned long long cur = slot_key[h];
+      if (cur == k) break;
+      if (cur == kEmpty) {
+        unsigned long long prev = atomicCAS(slot_key + h, kEmpty, k);
+        if (prev == kEmpty) {
+          unsigned int g = atomicAdd(header, 1u);
+          if (g < max_groups) out_keys[g] = (long long)k; else header[1] = 1u;
+          slot_gid[h] = g;
+          break;
+        }
+        if (prev == k) break;
+      }
+      h = (h + 1) & mask;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+agg_lookup_kernel(const long long* __restrict__ keys, const int64_t n, const unsigned long long* __restrict__ slot_key,
+                  const unsigned int* __restrict__ slot_gid, const unsigned long long mask,
+                  const unsigned int* __restrict__ header, unsigned int* __restrict__ row_gid,
+                  unsigned int* __restrict__ counts) {
+  const int64_t stride = int64_t(gridDim.x) * blockDim.x;
+  for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const unsigned long long k = (unsigned long long)__ldcs(keys + i);
+    unsigned int g;
+    if (k == kEmpty) {
+      g = header[3];
+    } else {
+      unsigned long long h = mix64(k) & mask;
+      while (slot_key[h] != k) h = (h + 1) & mask;
+      g = slot_gid[h];
+    }
+    row_gid[i] = g;
+    atomicAdd(counts + g, 1u);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+fill_u64_kernel(unsigned long long* __restrict__ p, const uint64_t n, const unsigned long long v) {
+  const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) p[i] = v;
+}
+
+// ---- exclusive scan of counts[0..m) into offsets[0..m], three small kernels -------------------
+constexpr int kScanTile = 2048;  // elements per CTA
+
+__global__ void __launch_bounds__(kThreads)
+scan_tile_sums_kernel(const unsigned int* __restrict__ in, const int64_t m, unsigned long long* __restrict__ tile_sums) {
+  __shared__ unsigned long long sm[kThreads];
+  const int64_t base = int64_t(blockIdx.x) * kScanTile;
+  unsigned long long s = 0;
+  for (int i = threadIdx.x; i < kScanTile; i += kThreads)
+    if (base + i < m) s += in[base + i];
+  sm[threadIdx.x] = s;
+  __syncthreads();
+  for (int w = kThreads / 2; w > 0; w >>= 1) {
+    if (threadIdx.x < w) sm[threadIdx.x] += sm[threadIdx.x + w];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) tile_sums[blockIdx.x] = sm[0];
+}
+
+__global__ void __launch_bounds__(1024)
+scan_tile_offsets_kernel(unsigned long long* __restrict__ tile_sums, const int64_t tiles) {
+  // single CTA: in-place exclusive scan, 1024 tiles per round with a running carry
+  __shared__ unsigned long long sm[1024];
+  __shared__ unsigned long long carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int64_t base = 0; base < tiles; base += 1024) {
+    const int64_t i = base + threadIdx.x;
+    const unsigned long long v = i < tiles ? tile_sums[i] : 0ULL;
+    sm[threadIdx.x] = v;
+    __syncthreads();
+    for (int d = 1; d < 1024; d <<= 1) {
+      unsigned long long t = threadIdx.x >= d ? sm[threadIdx.x - d] : 0ULL;
+      __syncthreads();
+      sm[threadIdx.x] += t;
+      __syncthreads();
+    }
+    if (i < tiles) tile_sums[i] = carry + sm[threadIdx.x] - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry += sm[1023];
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+scan_apply_kernel(const unsigned int* __restrict__ in, const int64_t m, const unsigned long long* __restrict__ tile_off,
+                  unsigned long long* __restrict__ offsets) {
+  // each thread owns kScanTile / kThreads consecutive elements
+  constexpr int PER = kScanTile / kThreads;
+  __shared__ unsigned long long sm[kThreads];
+  const int64_t base = int64_t(blockIdx.x) * kScanTile + int64_t(threadIdx.x) * PER;
+  unsigned int v[PER];
+  unsigned long long s = 0;
+#pragma unroll
+  for (int j = 0; j < PER; ++j) {
+    v[j] = base + j < m ? in[base + j] : 0u;
+    s += v[j];
+  }
+  sm[threadIdx.x] = s;
+  __syncthreads();
+  for (int d = 1; d < kThreads; d <<= 1) {
+    unsigned long long t = threadIdx.x >= d ? sm[threadIdx.x - d] : 0ULL;
+    __syncthreads();
+    sm[threadIdx.x] += t;
+    __syncthreads();
+  }
+  unsigned long long run = tile_off[blockIdx.x] + sm[threadIdx.x] - s;
+#pragma unroll
+  for (int j = 0; j < PER; ++j) {
+    if (base + j < m) offsets[base + j] = run;
+    run += v[j];
+  }
+  if (base <= m && m < base + PER) {
+    // the thread whose range contains index m writes the total
+    unsigned long long tot = tile_off[blockIdx.x] + sm[threadIdx.x] - s;
+    for (int j = 0; j < PER && base + j < m; ++j) tot += v[j];
+    offsets[m] = tot;
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+agg_scatter_kernel(const unsigned int* __restrict__ row_gid, const int64_t n,
+                   const unsigned long long* __restrict__ offsets, unsigned int* __restrict__ counts,
+                   unsigned int* __restrict__ perm) {
+  const int64_t stride = int64_t(gridDim.x) * blockDim.x;
+  for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const unsigned int g = __ldcs(row_gid + i);
+    const unsigned int pos = atomicSub(counts + g, 1u) - 1u;   // counts run down to zero
+    perm[offsets[g] + pos] = (unsigned int)i;
+  }
+}
+
+// ---- gather-reduce ---------------------------------------------------------------------------
+template <class T> struct Lim;
+template <> struct Lim<double> { static __device__ double hi() { return __longlong_as_double(0x7ff0000000000000LL); } };
+template <> struct Lim<float> { static __device__ float hi() { return __int_as_float(0x7f800000); } };
+template <> struct Lim<int> { static __device__ int hi() { return 0x7fffffff; } };
+template <> struct Lim<long long> { static __device__ long long hi() { return 0x7fffffffffffffffLL; } };
+template <class T> __device__ __forceinline__ T lowest_of();
+template <> __device__ __forceinline__ double lowest_of<double>() { return -Lim<double>::hi(); }
+template <> __device__ __forceinline__ float lowest_of<float>() { return -Lim<float>::hi(); }
+template <> __device__ __forceinline__ int lowest_of<int>() { return int(0x80000000u); }
+template <> __device__ __forceinline__ long long lowest_of<long long>() { return (long long)0x8000000000000000ULL; }
+
+template <class T, int OP> __device__ __forceinline__ T red_identity() {
+  if (OP == R_SUM) return T(0);
+  if (OP == R_MIN) return Lim<T>::hi();
+  return lowest_of<T>();
+}
+template <class T> __device__ __forceinline__ T add_wrap(T a, T b) { return a + b; }
+template <> __device__ __forceinline__ int add_wrap(int a, int b) { return int((unsigned)a + (unsigned)b); }
+template <> __device__ __forceinline__ long long add_wrap(long long a, long long b) {
+  return (long long)((unsigned long long)a + (unsigned long long)b);
+}
+template <> __device__ __forceinline__ float add_wrap(float a, float b) { return __fadd_rn(a, b); }
+template <> __device__ __forceinline__ double add_wrap(double a, double b) { return __dadd_rn(a, b); }
+template <class T, int OP> __device__ __forceinline__ T red_op(T a, T b) {
+  if (OP == R_SUM) return add_wrap<T>(a, b);
+  if (OP == R_MIN) return (b < a) ? b : a;
+  return (a < b) ? b : a;
+}
+
+template <class T, int V> struct VecT;
+template <> struct VecT<float, 4> { using type = float4; };
+template <> struct VecT<float, 2> { using type = float2; };
+template <> struct VecT<int, 4> { using type = int4; };
+template <> struct VecT<int, 2> { using type = int2; };
+template <> struct VecT<double, 2> { using type = double2; };
+template <> struct VecT<long long, 2> { using type = longlong2; };
+
+template <class T, int V>
+__device__ __forceinline__ void load_v(const T* p, T (&x)[V]) {
+  if constexpr (V == 1) {
+    x[0] = __ldcs(p);
+  } else {
+    using VT = typename VecT<T, V>::type;
+    VT t = __ldcs(reinterpret_cast<const VT*>(p));
+    if constexpr (V == 2) { x[0] = t.x; x[1] = t.y; }
+    else { x[0] = t.x; x[1] = t.y; x[2] = t.z; x[3] = t.w; }
+  }
+}
+
+// One warp per group.  The warp is split into R row-lanes x C col-lanes (R * C = 32, C a power
+// of two >= ceil(cell / V) when the cell fits, else C = 32 with a loop over column chunks).
+// kU rows are in flight per row-lane.
+template <class T, int OP, int V>
+__global__ void __launch_bounds__(kThreads)
+agg_gather_reduce_kernel(const T* __restrict__ payload, const int cell, const unsigned int* __restrict__ perm,
+                         const unsigned long long* __restrict__ offsets, const int64_t n_groups, const int col_lanes,
+                         T* __restrict__ out) {
+  constexpr int kU = 8;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
+  const int C = col_lanes, R = 32 / C;
+  const int cl = lane % C, rl = lane / C;
+  for (int64_t g = warp; g < n_groups; g += warps) {
+    const unsigned long long lo = offsets[g], hi = offsets[g + 1];
+    for (int cbase = 0; cbase < cell; cbase += C * V) {   // warp-uniform trip count
+      const int c0 = cbase + cl * V;
+      const bool active = c0 < cell;
+      T acc[V];
+#pragma unroll
+      for (int e = 0; e < V; ++e) acc[e] = red_identity<T, OP>();
+      if (active) {
+        unsigned long long r = lo + rl;
+        for (; r + (unsigned long long)(kU - 1) * R < hi; r += (unsigned long long)kU * R) {
+          unsigned int idx[kU];
+#pragma unroll
+          for (int u = 0; u < kU; ++u) idx[u] = __ldg(perm + r + (unsigned long long)u * R);
+          T x[kU][V];
+#pragma unroll
+          for (int u = 0; u < kU; ++u) load_v<T, V>(payload + (int64_t)idx[u] * cell + c0, x[u]);
+#pragma unroll
+          for (int u = 0; u < kU; ++u)
+#pragma unroll
+            for (int e = 0; e < V; ++e) acc[e] = red_op<T, OP>(acc[e], x[u][e]);
+        }
+        for (; r < hi; r += R) {
+          T x[V];
+          load_v<T, V>(payload + (int64_t)__ldg(perm + r) * cell + c0, x);
+#pragma unroll
+          for (int e = 0; e < V; ++e) acc[e] = red_op<T, OP>(acc[e], x[e]);
+        }
+      }
+      // fold the R row-lanes that share this column slice (every lane takes part)
+      for (int m = 16; m >= C; m >>= 1) {
+#pragma unroll
+        for (int e = 0; e < V; ++e) acc[e] = red_op<T, OP>(acc[e], __shfl_xor_sync(0xffffffffu, acc[e], m));
+      }
+      if (active && rl == 0) {
+#pragma unroll
+        for (int e = 0; e < V; ++e) out[g * cell + c0 + e] = acc[e];
+      }
+    }
+  }
+}
+
+template <class T, int OP>
+int launch_gather_t(const T* payload, int64_t cell, const unsigned int* perm, const unsigned long long* offsets,
+                    int64_t n_groups, T* out, const DeviceInfo& dev, cudaStream_t stream) {
+  if (n_groups <= 0 || cell <= 0) return 0;
+  constexpr int VMAX = 16 / int(sizeof(T));
+  int V = 1;
+  const bool aligned16 = (reinterpret_cast<uintptr_t>(payload) & 15) == 0;
+  if (aligned16 && cell % VMAX == 0 && cell >= 32 * VMAX) V = VMAX;
+  else if (aligned16 && VMAX == 4 && cell % 2 == 0 && cell >= 64) V = 2;
+  int need = int((cell + V - 1) / V);
+  int C = 1;
+  while (C < need && C < 32) C <<= 1;
+  const int64_t warps_per_cta = kThreads / 32;
+  int64_t grid = std::min<int64_t>((n_groups + warps_per_cta - 1) / warps_per_cta, int64_t(dev.sm_count) * 16);
+  if (grid < 1) grid = 1;
+  const int icell = int(cell);
+  if (V == 4) {
+    if constexpr (VMAX == 4)
+      agg_gather_reduce_kernel<T, OP, 4><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, n_groups, C, out);
+  } else if (V == 2) {
+    agg_gather_reduce_kernel<T, OP, 2><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, n_groups, C, out);
+  } else {
+    agg_gather_reduce_kernel<T, OP, 1><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, n_groups, C, out);
+  }
+  TFS_CUDA(cudaGetLastError());
+  return 1;
+}
+
+template <class T>
+int launch_gather_op(int red_op, const void* payload, int64_t cell, const unsigned int* perm,
+                     const unsigned long long* offsets, int64_t n_groups, void* out, const DeviceInfo& dev,
+                     cudaStream_t stream) {
+  const T* p = static_cast<const T*>(payload);
+  T* o = static_cast<T*>(out);
+  switch (red_op) {
+    case R_SUM: return launch_gather_t<T, R_SUM>(p, cell, perm, offsets, n_groups, o, dev, stream);
+    case R_MIN: return launch_gather_t<T, R_MIN>(p, cell, perm, offsets, n_groups, o, dev, stream);
+    default: return launch_gather_t<T, R_MAX>(p, cell, perm, offsets, n_groups, o, dev, stream);
+  }
+}
+
+int64_t grid_for(int64_t n, const DeviceInfo& dev) {
+  int64_t g = (n + kThreads - 1) / kThreads;
+  g = std::min<int64_t>(g, int64_t(dev.sm_count) * 8);
+  return g < 1 ? 1 : g;
+}
+
+}  // namespace
+
+AggLayout agg_layout(int64_t n_rows, int64_t max_groups) {
+  AggLayout L{};
+  uint64_t cap = 1024;
+  while (cap < 2 * uint64_t(std::max<int64_t>(max_groups, 1))) cap <<= 1;
+  L.table_slots = cap;
+  auto up = [](size_t x) { return (x + 255) / 256 * 256; };
+  size_t off = 0;
+  L.off_header = off; off += 256;
+  L.off_slot_key = off; off += up(cap * 8);
+  L.off_slot_gid = off; off += up(cap * 4);
+  L.off_row_gid = off; off += up(size_t(n_rows) * 4);
+  L.off_counts = off; off += up(size_t(max_groups + 1) * 4);
+  L.off_offsets = off; off += up(size_t(max_groups + 2) * 8);
+  L.off_tile_sums = off; off += up(size_t((max_groups + kScanTile) / kScanTile + 1) * 8);
+  L.off_perm = off; off += up(size_t(n_rows) * 4);
+  L.bytes = off;
+  return L;
+}
+
+int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, char* scratch, const AggLayout& L,
+                     int64_t* out_keys_dev, const DeviceInfo& dev, cudaStream_t stream) {
+  unsigned int* header = reinterpret_cast<unsigned int*>(scratch + L.off_header);
+  unsigned long long* slot_key = reinterpret_cast<unsigned long long*>(scratch + L.off_slot_key);
+  unsigned int* slot_gid = reinterpret_cast<unsigned int*>(scratch + L.off_slot_gid);
+  TFS_CUDA(cudaMemsetAsync(header, 0, 256, stream));
+  fill_u64_kernel<<<(unsigned)grid_for(int64_t(L.table_slots), dev), kThreads, 0, stream>>>(slot_key, L.table_slots, kEmpty);
+  TFS_CUDA(cudaGetLastError());
+  TFS_CUDA(cudaMemsetAsync(scratch + L.off_counts, 0, size_t(max_groups + 1) * 4, stream));
+  (void)slot_gid;
+  if (n_rows > 0) {
+    agg_insert_kernel<<<(unsigned)grid_for(n_rows, dev), kThreads, 0, stream>>>(
+        reinterpret_cast<const long long*>(keys), n_rows, slot_key, slot_gid, L.table_slots - 1, header,
+        reinterpret_cast<long long*>(out_keys_dev), (unsigned int)max_groups);
+    TFS_CUDA(cudaGetLastError());
+    return 2;
+  }
+  return 1;
+}
+
+int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, char* scratch, const AggLayout& L,
+                        const DeviceInfo& dev, cudaStream_t stream) {
+  if (n_rows <= 0) return 0;
+  unsigned int* header = reinterpret_cast<unsigned int*>(scratch + L.off_header);
+  unsigned long long* slot_key = reinterpret_cast<unsigned long long*>(scratch + L.off_slot_key);
+  unsigned int* slot_gid = reinterpret_cast<unsigned int*>(scratch + L.off_slot_gid);
+  unsigned int* row_gid = reinterpret_cast<unsigned int*>(scratch + L.off_row_gid);
+  unsigned int* counts = reinterpret_cast<unsigned int*>(scratch + L.off_counts);
+  unsigned long long* offsets = reinterpret_cast<unsigned long long*>(scratch + L.off_offsets);
+  unsigned long long* tile_sums = reinterpret_cast<unsigned long long*>(scratch + L.off_tile_sums);
+  unsigned int* perm = reinterpret_cast<unsigned int*>(scratch + L.off_perm);
+  const unsigned grid = (unsigned)grid_for(n_rows, dev);
+  agg_lookup_kernel<<<grid, kThreads, 0, stream>>>(reinterpret_cast<const long long*>(keys), n_rows, slot_key, slot_gid,
+                                                   L.table_slots - 1, header, row_gid, counts);
+  TFS_CUDA(cudaGetLastError());
+  const int64_t tiles = (n_groups + 1 + kScanTile - 1) / kScanTile;   // scan covers index n_groups for the total
+  scan_tile_sums_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(counts, n_groups, tile_sums);
+  TFS_CUDA(cudaGetLastError());
+  scan_tile_offsets_kernel<<<1, 1024, 0, stream>>>(tile_sums, tiles);
+  TFS_CUDA(cudaGetLastError());
+  scan_apply_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(counts, n_groups, tile_sums, offsets);
+  TFS_CUDA(cudaGetLastError());
+  agg_scatter_kernel<<<grid, kThreads, 0, stream>>>(row_gid, n_rows, offsets, counts, perm);
+  TFS_CUDA(cudaGetLastError());
+  return 5;
+}
+
+int launch_agg_reduce(int dtype, int red_op, const void* payload, int64_t cell, int64_t n_groups, char* scratch,
+                      const AggLayout& L, void* out, const DeviceInfo& dev, cudaStream_t stream) {
+  const unsigned int* perm = reinterpret_cast<const unsigned int*>(scratch + L.off_perm);
+  const unsigned long long* offsets = reinterpret_cast<const unsigned long long*>(scratch + L.off_offsets);
+  switch (dtype) {
+    case TFS_FLOAT: return launch_gather_op<float>(red_op, payload, cell, perm, offsets, n_groups, out, dev, stream);
+    case TFS_DOUBLE: return launch_gather_op<double>(red_op, payload, cell, perm, offsets, n_groups, out, dev, stream);
+    case TFS_INT32: return launch_gather_op<int>(red_op, payload, cell, perm, offsets, n_groups, out, dev, stream);
+    case TFS_INT64: return launch_gather_op<long long>(red_op, payload, cell, perm, offsets, n_groups, out, dev, stream);
+  }
+  fail(TFS_ERR_UNSUPPORTED, "aggregate: unsupported dtype");
+}
+
+}  // namespace tfs

@@ -201,15 +201,16 @@ __device__ __forceinline__ void apply_binary(int sub, bool swap, typename Slot<E
                                              const typename Slot<ES>::type (&x)[kJ][P],
                                              const int (&nvalid)[kJ], int* err) {
   using S = typename Slot<ES>::type;
-#define TFS_BIN(expr)                                             \
+#define TFS_BIN_LOOP(A, B, expr)                                  \
   _Pragma("unroll") for (int j = 0; j < kJ; ++j)                  \
   _Pragma("unroll") for (int e = 0; e < P; ++e) {                 \
-    T l = from_slot<T, S>(acc[j][e]);                             \
-    T r = from_slot<T, S>(x[j][e]);                               \
-    T a = swap ? r : l;                                           \
-    T b = swap ? l : r;                                           \
+    T a = from_slot<T, S>(A[j][e]);                               \
+    T b = from_slot<T, S>(B[j][e]);                               \
     acc[j][e] = to_slot<S, T>(expr);                              \
   }
+  // the operand order is warp-uniform: branch once instead of selecting per element
+#define TFS_BIN(expr)                                             \
+  if (swap) { TFS_BIN_LOOP(x, acc, expr) } else { TFS_BIN_LOOP(acc, x, expr) }
   switch (sub) {
     case E_ADD: TFS_BIN(Arith<T>::add(a, b)) break;
     case E_SUB: TFS_BIN(Arith<T>::sub(a, b)) break;
@@ -219,6 +220,7 @@ __device__ __forceinline__ void apply_binary(int sub, bool swap, typename Slot<E
     case E_MAX: TFS_BIN(Arith<T>::mx(a, b)) break;
     default: break;
   }
+#undef TFS_BIN_LOOP
 #undef TFS_BIN
 }
 

@@ -12,6 +12,9 @@
 // -> shared memory -> per-CTA partial in global scratch -> last CTA folds the
 // partials), so results are run-to-run deterministic; floating-point sums differ
 // from TF-CPU only by summation order.  HBM-bound: bytes read / HBM bandwidth.
+#include <cstdlib>
+#include <string>
+
 #include "kernels.h"
 
 namespace tfs {
@@ -82,10 +85,80 @@ __device__ __forceinline__ void load_p(const T* p, T (&v)[P]) {
 template <class T>
 __device__ __forceinline__ T shfl_xor(T v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
 
+// CTA combine + grid combine shared by the LDG and the TMA variants.  `a` holds the thread's P
+// lane accumulators; thread t of the CTA owns flat slots (t % q) * P + e of the L-periodic pattern.
+template <class T, int OP, int P>
+__device__ __forceinline__ void combine_and_finish(T (&a)[P], const T* __restrict__ in, const int64_t n,
+                                                   const int64_t n_vec, const int inner, const int L, const int q,
+                                                   T* __restrict__ partials, unsigned int* __restrict__ counter,
+                                                   T* __restrict__ out, T* sm, T* sm2, bool* is_last) {
+  using R = Red<T, OP>;
+  const int b = blockDim.x;
+  // lanes whose index differs by a multiple of q hold the same columns
+  const bool shuffle_ok = (q <= 32) && ((q & (q - 1)) == 0);
+  int contributors;  // threads per CTA whose `a` still matters, laid out class-major below
+  if (shuffle_ok) {
+    for (int m = 16; m >= q; m >>= 1) {
+#pragma unroll
+      for (int e = 0; e < P; ++e) a[e] = R::op(a[e], shfl_xor(a[e], m));
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane < q) {
+#pragma unroll
+      for (int e = 0; e < P; ++e) sm[(warp * q + lane) * P + e] = a[e];
+    }
+    contributors = (b >> 5) * q;   // b is a multiple of 32 here (q | 32 and b = (256/q)*q)
+  } else {
+#pragma unroll
+    for (int e = 0; e < P; ++e) sm[threadIdx.x * P + e] = a[e];
+    contributors = b;
+  }
+  __syncthreads();
+  if (threadIdx.x < L) {
+    const int tc = threadIdx.x / P, e = threadIdx.x % P;
+    T r = R::identity();
+    for (int t = tc; t < contributors; t += q) r = R::op(r, sm[t * P + e]);
+    partials[int64_t(blockIdx.x) * L + threadIdx.x] = r;
+  }
+  // ---- grid combine by the last CTA to finish
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int ticket = atomicAdd(counter, 1u);
+    *is_last = (ticket == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!*is_last) return;
+  __threadfence();
+  const int bl = (b / L) * L;            // threads used, a multiple of L (L <= b by construction)
+  T r = R::identity();
+  if (threadIdx.x < bl) {
+    const int64_t total = int64_t(gridDim.x) * L;
+    for (int64_t i = threadIdx.x; i < total; i += bl) r = R::op(r, __ldcg(partials + i));
+  }
+  sm2[threadIdx.x] = r;
+  __syncthreads();
+  if (threadIdx.x < L) {
+    T s = R::identity();
+    for (int t = threadIdx.x; t < bl; t += L) s = R::op(s, sm2[t]);
+    sm[threadIdx.x] = s;   // per flat-slot f totals
+  }
+  __syncthreads();
+  if (threadIdx.x < inner) {
+    T s = R::identity();
+    for (int f = threadIdx.x; f < L; f += inner) s = R::op(s, sm[f]);
+    // elements past the last full vector (n % P of them)
+    for (int64_t i = n_vec * P; i < n; ++i)
+      if (int(i % inner) == int(threadIdx.x)) s = R::op(s, in[i]);
+    out[threadIdx.x] = s;
+  }
+  if (threadIdx.x == 0) *counter = 0;
+}
+
 // in: n = outer*inner elements. L = lcm(inner, P), q = L / P, blockDim.x % q == 0.
 // partials: [gridDim.x][L]. counter: zero on entry, zero again on exit.
 template <class T, int OP, int P>
-__global__ void __launch_bounds__(kMaxThreads)
+__global__ void __launch_bounds__(kMaxThreads, 5)
 reduce_axis0_flat_kernel(const T* __restrict__ in, const int64_t n, const int inner, const int L, const int q,
                          T* __restrict__ partials, unsigned int* __restrict__ counter, T* __restrict__ out) {
   using R = Red<T, OP>;
@@ -122,66 +195,115 @@ reduce_axis0_flat_kernel(const T* __restrict__ in, const int64_t n, const int in
   T a[P];
 #pragma unroll
   for (int e = 0; e < P; ++e) a[e] = R::op(R::op(acc[0][e], acc[1][e]), R::op(acc[2][e], acc[3][e]));
+  combine_and_finish<T, OP, P>(a, in, n, n_vec, inner, L, q, partials, counter, out, sm, sm2, &is_last);
+}
 
-  // ---- CTA combine: lanes whose index differs by a multiple of q hold the same columns
-  const bool shuffle_ok = (q <= 32) && ((q & (q - 1)) == 0);
-  int contributors;  // threads per CTA whose `a` still matters, laid out class-major below
-  if (shuffle_ok) {
-    for (int m = 16; m >= q; m >>= 1) {
-#pragma unroll
-      for (int e = 0; e < P; ++e) a[e] = R::op(a[e], shfl_xor(a[e], m));
-    }
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (lane < q) {
-#pragma unroll
-      for (int e = 0; e < P; ++e) sm[(warp * q + lane) * P + e] = a[e];
-    }
-    contributors = (b >> 5) * q;   // b is a multiple of 32 here (q | 32 and b = (256/q)*q)
-  } else {
-#pragma unroll
-    for (int e = 0; e < P; ++e) sm[threadIdx.x * P + e] = a[e];
-    contributors = b;
-  }
-  __syncthreads();
-  if (threadIdx.x < L) {
-    const int tc = threadIdx.x / P, e = threadIdx.x % P;
-    T r = R::identity();
-    for (int t = tc; t < contributors; t += q) r = R::op(r, sm[t * P + e]);
-    partials[int64_t(blockIdx.x) * L + threadIdx.x] = r;
-  }
-  // ---- grid combine by the last CTA to finish
-  __threadfence();
-  __syncthreads();
+// ---- TMA-staged variant -------------------------------------------------------------------------
+// One persistent CTA per SM.  An elected thread streams kStageBytes chunks of the block into a
+// ring of shared-memory stages with cp.async.bulk (the TMA unit, no registers or LSU slots held
+// while the bytes are in flight: kStages * kStageBytes per SM), completion is signalled on an
+// mbarrier per stage, and all threads fold the landed stage with conflict-free 128-bit shared
+// loads.  The stage size is a multiple of blockDim.x * P elements, so a thread's lanes keep the
+// same columns in every stage, exactly like the LDG variant.
+constexpr int kStages = 6;
+constexpr int kVecPerThread = 8;   // 16-byte vectors per thread per stage: 256 * 8 * 16 B = 32 KB stages
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t"
+        "}" : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+               "r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+template <class T, int OP, int P>
+__global__ void __launch_bounds__(kMaxThreads, 1)
+reduce_axis0_tma_kernel(const T* __restrict__ in, const int64_t n, const int inner, const int L, const int q,
+                        T* __restrict__ partials, unsigned int* __restrict__ counter, T* __restrict__ out) {
+  using R = Red<T, OP>;
+  extern __shared__ __align__(128) unsigned char dyn_smem[];
+  __shared__ __align__(8) uint64_t full_bar[kStages];
+  __shared__ T sm[kMaxThreads * P];
+  __shared__ T sm2[kMaxThreads];
+  __shared__ bool is_last;
+
+  const int b = blockDim.x;
+  const int64_t n_vec = n / P;
+  const int64_t chunk_vecs = int64_t(b) * kVecPerThread;          // vectors per stage
+  const uint32_t stage_bytes = uint32_t(chunk_vecs) * 16u;
+  const int64_t n_chunks = (n_vec + chunk_vecs - 1) / chunk_vecs;
+  // chunks are dealt round-robin: CTA c owns chunks c, c + grid, ...
+  const int64_t my_chunks = n_chunks > blockIdx.x ? (n_chunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+
   if (threadIdx.x == 0) {
-    unsigned int ticket = atomicAdd(counter, 1u);
-    is_last = (ticket == gridDim.x - 1);
+    for (int s = 0; s < kStages; ++s) mbar_init(&full_bar[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  if (!is_last) return;
-  __threadfence();
-  const int bl = (b / L) * L;            // threads used, a multiple of L (L <= b by construction)
-  T r = R::identity();
-  if (threadIdx.x < bl) {
-    const int64_t total = int64_t(gridDim.x) * L;
-    for (int64_t i = threadIdx.x; i < total; i += bl) r = R::op(r, __ldcg(partials + i));
+
+  auto issue = [&](int64_t k) {   // thread 0 only
+    const int64_t chunk = blockIdx.x + k * gridDim.x;
+    const int64_t v0 = chunk * chunk_vecs;
+    const int64_t vecs = (n_vec - v0) < chunk_vecs ? (n_vec - v0) : chunk_vecs;
+    const uint32_t bytes = uint32_t(vecs) * 16u;
+    const int st = int(k % kStages);
+    mbar_expect_tx(&full_bar[st], bytes);
+    bulk_load(dyn_smem + size_t(st) * stage_bytes, in + v0 * P, bytes, &full_bar[st]);
+  };
+  if (threadIdx.x == 0)
+    for (int64_t k = 0; k < kStages - 1 && k < my_chunks; ++k) issue(k);
+
+  T acc[2][P];
+#pragma unroll
+  for (int e = 0; e < P; ++e) acc[0][e] = acc[1][e] = R::identity();
+
+  using V = typename Vec<T, P>::type;
+  for (int64_t k = 0; k < my_chunks; ++k) {
+    __syncthreads();   // every thread is done with the stage that chunk k + kStages - 1 will overwrite
+    if (threadIdx.x == 0 && k + kStages - 1 < my_chunks) issue(k + kStages - 1);
+    const int st = int(k % kStages);
+    mbar_wait(&full_bar[st], uint32_t((k / kStages) & 1));
+    const int64_t chunk = blockIdx.x + k * gridDim.x;
+    const int64_t left = n_vec - chunk * chunk_vecs;   // valid vectors in this stage
+    const V* stage = reinterpret_cast<const V*>(dyn_smem + size_t(st) * stage_bytes);
+    if (left >= chunk_vecs) {
+#pragma unroll
+      for (int j = 0; j < kVecPerThread; ++j) {
+        const V t = stage[j * b + threadIdx.x];
+        const T* tv = reinterpret_cast<const T*>(&t);
+#pragma unroll
+        for (int e = 0; e < P; ++e) acc[j & 1][e] = R::op(acc[j & 1][e], tv[e]);
+      }
+    } else {
+      for (int j = 0; j < kVecPerThread; ++j) {
+        if (int64_t(j) * b + threadIdx.x < left) {
+          const V t = stage[j * b + threadIdx.x];
+          const T* tv = reinterpret_cast<const T*>(&t);
+#pragma unroll
+          for (int e = 0; e < P; ++e) acc[j & 1][e] = R::op(acc[j & 1][e], tv[e]);
+        }
+      }
+    }
   }
-  sm2[threadIdx.x] = r;
-  __syncthreads();
-  if (threadIdx.x < L) {
-    T s = R::identity();
-    for (int t = threadIdx.x; t < bl; t += L) s = R::op(s, sm2[t]);
-    sm[threadIdx.x] = s;   // per flat-slot f totals
-  }
-  __syncthreads();
-  if (threadIdx.x < inner) {
-    T s = R::identity();
-    for (int f = threadIdx.x; f < L; f += inner) s = R::op(s, sm[f]);
-    // elements past the last full vector (n % P of them)
-    for (int64_t i = n_vec * P; i < n; ++i)
-      if (int(i % inner) == int(threadIdx.x)) s = R::op(s, in[i]);
-    out[threadIdx.x] = s;
-  }
-  if (threadIdx.x == 0) *counter = 0;
+  T a[P];
+#pragma unroll
+  for (int e = 0; e < P; ++e) a[e] = R::op(acc[0][e], acc[1][e]);
+  combine_and_finish<T, OP, P>(a, in, n, n_vec, inner, L, q, partials, counter, out, sm, sm2, &is_last);
 }
 
 // Wide cells: one thread per column, a slice of rows per blockIdx.y; partials[split][inner].
@@ -252,6 +374,27 @@ FlatGeom flat_geometry(int es, const void* in, int64_t inner, const DeviceInfo& 
   return g;
 }
 
+// TFS_REDUCE_IMPL=ldg selects the register-staged kernel for A/B measurements; default is TMA.
+int reduce_impl_from_env() {
+  const char* e = std::getenv("TFS_REDUCE_IMPL");
+  if (e && std::string(e) == "ldg") return 0;
+  return 1;
+}
+
+// resident CTAs per SM of the LDG kernel (persistent single wave)
+template <class T, int OP, int PV>
+int blocks_per_sm(int P) {
+  static int cached[2] = {0, 0};
+  int& c = cached[P == 1 ? 0 : 1];
+  if (c == 0) {
+    int b = 0;
+    if (P == 1) TFS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, reduce_axis0_flat_kernel<T, OP, 1>, kMaxThreads, 0));
+    else TFS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, reduce_axis0_flat_kernel<T, OP, PV>, kMaxThreads, 0));
+    c = b > 0 ? b : 1;
+  }
+  return c;
+}
+
 template <class T, int OP>
 int launch_axis0_t(const T* in, int64_t outer, int64_t inner, T* out, void* scratch, const DeviceInfo& dev,
                    cudaStream_t stream) {
@@ -261,9 +404,26 @@ int launch_axis0_t(const T* in, int64_t outer, int64_t inner, T* out, void* scra
   T* partials = reinterpret_cast<T*>(static_cast<char*>(scratch) + kCounterBytes);
   if (g.ok) {
     int64_t n_vec = n / g.P;
-    int64_t want = (n_vec + int64_t(g.threads) * kJ - 1) / (int64_t(g.threads) * kJ);
-    int grid = int(std::max<int64_t>(1, std::min<int64_t>(g.grid, want)));
     constexpr int PV = 16 / int(sizeof(T));
+    static const int impl = reduce_impl_from_env();
+    const int64_t chunk_vecs = int64_t(g.threads) * kVecPerThread;
+    if (impl == 1 && g.P == PV && n_vec >= 4 * chunk_vecs) {
+      // TMA-staged: one persistent CTA per SM
+      const size_t dyn = size_t(kStages) * size_t(chunk_vecs) * 16;
+      static bool attr_set = false;
+      if (!attr_set) {
+        TFS_CUDA(cudaFuncSetAttribute(reduce_axis0_tma_kernel<T, OP, PV>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      int(size_t(kStages) * kMaxThreads * kVecPerThread * 16)));
+        attr_set = true;
+      }
+      const int64_t n_chunks = (n_vec + chunk_vecs - 1) / chunk_vecs;
+      int grid = int(std::max<int64_t>(1, std::min<int64_t>(dev.sm_count, n_chunks)));
+      reduce_axis0_tma_kernel<T, OP, PV><<<grid, g.threads, dyn, stream>>>(in, n, int(inner), g.L, g.q, partials, counter, out);
+      TFS_CUDA(cudaGetLastError());
+      return 1;
+    }
+    int64_t want = (n_vec + int64_t(g.threads) * kJ - 1) / (int64_t(g.threads) * kJ);
+    int grid = int(std::max<int64_t>(1, std::min<int64_t>(int64_t(dev.sm_count) * blocks_per_sm<T, OP, PV>(g.P), want)));
     if (g.P == 1)
       reduce_axis0_flat_kernel<T, OP, 1><<<grid, g.threads, 0, stream>>>(in, n, int(inner), g.L, g.q, partials, counter, out);
     else

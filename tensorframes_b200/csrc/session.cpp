@@ -659,9 +659,108 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
   if (any_host) check_device_error();
 }
 
-void Session::aggregate(int64_t, const int64_t*, const std::vector<TensorArg>&, const std::vector<TensorArg>&,
-                        int64_t, int64_t*, int64_t*) {
-  fail(TFS_ERR_UNSUPPORTED, "aggregate is not available in this build");
+// ---------------------------------------------------------------------------
+// aggregate: the TensorFlowUDAF of the reference for one block (impl/DebugRowOps.scala:601-695)
+// ---------------------------------------------------------------------------
+void Session::aggregate(int64_t n_rows, const int64_t* keys, const std::vector<TensorArg>& feeds,
+                        const std::vector<TensorArg>& fetches, int64_t max_groups, int64_t* out_keys,
+                        int64_t* n_groups_out) {
+  TFS_CHECK(n_rows >= 0 && max_groups >= 0, TFS_ERR_INVALID, "negative row or group count");
+  TFS_CHECK(n_rows < (int64_t(1) << 32), TFS_ERR_UNSUPPORTED, "aggregate: blocks of 2^32 rows or more are not supported");
+  TFS_CHECK(n_rows == 0 || keys != nullptr, TFS_ERR_INVALID, "null key column");
+  TFS_CHECK(max_groups == 0 || out_keys != nullptr, TFS_ERR_INVALID, "null out_keys");
+  // Every fetch must be Sum/Min/Max over axis 0 of a fed placeholder: the keyed form of the
+  // reduce contract (fetch X <- placeholder X_input, impl/DebugRowOps.scala:80-170).
+  struct Item { int node; int feed; int64_t cell; size_t fetch; };
+  std::vector<Item> items;
+  for (size_t i = 0; i < fetches.size(); ++i) {
+    int idx = g_.find(fetches[i].name);
+    TFS_CHECK(idx >= 0, TFS_ERR_INVALID, "fetch '" + fetches[i].name + "' is not a node of the graph");
+    const Node& n = g_.nodes[size_t(idx)];
+    TFS_CHECK(n.cls == OpClass::Reduce, TFS_ERR_UNSUPPORTED,
+              "aggregate: fetch '" + n.name + "' (" + n.op + ") must be a Sum, Min or Max over axis 0 of its placeholder");
+    const Node& src = g_.nodes[size_t(n.in[0])];
+    TFS_CHECK(src.cls == OpClass::Placeholder, TFS_ERR_UNSUPPORTED,
+              "aggregate: fetch '" + n.name + "' must reduce a placeholder directly, found '" + src.name + "' (" + src.op + ")");
+    int feed = -1;
+    for (size_t f = 0; f < feeds.size(); ++f)
+      if (g_.find(feeds[f].name) == n.in[0]) feed = int(f);
+    TFS_CHECK(feed >= 0, TFS_ERR_INVALID, "placeholder '" + src.name + "' is needed by the fetches but was not fed");
+    const TensorArg& fa = feeds[size_t(feed)];
+    TFS_CHECK(fa.dtype == src.dtype, TFS_ERR_INVALID,
+              "The type of node '" + src.name + "' (" + dtype_name(src.dtype) +
+                  ") is not compatible with the data type of the feed (" + dtype_name(fa.dtype) + ")");
+    TFS_CHECK(fa.shape.fully_known() && fa.shape.rank >= 1 && fa.shape.d[0] == n_rows, TFS_ERR_INVALID,
+              "feed '" + src.name + "' must have " + std::to_string(n_rows) + " rows, got shape " + fa.shape.str());
+    std::vector<int> axes = normalize_axes(n, fa.shape.rank);
+    TFS_CHECK(axes.size() == 1 && axes[0] == 0, TFS_ERR_UNSUPPORTED,
+              "aggregate: fetch '" + n.name + "' must reduce axis 0 only");
+    int64_t cell = 1;
+    for (int d = 1; d < fa.shape.rank; ++d) cell *= fa.shape.d[d];
+    TFS_CHECK(fetches[i].data != nullptr || max_groups * cell == 0, TFS_ERR_INVALID,
+              "fetch '" + n.name + "' has no output buffer");
+    items.push_back({idx, feed, cell, i});
+  }
+  TFS_CHECK(!items.empty(), TFS_ERR_INVALID, "Output cannot be empty: no fetch requested");
+
+  ensure_device();
+  *n_groups_out = 0;
+  if (n_rows == 0) return;
+  TFS_CHECK(max_groups > 0, TFS_ERR_INVALID, "aggregate: max_groups must be positive for a non-empty block");
+
+  const AggLayout L = agg_layout(n_rows, max_groups);
+  auto up = [](size_t x) { return align_up(x); };
+  // workspace: [agg scratch][out_keys][staged keys][staged feeds][staged outputs]
+  size_t off = up(L.bytes);
+  const size_t off_out_keys = off; off += up(size_t(max_groups) * 8);
+  const bool keys_dev = is_device_pointer(keys);
+  size_t off_keys = 0;
+  if (!keys_dev) { off_keys = off; off += up(size_t(n_rows) * 8); }
+  std::vector<size_t> off_feed(items.size(), SIZE_MAX), off_out(items.size(), SIZE_MAX);
+  for (size_t k = 0; k < items.size(); ++k) {
+    const Node& n = g_.nodes[size_t(items[k].node)];
+    const size_t es = size_t(dtype_size(n.dtype));
+    if (!is_device_pointer(feeds[size_t(items[k].feed)].data)) { off_feed[k] = off; off += up(size_t(n_rows) * items[k].cell * es); }
+    if (!is_device_pointer(fetches[items[k].fetch].data)) { off_out[k] = off; off += up(size_t(max_groups) * items[k].cell * es); }
+  }
+  reserve_workspace(off);
+  char* scratch = ws_;
+  int64_t* d_out_keys = reinterpret_cast<int64_t*>(ws_ + off_out_keys);
+  const int64_t* d_keys = keys;
+  if (!keys_dev) {
+    TFS_CUDA(cudaMemcpyAsync(ws_ + off_keys, keys, size_t(n_rows) * 8, cudaMemcpyHostToDevice, stream_));
+    d_keys = reinterpret_cast<const int64_t*>(ws_ + off_keys);
+  }
+  launches_ += launch_agg_build(d_keys, n_rows, max_groups, scratch, L, d_out_keys, dev_, stream_);
+  // the number of groups sizes every later launch: one small readback
+  unsigned int header[4] = {0, 0, 0, 0};
+  TFS_CUDA(cudaMemcpyAsync(header, scratch + L.off_header, sizeof(header), cudaMemcpyDeviceToHost, stream_));
+  TFS_CUDA(cudaStreamSynchronize(stream_));
+  TFS_CHECK(header[1] == 0 && int64_t(header[0]) <= max_groups, TFS_ERR_INVALID,
+            "aggregate: the block holds more than max_groups = " + std::to_string(max_groups) + " distinct keys");
+  const int64_t n_groups = header[0];
+  launches_ += launch_agg_segments(d_keys, n_rows, n_groups, scratch, L, dev_, stream_);
+  for (size_t k = 0; k < items.size(); ++k) {
+    const Node& n = g_.nodes[size_t(items[k].node)];
+    const size_t es = size_t(dtype_size(n.dtype));
+    const void* payload = feeds[size_t(items[k].feed)].data;
+    if (off_feed[k] != SIZE_MAX) {
+      TFS_CUDA(cudaMemcpyAsync(ws_ + off_feed[k], payload, size_t(n_rows) * items[k].cell * es, cudaMemcpyHostToDevice, stream_));
+      payload = ws_ + off_feed[k];
+    }
+    void* out = off_out[k] != SIZE_MAX ? static_cast<void*>(ws_ + off_out[k]) : fetches[items[k].fetch].data;
+    launches_ += launch_agg_reduce(n.dtype, n.red_op, payload, items[k].cell, n_groups, scratch, L, out, dev_, stream_);
+    if (off_out[k] != SIZE_MAX && n_groups * items[k].cell > 0)
+      TFS_CUDA(cudaMemcpyAsync(fetches[items[k].fetch].data, out, size_t(n_groups) * items[k].cell * es,
+                               cudaMemcpyDeviceToHost, stream_));
+  }
+  if (n_groups > 0) {
+    const bool ok_dev = is_device_pointer(out_keys);
+    TFS_CUDA(cudaMemcpyAsync(out_keys, d_out_keys, size_t(n_groups) * 8,
+                             ok_dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, stream_));
+  }
+  TFS_CUDA(cudaStreamSynchronize(stream_));
+  *n_groups_out = n_groups;
 }
 
 }  // namespace tfs

@@ -336,6 +336,7 @@ def _reducer(op_name: str, parent: Node, reduction_indices: Optional[Sequence[in
         idx = [int(i) for i in reduction_indices]
 
     def internal(_p: str) -> List[Node]:
+        parent.freeze()
         return [constant(np.asarray(idx, dtype=np.int32)).named(parent.name + "/reduction_indices")]
 
     return Node(name, op_name, parent.scalarType, _reduce_shape(parent.shape, idx), [parent], internal, True,

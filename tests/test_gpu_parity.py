@@ -399,3 +399,85 @@ def test_reduce_blocks_over_partitions_matches_oracle():
         s, m = tfs.reduce_blocks([dsl.reduce_sum(yi, [0]).named("y"), dsl.reduce_min(zi, [0]).named("z")], df)
     assert np.all(np.abs(s - tf_ops.exact_sum_f64(y, 0)) <= 1e-12 * np.abs(y).sum(axis=0))
     assert m.tolist() == y.min(axis=0).tolist()
+
+
+# ---- keyed aggregate (K3) through the C ABI -----------------------------------------------------------
+def numpy_group_reduce(keys, v, op):
+    uniq, inv = np.unique(keys, return_inverse=True)
+    out = np.empty((len(uniq),) + v.shape[1:], dtype=v.dtype)
+    absum = np.empty((len(uniq),) + v.shape[1:], dtype=np.float64)
+    order = np.argsort(inv, kind="stable")
+    bounds = np.searchsorted(inv[order], np.arange(len(uniq) + 1))
+    for g in range(len(uniq)):
+        rows = v[order[bounds[g]:bounds[g + 1]]]
+        if op == "sum":
+            if v.dtype.kind == "f":
+                out[g] = rows.astype(np.longdouble).sum(axis=0).astype(v.dtype)
+            else:
+                out[g] = rows.sum(axis=0, dtype=v.dtype)
+        elif op == "min":
+            out[g] = rows.min(axis=0)
+        else:
+            out[g] = rows.max(axis=0)
+        absum[g] = np.abs(rows.astype(np.float64)).sum(axis=0)
+    return uniq, out, absum
+
+
+def aggregate_graph(st, cell_shape, op):
+    with dsl.withGraph():
+        p = dsl.placeholder(st, dsl.Unknown, *cell_shape).named("v_input")
+        return dsl.build_graph(RED[op](p, [0]).named("v"))
+
+
+@pytest.mark.parametrize("dt", list(T))
+@pytest.mark.parametrize("op", list(RED))
+@pytest.mark.parametrize("cell", [(), (1,), (3,), (64,), (100,), (8, 8), (257,)])
+def test_aggregate_matches_numpy_groupby(dt, op, cell):
+    st = T[dt]
+    rng = np.random.default_rng(len(cell) * 7 + 1)
+    n, n_keys = 20011, 257
+    table = rng.integers(-2**62, 2**62, n_keys)           # sparse 64-bit keys: the hash is really exercised
+    table[0] = -2**63                                       # the value the table uses as its empty marker
+    keys = table[rng.integers(0, n_keys, n)].astype(np.int64)
+    v = rand(rng, st, (n,) + cell)
+    g = aggregate_graph(st, cell, op)
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        got_keys, (got,) = s.aggregate(keys, {"v_input": v}, ["v"], max_groups=n_keys)
+    want_keys, want, absum = numpy_group_reduce(keys, v, op)
+    order = np.argsort(got_keys)
+    assert got_keys[order].tolist() == want_keys.tolist()       # keys bit-exact, each exactly once
+    got = got[order]
+    if op == "sum" and st.np_dtype.kind == "f":
+        err = np.abs(got.astype(np.float64) - want.astype(np.float64))
+        assert np.all(err <= TOL[st.np_dtype] * np.maximum(absum, 1e-300))
+    else:
+        assert_same(got, want)
+
+
+def test_aggregate_config4_shape_and_group_overflow():
+    """BASELINE config 4 at reduced scale: int64 keys, FloatType[?,64] payload, reduce_sum."""
+    rng = np.random.default_rng(4)
+    n, n_keys = 400_003, 10_000
+    table = rng.integers(-2**63, 2**63 - 1, n_keys, dtype=np.int64)
+    keys = table[rng.integers(0, n_keys, n)]
+    v = rng.uniform(0, 1, (n, 64)).astype(np.float32)
+    g = aggregate_graph(tfs.FloatType, (64,), "sum")
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        got_keys, (got,) = s.aggregate(keys, {"v_input": v}, ["v"], max_groups=n_keys)
+        with pytest.raises(_native.NativeError, match="more than max_groups"):
+            s.aggregate(keys, {"v_input": v}, ["v"], max_groups=n_keys // 2)
+        again_keys, (again,) = s.aggregate(keys, {"v_input": v}, ["v"], max_groups=n)   # session still usable
+    want_keys, want, absum = numpy_group_reduce(keys, v, "sum")
+    for k_, o_ in ((got_keys, got), (again_keys, again)):
+        order = np.argsort(k_)
+        assert k_[order].tolist() == want_keys.tolist()
+        assert np.all(np.abs(o_[order].astype(np.float64) - want.astype(np.float64)) <= 1e-5 * absum)
+
+
+def test_aggregate_rejects_non_reducer_graphs():
+    with dsl.withGraph():
+        p = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x_input")
+        g = dsl.build_graph(dsl.identity(p).named("x"))
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        with pytest.raises(_native.UnsupportedError, match="must be a Sum, Min or Max"):
+            s.aggregate(np.zeros(4, np.int64), {"x_input": np.zeros(4)}, ["x"], max_groups=4)
