@@ -11,8 +11,10 @@
 // coalesced 128-bit -- or 64-bit for a 4-byte column next to an 8-byte one --
 // transaction, kJ of them in flight per thread).  The group's program
 // (program.h) is interpreted once per tile with the accumulator tile held in
-// registers; the opcode switch is warp-uniform, so there is no divergence and
-// its cost is amortised over kJ*P elements.  HBM-bound: the roofline is
+// registers.  Each instruction is one flat opcode (operation, dtype, operand
+// kind and operand order pre-resolved on the host), so decoding is a single
+// warp-uniform jump whose cost is amortised over kJ*P elements; immediates are
+// applied straight from the instruction word.  HBM-bound: the roofline is
 // (bytes read + bytes written) / HBM bandwidth.
 //
 // Arithmetic follows the TF 1.1 CPU kernels: IEEE round-to-nearest for + - * /
@@ -174,58 +176,66 @@ __device__ __forceinline__ void store_vec(const BufRef& b, int64_t elem, int nva
   }
 }
 
-// ---- typed application over the register tile -------------------------------
-template <class T, int ES, int P>
-__device__ __forceinline__ void apply_unary(int sub, typename Slot<ES>::type (&acc)[kJ][P]) {
-  using S = typename Slot<ES>::type;
-#define TFS_UN(expr)                                              \
-  _Pragma("unroll") for (int j = 0; j < kJ; ++j)                  \
-  _Pragma("unroll") for (int e = 0; e < P; ++e) {                 \
-    T a = from_slot<T, S>(acc[j][e]);                             \
-    acc[j][e] = to_slot<S, T>(expr);                              \
-  }
-  switch (sub) {
-    case E_NEG: TFS_UN(Arith<T>::neg(a)) break;
-    case E_RELU: TFS_UN(Arith<T>::mx(a, T(0))) break;
-    case E_SQUARE: TFS_UN(Arith<T>::mul(a, a)) break;
-    case E_ABS: TFS_UN(Arith<T>::abs(a)) break;
-    case E_SQRT: TFS_UN(Arith<T>::sqrt(a)) break;
-    case E_RECIP: TFS_UN(Arith<T>::recip(a)) break;
-    default: break;  // E_IDENTITY
-  }
-#undef TFS_UN
+// ---- typed handlers over the register tile ----------------------------------------------------
+template <class T, int SUB>
+__device__ __forceinline__ T bin_eval(T a, T b, bool valid, int* err) {
+  if constexpr (SUB == B_ADD) return Arith<T>::add(a, b);
+  else if constexpr (SUB == B_SUB) return Arith<T>::sub(a, b);
+  else if constexpr (SUB == B_MUL) return Arith<T>::mul(a, b);
+  else if constexpr (SUB == B_DIV) return Arith<T>::div(a, b, valid, err);
+  else if constexpr (SUB == B_MIN) return Arith<T>::mn(a, b);
+  else return Arith<T>::mx(a, b);
 }
 
-template <class T, int ES, int P>
-__device__ __forceinline__ void apply_binary(int sub, bool swap, typename Slot<ES>::type (&acc)[kJ][P],
-                                             const typename Slot<ES>::type (&x)[kJ][P],
-                                             const int (&nvalid)[kJ], int* err) {
+template <class T, int SUB, bool SWAP, int ES, int P>
+__device__ __forceinline__ void do_bin_x(typename Slot<ES>::type (&acc)[kJ][P],
+                                         const typename Slot<ES>::type (&x)[kJ][P], const int (&nvalid)[kJ], int* err) {
   using S = typename Slot<ES>::type;
-#define TFS_BIN_LOOP(A, B, expr)                                  \
-  _Pragma("unroll") for (int j = 0; j < kJ; ++j)                  \
-  _Pragma("unroll") for (int e = 0; e < P; ++e) {                 \
-    T a = from_slot<T, S>(A[j][e]);                               \
-    T b = from_slot<T, S>(B[j][e]);                               \
-    acc[j][e] = to_slot<S, T>(expr);                              \
-  }
-  // the operand order is warp-uniform: branch once instead of selecting per element
-#define TFS_BIN(expr)                                             \
-  if (swap) { TFS_BIN_LOOP(x, acc, expr) } else { TFS_BIN_LOOP(acc, x, expr) }
-  switch (sub) {
-    case E_ADD: TFS_BIN(Arith<T>::add(a, b)) break;
-    case E_SUB: TFS_BIN(Arith<T>::sub(a, b)) break;
-    case E_MUL: TFS_BIN(Arith<T>::mul(a, b)) break;
-    case E_DIV: TFS_BIN(Arith<T>::div(a, b, e < nvalid[j], err)) break;
-    case E_MIN: TFS_BIN(Arith<T>::mn(a, b)) break;
-    case E_MAX: TFS_BIN(Arith<T>::mx(a, b)) break;
-    default: break;
-  }
-#undef TFS_BIN_LOOP
-#undef TFS_BIN
+#pragma unroll
+  for (int j = 0; j < kJ; ++j)
+#pragma unroll
+    for (int e = 0; e < P; ++e) {
+      const T l = from_slot<T, S>(acc[j][e]);
+      const T r = from_slot<T, S>(x[j][e]);
+      acc[j][e] = to_slot<S, T>(SWAP ? bin_eval<T, SUB>(r, l, e < nvalid[j], err) : bin_eval<T, SUB>(l, r, e < nvalid[j], err));
+    }
+}
+
+template <class T, int SUB, bool SWAP, int ES, int P>
+__device__ __forceinline__ void do_bin_imm(typename Slot<ES>::type (&acc)[kJ][P], const unsigned long long imm,
+                                           const int (&nvalid)[kJ], int* err) {
+  using S = typename Slot<ES>::type;
+  const T r = from_slot<T, unsigned long long>(imm);
+#pragma unroll
+  for (int j = 0; j < kJ; ++j)
+#pragma unroll
+    for (int e = 0; e < P; ++e) {
+      const T l = from_slot<T, S>(acc[j][e]);
+      acc[j][e] = to_slot<S, T>(SWAP ? bin_eval<T, SUB>(r, l, e < nvalid[j], err) : bin_eval<T, SUB>(l, r, e < nvalid[j], err));
+    }
+}
+
+template <class T, int SUB, int ES, int P>
+__device__ __forceinline__ void do_unary(typename Slot<ES>::type (&acc)[kJ][P]) {
+  using S = typename Slot<ES>::type;
+#pragma unroll
+  for (int j = 0; j < kJ; ++j)
+#pragma unroll
+    for (int e = 0; e < P; ++e) {
+      const T a = from_slot<T, S>(acc[j][e]);
+      T r;
+      if constexpr (SUB == U_NEG) r = Arith<T>::neg(a);
+      else if constexpr (SUB == U_RELU) r = Arith<T>::mx(a, T(0));
+      else if constexpr (SUB == U_SQUARE) r = Arith<T>::mul(a, a);
+      else if constexpr (SUB == U_ABS) r = Arith<T>::abs(a);
+      else if constexpr (SUB == U_SQRT) r = Arith<T>::sqrt(a);
+      else r = Arith<T>::recip(a);
+      acc[j][e] = to_slot<S, T>(r);
+    }
 }
 
 template <class From, class To, int ES, int P>
-__device__ __forceinline__ void apply_cast(typename Slot<ES>::type (&acc)[kJ][P]) {
+__device__ __forceinline__ void do_cast(typename Slot<ES>::type (&acc)[kJ][P]) {
   using S = typename Slot<ES>::type;
 #pragma unroll
   for (int j = 0; j < kJ; ++j)
@@ -234,15 +244,48 @@ __device__ __forceinline__ void apply_cast(typename Slot<ES>::type (&acc)[kJ][P]
       acc[j][e] = to_slot<S, To>(static_cast<To>(from_slot<From, S>(acc[j][e])));
 }
 
-template <class From, int ES, int P>
-__device__ __forceinline__ void cast_from(int dt2, typename Slot<ES>::type (&acc)[kJ][P]) {
-  switch (dt2) {
-    case DI_F32: apply_cast<From, float, ES, P>(acc); break;
-    case DI_I32: apply_cast<From, int, ES, P>(acc); break;
-    case DI_F64: if constexpr (ES == 8) apply_cast<From, double, ES, P>(acc); break;
-    case DI_I64: if constexpr (ES == 8) apply_cast<From, long long, ES, P>(acc); break;
-  }
+template <int ES, int P>
+__device__ __forceinline__ void copy_tile(typename Slot<ES>::type (&dst)[kJ][P], const typename Slot<ES>::type (&src)[kJ][P]) {
+#pragma unroll
+  for (int j = 0; j < kJ; ++j)
+#pragma unroll
+    for (int e = 0; e < P; ++e) dst[j][e] = src[j][e];
 }
+
+// 64-bit dtypes only exist in the ES == 8 instantiation
+#define TFS_WIDE(stmt) if constexpr (ES == 8) { stmt; }
+
+// the 8 opcodes of one binary sub-op with a tensor operand / with an immediate
+#define TFS_BIN_CASES(SUB)                                                                             \
+  case C_BIN_X + SUB * 8 + DI_F32 * 2 + 0: do_bin_x<float, SUB, false, ES, P>(acc, x, nvalid, prog.err); break;       \
+  case C_BIN_X + SUB * 8 + DI_F32 * 2 + 1: do_bin_x<float, SUB, true, ES, P>(acc, x, nvalid, prog.err); break;        \
+  case C_BIN_X + SUB * 8 + DI_I32 * 2 + 0: do_bin_x<int, SUB, false, ES, P>(acc, x, nvalid, prog.err); break;         \
+  case C_BIN_X + SUB * 8 + DI_I32 * 2 + 1: do_bin_x<int, SUB, true, ES, P>(acc, x, nvalid, prog.err); break;          \
+  case C_BIN_X + SUB * 8 + DI_F64 * 2 + 0: TFS_WIDE((do_bin_x<double, SUB, false, ES, P>(acc, x, nvalid, prog.err))) break;    \
+  case C_BIN_X + SUB * 8 + DI_F64 * 2 + 1: TFS_WIDE((do_bin_x<double, SUB, true, ES, P>(acc, x, nvalid, prog.err))) break;     \
+  case C_BIN_X + SUB * 8 + DI_I64 * 2 + 0: TFS_WIDE((do_bin_x<long long, SUB, false, ES, P>(acc, x, nvalid, prog.err))) break; \
+  case C_BIN_X + SUB * 8 + DI_I64 * 2 + 1: TFS_WIDE((do_bin_x<long long, SUB, true, ES, P>(acc, x, nvalid, prog.err))) break;  \
+  case C_BIN_IMM + SUB * 8 + DI_F32 * 2 + 0: do_bin_imm<float, SUB, false, ES, P>(acc, in.imm, nvalid, prog.err); break;     \
+  case C_BIN_IMM + SUB * 8 + DI_F32 * 2 + 1: do_bin_imm<float, SUB, true, ES, P>(acc, in.imm, nvalid, prog.err); break;      \
+  case C_BIN_IMM + SUB * 8 + DI_I32 * 2 + 0: do_bin_imm<int, SUB, false, ES, P>(acc, in.imm, nvalid, prog.err); break;       \
+  case C_BIN_IMM + SUB * 8 + DI_I32 * 2 + 1: do_bin_imm<int, SUB, true, ES, P>(acc, in.imm, nvalid, prog.err); break;        \
+  case C_BIN_IMM + SUB * 8 + DI_F64 * 2 + 0: TFS_WIDE((do_bin_imm<double, SUB, false, ES, P>(acc, in.imm, nvalid, prog.err))) break;    \
+  case C_BIN_IMM + SUB * 8 + DI_F64 * 2 + 1: TFS_WIDE((do_bin_imm<double, SUB, true, ES, P>(acc, in.imm, nvalid, prog.err))) break;     \
+  case C_BIN_IMM + SUB * 8 + DI_I64 * 2 + 0: TFS_WIDE((do_bin_imm<long long, SUB, false, ES, P>(acc, in.imm, nvalid, prog.err))) break; \
+  case C_BIN_IMM + SUB * 8 + DI_I64 * 2 + 1: TFS_WIDE((do_bin_imm<long long, SUB, true, ES, P>(acc, in.imm, nvalid, prog.err))) break;
+
+#define TFS_UN_CASES(SUB)                                                                   \
+  case C_UNARY + SUB * 4 + DI_F32: do_unary<float, SUB, ES, P>(acc); break;                 \
+  case C_UNARY + SUB * 4 + DI_I32: do_unary<int, SUB, ES, P>(acc); break;                   \
+  case C_UNARY + SUB * 4 + DI_F64: TFS_WIDE((do_unary<double, SUB, ES, P>(acc))) break;     \
+  case C_UNARY + SUB * 4 + DI_I64: TFS_WIDE((do_unary<long long, SUB, ES, P>(acc))) break;
+
+#define TFS_CAST_CASES(FROM_DI, FROM_T, GUARD)                                                        \
+  case C_CAST + FROM_DI * 4 + DI_F32: GUARD((do_cast<FROM_T, float, ES, P>(acc))) break;              \
+  case C_CAST + FROM_DI * 4 + DI_I32: GUARD((do_cast<FROM_T, int, ES, P>(acc))) break;                \
+  case C_CAST + FROM_DI * 4 + DI_F64: TFS_WIDE((do_cast<FROM_T, double, ES, P>(acc))) break;          \
+  case C_CAST + FROM_DI * 4 + DI_I64: TFS_WIDE((do_cast<FROM_T, long long, ES, P>(acc))) break;
+#define TFS_ALWAYS(stmt) { stmt; }
 
 template <int ES, int P>
 __global__ void __launch_bounds__(kThreads, 3)
@@ -268,89 +311,63 @@ eltwise_kernel(const __grid_constant__ EltProgram prog, const int64_t n) {
     }
     for (int pc = 0; pc < prog.n_instr; ++pc) {
       const Instr in = prog.ins[pc];
-      // operand fetch into x (M_LOAD then moves it to acc: register moves only, and it
-      // keeps both tiles statically indexed so they stay in registers)
-      if (in.op == M_LOAD || in.op == M_BINARY) {
-        S(&dst)[kJ][P] = x;
-        switch (in.src) {
-          case S_BUF: {
-            const BufRef b = prog.bufs[in.arg];
+      switch (in.code) {
+        case C_LOAD_BUF: {
+          const BufRef b = prog.bufs[in.arg];
 #pragma unroll
-            for (int j = 0; j < kJ; ++j) load_vec<ES, P>(b, elem[j], nvalid[j], dst[j]);
-            break;
-          }
-          case S_PERIODIC: {
-            const BufRef b = prog.bufs[in.arg];
-#pragma unroll
-            for (int j = 0; j < kJ; ++j) load_periodic<ES, P>(b, elem[j], nvalid[j], dst[j]);
-            break;
-          }
-          case S_IMM:
-#pragma unroll
-            for (int j = 0; j < kJ; ++j)
-#pragma unroll
-              for (int e = 0; e < P; ++e) dst[j][e] = S(in.imm);
-            break;
-          case S_TMP:
-#pragma unroll
-            for (int j = 0; j < kJ; ++j)
-#pragma unroll
-              for (int e = 0; e < P; ++e) dst[j][e] = tmp[in.arg][j][e];
-            break;
-          case S_ACC:
-#pragma unroll
-            for (int j = 0; j < kJ; ++j)
-#pragma unroll
-              for (int e = 0; e < P; ++e) dst[j][e] = acc[j][e];
-            break;
-          default: break;
+          for (int j = 0; j < kJ; ++j) load_vec<ES, P>(b, elem[j], nvalid[j], acc[j]);
+          break;
         }
-      }
-      switch (in.op) {
-        case M_LOAD:
+        case C_FETCH_BUF: {
+          const BufRef b = prog.bufs[in.arg];
+#pragma unroll
+          for (int j = 0; j < kJ; ++j) load_vec<ES, P>(b, elem[j], nvalid[j], x[j]);
+          break;
+        }
+        case C_LOAD_PER: {
+          const BufRef b = prog.bufs[in.arg];
+#pragma unroll
+          for (int j = 0; j < kJ; ++j) load_periodic<ES, P>(b, elem[j], nvalid[j], acc[j]);
+          break;
+        }
+        case C_FETCH_PER: {
+          const BufRef b = prog.bufs[in.arg];
+#pragma unroll
+          for (int j = 0; j < kJ; ++j) load_periodic<ES, P>(b, elem[j], nvalid[j], x[j]);
+          break;
+        }
+        case C_LOAD_IMM:
 #pragma unroll
           for (int j = 0; j < kJ; ++j)
 #pragma unroll
-            for (int e = 0; e < P; ++e) acc[j][e] = x[j][e];
+            for (int e = 0; e < P; ++e) acc[j][e] = S(in.imm);
           break;
-        case M_STORE: {
+        case C_LOAD_TMP: copy_tile<ES, P>(acc, tmp[in.arg]); break;
+        case C_FETCH_TMP: copy_tile<ES, P>(x, tmp[in.arg]); break;
+        case C_FETCH_ACC: copy_tile<ES, P>(x, acc); break;
+        case C_STTMP: copy_tile<ES, P>(tmp[in.arg], acc); break;
+        case C_STORE: {
           const BufRef b = prog.bufs[in.arg];
 #pragma unroll
           for (int j = 0; j < kJ; ++j) store_vec<ES, P>(b, elem[j], nvalid[j], acc[j]);
           break;
         }
-        case M_STTMP:
-#pragma unroll
-          for (int j = 0; j < kJ; ++j)
-#pragma unroll
-            for (int e = 0; e < P; ++e) tmp[in.arg][j][e] = acc[j][e];
-          break;
-        case M_UNARY:
-          switch (in.dt) {
-            case DI_F32: apply_unary<float, ES, P>(in.sub, acc); break;
-            case DI_I32: apply_unary<int, ES, P>(in.sub, acc); break;
-            case DI_F64: if constexpr (ES == 8) apply_unary<double, ES, P>(in.sub, acc); break;
-            case DI_I64: if constexpr (ES == 8) apply_unary<long long, ES, P>(in.sub, acc); break;
-          }
-          break;
-        case M_CAST:
-          switch (in.dt) {
-            case DI_F32: cast_from<float, ES, P>(in.dt2, acc); break;
-            case DI_I32: cast_from<int, ES, P>(in.dt2, acc); break;
-            case DI_F64: if constexpr (ES == 8) cast_from<double, ES, P>(in.dt2, acc); break;
-            case DI_I64: if constexpr (ES == 8) cast_from<long long, ES, P>(in.dt2, acc); break;
-          }
-          break;
-        case M_BINARY: {
-          const bool swap = (in.flags & F_SWAP) != 0;
-          switch (in.dt) {
-            case DI_F32: apply_binary<float, ES, P>(in.sub, swap, acc, x, nvalid, prog.err); break;
-            case DI_I32: apply_binary<int, ES, P>(in.sub, swap, acc, x, nvalid, prog.err); break;
-            case DI_F64: if constexpr (ES == 8) apply_binary<double, ES, P>(in.sub, swap, acc, x, nvalid, prog.err); break;
-            case DI_I64: if constexpr (ES == 8) apply_binary<long long, ES, P>(in.sub, swap, acc, x, nvalid, prog.err); break;
-          }
-          break;
-        }
+        TFS_BIN_CASES(B_ADD)
+        TFS_BIN_CASES(B_SUB)
+        TFS_BIN_CASES(B_MUL)
+        TFS_BIN_CASES(B_DIV)
+        TFS_BIN_CASES(B_MIN)
+        TFS_BIN_CASES(B_MAX)
+        TFS_UN_CASES(U_NEG)
+        TFS_UN_CASES(U_RELU)
+        TFS_UN_CASES(U_SQUARE)
+        TFS_UN_CASES(U_ABS)
+        TFS_UN_CASES(U_SQRT)
+        TFS_UN_CASES(U_RECIP)
+        TFS_CAST_CASES(DI_F32, float, TFS_ALWAYS)
+        TFS_CAST_CASES(DI_I32, int, TFS_ALWAYS)
+        TFS_CAST_CASES(DI_F64, double, TFS_WIDE)
+        TFS_CAST_CASES(DI_I64, long long, TFS_WIDE)
         default: break;
       }
     }

@@ -7,6 +7,10 @@
 // replaces the chain of separate Eigen kernels TF-CPU runs for the same nodes
 // behind Session.run (reference: impl/DebugRowOps.scala:794), each of which
 // reads and writes a full intermediate tensor.
+//
+// Every instruction carries ONE flat opcode in which the operation, the dtype,
+// the operand kind and the operand order are already resolved, so the device
+// decodes an instruction with a single warp-uniform jump.
 #pragma once
 #include <cstdint>
 
@@ -19,42 +23,43 @@ constexpr int kMaxTmp = 4;
 // dtype index used on the device: 0 f32, 1 f64, 2 i32, 3 i64 (see common.h dtype_index).
 enum : uint8_t { DI_F32 = 0, DI_F64 = 1, DI_I32 = 2, DI_I64 = 3 };
 
-// machine opcodes
-enum : uint8_t {
-  M_LOAD = 0,   // acc <- src
-  M_STORE = 1,  // bufs[arg] <- acc            (dt = dtype of acc)
-  M_STTMP = 2,  // tmp[arg] <- acc
-  M_UNARY = 3,  // acc <- un(sub, acc)         (sub = EltOp, dt)
-  M_CAST = 4,   // acc <- cast<dt2>(acc as dt)
-  M_BINARY = 5, // acc <- bin(sub, acc, src)   (flag SWAP: bin(sub, src, acc))
-};
+// binary sub-ops, in opcode order
+enum : uint8_t { B_ADD = 0, B_SUB = 1, B_MUL = 2, B_DIV = 3, B_MIN = 4, B_MAX = 5, B_COUNT = 6 };
+// unary sub-ops
+enum : uint8_t { U_NEG = 0, U_RELU = 1, U_SQUARE = 2, U_ABS = 3, U_SQRT = 4, U_RECIP = 5, U_COUNT = 6 };
 
-// operand kinds
+// flat opcodes
 enum : uint8_t {
-  S_NONE = 0,
-  S_BUF = 1,       // bufs[arg], same flat index as the output
-  S_PERIODIC = 2,  // bufs[arg][flat % period]  (row-broadcast of a cell-shaped tensor, or a computed scalar)
-  S_IMM = 3,       // scalar immediate (bits in imm, typed by dt)
-  S_TMP = 4,       // tmp[arg]
-  S_ACC = 5,       // the accumulator itself (x + x)
+  C_LOAD_BUF = 1,    // acc <- bufs[arg][flat]
+  C_LOAD_PER = 2,    // acc <- bufs[arg][flat % period]
+  C_LOAD_IMM = 3,    // acc <- imm
+  C_LOAD_TMP = 4,    // acc <- tmp[arg]
+  C_FETCH_BUF = 5,   // x <- bufs[arg][flat]            (operand of a following C_BIN_X)
+  C_FETCH_PER = 6,   // x <- bufs[arg][flat % period]
+  C_FETCH_TMP = 7,   // x <- tmp[arg]
+  C_FETCH_ACC = 8,   // x <- acc                         (x + x)
+  C_STORE = 9,       // bufs[arg][flat] <- acc
+  C_STTMP = 10,      // tmp[arg] <- acc
+  // acc <- op(acc, x)   (swap: op(x, acc));   code = C_BIN_X + sub * 8 + dt * 2 + swap
+  C_BIN_X = 32,
+  // acc <- op(acc, imm) (swap: op(imm, acc)); code = C_BIN_IMM + sub * 8 + dt * 2 + swap
+  C_BIN_IMM = 96,
+  // acc <- un(acc);                            code = C_UNARY + sub * 4 + dt
+  C_UNARY = 160,
+  // acc <- cast<to>(acc as from);              code = C_CAST + from * 4 + to
+  C_CAST = 192,
 };
-
-enum : uint8_t { F_SWAP = 1 };
 
 struct Instr {
-  uint8_t op;
-  uint8_t sub;    // EltOp for M_UNARY / M_BINARY
-  uint8_t dt;     // dtype index the op computes in
-  uint8_t dt2;    // M_CAST: destination dtype index
-  uint8_t src;    // operand kind
-  uint8_t flags;
-  uint16_t arg;   // buffer or tmp index
-  uint64_t imm;
+  uint8_t code;
+  uint8_t arg;      // buffer or tmp index
+  uint8_t pad[6];
+  uint64_t imm;     // immediate operand bits (low 32 bits for 4-byte dtypes)
 };
 
 struct BufRef {
   void* ptr;
-  int64_t period;  // S_PERIODIC: number of elements in the small tensor
+  int64_t period;  // C_*_PER: number of elements in the small tensor
   int32_t dt;      // dtype index of the buffer's elements
   int32_t pad;
 };

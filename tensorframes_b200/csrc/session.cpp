@@ -341,6 +341,9 @@ struct GroupCompiler {
   std::set<int> done;
   bool tmp_busy[kMaxTmp] = {false, false, false, false};
 
+  // where an operand comes from
+  struct Source { enum Kind { BUF, PERIODIC, IMM, TMP } kind; int arg = 0; uint64_t imm = 0; };
+
   GroupCompiler(const Graph& g_, const std::vector<Shape>& sh, const std::vector<void*>& dp,
                 const std::vector<char>& mat, const Step& st)
       : g(g_), shape(sh), dev_ptr(dp), materialize(mat), step(st) {
@@ -357,14 +360,16 @@ struct GroupCompiler {
   }
 
   const Node& node(int i) const { return g.nodes[size_t(i)]; }
-  uint8_t di(int n) const { return uint8_t(dtype_index(node(n).dtype)); }
+  int di(int n) const { return dtype_index(node(n).dtype); }
 
-  Instr& emit(uint8_t op) {
+  Instr& emit(int code, int arg = 0, uint64_t imm = 0) {
     TFS_CHECK(prog.n_instr < kMaxInstr, TFS_ERR_UNSUPPORTED,
               "element-wise group too large for one kernel (" + std::to_string(kMaxInstr) + " instructions)");
     Instr& in = prog.ins[prog.n_instr++];
     in = Instr{};
-    in.op = op;
+    in.code = uint8_t(code);
+    in.arg = uint8_t(arg);
+    in.imm = imm;
     return in;
   }
   int alloc_tmp() {
@@ -387,31 +392,30 @@ struct GroupCompiler {
     return prog.n_bufs++;
   }
 
-  // Fills src/arg/imm of `in` for operand `o` (an external tensor or a member held in a tmp).
-  void set_source(Instr& in, int o) {
+  // Operand `o`: an external tensor, or a member already held in a temporary (whose use is consumed).
+  Source source_of(int o) {
+    Source src;
     if (members.count(o)) {
       auto it = tmp_of.find(o);
       TFS_CHECK(it != tmp_of.end(), TFS_ERR_INVALID, "internal: member operand without a temporary");
-      in.src = S_TMP;
-      in.arg = uint16_t(it->second);
+      src.kind = Source::TMP;
+      src.arg = it->second;
       if (--uses[o] == 0) { tmp_busy[it->second] = false; tmp_of.erase(it); }
-      return;
+      return src;
     }
     const Shape& os = shape[size_t(o)];
     const Shape& it = step.shape;
     const int64_t on = os.numel(), n = it.numel();
     const Node& no = node(o);
     if (on == 1 && no.cls == OpClass::Const) {
-      in.src = S_IMM;
-      uint64_t bits = 0;
-      memcpy(&bits, no.value.bytes.data(), size_t(dtype_size(no.dtype)));
-      in.imm = bits;
-      return;
+      src.kind = Source::IMM;
+      memcpy(&src.imm, no.value.bytes.data(), size_t(dtype_size(no.dtype)));
+      return src;
     }
     if (on == n) {
-      in.src = S_BUF;
-      in.arg = uint16_t(buffer(o, 0));
-      return;
+      src.kind = Source::BUF;
+      src.arg = buffer(o, 0);
+      return src;
     }
     // row broadcast: operand dims (leading 1s dropped) must equal the trailing dims of the block
     int lead = 0;
@@ -422,8 +426,9 @@ struct GroupCompiler {
     TFS_CHECK(ok, TFS_ERR_UNSUPPORTED,
               "broadcasting " + os.str() + " against " + it.str() + " (operand '" + no.name +
                   "') is not supported: only scalars and trailing-dimension broadcasts are");
-    in.src = S_PERIODIC;
-    in.arg = uint16_t(buffer(o, on));
+    src.kind = Source::PERIODIC;
+    src.arg = buffer(o, on);
+    return src;
   }
 
   bool needs_compute(int o) const { return members.count(o) && !tmp_of.count(o); }
@@ -431,11 +436,52 @@ struct GroupCompiler {
   void into_acc(int o) {
     if (needs_compute(o)) {
       compute(o, true);
-    } else {
-      Instr& in = emit(M_LOAD);
-      in.dt = di(o);
-      set_source(in, o);
+      return;
     }
+    Source s = source_of(o);
+    switch (s.kind) {
+      case Source::BUF: emit(C_LOAD_BUF, s.arg); break;
+      case Source::PERIODIC: emit(C_LOAD_PER, s.arg); break;
+      case Source::IMM: emit(C_LOAD_IMM, 0, s.imm); break;
+      case Source::TMP: emit(C_LOAD_TMP, s.arg); break;
+    }
+  }
+
+  static int bin_sub(int elt_op) {
+    switch (elt_op) {
+      case E_ADD: return B_ADD;
+      case E_SUB: return B_SUB;
+      case E_MUL: return B_MUL;
+      case E_DIV: return B_DIV;
+      case E_MIN: return B_MIN;
+      default: return B_MAX;
+    }
+  }
+  static int un_sub(int elt_op) {
+    switch (elt_op) {
+      case E_NEG: return U_NEG;
+      case E_RELU: return U_RELU;
+      case E_SQUARE: return U_SQUARE;
+      case E_ABS: return U_ABS;
+      case E_SQRT: return U_SQRT;
+      default: return U_RECIP;
+    }
+  }
+
+  // acc <- op(acc, operand)  (swap: op(operand, acc)), operand being a leaf
+  void binary_with(int n, int operand, bool swap) {
+    const int sub = bin_sub(node(n).elt_op), dt = di(n), sw = swap ? 1 : 0;
+    Source s = source_of(operand);
+    if (s.kind == Source::IMM) {
+      emit(C_BIN_IMM + sub * 8 + dt * 2 + sw, 0, s.imm);
+      return;
+    }
+    switch (s.kind) {
+      case Source::BUF: emit(C_FETCH_BUF, s.arg); break;
+      case Source::PERIODIC: emit(C_FETCH_PER, s.arg); break;
+      default: emit(C_FETCH_TMP, s.arg); break;
+    }
+    emit(C_BIN_X + sub * 8 + dt * 2 + sw);
   }
 
   // Leaves the value of member n in the accumulator.
@@ -446,58 +492,41 @@ struct GroupCompiler {
     if (nd.cls == OpClass::Fill || nd.cls == OpClass::Unary) {
       into_acc(ops[0]);
       if (nd.cls == OpClass::Unary && nd.elt_op == E_CAST) {
-        Instr& in = emit(M_CAST);
-        in.dt = di(ops[0]);
-        in.dt2 = di(n);
+        if (di(ops[0]) != di(n)) emit(C_CAST + di(ops[0]) * 4 + di(n));
       } else if (nd.cls == OpClass::Unary && nd.elt_op != E_IDENTITY) {
-        Instr& in = emit(M_UNARY);
-        in.sub = uint8_t(nd.elt_op);
-        in.dt = di(n);
+        emit(C_UNARY + un_sub(nd.elt_op) * 4 + di(n));
       }
     } else {
       const int a = ops[0], b = ops[1];
-      auto bin = [&](int operand, bool swap) -> Instr& {
-        Instr& in = emit(M_BINARY);
-        in.sub = uint8_t(nd.elt_op);
-        in.dt = di(n);
-        in.flags = swap ? F_SWAP : 0;
-        (void)operand;
-        return in;
-      };
+      const int sub = bin_sub(nd.elt_op), dt = di(n);
       if (a == b) {
         into_acc(a);
-        bin(a, false).src = S_ACC;
+        emit(C_FETCH_ACC);
+        emit(C_BIN_X + sub * 8 + dt * 2);
       } else if (needs_compute(a) && needs_compute(b)) {
         compute(a, true);
         int t = alloc_tmp();
-        Instr& st = emit(M_STTMP);
-        st.arg = uint16_t(t);
+        emit(C_STTMP, t);
         compute(b, true);
-        Instr& in = bin(a, true);   // acc holds b, tmp holds a: result = op(tmp, acc)
-        in.src = S_TMP;
-        in.arg = uint16_t(t);
+        emit(C_FETCH_TMP, t);                   // acc holds b, x holds a: result = op(x, acc)
+        emit(C_BIN_X + sub * 8 + dt * 2 + 1);
         tmp_busy[t] = false;
       } else if (needs_compute(b)) {
         compute(b, true);
-        set_source(bin(a, true), a);
+        binary_with(n, a, true);
       } else {
         into_acc(a);
-        set_source(bin(b, false), b);
+        binary_with(n, b, false);
       }
     }
     done.insert(n);
-    if (materialize[size_t(n)]) {
-      Instr& in = emit(M_STORE);
-      in.dt = di(n);
-      in.arg = uint16_t(buffer(n, 0));
-    }
+    if (materialize[size_t(n)]) emit(C_STORE, buffer(n, 0));
     int remaining = uses.count(n) ? uses[n] : 0;
     if (consumer_takes_acc) remaining -= 1;
     uses[n] = remaining;
     if (remaining > 0) {
       int t = alloc_tmp();
-      Instr& in = emit(M_STTMP);
-      in.arg = uint16_t(t);
+      emit(C_STTMP, t);
       tmp_of[n] = t;
     }
   }
