@@ -24,6 +24,9 @@ struct DeviceInfo {
 // 64-bit dtype. Returns the number of kernels launched.
 int launch_eltwise(const EltProgram& prog, int64_t n, bool wide, const DeviceInfo& dev, cudaStream_t stream);
 
+// K1 fast path: a linear chain (one input column, unary / binary-with-leaf ops, optional final cast).
+int launch_chain(const ChainProgram& prog, int64_t n, const DeviceInfo& dev, cudaStream_t stream);
+
 // K2: reduction of in[outer, inner] along axis 0 into out[inner].
 // `scratch` must hold reduce_scratch_bytes(...) bytes; its first 256 bytes are a
 // counter block that must be zero before the first launch (kernels re-zero it).

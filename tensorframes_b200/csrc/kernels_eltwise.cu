@@ -34,70 +34,34 @@ template <int ES> struct Slot;
 template <> struct Slot<8> { using type = unsigned long long; };
 template <> struct Slot<4> { using type = unsigned int; };
 
+// bit casts between the untyped register slots and the typed values (pure register moves)
+template <class T> struct Bits;
+template <> struct Bits<float> {
+  static __device__ __forceinline__ float from(unsigned long long s) { return __uint_as_float((unsigned int)s); }
+  static __device__ __forceinline__ float from(unsigned int s) { return __uint_as_float(s); }
+  static __device__ __forceinline__ unsigned int to(float v) { return __float_as_uint(v); }
+};
+template <> struct Bits<int> {
+  static __device__ __forceinline__ int from(unsigned long long s) { return (int)(unsigned int)s; }
+  static __device__ __forceinline__ int from(unsigned int s) { return (int)s; }
+  static __device__ __forceinline__ unsigned int to(int v) { return (unsigned int)v; }
+};
+template <> struct Bits<double> {
+  static __device__ __forceinline__ double from(unsigned long long s) { return __longlong_as_double((long long)s); }
+  static __device__ __forceinline__ double from(unsigned int) { return 0.0; }   // never instantiated meaningfully
+  static __device__ __forceinline__ unsigned long long to(double v) { return (unsigned long long)__double_as_longlong(v); }
+};
+template <> struct Bits<long long> {
+  static __device__ __forceinline__ long long from(unsigned long long s) { return (long long)s; }
+  static __device__ __forceinline__ long long from(unsigned int) { return 0; }
+  static __device__ __forceinline__ unsigned long long to(long long v) { return (unsigned long long)v; }
+};
 template <class T, class S>
-__device__ __forceinline__ T from_slot(S s) {
-  if constexpr (sizeof(T) == sizeof(S)) {
-    return *reinterpret_cast<T*>(&s);
-  } else {
-    unsigned int lo = static_cast<unsigned int>(s);
-    return *reinterpret_cast<T*>(&lo);
-  }
-}
+__device__ __forceinline__ T from_slot(S s) { return Bits<T>::from(s); }
 template <class S, class T>
-__device__ __forceinline__ S to_slot(T t) {
-  if constexpr (sizeof(T) == sizeof(S)) {
-    return *reinterpret_cast<S*>(&t);
-  } else {
-    return static_cast<S>(*reinterpret_cast<unsigned int*>(&t));
-  }
-}
+__device__ __forceinline__ S to_slot(T t) { return (S)Bits<T>::to(t); }
 
-template <class T> struct Arith;
-template <> struct Arith<double> {
-  static __device__ __forceinline__ double add(double a, double b) { return __dadd_rn(a, b); }
-  static __device__ __forceinline__ double sub(double a, double b) { return __dsub_rn(a, b); }
-  static __device__ __forceinline__ double mul(double a, double b) { return __dmul_rn(a, b); }
-  static __device__ __forceinline__ double div(double a, double b, bool, int*) { return __ddiv_rn(a, b); }
-  static __device__ __forceinline__ double mn(double a, double b) { return (b < a) ? b : a; }
-  static __device__ __forceinline__ double mx(double a, double b) { return (a < b) ? b : a; }
-  static __device__ __forceinline__ double neg(double a) { return -a; }
-  static __device__ __forceinline__ double abs(double a) { return fabs(a); }
-  static __device__ __forceinline__ double sqrt(double a) { return __dsqrt_rn(a); }
-  static __device__ __forceinline__ double recip(double a) { return __ddiv_rn(1.0, a); }
-};
-template <> struct Arith<float> {
-  static __device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
-  static __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
-  static __device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
-  static __device__ __forceinline__ float div(float a, float b, bool, int*) { return __fdiv_rn(a, b); }
-  static __device__ __forceinline__ float mn(float a, float b) { return (b < a) ? b : a; }
-  static __device__ __forceinline__ float mx(float a, float b) { return (a < b) ? b : a; }
-  static __device__ __forceinline__ float neg(float a) { return -a; }
-  static __device__ __forceinline__ float abs(float a) { return fabsf(a); }
-  static __device__ __forceinline__ float sqrt(float a) { return __fsqrt_rn(a); }
-  static __device__ __forceinline__ float recip(float a) { return __fdiv_rn(1.0f, a); }
-};
-template <class I, class U> struct IntArith {
-  static __device__ __forceinline__ I add(I a, I b) { return I(U(a) + U(b)); }
-  static __device__ __forceinline__ I sub(I a, I b) { return I(U(a) - U(b)); }
-  static __device__ __forceinline__ I mul(I a, I b) { return I(U(a) * U(b)); }
-  static __device__ __forceinline__ I div(I a, I b, bool valid, int* err) {
-    if (b == 0) {
-      if (valid) *err = 1;
-      return 0;
-    }
-    if (b == I(-1)) return I(U(0) - U(a));  // avoids the INT_MIN / -1 trap value
-    return a / b;
-  }
-  static __device__ __forceinline__ I mn(I a, I b) { return (b < a) ? b : a; }
-  static __device__ __forceinline__ I mx(I a, I b) { return (a < b) ? b : a; }
-  static __device__ __forceinline__ I neg(I a) { return I(U(0) - U(a)); }
-  static __device__ __forceinline__ I abs(I a) { return a < 0 ? I(U(0) - U(a)) : a; }
-  static __device__ __forceinline__ I sqrt(I a) { return a; }   // rejected at import
-  static __device__ __forceinline__ I recip(I a) { return a; }  // rejected at import
-};
-template <> struct Arith<int> : IntArith<int, unsigned int> {};
-template <> struct Arith<long long> : IntArith<long long, unsigned long long> {};
+#include "arith.inc"
 
 // ---- global memory access -------------------------------------------------
 template <int ES, int P>
@@ -288,7 +252,7 @@ __device__ __forceinline__ void copy_tile(typename Slot<ES>::type (&dst)[kJ][P],
 #define TFS_ALWAYS(stmt) { stmt; }
 
 template <int ES, int P>
-__global__ void __launch_bounds__(kThreads, 3)
+__global__ void __launch_bounds__(kThreads, 2)
 eltwise_kernel(const __grid_constant__ EltProgram prog, const int64_t n) {
   using S = typename Slot<ES>::type;
   const int64_t n_vec = (n + P - 1) / P;

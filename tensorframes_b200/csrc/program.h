@@ -41,13 +41,13 @@ enum : uint8_t {
   C_STORE = 9,       // bufs[arg][flat] <- acc
   C_STTMP = 10,      // tmp[arg] <- acc
   // acc <- op(acc, x)   (swap: op(x, acc));   code = C_BIN_X + sub * 8 + dt * 2 + swap
-  C_BIN_X = 32,
+  C_BIN_X = 11,
   // acc <- op(acc, imm) (swap: op(imm, acc)); code = C_BIN_IMM + sub * 8 + dt * 2 + swap
-  C_BIN_IMM = 96,
+  C_BIN_IMM = 59,
   // acc <- un(acc);                            code = C_UNARY + sub * 4 + dt
-  C_UNARY = 160,
+  C_UNARY = 107,
   // acc <- cast<to>(acc as from);              code = C_CAST + from * 4 + to
-  C_CAST = 192,
+  C_CAST = 131,
 };
 
 struct Instr {
@@ -70,6 +70,29 @@ struct EltProgram {
   int32_t* err;    // device flag: set to 1 on integer division by zero
   Instr ins[kMaxInstr];
   BufRef bufs[kMaxBufs];
+};
+
+// ---- linear-chain fast path (kernels_chain.cu) --------------------------------------------
+constexpr int kChainSlots = 6;
+enum : uint8_t {
+  CH_NOP = 0, CH_ADD, CH_SUB, CH_RSUB, CH_MUL, CH_DIV, CH_RDIV, CH_MIN, CH_RMIN, CH_MAX, CH_RMAX,
+  CH_NEG, CH_RELU, CH_SQUARE, CH_ABS, CH_SQRT, CH_RECIP,
+};
+struct ChainSlot {
+  const void* operand_buf;  // second operand column (same dtype, same flat index), or null: use imm
+  uint64_t imm;
+  uint8_t op;
+  uint8_t pad[7];
+};
+struct ChainProgram {
+  const void* in;
+  void* out;
+  int32_t* err;
+  int32_t n_slots;
+  uint8_t dt;       // dtype index the chain computes in
+  uint8_t out_dt;   // dtype index of the output (differs when the chain ends in a Cast)
+  uint8_t pad[2];
+  ChainSlot slots[kChainSlots];
 };
 
 }  // namespace tfs

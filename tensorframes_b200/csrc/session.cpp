@@ -538,6 +538,73 @@ struct GroupCompiler {
   }
 };
 
+// Recognises a compiled group that is a linear chain (see kernels_chain.cu) and rewrites it for
+// the straight-line kernel.  Returns false when the program needs the general interpreter.
+bool make_chain(const EltProgram& prog, ChainProgram& ch) {
+  if (prog.n_instr < 2) return false;
+  const Instr& first = prog.ins[0];
+  const Instr& last = prog.ins[prog.n_instr - 1];
+  if (first.code != C_LOAD_BUF || last.code != C_STORE) return false;
+  const BufRef& in = prog.bufs[first.arg];
+  const BufRef& out = prog.bufs[last.arg];
+  auto aligned = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  if (!aligned(in.ptr) || !aligned(out.ptr)) return false;
+  ch = ChainProgram{};
+  ch.in = in.ptr;
+  ch.out = out.ptr;
+  ch.err = prog.err;
+  ch.dt = uint8_t(in.dt);
+  ch.out_dt = ch.dt;
+  const int dt = in.dt;
+  static const uint8_t kFwd[B_COUNT] = {CH_ADD, CH_SUB, CH_MUL, CH_DIV, CH_MIN, CH_MAX};
+  static const uint8_t kRev[B_COUNT] = {CH_ADD, CH_RSUB, CH_MUL, CH_RDIV, CH_RMIN, CH_RMAX};
+  static const uint8_t kUn[U_COUNT] = {CH_NEG, CH_RELU, CH_SQUARE, CH_ABS, CH_SQRT, CH_RECIP};
+  const void* pending = nullptr;   // operand fetched by a C_FETCH_BUF awaiting its C_BIN_X
+  bool have_pending = false, cast_seen = false;
+  for (int pc = 1; pc < prog.n_instr - 1; ++pc) {
+    const Instr& in_ = prog.ins[pc];
+    const int c = in_.code;
+    if (cast_seen) return false;                       // a cast may only end the chain
+    if (c == C_FETCH_BUF) {
+      if (have_pending) return false;
+      const BufRef& b = prog.bufs[in_.arg];
+      if (b.dt != dt || !aligned(b.ptr)) return false;
+      pending = b.ptr;
+      have_pending = true;
+      continue;
+    }
+    ChainSlot slot{};
+    if (c >= C_BIN_X && c < C_BIN_X + B_COUNT * 8) {
+      const int k = c - C_BIN_X;
+      if (!have_pending || (k % 8) / 2 != dt) return false;
+      slot.op = (k & 1) ? kRev[k / 8] : kFwd[k / 8];
+      slot.operand_buf = pending;
+      have_pending = false;
+    } else if (c >= C_BIN_IMM && c < C_BIN_IMM + B_COUNT * 8) {
+      const int k = c - C_BIN_IMM;
+      if (have_pending || (k % 8) / 2 != dt) return false;
+      slot.op = (k & 1) ? kRev[k / 8] : kFwd[k / 8];
+      slot.imm = in_.imm;
+    } else if (c >= C_UNARY && c < C_UNARY + U_COUNT * 4) {
+      const int k = c - C_UNARY;
+      if (have_pending || k % 4 != dt) return false;
+      slot.op = kUn[k / 4];
+    } else if (c >= C_CAST && c < C_CAST + 16) {
+      const int k = c - C_CAST;
+      if (have_pending || k / 4 != dt) return false;
+      ch.out_dt = uint8_t(k % 4);
+      cast_seen = true;
+      continue;
+    } else {
+      return false;
+    }
+    if (ch.n_slots >= kChainSlots) return false;
+    ch.slots[ch.n_slots++] = slot;
+  }
+  if (have_pending) return false;
+  return out.dt == ch.out_dt;
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------
@@ -643,7 +710,9 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
         if (s.shape.numel() == 0) break;
         GroupCompiler gc(g_, plan.shape, dev_ptr, plan.materialize, s);
         gc.build(err_flag_);
-        launches_ += launch_eltwise(gc.prog, s.shape.numel(), gc.wide, dev_, stream_);
+        ChainProgram chain;
+        if (make_chain(gc.prog, chain)) launches_ += launch_chain(chain, s.shape.numel(), dev_, stream_);
+        else launches_ += launch_eltwise(gc.prog, s.shape.numel(), gc.wide, dev_, stream_);
         break;
       }
       case Step::REDUCE_AXIS0: {

@@ -481,3 +481,67 @@ def test_aggregate_rejects_non_reducer_graphs():
     with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
         with pytest.raises(_native.UnsupportedError, match="must be a Sum, Min or Max"):
             s.aggregate(np.zeros(4, np.int64), {"x_input": np.zeros(4)}, ["x"], max_groups=4)
+
+
+# ---- linear-chain fast path (kernels_chain.cu): single-fetch graphs, one run per graph -----------------
+def _chain_graphs(st):
+    """(name, builder) pairs; each builder returns the single fetch node from placeholders a, b."""
+    two = st.np_dtype.type(2)
+    three = st.np_dtype.type(3)
+    gs = [
+        ("add_imm", lambda a, b: a + dsl.constant(three)),
+        ("rsub_imm", lambda a, b: dsl.constant(three) - a),
+        ("sub_imm", lambda a, b: a - dsl.constant(three)),
+        ("mul_imm", lambda a, b: a * dsl.constant(two)),
+        ("div_imm", lambda a, b: dsl.div(a, dsl.constant(three))),
+        ("rdiv_imm", lambda a, b: dsl.div(dsl.constant(three), a)),
+        ("min_imm", lambda a, b: dsl.minimum(a, dsl.constant(two))),
+        ("rmax_imm", lambda a, b: dsl.maximum(dsl.constant(two), a)),
+        ("two_columns", lambda a, b: (a + b) * b - a),
+        ("rdiv_column", lambda a, b: dsl.div(b, a)),
+        ("unaries", lambda a, b: dsl._build("Abs", parents=[dsl.neg(dsl.relu(dsl._build("Square", parents=[a])))])),
+        ("affine_relu", lambda a, b: dsl.maximum(a * dsl.constant(two) + dsl.constant(three), dsl.constant(st.np_dtype.type(0)))),
+        ("long_chain", lambda a, b: ((((((a + b) - b) + b) - b) + b) - b) + b),      # 7 slots: interpreter fallback
+        ("identity", lambda a, b: dsl.identity(a)),
+    ]
+    for k, dst in T.items():
+        gs.append(("cast_" + k, lambda a, b, dst=dst: dsl.cast(a * dsl.constant(two), dst)))
+    if st.np_dtype.kind == "f":
+        gs.append(("sqrt_recip", lambda a, b: dsl._build("Reciprocal", parents=[dsl._build("Sqrt", parents=[dsl._build("Abs", parents=[a])])])))
+    return gs
+
+
+@pytest.mark.parametrize("dt", list(T))
+def test_chain_fast_path_bit_exact(dt):
+    st = T[dt]
+    for n in (1, 5, 2049, 100003):
+        rng = np.random.default_rng(n)
+        a, b = rand(rng, st, n, nonzero=True), rand(rng, st, n, nonzero=True)
+        for name, build in _chain_graphs(st):
+            with dsl.withGraph():
+                pa = dsl.placeholder(st, dsl.Unknown).named("a")
+                pb = dsl.placeholder(st, dsl.Unknown).named("b")
+                g = dsl.build_graph(build(pa, pb).named("out"))
+            feeds = {"a": a, "b": b}
+            used = {nd.name for nd in __import__("oracle.graphdef", fromlist=["x"]).parse_graph(g) if nd.op == "Placeholder"}
+            feeds = {k: v for k, v in feeds.items() if k in used}
+            (got,) = run_native(g, feeds, ["out"])
+            (want,) = tf_ops.evaluate(g, feeds, ["out"])
+            assert got.dtype == want.dtype and got.tobytes() == want.tobytes(), (dt, n, name)
+
+
+def test_chain_fast_path_unaligned_device_pointers():
+    torch = pytest.importorskip("torch")
+    n = 50001
+    x = np.random.default_rng(0).uniform(-1, 1, n + 1)
+    with dsl.withGraph():
+        p = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x")
+        g = dsl.build_graph(dsl.cast(dsl.maximum(p * 1.5 + 0.25, 0.0), tfs.FloatType).named("z"))
+    dx = torch.from_numpy(x).cuda()
+    dz = torch.empty(n + 1, dtype=torch.float32, device="cuda")
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        s.run_into({"x": _native.DeviceArray(dx.data_ptr() + 8, tfs.DoubleType, (n,), owner=dx)},
+                   {"z": _native.DeviceArray(dz.data_ptr() + 4, tfs.FloatType, (n,), owner=dz)})
+        s.sync()
+    want = np.maximum(x[1:] * 1.5 + 0.25, 0).astype(np.float32)
+    assert dz.cpu().numpy()[1:].tobytes() == want.tobytes()
