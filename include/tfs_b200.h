@@ -169,6 +169,30 @@ int tfs_session_aggregate(tfs_session* s, int64_t n_rows, const int64_t* keys,
                           int n_fetches, const tfs_tensor* fetches,
                           int64_t max_groups, int64_t* out_keys, int64_t* n_groups);
 
+/* ---- block reduction without any allocation ------------------------------------
+ * (No counterpart in the reference: TF-Java gives its callers no say over allocation.)
+ *
+ * For callers that may not allocate device memory when they call in -- an executor whose GPU
+ * memory is wholly owned by a pool allocator, a task that must not cause the device-wide
+ * synchronisation a cudaMalloc/cudaFree implies, a process with a fixed memory budget.
+ * Reduces in[outer, inner] (row-major, dtype = TFS_FLOAT/DOUBLE/INT32/INT64) along axis 0 into
+ * out[inner] with Sum, Min or Max -- what tfs_session_run does for `reduce_sum(x_input, [0])` --
+ * but `in` and `out` must already be device pointers on `device`, and the kernel's scratch is a
+ * fixed array inside the library image instead of a grown workspace.
+ *   - limit: inner <= 256 elements (TFS_ERR_UNSUPPORTED beyond; outer is unlimited); the array
+ *     (about 0.5 MiB) stays resident on every GPU that loads the library until process exit;
+ *   - no cudaMalloc / cudaFree / allocating call is made; the work is enqueued on `cuda_stream`
+ *     (NULL = the legacy default stream) and the call returns without synchronising;
+ *   - the first call for a device looks up the array's device address: make it at start-up,
+ *     before any stream capture;
+ *   - every call on a device shares that one array: calls whose kernels could overlap on the
+ *     GPU (other streams, other threads) must be serialised by the caller. */
+#define TFS_REDUCE_SUM 0
+#define TFS_REDUCE_MIN 1
+#define TFS_REDUCE_MAX 2
+int tfs_reduce_axis0_noalloc(int device, void* cuda_stream, int32_t dtype, int32_t red_op,
+                             const void* in, int64_t outer, int64_t inner, void* out);
+
 /* ---- host memory helpers ----------------------------------------------------
  * Page-locked host buffers so that packed column blocks DMA at full PCIe rate;
  * the counterpart of TensorConverter.reserve (impl/datatypes.scala:334-338). */

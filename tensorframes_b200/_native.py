@@ -63,6 +63,8 @@ SYMBOLS = {
     "tfs_session_run": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(Tensor), C.c_int, C.POINTER(Tensor)]),
     "tfs_session_aggregate": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.POINTER(Tensor), C.c_int,
                                         C.POINTER(Tensor), C.c_int64, C.c_void_p, C.POINTER(C.c_int64)]),
+    "tfs_reduce_axis0_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_int64,
+                                           C.c_void_p]),
     "tfs_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
     "tfs_host_free": (C.c_int, [C.c_void_p]),
 }

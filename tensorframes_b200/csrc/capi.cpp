@@ -57,6 +57,11 @@ std::vector<tfs::TensorArg> args_from(int n, const tfs_tensor* t, const char* wh
 
 }  // namespace
 
+namespace tfs {
+// lets an entry point defined in another translation unit report through tfs_last_error()
+void set_last_error(const std::string& msg) { g_last_error = msg; }
+}  // namespace tfs
+
 extern "C" {
 
 const char* tfs_last_error(void) { return g_last_error.c_str(); }
