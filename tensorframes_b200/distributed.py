@@ -31,9 +31,9 @@ def gather_partials(partials: Sequence, dist=None) -> List:
     world = dist.get_world_size()
     out = []
     for p in partials:
-        stacked = torch.empty((world,) + tuple(p.shape), dtype=p.dtype, device=p.device)
-        dist.all_gather_into_tensor(stacked, p.contiguous())
-        out.append(stacked)
+        flat = torch.empty(world * p.numel(), dtype=p.dtype, device=p.device)
+        dist.all_gather_into_tensor(flat, p.contiguous().reshape(-1))   # flat form works on NCCL and gloo alike
+        out.append(flat.reshape((world,) + tuple(p.shape)))
     return out
 
 
