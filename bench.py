@@ -34,7 +34,9 @@ import numpy as np  # noqa: E402
 
 ROWS_C2 = 100_000_000
 ROWS_C3 = 1_000_000_000
-ALG_BYTES_PER_ROW = {"c2": 32, "c3": 12}
+ROWS_C4 = 250_000_000          # BASELINE config 4 names 5e8 rows (132 GB); see config.workload
+KEYS_C4 = 1_000_000
+ALG_BYTES_PER_ROW = {"c2": 32, "c3": 12, "c4": 264}
 FALLBACK_HBM_GBS = 6650.0                   # /opt/skills/guides/B200_PROFILING.md
 
 
@@ -124,6 +126,9 @@ def build_graph(workload):
             y = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("y_input")
             z = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("z_input")
             return dsl.build_graph(dsl.reduce_sum(y, [0]).named("y"), dsl.reduce_min(z, [0]).named("z"))
+        if workload == "c4":
+            v = dsl.placeholder(tfs.FloatType, dsl.Unknown, 64).named("v_input")
+            return dsl.build_graph(dsl.reduce_sum(v, [0]).named("v"))
         x = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x")
         return dsl.build_graph(dsl.cast(dsl.maximum(x * 1.5 + 0.25, 0.0), tfs.FloatType).named("z"))
 
@@ -137,6 +142,15 @@ def make_inputs(torch, workload, rows, seed, device):
         u = torch.rand(rows, generator=g, device=device, dtype=torch.float64)
         z = torch.stack([u, -u], dim=1).contiguous()
         return {"y_input": y, "z_input": z}
+    if workload == "c4":
+        # keys: a table of 1e6 distinct random 64-bit values (not dense ids, so the hash is really exercised)
+        table = torch.randint(-2**62, 2**62, (KEYS_C4,), generator=g, device=device, dtype=torch.int64)
+        table = torch.unique(table)
+        idx = torch.randint(0, table.numel(), (rows,), generator=g, device=device, dtype=torch.int64)
+        keys = table[idx]
+        del idx
+        v = torch.rand((rows, 64), generator=g, device=device, dtype=torch.float32)
+        return {"keys": keys, "v_input": v}
     x = torch.rand(rows, generator=g, device=device, dtype=torch.float64) * 2.0 - 1.0
     return {"x": x}
 
@@ -158,8 +172,10 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
     wl = args.workload
-    rows = args.rows or (ROWS_C2 if wl == "c2" else ROWS_C3)
+    rows = args.rows or {"c2": ROWS_C2, "c3": ROWS_C3, "c4": ROWS_C4}[wl]
     DA = _native.DeviceArray.from_torch
+    if wl == "c4":
+        return run_c4(args, torch, dist, _native, world, rank, local, device, rows)
 
     graph_bytes = build_graph(wl)
     graph = _native.Graph(graph_bytes)
@@ -327,6 +343,75 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_c4(args, torch, dist, _native, world, rank, local, device, rows):
+    """BASELINE config 4: groupBy(int64 key).aggregate(reduce_sum(v_input, [0])), FloatType[?,64].
+    One block per GPU; the cross-GPU key-owner exchange is not part of this measurement yet."""
+    DA = _native.DeviceArray.from_torch
+    graph = _native.Graph(build_graph("c4"))
+    sess = _native.Session(graph, local)
+    stream = torch.cuda.Stream(device=device)
+    torch.cuda.set_stream(stream)
+    sess.set_stream(stream.cuda_stream)
+    t = make_inputs(torch, "c4", rows, seed=4 + 1000 * rank, device=device)
+    keys, v = t["keys"], t["v_input"]
+    out_keys = torch.empty(KEYS_C4, dtype=torch.int64, device=device)
+    out = torch.empty((KEYS_C4, 64), dtype=torch.float32, device=device)
+
+    def step():
+        return sess.aggregate_into(DA(keys), {"v_input": DA(v)}, {"v": DA(out)}, DA(out_keys))
+
+    for _ in range(args.warmup):
+        n_groups = step()
+    torch.cuda.synchronize()
+    launches0 = sess.launch_count
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clocks:
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        start.record(stream)
+        for _ in range(args.steps):
+            n_groups = step()
+        end.record(stream)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+    elapsed_ms = start.elapsed_time(end)
+    tt = torch.tensor([elapsed_ms], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    elapsed_ms = float(tt.item())
+    launches = sess.launch_count - launches0
+    # parity spot check on the device: keys exactly once each, sums within the f32 tolerance
+    ref_keys, inv = torch.unique(keys, return_inverse=True)
+    assert n_groups == ref_keys.numel()
+    order = torch.argsort(out_keys[:n_groups])
+    assert torch.equal(out_keys[:n_groups][order], ref_keys)
+    ref = torch.zeros((n_groups, 64), dtype=torch.float64, device=device)
+    chk = min(rows, 20_000_000)
+    ref.index_add_(0, inv[:chk], v[:chk].double())
+    if chk == rows:
+        assert torch.all((out[:n_groups][order].double() - ref).abs() <= 1e-5 * ref.abs().clamp_min(1e-30))
+    if rank == 0:
+        peak, peak_src = hbm_peak()
+        step_s = elapsed_ms / 1e3 / args.steps
+        achieved = rows * 264 / step_s / 1e9
+        print(json.dumps({
+            "metric": "rows/s for aggregate (groupBy int64 key, reduce_sum over FloatType[?,64])",
+            "value": world * rows / step_s, "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"BASELINE configs[3]: aggregate groupBy int64 key ({n_groups} distinct), reduce_sum "
+                                   f"FloatType[?,64], {rows} rows per GPU (config names 5e8; reduced to bound memory)",
+                       "rows_per_gpu": rows, "l2": "inputs larger than L2 (no flush needed)", "exchange": "none (per-GPU blocks)"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": ncu_traffic("c4"), "peak_source": peak_src, "kernel": "whole step (5 passes, agg_gather_reduce_kernel dominant)",
+                         "algorithmic_bytes_per_launch": rows * 264.0, "frac_of_nominal_8000": achieved / 8000.0},
+            "e2e": None, "gpu_launches": int(launches), "clocks": clocks.summary(), "cpu_baseline": None}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def cpu_baseline_leg(wl, host_feeds, rows, budget_s=12.0):
     """oracle/cpu_ref.c on a bounded sample: the whole block if it finishes within the budget,
     else a prefix sized from a calibration run."""
@@ -404,7 +489,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4"])
     ap.add_argument("--rows", type=int, default=0, help="rows per GPU (default: the BASELINE config's)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

@@ -271,6 +271,18 @@ class Session:
         return out_keys[:g].copy(), [o[:g].copy() for o in outs]
 
 
+    def aggregate_into(self, keys: DeviceArray, feeds: Dict[str, object], fetches: Dict[str, object],
+                       out_keys: DeviceArray) -> int:
+        """Keyed reduction with caller-provided buffers (device or host). fetches[name] has max_groups rows.
+        Returns the number of groups."""
+        farr, keep = self._feed_array(feeds)
+        oarr, keep2 = self._feed_array(fetches)
+        n_groups = C.c_int64(0)
+        _check(lib().tfs_session_aggregate(self._h, keys.shape[0], C.c_void_p(keys.ptr), len(feeds), farr, len(fetches),
+                                           oarr, out_keys.shape[0], C.c_void_p(out_keys.ptr), C.byref(n_groups)))
+        return int(n_groups.value)
+
+
 class PinnedBuffer:
     """Page-locked host memory from tfs_host_alloc, viewed as a numpy array."""
 
