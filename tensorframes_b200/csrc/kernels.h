@@ -41,18 +41,21 @@ int launch_reduce_rows(int dtype, int red_op, const void* in, int64_t outer, int
 // K3: keyed block reduction. Scratch layout for n_rows rows and at most max_groups groups.
 struct AggLayout {
   uint64_t table_slots;
-  size_t off_header, off_slot_key, off_slot_gid, off_row_gid, off_counts, off_offsets, off_tile_sums, off_perm;
+  size_t off_header, off_slot_key, off_counts, off_offsets, off_group_slot, off_tile_sums, off_row_slot, off_row_id,
+      off_sorted_slot, off_perm, off_sort_temp;
+  size_t sort_temp_bytes;
   size_t bytes;
 };
 AggLayout agg_layout(int64_t n_rows, int64_t max_groups);
-// pass 1: hash-insert the keys, assign dense group ids, write out_keys[gid]. header (first 16 bytes of
-// scratch): [0] = number of groups, [1] = overflow flag (more than max_groups distinct keys).
+// passes 1-2: hash-insert the keys (each row records its slot, each slot counts its rows), then scan the
+// table: segment offsets, dense group ids, out_keys[gid]. header (first 16 bytes of scratch):
+// [0] = occupied slots, [1] = overflow flag (more than max_groups distinct keys), [2] = number of groups.
 int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, char* scratch, const AggLayout& L,
                      int64_t* out_keys_dev, const DeviceInfo& dev, cudaStream_t stream);
-// passes 2-4: group id per row, segment offsets, row permutation.
+// pass 3: stable sort of the rows by slot -> row permutation.
 int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, char* scratch, const AggLayout& L,
                         const DeviceInfo& dev, cudaStream_t stream);
-// pass 5: out[g, :] = reduce over the rows of group g of payload[row, :].
+// pass 4: out[g, :] = reduce over the rows of group g of payload[row, :].
 int launch_agg_reduce(int dtype, int red_op, const void* payload, int64_t cell, int64_t n_groups, char* scratch,
                       const AggLayout& L, void* out, const DeviceInfo& dev, cudaStream_t stream);
 

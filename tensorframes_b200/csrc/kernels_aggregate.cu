@@ -3,22 +3,24 @@
 // Stands in for the whole TensorFlowUDAF machinery of the reference
 // (impl/DebugRowOps.scala:601-695): there, Spark hashes rows to per-key buffers of <= 11 rows
 // and block-reduces each buffer through a fresh TF session.  Here one block is reduced in
-// five passes, all HBM-bound:
+// four passes, all HBM-bound:
 //
-//   1. insert    every key into an open-addressing table (64-bit CAS on the key slot); the
-//                thread that claims a slot assigns the next dense group id      8 B/row read
-//   2. lookup    group id per row + per-group row count                          8 B read, 4 B write
-//   3. scan      exclusive prefix sum of the counts -> segment offsets           (groups only)
-//   4. scatter   row index into its group's segment (perm)                       4 B read, 4 B write
-//   5. gather-reduce  one warp per group walks its segment and gathers the payload rows --
-//                each a contiguous cell, read with coalesced vector loads -- accumulating in
-//                registers; one coalesced store per group.          cell bytes/row read
+//   1. insert   every key into an open-addressing table (64-bit CAS on the key slot); the row
+//               remembers its slot and the slot counts its rows          8 B read + 8 B written / row
+//   2. scan     one pass over the table: segment offset of every slot, dense group id of every
+//               occupied slot, out_keys                                   (table only)
+//   3. sort     rows by slot (stable LSD radix sort of (slot, row) pairs -- cub::DeviceRadixSort,
+//               the one library call on this path, used as plain plumbing)  ~50 B / row, coalesced
+//   4. gather-reduce  one warp per group walks its segment of the sorted row list and gathers
+//               the payload rows -- each a contiguous cell, read with coalesced vector loads --
+//               accumulating in registers; one coalesced store per group.      cell bytes / row
 //
-// The payload (the dominant traffic: 256 B/row at BASELINE config 4) is read exactly once
-// and no accumulator table is read-modify-written, unlike a scatter-add formulation.
-// Keys are compared bit-exactly.  Group order and the order of rows inside a group follow
-// atomic arrival order, so float sums may differ between runs by summation order (the
-// north-star tolerance); integer sums, Min and Max are exact.
+// The payload (the dominant traffic: 256 B/row at BASELINE config 4) is read exactly once and
+// no accumulator table is read-modify-written, unlike a scatter-add formulation.  Keys are
+// compared bit-exactly.  Groups come out in table order and, the sort being stable, the rows of
+// a group are folded in block order: results are run-to-run deterministic, floats included.
+#include <cub/device/device_radix_sort.cuh>
+
 #include "kernels.h"
 
 namespace tfs {
@@ -34,59 +36,39 @@ __device__ __forceinline__ unsigned long long mix64(unsigned long long x) {
   return x;
 }
 
-// header[0] = number of groups, header[1] = overflow flag, header[2] = sentinel state, header[3] = sentinel gid
+// header[0] = occupied slots so far, header[1] = overflow flag, header[2] = number of groups (after the scan)
+// Slot `slots` (one past the table) belongs to the one key value that equals the empty marker.
 __global__ void __launch_bounds__(kThreads)
 agg_insert_kernel(const long long* __restrict__ keys, const int64_t n, unsigned long long* __restrict__ slot_key,
-                  unsigned int* __restrict__ slot_gid, const unsigned long long mask, unsigned int* __restrict__ header,
-                  long long* __restrict__ out_keys, const unsigned int max_groups) {
+                  unsigned int* __restrict__ counts, const unsigned long long slots, unsigned int* __restrict__ header,
+                  const unsigned int max_groups, unsigned int* __restrict__ row_slot, unsigned int* __restrict__ row_id) {
+  const unsigned long long mask = slots - 1;
   const int64_t stride = int64_t(gridDim.x) * blockDim.x;
   for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
     const unsigned long long k = (unsigned long long)__ldcs(keys + i);
-    if (k == kEmpty) {  // the one key value that collides with the empty marker
-      if (atomicCAS(header + 2, 0u, 1u) == 0u) {
-        unsigned int g = atomicAdd(header, 1u);
-        if (g < max_groups) out_keys[g] = (long long)k; else header[1] = 1u;
-        header[3] = g;
-      }
-      continue;
-    }
-    unsigned long long h = mix64(k) & mask;
-    while (true) {
-      unsigned long long cur = slot_key[h];
-      if (cur == k) break;
-      if (cur == kEmpty) {
-        unsigned long long prev = atomicCAS(slot_key + h, kEmpty, k);
-        if (prev == kEmpty) {
-          unsigned int g = atomicAdd(header, 1u);
-          if (g < max_groups) out_keys[g] = (long long)k; else header[1] = 1u;
-          slot_gid[h] = g;
-          break;
-        }
-        if (prev == k) break;
-      }
-      h = (h + 1) & mask;
-    }
-  }
-}
-
-__global__ void __launch_bounds__(kThreads)
-agg_lookup_kernel(const long long* __restrict__ keys, const int64_t n, const unsigned long long* __restrict__ slot_key,
-                  const unsigned int* __restrict__ slot_gid, const unsigned long long mask,
-                  const unsigned int* __restrict__ header, unsigned int* __restrict__ row_gid,
-                  unsigned int* __restrict__ counts) {
-  const int64_t stride = int64_t(gridDim.x) * blockDim.x;
-  for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const unsigned long long k = (unsigned long long)__ldcs(keys + i);
-    unsigned int g;
+    unsigned long long h;
+    bool claimed = false;
     if (k == kEmpty) {
-      g = header[3];
+      h = slots;
+      claimed = atomicCAS(slot_key + h, 0ULL, kEmpty) == 0ULL;   // this slot starts as 0, not as the marker
     } else {
-      unsigned long long h = mix64(k) & mask;
-      while (slot_key[h] != k) h = (h + 1) & mask;
-      g = slot_gid[h];
+      h = mix64(k) & mask;
+      while (true) {
+        const unsigned long long cur = slot_key[h];
+        if (cur == k) break;
+        if (cur == kEmpty) {
+          const unsigned long long prev = atomicCAS(slot_key + h, kEmpty, k);
+          if (prev == kEmpty) { claimed = true; break; }
+          if (prev == k) break;
+        }
+        h = (h + 1) & mask;
+        if (*reinterpret_cast<volatile unsigned int*>(header + 1)) break;   // too many distinct keys: give up
+      }
     }
-    row_gid[i] = g;
-    atomicAdd(counts + g, 1u);
+    if (claimed && atomicAdd(header, 1u) >= max_groups) header[1] = 1u;
+    row_slot[i] = (unsigned int)h;
+    row_id[i] = (unsigned int)i;
+    atomicAdd(counts + h, 1u);
   }
 }
 
@@ -96,16 +78,20 @@ fill_u64_kernel(unsigned long long* __restrict__ p, const uint64_t n, const unsi
   for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) p[i] = v;
 }
 
-// ---- exclusive scan of counts[0..m) into offsets[0..m], three small kernels -------------------
-constexpr int kScanTile = 2048;  // elements per CTA
+// ---- one scan over the table: (rows, occupied) prefix sums packed in 64 bits -------------------------
+constexpr int kScanTile = 2048;  // slots per CTA
+
+__device__ __forceinline__ unsigned long long pack_count(unsigned int c) {
+  return (unsigned long long)c | ((unsigned long long)(c != 0u) << 32);
+}
 
 __global__ void __launch_bounds__(kThreads)
-scan_tile_sums_kernel(const unsigned int* __restrict__ in, const int64_t m, unsigned long long* __restrict__ tile_sums) {
+scan_tile_sums_kernel(const unsigned int* __restrict__ counts, const int64_t m, unsigned long long* __restrict__ tile_sums) {
   __shared__ unsigned long long sm[kThreads];
   const int64_t base = int64_t(blockIdx.x) * kScanTile;
   unsigned long long s = 0;
   for (int i = threadIdx.x; i < kScanTile; i += kThreads)
-    if (base + i < m) s += in[base + i];
+    if (base + i < m) s += pack_count(counts[base + i]);
   sm[threadIdx.x] = s;
   __syncthreads();
   for (int w = kThreads / 2; w > 0; w >>= 1) {
@@ -116,7 +102,7 @@ scan_tile_sums_kernel(const unsigned int* __restrict__ in, const int64_t m, unsi
 }
 
 __global__ void __launch_bounds__(1024)
-scan_tile_offsets_kernel(unsigned long long* __restrict__ tile_sums, const int64_t tiles) {
+scan_tile_offsets_kernel(unsigned long long* __restrict__ tile_sums, const int64_t tiles, unsigned int* __restrict__ header) {
   // single CTA: in-place exclusive scan, 1024 tiles per round with a running carry
   __shared__ unsigned long long sm[1024];
   __shared__ unsigned long long carry;
@@ -138,21 +124,23 @@ scan_tile_offsets_kernel(unsigned long long* __restrict__ tile_sums, const int64
     if (threadIdx.x == 1023) carry += sm[1023];
     __syncthreads();
   }
+  if (threadIdx.x == 0) header[2] = (unsigned int)(carry >> 32);   // number of groups
 }
 
+// offsets[slot] = rows before this slot; occupied slots get the next dense group id and publish their key.
 __global__ void __launch_bounds__(kThreads)
-scan_apply_kernel(const unsigned int* __restrict__ in, const int64_t m, const unsigned long long* __restrict__ tile_off,
-                  unsigned long long* __restrict__ offsets) {
-  // each thread owns kScanTile / kThreads consecutive elements
+scan_apply_kernel(const unsigned int* __restrict__ counts, const int64_t m, const unsigned long long* __restrict__ tile_off,
+                  const unsigned long long* __restrict__ slot_key, unsigned int* __restrict__ offsets,
+                  unsigned int* __restrict__ group_slot, long long* __restrict__ out_keys, const unsigned int max_groups) {
   constexpr int PER = kScanTile / kThreads;
   __shared__ unsigned long long sm[kThreads];
   const int64_t base = int64_t(blockIdx.x) * kScanTile + int64_t(threadIdx.x) * PER;
-  unsigned int v[PER];
+  unsigned int c[PER];
   unsigned long long s = 0;
 #pragma unroll
   for (int j = 0; j < PER; ++j) {
-    v[j] = base + j < m ? in[base + j] : 0u;
-    s += v[j];
+    c[j] = base + j < m ? counts[base + j] : 0u;
+    s += pack_count(c[j]);
   }
   sm[threadIdx.x] = s;
   __syncthreads();
@@ -165,26 +153,17 @@ scan_apply_kernel(const unsigned int* __restrict__ in, const int64_t m, const un
   unsigned long long run = tile_off[blockIdx.x] + sm[threadIdx.x] - s;
 #pragma unroll
   for (int j = 0; j < PER; ++j) {
-    if (base + j < m) offsets[base + j] = run;
-    run += v[j];
-  }
-  if (base <= m && m < base + PER) {
-    // the thread whose range contains index m writes the total
-    unsigned long long tot = tile_off[blockIdx.x] + sm[threadIdx.x] - s;
-    for (int j = 0; j < PER && base + j < m; ++j) tot += v[j];
-    offsets[m] = tot;
-  }
-}
-
-__global__ void __launch_bounds__(kThreads)
-agg_scatter_kernel(const unsigned int* __restrict__ row_gid, const int64_t n,
-                   const unsigned long long* __restrict__ offsets, unsigned int* __restrict__ counts,
-                   unsigned int* __restrict__ perm) {
-  const int64_t stride = int64_t(gridDim.x) * blockDim.x;
-  for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const unsigned int g = __ldcs(row_gid + i);
-    const unsigned int pos = atomicSub(counts + g, 1u) - 1u;   // counts run down to zero
-    perm[offsets[g] + pos] = (unsigned int)i;
+    if (base + j < m) {
+      offsets[base + j] = (unsigned int)run;
+      if (c[j] != 0u) {
+        const unsigned int g = (unsigned int)(run >> 32);
+        if (g < max_groups) {
+          group_slot[g] = (unsigned int)(base + j);
+          out_keys[g] = (long long)slot_key[base + j];
+        }
+      }
+    }
+    run += pack_count(c[j]);
   }
 }
 
@@ -244,7 +223,8 @@ __device__ __forceinline__ void load_v(const T* p, T (&x)[V]) {
 template <class T, int OP, int V>
 __global__ void __launch_bounds__(kThreads)
 agg_gather_reduce_kernel(const T* __restrict__ payload, const int cell, const unsigned int* __restrict__ perm,
-                         const unsigned long long* __restrict__ offsets, const int64_t n_groups, const int col_lanes,
+                         const unsigned int* __restrict__ offsets, const unsigned int* __restrict__ counts,
+                         const unsigned int* __restrict__ group_slot, const int64_t n_groups, const int col_lanes,
                          T* __restrict__ out) {
   constexpr int kU = 8;
   const int lane = threadIdx.x & 31;
@@ -253,7 +233,8 @@ agg_gather_reduce_kernel(const T* __restrict__ payload, const int cell, const un
   const int C = col_lanes, R = 32 / C;
   const int cl = lane % C, rl = lane / C;
   for (int64_t g = warp; g < n_groups; g += warps) {
-    const unsigned long long lo = offsets[g], hi = offsets[g + 1];
+    const unsigned int slot = group_slot[g];
+    const unsigned long long lo = offsets[slot], hi = lo + counts[slot];
     for (int cbase = 0; cbase < cell; cbase += C * V) {   // warp-uniform trip count
       const int c0 = cbase + cl * V;
       const bool active = c0 < cell;
@@ -295,8 +276,9 @@ agg_gather_reduce_kernel(const T* __restrict__ payload, const int cell, const un
 }
 
 template <class T, int OP>
-int launch_gather_t(const T* payload, int64_t cell, const unsigned int* perm, const unsigned long long* offsets,
-                    int64_t n_groups, T* out, const DeviceInfo& dev, cudaStream_t stream) {
+int launch_gather_t(const T* payload, int64_t cell, const unsigned int* perm, const unsigned int* offsets,
+                    const unsigned int* counts, const unsigned int* group_slot, int64_t n_groups, T* out,
+                    const DeviceInfo& dev, cudaStream_t stream) {
   if (n_groups <= 0 || cell <= 0) return 0;
   constexpr int VMAX = 16 / int(sizeof(T));
   int V = 1;
@@ -312,11 +294,11 @@ int launch_gather_t(const T* payload, int64_t cell, const unsigned int* perm, co
   const int icell = int(cell);
   if (V == 4) {
     if constexpr (VMAX == 4)
-      agg_gather_reduce_kernel<T, OP, 4><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, n_groups, C, out);
+      agg_gather_reduce_kernel<T, OP, 4><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, counts, group_slot, n_groups, C, out);
   } else if (V == 2) {
-    agg_gather_reduce_kernel<T, OP, 2><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, n_groups, C, out);
+    agg_gather_reduce_kernel<T, OP, 2><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, counts, group_slot, n_groups, C, out);
   } else {
-    agg_gather_reduce_kernel<T, OP, 1><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, n_groups, C, out);
+    agg_gather_reduce_kernel<T, OP, 1><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, counts, group_slot, n_groups, C, out);
   }
   TFS_CUDA(cudaGetLastError());
   return 1;
@@ -324,14 +306,14 @@ int launch_gather_t(const T* payload, int64_t cell, const unsigned int* perm, co
 
 template <class T>
 int launch_gather_op(int red_op, const void* payload, int64_t cell, const unsigned int* perm,
-                     const unsigned long long* offsets, int64_t n_groups, void* out, const DeviceInfo& dev,
-                     cudaStream_t stream) {
+                     const unsigned int* offsets, const unsigned int* counts, const unsigned int* group_slot,
+                     int64_t n_groups, void* out, const DeviceInfo& dev, cudaStream_t stream) {
   const T* p = static_cast<const T*>(payload);
   T* o = static_cast<T*>(out);
   switch (red_op) {
-    case R_SUM: return launch_gather_t<T, R_SUM>(p, cell, perm, offsets, n_groups, o, dev, stream);
-    case R_MIN: return launch_gather_t<T, R_MIN>(p, cell, perm, offsets, n_groups, o, dev, stream);
-    default: return launch_gather_t<T, R_MAX>(p, cell, perm, offsets, n_groups, o, dev, stream);
+    case R_SUM: return launch_gather_t<T, R_SUM>(p, cell, perm, offsets, counts, group_slot, n_groups, o, dev, stream);
+    case R_MIN: return launch_gather_t<T, R_MIN>(p, cell, perm, offsets, counts, group_slot, n_groups, o, dev, stream);
+    default: return launch_gather_t<T, R_MAX>(p, cell, perm, offsets, counts, group_slot, n_groups, o, dev, stream);
   }
 }
 
@@ -339,6 +321,20 @@ int64_t grid_for(int64_t n, const DeviceInfo& dev) {
   int64_t g = (n + kThreads - 1) / kThreads;
   g = std::min<int64_t>(g, int64_t(dev.sm_count) * 8);
   return g < 1 ? 1 : g;
+}
+
+int slot_bits(uint64_t slots) {   // bits needed for slot indices 0..slots (inclusive: the marker-key slot)
+  int b = 1;
+  while ((uint64_t(1) << b) <= slots) ++b;
+  return b;
+}
+
+size_t sort_temp_bytes(int64_t n_rows, uint64_t slots) {
+  size_t bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, bytes, static_cast<const unsigned int*>(nullptr), static_cast<unsigned int*>(nullptr),
+                                  static_cast<const unsigned int*>(nullptr), static_cast<unsigned int*>(nullptr),
+                                  n_rows, 0, slot_bits(slots));
+  return bytes;
 }
 
 }  // namespace
@@ -351,13 +347,17 @@ AggLayout agg_layout(int64_t n_rows, int64_t max_groups) {
   auto up = [](size_t x) { return (x + 255) / 256 * 256; };
   size_t off = 0;
   L.off_header = off; off += 256;
-  L.off_slot_key = off; off += up(cap * 8);
-  L.off_slot_gid = off; off += up(cap * 4);
-  L.off_row_gid = off; off += up(size_t(n_rows) * 4);
-  L.off_counts = off; off += up(size_t(max_groups + 1) * 4);
-  L.off_offsets = off; off += up(size_t(max_groups + 2) * 8);
-  L.off_tile_sums = off; off += up(size_t((max_groups + kScanTile) / kScanTile + 1) * 8);
+  L.off_slot_key = off; off += up((cap + 1) * 8);
+  L.off_counts = off; off += up((cap + 1) * 4);
+  L.off_offsets = off; off += up((cap + 2) * 4);
+  L.off_group_slot = off; off += up(size_t(max_groups + 1) * 4);
+  L.off_tile_sums = off; off += up(size_t((cap + 1 + kScanTile) / kScanTile + 1) * 8);
+  L.off_row_slot = off; off += up(size_t(n_rows) * 4);
+  L.off_row_id = off; off += up(size_t(n_rows) * 4);
+  L.off_sorted_slot = off; off += up(size_t(n_rows) * 4);
   L.off_perm = off; off += up(size_t(n_rows) * 4);
+  L.sort_temp_bytes = n_rows > 0 ? sort_temp_bytes(n_rows, cap) : 0;
+  L.off_sort_temp = off; off += up(L.sort_temp_bytes);
   L.bytes = off;
   return L;
 }
@@ -366,58 +366,62 @@ int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, ch
                      int64_t* out_keys_dev, const DeviceInfo& dev, cudaStream_t stream) {
   unsigned int* header = reinterpret_cast<unsigned int*>(scratch + L.off_header);
   unsigned long long* slot_key = reinterpret_cast<unsigned long long*>(scratch + L.off_slot_key);
-  unsigned int* slot_gid = reinterpret_cast<unsigned int*>(scratch + L.off_slot_gid);
+  unsigned int* counts = reinterpret_cast<unsigned int*>(scratch + L.off_counts);
+  unsigned int* offsets = reinterpret_cast<unsigned int*>(scratch + L.off_offsets);
+  unsigned int* group_slot = reinterpret_cast<unsigned int*>(scratch + L.off_group_slot);
+  unsigned long long* tile_sums = reinterpret_cast<unsigned long long*>(scratch + L.off_tile_sums);
+  unsigned int* row_slot = reinterpret_cast<unsigned int*>(scratch + L.off_row_slot);
+  unsigned int* row_id = reinterpret_cast<unsigned int*>(scratch + L.off_row_id);
+  const int64_t m = int64_t(L.table_slots) + 1;   // table + the marker-key slot
   TFS_CUDA(cudaMemsetAsync(header, 0, 256, stream));
+  TFS_CUDA(cudaMemsetAsync(counts, 0, size_t(m) * 4, stream));
   fill_u64_kernel<<<(unsigned)grid_for(int64_t(L.table_slots), dev), kThreads, 0, stream>>>(slot_key, L.table_slots, kEmpty);
   TFS_CUDA(cudaGetLastError());
-  TFS_CUDA(cudaMemsetAsync(scratch + L.off_counts, 0, size_t(max_groups + 1) * 4, stream));
-  (void)slot_gid;
+  TFS_CUDA(cudaMemsetAsync(slot_key + L.table_slots, 0, 8, stream));
+  int launches = 1;
   if (n_rows > 0) {
     agg_insert_kernel<<<(unsigned)grid_for(n_rows, dev), kThreads, 0, stream>>>(
-        reinterpret_cast<const long long*>(keys), n_rows, slot_key, slot_gid, L.table_slots - 1, header,
-        reinterpret_cast<long long*>(out_keys_dev), (unsigned int)max_groups);
+        reinterpret_cast<const long long*>(keys), n_rows, slot_key, counts, L.table_slots, header,
+        (unsigned int)max_groups, row_slot, row_id);
     TFS_CUDA(cudaGetLastError());
-    return 2;
+    ++launches;
   }
-  return 1;
+  const int64_t tiles = (m + kScanTile - 1) / kScanTile;
+  scan_tile_sums_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(counts, m, tile_sums);
+  TFS_CUDA(cudaGetLastError());
+  scan_tile_offsets_kernel<<<1, 1024, 0, stream>>>(tile_sums, tiles, header);
+  TFS_CUDA(cudaGetLastError());
+  scan_apply_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(counts, m, tile_sums, slot_key, offsets, group_slot,
+                                                            reinterpret_cast<long long*>(out_keys_dev), (unsigned int)max_groups);
+  TFS_CUDA(cudaGetLastError());
+  return launches + 3;
 }
 
 int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, char* scratch, const AggLayout& L,
                         const DeviceInfo& dev, cudaStream_t stream) {
+  (void)keys; (void)n_groups; (void)dev;
   if (n_rows <= 0) return 0;
-  unsigned int* header = reinterpret_cast<unsigned int*>(scratch + L.off_header);
-  unsigned long long* slot_key = reinterpret_cast<unsigned long long*>(scratch + L.off_slot_key);
-  unsigned int* slot_gid = reinterpret_cast<unsigned int*>(scratch + L.off_slot_gid);
-  unsigned int* row_gid = reinterpret_cast<unsigned int*>(scratch + L.off_row_gid);
-  unsigned int* counts = reinterpret_cast<unsigned int*>(scratch + L.off_counts);
-  unsigned long long* offsets = reinterpret_cast<unsigned long long*>(scratch + L.off_offsets);
-  unsigned long long* tile_sums = reinterpret_cast<unsigned long long*>(scratch + L.off_tile_sums);
+  const unsigned int* row_slot = reinterpret_cast<const unsigned int*>(scratch + L.off_row_slot);
+  const unsigned int* row_id = reinterpret_cast<const unsigned int*>(scratch + L.off_row_id);
+  unsigned int* sorted_slot = reinterpret_cast<unsigned int*>(scratch + L.off_sorted_slot);
   unsigned int* perm = reinterpret_cast<unsigned int*>(scratch + L.off_perm);
-  const unsigned grid = (unsigned)grid_for(n_rows, dev);
-  agg_lookup_kernel<<<grid, kThreads, 0, stream>>>(reinterpret_cast<const long long*>(keys), n_rows, slot_key, slot_gid,
-                                                   L.table_slots - 1, header, row_gid, counts);
-  TFS_CUDA(cudaGetLastError());
-  const int64_t tiles = (n_groups + 1 + kScanTile - 1) / kScanTile;   // scan covers index n_groups for the total
-  scan_tile_sums_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(counts, n_groups, tile_sums);
-  TFS_CUDA(cudaGetLastError());
-  scan_tile_offsets_kernel<<<1, 1024, 0, stream>>>(tile_sums, tiles);
-  TFS_CUDA(cudaGetLastError());
-  scan_apply_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(counts, n_groups, tile_sums, offsets);
-  TFS_CUDA(cudaGetLastError());
-  agg_scatter_kernel<<<grid, kThreads, 0, stream>>>(row_gid, n_rows, offsets, counts, perm);
-  TFS_CUDA(cudaGetLastError());
-  return 5;
+  size_t temp = L.sort_temp_bytes;
+  TFS_CUDA(cub::DeviceRadixSort::SortPairs(scratch + L.off_sort_temp, temp, row_slot, sorted_slot, row_id, perm, n_rows, 0,
+                                           slot_bits(L.table_slots), stream));
+  return 1;   // counted as one launch of ours: the sort's internal kernels are library code
 }
 
 int launch_agg_reduce(int dtype, int red_op, const void* payload, int64_t cell, int64_t n_groups, char* scratch,
                       const AggLayout& L, void* out, const DeviceInfo& dev, cudaStream_t stream) {
   const unsigned int* perm = reinterpret_cast<const unsigned int*>(scratch + L.off_perm);
-  const unsigned long long* offsets = reinterpret_cast<const unsigned long long*>(scratch + L.off_offsets);
+  const unsigned int* offsets = reinterpret_cast<const unsigned int*>(scratch + L.off_offsets);
+  const unsigned int* counts = reinterpret_cast<const unsigned int*>(scratch + L.off_counts);
+  const unsigned int* group_slot = reinterpret_cast<const unsigned int*>(scratch + L.off_group_slot);
   switch (dtype) {
-    case TFS_FLOAT: return launch_gather_op<float>(red_op, payload, cell, perm, offsets, n_groups, out, dev, stream);
-    case TFS_DOUBLE: return launch_gather_op<double>(red_op, payload, cell, perm, offsets, n_groups, out, dev, stream);
-    case TFS_INT32: return launch_gather_op<int>(red_op, payload, cell, perm, offsets, n_groups, out, dev, stream);
-    case TFS_INT64: return launch_gather_op<long long>(red_op, payload, cell, perm, offsets, n_groups, out, dev, stream);
+    case TFS_FLOAT: return launch_gather_op<float>(red_op, payload, cell, perm, offsets, counts, group_slot, n_groups, out, dev, stream);
+    case TFS_DOUBLE: return launch_gather_op<double>(red_op, payload, cell, perm, offsets, counts, group_slot, n_groups, out, dev, stream);
+    case TFS_INT32: return launch_gather_op<int>(red_op, payload, cell, perm, offsets, counts, group_slot, n_groups, out, dev, stream);
+    case TFS_INT64: return launch_gather_op<long long>(red_op, payload, cell, perm, offsets, counts, group_slot, n_groups, out, dev, stream);
   }
   fail(TFS_ERR_UNSUPPORTED, "aggregate: unsupported dtype");
 }

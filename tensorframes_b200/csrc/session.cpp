@@ -834,9 +834,9 @@ void Session::aggregate(int64_t n_rows, const int64_t* keys, const std::vector<T
   unsigned int header[4] = {0, 0, 0, 0};
   TFS_CUDA(cudaMemcpyAsync(header, scratch + L.off_header, sizeof(header), cudaMemcpyDeviceToHost, stream_));
   TFS_CUDA(cudaStreamSynchronize(stream_));
-  TFS_CHECK(header[1] == 0 && int64_t(header[0]) <= max_groups, TFS_ERR_INVALID,
+  TFS_CHECK(header[1] == 0 && int64_t(header[2]) <= max_groups, TFS_ERR_INVALID,
             "aggregate: the block holds more than max_groups = " + std::to_string(max_groups) + " distinct keys");
-  const int64_t n_groups = header[0];
+  const int64_t n_groups = header[2];
   launches_ += launch_agg_segments(d_keys, n_rows, n_groups, scratch, L, dev_, stream_);
   for (size_t k = 0; k < items.size(); ++k) {
     const Node& n = g_.nodes[size_t(items[k].node)];
