@@ -38,6 +38,18 @@ int launch_reduce_axis0(int dtype, int red_op, const void* in, int64_t outer, in
 int launch_reduce_rows(int dtype, int red_op, const void* in, int64_t outer, int64_t inner, void* out,
                        const DeviceInfo& dev, cudaStream_t stream);
 
+// K4: out[M, N] = op(a) * op(b) (+ bias[N]); float32. The SIMT kernel takes any shape.
+int launch_matmul_simt(const float* a, const float* b, const float* bias, float* out, int64_t M, int64_t N, int64_t K,
+                       bool ta, bool tb, const DeviceInfo& dev, cudaStream_t stream);
+
+// tcgen05 path for x[M, K] * w[K, N] (+ bias): K % 32 == 0, N % 16 == 0, N <= 256, x not transposed.
+// w is passed pre-split into tf32-exact hi / lo parts laid out [N, K] (launch_split_weights).
+bool matmul_tc_supported(const void* a, const void* out, int64_t M, int64_t N, int64_t K, bool ta);
+size_t matmul_tc_weight_bytes(int64_t N, int64_t K);
+int launch_split_weights(const float* w, bool transposed, int64_t K, int64_t N, float* hi, float* lo, cudaStream_t stream);
+int launch_matmul_tc(const float* x, const float* w_hi, const float* w_lo, const float* bias, float* out, int64_t M,
+                     int64_t N, int64_t K, const DeviceInfo& dev, cudaStream_t stream);
+
 // K3: keyed block reduction. Scratch layout for n_rows rows and at most max_groups groups.
 struct AggLayout {
   uint64_t table_slots;

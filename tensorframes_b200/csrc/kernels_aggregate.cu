@@ -53,6 +53,7 @@ agg_insert_kernel(const long long* __restrict__ keys, const int64_t n, unsigned 
       claimed = atomicCAS(slot_key + h, 0ULL, kEmpty) == 0ULL;   // this slot starts as 0, not as the marker
     } else {
       h = mix64(k) & mask;
+      unsigned int probes = 0;
       while (true) {
         const unsigned long long cur = slot_key[h];
         if (cur == k) break;
@@ -62,7 +63,9 @@ agg_insert_kernel(const long long* __restrict__ keys, const int64_t n, unsigned 
           if (prev == k) break;
         }
         h = (h + 1) & mask;
-        if (*reinterpret_cast<volatile unsigned int*>(header + 1)) break;   // too many distinct keys: give up
+        // a table this crowded means more distinct keys than max_groups: look at the overflow flag now and
+        // then (not on every probe: the whole grid would hammer one address) and give up when it is set
+        if ((++probes & 255u) == 0u && *reinterpret_cast<volatile unsigned int*>(header + 1)) break;
       }
     }
     if (claimed && atomicAdd(header, 1u) >= max_groups) header[1] = 1u;

@@ -38,6 +38,7 @@ struct Step {
   std::vector<int> nodes;   // ELT: the group (topological order); others: one node
   Shape shape;              // ELT: iteration shape
   int64_t outer = 0, inner = 0;  // reductions
+  int out_node = -1, bias_node = -1;  // MATMUL with a fused "+ bias[N]" epilogue: the Add node and its bias operand
 };
 
 }  // namespace
@@ -60,6 +61,7 @@ Session::~Session() {
   cudaStreamSynchronize(stream_);
   if (stream_ != own_stream_) cudaStreamSynchronize(own_stream_);
   for (auto& kv : const_dev_) cudaFree(kv.second);
+  for (auto& kv : tc_weights_) { cudaFree(kv.second.first); cudaFree(kv.second.second); }
   if (ws_) cudaFree(ws_);
   if (red_scratch_) cudaFree(red_scratch_);
   if (err_flag_) cudaFree(err_flag_);
@@ -221,11 +223,41 @@ void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<
     level[size_t(idx)] = l;
   }
 
+  // MatMul followed only by "+ bias[N]" becomes one step: the bias is added in the MatMul epilogue
+  std::vector<int> consumers(N, 0), fused_from(N, -1), fused_bias(N, -1);
+  std::vector<char> fetched(N, 0);
+  for (int idx : plan.needed)
+    for (int k : g_.nodes[size_t(idx)].in) consumers[size_t(k)]++;
+  for (int f : plan.fetch_nodes) fetched[size_t(f)] = 1;
+  for (int idx : plan.needed) {
+    const Node& n = g_.nodes[size_t(idx)];
+    if (n.cls != OpClass::Binary || n.elt_op != E_ADD) continue;
+    for (int side = 0; side < 2; ++side) {
+      const int mm = n.in[size_t(side)], b = n.in[size_t(1 - side)];
+      const Node& nm = g_.nodes[size_t(mm)];
+      if (nm.cls != OpClass::MatMul || consumers[size_t(mm)] != 1 || fetched[size_t(mm)] || mm == b) continue;
+      const Shape& bs = plan.shape[size_t(b)];
+      const int64_t ncols = plan.shape[size_t(mm)].d[1];
+      int lead = 0;
+      while (lead < bs.rank && bs.d[lead] == 1) ++lead;
+      if (bs.rank - lead == 1 && bs.d[lead] == ncols && g_.nodes[size_t(b)].cls != OpClass::MatMul) {
+        fused_from[size_t(idx)] = mm;
+        fused_bias[size_t(mm)] = b;
+        break;
+      }
+    }
+  }
+
   // steps: element-wise nodes of equal (level, shape) fuse into one group
   std::map<std::string, int> group_of_key;
   for (int idx : plan.needed) {
     const Node& n = g_.nodes[size_t(idx)];
-    if (is_elt(n)) {
+    if (fused_from[size_t(idx)] >= 0) {
+      const int st = plan.step_of[size_t(fused_from[size_t(idx)])];
+      plan.steps[size_t(st)].out_node = idx;
+      plan.steps[size_t(st)].bias_node = fused_bias[size_t(fused_from[size_t(idx)])];
+      plan.step_of[size_t(idx)] = st;
+    } else if (is_elt(n)) {
       std::string key = std::to_string(level[size_t(idx)]) + "|" + plan.shape[size_t(idx)].str();
       auto it = group_of_key.find(key);
       if (it == group_of_key.end()) {
@@ -283,6 +315,7 @@ void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<
     const Node& n = g_.nodes[size_t(idx)];
     std::vector<int> operands = is_elt(n) ? elt_operands(n) : std::vector<int>{n.in[0]};
     if (n.cls == OpClass::MatMul) operands = n.in;
+    if (fused_from[size_t(idx)] >= 0) operands = {fused_from[size_t(idx)], fused_bias[size_t(fused_from[size_t(idx)])]};
     for (int k : operands) {
       int sk = plan.step_of[size_t(k)];
       if (sk != st) plan.materialize[size_t(k)] = 1;
@@ -629,9 +662,6 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
                 "fetch '" + n.name + "' has shape " + plan.shape[size_t(idx)].str() + " but the output buffer is declared " +
                     fetches[i].shape.str());
   }
-  for (const Step& s : plan.steps)
-    TFS_CHECK(s.kind != Step::MATMUL, TFS_ERR_UNSUPPORTED, "MatMul execution is not available in this build");
-
   ensure_device();
   const size_t N = g_.nodes.size();
   std::vector<void*> dev_ptr(N, nullptr);
@@ -735,8 +765,33 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
                                    cudaMemcpyDeviceToDevice, stream_));
         break;
       }
-      case Step::MATMUL:
+      case Step::MATMUL: {
+        const int mm = s.nodes[0];
+        const Node& n = g_.nodes[size_t(mm)];
+        const Shape& as = plan.shape[size_t(n.in[0])];
+        const Shape& os = plan.shape[size_t(mm)];
+        const int64_t M = os.d[0], Nc = os.d[1], K = n.transpose_a ? as.d[0] : as.d[1];
+        const float* a = static_cast<const float*>(dev_ptr[size_t(n.in[0])]);
+        const float* b = static_cast<const float*>(dev_ptr[size_t(n.in[1])]);
+        const float* bias = s.bias_node >= 0 ? static_cast<const float*>(dev_ptr[size_t(s.bias_node)]) : nullptr;
+        float* out = static_cast<float*>(dev_ptr[size_t(s.out_node >= 0 ? s.out_node : mm)]);
+        if (M * Nc == 0) break;
+        const bool const_b = g_.nodes[size_t(n.in[1])].cls == OpClass::Const;
+        if (const_b && matmul_tc_supported(a, out, M, Nc, K, n.transpose_a)) {
+          auto it = tc_weights_.find(n.in[1] * 2 + (n.transpose_b ? 1 : 0));
+          if (it == tc_weights_.end()) {   // split the constant once per session: [N, K] K-major hi / lo parts
+            float *hi = nullptr, *lo = nullptr;
+            TFS_CUDA(cudaMalloc(reinterpret_cast<void**>(&hi), matmul_tc_weight_bytes(Nc, K)));
+            TFS_CUDA(cudaMalloc(reinterpret_cast<void**>(&lo), matmul_tc_weight_bytes(Nc, K)));
+            launches_ += launch_split_weights(b, n.transpose_b, K, Nc, hi, lo, stream_);
+            it = tc_weights_.emplace(n.in[1] * 2 + (n.transpose_b ? 1 : 0), std::make_pair(hi, lo)).first;
+          }
+          launches_ += launch_matmul_tc(a, it->second.first, it->second.second, bias, out, M, Nc, K, dev_, stream_);
+        } else {
+          launches_ += launch_matmul_simt(a, b, bias, out, M, Nc, K, n.transpose_a, n.transpose_b, dev_, stream_);
+        }
         break;
+      }
     }
   }
 

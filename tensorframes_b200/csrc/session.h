@@ -59,6 +59,7 @@ class Session {
   int32_t* err_flag_ = nullptr;       // device
   int32_t* err_host_ = nullptr;       // pinned
   std::unordered_map<int, void*> const_dev_;
+  std::unordered_map<int, std::pair<float*, float*>> tc_weights_;   // MatMul constants split into tf32 hi / lo parts
   int64_t launches_ = 0;
 };
 

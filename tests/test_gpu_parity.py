@@ -545,3 +545,49 @@ def test_chain_fast_path_unaligned_device_pointers():
         s.sync()
     want = np.maximum(x[1:] * 1.5 + 0.25, 0).astype(np.float32)
     assert dz.cpu().numpy()[1:].tobytes() == want.tobytes()
+
+
+# ---- MatMul (K4) ---------------------------------------------------------------------------------------
+def check_matmul(got, a, b, bias=None):
+    """float32 result within 1e-5, normwise: |got - exact| <= 1e-5 * sum_k |a_ik||b_kj| (+|bias|)."""
+    exact = a.astype(np.float64) @ b.astype(np.float64)
+    scale = np.abs(a).astype(np.float64) @ np.abs(b).astype(np.float64)
+    if bias is not None:
+        exact = exact + bias.astype(np.float64)
+        scale = scale + np.abs(bias).astype(np.float64)
+    assert got.dtype == np.float32 and got.shape == exact.shape
+    err = np.abs(got.astype(np.float64) - exact)
+    assert np.all(err <= 1e-5 * np.maximum(scale, 1e-30)), float((err / np.maximum(scale, 1e-30)).max())
+
+
+@pytest.mark.parametrize("shape", [(1, 1, 1), (7, 5, 3), (33, 100, 10), (1000, 256, 256), (257, 64, 48), (4099, 256, 256)])
+def test_matmul_against_float64(shape):
+    m, k, n = shape
+    rng = np.random.default_rng(m + k + n)
+    a = rng.uniform(0, 1, (m, k)).astype(np.float32)
+    w = rng.uniform(-1 / 16, 1 / 16, (k, n)).astype(np.float32)
+    bias = rng.uniform(-1, 1, n).astype(np.float32)
+    with dsl.withGraph():
+        p = dsl.placeholder(tfs.FloatType, dsl.Unknown, k).named("x")
+        mm = dsl.matmul(p, dsl.constant(w)).named("mm")
+        y = (dsl.matmul(p, dsl.constant(w)) + dsl.constant(bias)).named("y")
+        g = dsl.build_graph(mm, y)
+    got_mm, got_y = run_native(g, {"x": a}, ["mm", "y"])
+    check_matmul(got_mm, a, w)
+    check_matmul(got_y, a, w, bias)
+    want = tf_ops.evaluate(g, {"x": a}, ["mm", "y"])
+    check_matmul(want[0], a, w)          # the oracle itself meets the same bar
+
+
+def test_matmul_transposes_and_two_columns():
+    rng = np.random.default_rng(8)
+    a = rng.normal(size=(50, 20)).astype(np.float32)
+    b = rng.normal(size=(30, 20)).astype(np.float32)
+    with dsl.withGraph():
+        pa = dsl.placeholder(tfs.FloatType, dsl.Unknown, 20).named("a")
+        pb = dsl.placeholder(tfs.FloatType, dsl.Unknown, 20).named("b")
+        g = dsl.build_graph(dsl.matmul(pa, pb, transpose_b=True).named("abt"),
+                            dsl.matmul(pa, pa, transpose_a=True).named("ata"))
+    abt, ata = run_native(g, {"a": a, "b": b}, ["abt", "ata"])
+    check_matmul(abt, a, b.T)
+    check_matmul(ata, a.T, a)
