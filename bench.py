@@ -36,7 +36,8 @@ ROWS_C2 = 100_000_000
 ROWS_C3 = 1_000_000_000
 ROWS_C4 = 250_000_000          # BASELINE config 4 names 5e8 rows (132 GB); see config.workload
 KEYS_C4 = 1_000_000
-ALG_BYTES_PER_ROW = {"c2": 32, "c3": 12, "c4": 264}
+ROWS_C5 = 1 << 24               # BASELINE config 5: FloatType[?,256] x 256x256 + bias, 2^24 rows per GPU
+ALG_BYTES_PER_ROW = {"c2": 32, "c3": 12, "c4": 264, "c5": 2048}
 FALLBACK_HBM_GBS = 6650.0                   # /opt/skills/guides/B200_PROFILING.md
 
 
@@ -126,6 +127,12 @@ def build_graph(workload):
             y = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("y_input")
             z = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("z_input")
             return dsl.build_graph(dsl.reduce_sum(y, [0]).named("y"), dsl.reduce_min(z, [0]).named("z"))
+        if workload == "c5":
+            rng = np.random.default_rng(5)
+            w = rng.uniform(-1 / 16, 1 / 16, (256, 256)).astype(np.float32)
+            b = rng.uniform(-1, 1, 256).astype(np.float32)
+            x = dsl.placeholder(tfs.FloatType, dsl.Unknown, 256).named("x")
+            return dsl.build_graph((dsl.matmul(x, dsl.constant(w)) + dsl.constant(b)).named("y"))
         if workload == "c4":
             v = dsl.placeholder(tfs.FloatType, dsl.Unknown, 64).named("v_input")
             return dsl.build_graph(dsl.reduce_sum(v, [0]).named("v"))
@@ -172,10 +179,12 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
     wl = args.workload
-    rows = args.rows or {"c2": ROWS_C2, "c3": ROWS_C3, "c4": ROWS_C4}[wl]
+    rows = args.rows or {"c2": ROWS_C2, "c3": ROWS_C3, "c4": ROWS_C4, "c5": ROWS_C5}[wl]
     DA = _native.DeviceArray.from_torch
     if wl == "c4":
         return run_c4(args, torch, dist, _native, world, rank, local, device, rows)
+    if wl == "c5":
+        return run_c5(args, torch, dist, _native, world, rank, local, device, rows)
 
     graph_bytes = build_graph(wl)
     graph = _native.Graph(graph_bytes)
@@ -412,6 +421,80 @@ def run_c4(args, torch, dist, _native, world, rank, local, device, rows):
         dist.destroy_process_group()
 
 
+def run_c5(args, torch, dist, _native, world, rank, local, device, rows):
+    """BASELINE config 5: map_blocks with MatMul(x[rows,256], W[256,256]) + bias on the tcgen05 path."""
+    DA = _native.DeviceArray.from_torch
+    graph = _native.Graph(build_graph("c5"))
+    sess = _native.Session(graph, local)
+    stream = torch.cuda.Stream(device=device)
+    torch.cuda.set_stream(stream)
+    sess.set_stream(stream.cuda_stream)
+    g = torch.Generator(device=device)
+    g.manual_seed(5 + 1000 * rank)
+    x = torch.rand((rows, 256), generator=g, device=device, dtype=torch.float32)
+    y = torch.empty((rows, 256), dtype=torch.float32, device=device)
+
+    def step():
+        sess.run_into({"x": DA(x)}, {"y": DA(y)})
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    launches0 = sess.launch_count
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clocks:
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        start.record(stream)
+        for _ in range(args.steps):
+            step()
+        end.record(stream)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+    elapsed_ms = start.elapsed_time(end)
+    tt = torch.tensor([elapsed_ms], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    elapsed_ms = float(tt.item())
+    launches = sess.launch_count - launches0
+    # parity spot check against float64 on a slice (normwise 1e-5)
+    rng = np.random.default_rng(5)
+    w = torch.from_numpy(rng.uniform(-1 / 16, 1 / 16, (256, 256)).astype(np.float32)).to(device)
+    b = torch.from_numpy(rng.uniform(-1, 1, 256).astype(np.float32)).to(device)
+    xs = x[:65536].double()
+    exact = xs @ w.double() + b.double()
+    scale = xs.abs() @ w.double().abs() + b.double().abs()
+    assert torch.all((y[:65536].double() - exact).abs() <= 1e-5 * scale)
+    if rank == 0:
+        peaks = {}
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                peaks = json.load(f)
+        except Exception:
+            pass
+        bf16 = float(peaks.get("bf16_tflops_sustained", 1400.0))
+        step_s = elapsed_ms / 1e3 / args.steps
+        tflops = rows * 131072.0 / step_s / 1e12
+        hbm, _ = hbm_peak()
+        print(json.dumps({
+            "metric": "rows/s for mapBlocks (MatMul FloatType[?,256] x 256x256 + bias)",
+            "value": world * rows / step_s, "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 (3xTF32 on tcgen05, fp32 accumulate)", "data": "synthetic",
+            "config": {"workload": f"BASELINE configs[4]: map_blocks matmul FloatType[?,256] x 256x256 + bias, {rows} rows per GPU",
+                       "rows_per_gpu": rows, "l2": "inputs larger than L2 (no flush needed)", "exchange": "none"},
+            "roofline": {"bound": "tensor", "achieved": tflops, "peak": bf16, "unit": "TFLOP/s", "frac": tflops / bf16,
+                         "traffic": ncu_traffic("c5"), "peak_source": "measured bf16 sustained; tf32 runs at half of it and "
+                         "each fp32 product costs 3 tf32 MMAs, so the attainable ceiling is ~peak/6",
+                         "kernel": "matmul_tc_kernel", "mma_tflops_issued": 3 * tflops,
+                         "hbm_gbs": rows * 2048.0 / step_s / 1e9, "hbm_frac": rows * 2048.0 / step_s / 1e9 / hbm},
+            "e2e": None, "gpu_launches": int(launches), "clocks": clocks.summary(), "cpu_baseline": None}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def cpu_baseline_leg(wl, host_feeds, rows, budget_s=12.0):
     """oracle/cpu_ref.c on a bounded sample: the whole block if it finishes within the budget,
     else a prefix sized from a calibration run."""
@@ -489,7 +572,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5"])
     ap.add_argument("--rows", type=int, default=0, help="rows per GPU (default: the BASELINE config's)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

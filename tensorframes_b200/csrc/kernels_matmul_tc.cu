@@ -9,7 +9,8 @@
 // Structure (one persistent CTA per SM, 128-row tiles, the whole N <= 256 per tile):
 //   warp 0      TMA producer   cp.async.bulk.tensor loads of the x chunk [128 x 32] and the two
 //                              weight chunks [N x 32] (hi, lo) per K step, 128B-swizzled, 2 stages
-//   warps 6-9   splitter       turn the landed x chunk into its hi part (in place) and lo part
+//   warps 6-9   splitter       compute lo(x) = x - trunc_tf32(x) of the landed x chunk into a second buffer
+//                              (the raw chunk serves as hi(x): the tensor core ignores the low 13 bits)
 //   warp 1      MMA issuer     one elected thread: 12 tcgen05.mma.kind::tf32 (M128 x N x K8) per K step
 //                              into one of two TMEM accumulators (2 x 256 columns)
 //   warps 2-5   epilogue       tcgen05.ld the finished accumulator, add bias, store rows -- while the
@@ -160,19 +161,27 @@ matmul_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
       for (int kc = 0; kc < k_chunks; ++kc, ++it) {
         const int s = it % kStages;
         const uint32_t ph = (it / kStages) & 1;
+        const uint64_t a_hi = umma_desc(stage_x_hi(s)), a_lo = umma_desc(stage_x_lo(s));
+        const uint64_t b_hi = umma_desc(stage_w_hi(s)), b_lo = umma_desc(stage_w_lo(s));
+        // The tensor core reads only the top 19 bits of each fp32 operand, so the landed x chunk already
+        // acts as its own hi part: the two products that need nothing else start as soon as TMA is done ...
         mbar_wait(&sh.full[s], ph);
-        mbar_wait(&sh.split[s], ph);
         asm volatile("tcgen05.fence::after_thread_sync;");
         if (lane == 0) {
-          const uint64_t a_hi = umma_desc(stage_x_hi(s)), a_lo = umma_desc(stage_x_lo(s));
-          const uint64_t b_hi = umma_desc(stage_w_hi(s)), b_lo = umma_desc(stage_w_lo(s));
 #pragma unroll
           for (int k = 0; k < kChunkK / 8; ++k) {          // UMMA_K = 8 tf32 values = 32 bytes: +2 in 16-byte units
             const uint64_t o = uint64_t(k * 2);
             umma_tf32(d, a_hi + o, b_hi + o, idesc, (kc | k) != 0);
-            umma_tf32(d, a_lo + o, b_hi + o, idesc, 1);
             umma_tf32(d, a_hi + o, b_lo + o, idesc, 1);
           }
+        }
+        __syncwarp();
+        // ... and the lo(x) * hi(w) product follows once the splitter has written lo(x)
+        mbar_wait(&sh.split[s], ph);
+        asm volatile("tcgen05.fence::after_thread_sync;");
+        if (lane == 0) {
+#pragma unroll
+          for (int k = 0; k < kChunkK / 8; ++k) umma_tf32(d, a_lo + uint64_t(k * 2), b_hi + uint64_t(k * 2), idesc, 1);
           umma_commit(&sh.empty[s]);                       // stage reusable once these MMAs have read it
           if (kc == k_chunks - 1) umma_commit(&sh.tmem_full[buf]);
         }
@@ -220,7 +229,7 @@ matmul_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
       for (int kc = 0; kc < k_chunks; ++kc, ++it) {
         const int s = it % kStages;
         mbar_wait(&sh.full[s], (it / kStages) & 1);
-        uint4* hi = reinterpret_cast<uint4*>(stage_x_hi(s));
+        const uint4* hi = reinterpret_cast<const uint4*>(stage_x_hi(s));
         uint4* lo = reinterpret_cast<uint4*>(stage_x_lo(s));
 #pragma unroll
         for (int j = 0; j < int(kABytes / 16 / 128); ++j) {     // 1024 16-byte vectors over 128 threads
@@ -231,7 +240,6 @@ matmul_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
           l.y = __float_as_uint(__fsub_rn(__uint_as_float(v.y), __uint_as_float(h.y)));
           l.z = __float_as_uint(__fsub_rn(__uint_as_float(v.z), __uint_as_float(h.z)));
           l.w = __float_as_uint(__fsub_rn(__uint_as_float(v.w), __uint_as_float(h.w)));
-          hi[idx] = h;
           lo[idx] = l;
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the MMA unit

@@ -2,6 +2,7 @@
 #include "session.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <map>
 #include <set>
 
@@ -777,7 +778,8 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
         float* out = static_cast<float*>(dev_ptr[size_t(s.out_node >= 0 ? s.out_node : mm)]);
         if (M * Nc == 0) break;
         const bool const_b = g_.nodes[size_t(n.in[1])].cls == OpClass::Const;
-        if (const_b && matmul_tc_supported(a, out, M, Nc, K, n.transpose_a)) {
+        static const bool force_simt = [] { const char* e = std::getenv("TFS_MATMUL_IMPL"); return e && std::string(e) == "simt"; }();
+        if (!force_simt && const_b && matmul_tc_supported(a, out, M, Nc, K, n.transpose_a)) {
           auto it = tc_weights_.find(n.in[1] * 2 + (n.transpose_b ? 1 : 0));
           if (it == tc_weights_.end()) {   // split the constant once per session: [N, K] K-major hi / lo parts
             float *hi = nullptr, *lo = nullptr;

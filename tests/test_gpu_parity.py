@@ -591,3 +591,20 @@ def test_matmul_transposes_and_two_columns():
     abt, ata = run_native(g, {"a": a, "b": b}, ["abt", "ata"])
     check_matmul(abt, a, b.T)
     check_matmul(ata, a.T, a)
+
+
+def test_matmul_tensor_core_path_is_fp32_accurate():
+    """The 3xTF32 split must behave like a float32 GEMM (error ~1e-7 normwise), far inside the 1e-5 bar;
+    a single TF32 pass, or an operand rounded instead of truncated by the tensor core, would be ~1e-4."""
+    rng = np.random.default_rng(55)
+    m, k, n = 8192, 256, 256
+    a = rng.normal(size=(m, k)).astype(np.float32)             # zero-mean data: the hard case for splitting
+    w = rng.normal(size=(k, n)).astype(np.float32)
+    with dsl.withGraph():
+        p = dsl.placeholder(tfs.FloatType, dsl.Unknown, k).named("x")
+        g = dsl.build_graph(dsl.matmul(p, dsl.constant(w)).named("y"))
+    (got,) = run_native(g, {"x": a}, ["y"])
+    exact = a.astype(np.float64) @ w.astype(np.float64)
+    scale = np.abs(a).astype(np.float64) @ np.abs(w).astype(np.float64)
+    worst = float((np.abs(got.astype(np.float64) - exact) / scale).max())
+    assert worst <= 2e-6, worst
