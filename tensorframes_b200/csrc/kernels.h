@@ -53,8 +53,7 @@ int launch_matmul_tc(const float* x, const float* w_hi, const float* w_lo, const
 // K3: keyed block reduction. Scratch layout for n_rows rows and at most max_groups groups.
 struct AggLayout {
   uint64_t table_slots;
-  size_t off_header, off_slot_key, off_counts, off_offsets, off_group_slot, off_tile_sums, off_row_slot, off_row_id,
-      off_sorted_slot, off_perm, off_sort_temp;
+  size_t off_header, off_slot_key, off_counts, off_offsets, off_group_slot, off_tile_sums, off_row_tag, off_perm, off_sort_temp;
   size_t sort_temp_bytes;
   size_t bytes;
 };
