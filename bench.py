@@ -57,11 +57,17 @@ def hbm_peak():
         return FALLBACK_HBM_GBS, "fallback"
 
 
-def ncu_traffic(workload):
-    """Per-launch DRAM bytes of the dominant kernel from the committed ncu capture, if any."""
+def ncu_traffic(workload, rows=None):
+    """Per-launch DRAM bytes of the dominant kernel from the committed ncu capture (profiles/traffic.json),
+    scaled by rows when this run's block differs from the captured one; None when there is no capture."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            return json.load(f).get(workload)
+            e = json.load(f).get(workload)
+        if not e:
+            return None
+        if rows is None or rows == e["rows"]:
+            return e["bytes"]
+        return e["bytes"] * rows / e["rows"]
     except Exception:
         return None
 
@@ -338,8 +344,8 @@ def run_ours(args):
                        "l2": "inputs larger than L2 (no flush needed)",
                        "exchange": "all_gather of partial rows + merge run" if (wl == "c2" and world > 1) else "none"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": ncu_traffic(wl), "peak_source": peak_src,
-                         "kernel": "reduce_axis0_flat_kernel" if wl == "c2" else "eltwise_kernel",
+                         "frac": achieved / peak, "traffic": ncu_traffic(wl, rows), "peak_source": peak_src,
+                         "kernel": "reduce_axis0_tma_kernel" if wl == "c2" else "chain_kernel",
                          "algorithmic_bytes_per_launch": bytes_per_launch,
                          "avg_launch_ms": avg_launch_s * 1e3, "frac_of_nominal_8000": achieved / 8000.0},
             "e2e": e2e,
@@ -414,7 +420,7 @@ def run_c4(args, torch, dist, _native, world, rank, local, device, rows):
                                    f"FloatType[?,64], {rows} rows per GPU (config names 5e8; reduced to bound memory)",
                        "rows_per_gpu": rows, "l2": "inputs larger than L2 (no flush needed)", "exchange": "none (per-GPU blocks)"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": ncu_traffic("c4"), "peak_source": peak_src, "kernel": "whole step (5 passes, agg_gather_reduce_kernel dominant)",
+                         "traffic": ncu_traffic("c4", rows), "peak_source": peak_src, "kernel": "whole step (5 passes, agg_gather_reduce_kernel dominant)",
                          "algorithmic_bytes_per_launch": rows * 264.0, "frac_of_nominal_8000": achieved / 8000.0},
             "e2e": None, "gpu_launches": int(launches), "clocks": clocks.summary(), "cpu_baseline": None}))
     if world > 1:
@@ -486,7 +492,7 @@ def run_c5(args, torch, dist, _native, world, rank, local, device, rows):
             "config": {"workload": f"BASELINE configs[4]: map_blocks matmul FloatType[?,256] x 256x256 + bias, {rows} rows per GPU",
                        "rows_per_gpu": rows, "l2": "inputs larger than L2 (no flush needed)", "exchange": "none"},
             "roofline": {"bound": "tensor", "achieved": tflops, "peak": bf16, "unit": "TFLOP/s", "frac": tflops / bf16,
-                         "traffic": ncu_traffic("c5"), "peak_source": "measured bf16 sustained; tf32 runs at half of it and "
+                         "traffic": ncu_traffic("c5", rows), "peak_source": "measured bf16 sustained; tf32 runs at half of it and "
                          "each fp32 product costs 3 tf32 MMAs, so the attainable ceiling is ~peak/6",
                          "kernel": "matmul_tc_kernel", "mma_tflops_issued": 3 * tflops,
                          "hbm_gbs": rows * 2048.0 / step_s / 1e9, "hbm_frac": rows * 2048.0 / step_s / 1e9 / hbm},
