@@ -360,7 +360,8 @@ def run_ours(args):
 
 def run_c4(args, torch, dist, _native, world, rank, local, device, rows):
     """BASELINE config 4: groupBy(int64 key).aggregate(reduce_sum(v_input, [0])), FloatType[?,64].
-    One block per GPU; the cross-GPU key-owner exchange is not part of this measurement yet."""
+    One block per GPU; with N > 1 the step also moves every partial group to the rank owning its key
+    (all_to_all) and merges there, so the result is one row per distinct key, sharded by owner."""
     DA = _native.DeviceArray.from_torch
     graph = _native.Graph(build_graph("c4"))
     sess = _native.Session(graph, local)
@@ -372,8 +373,18 @@ def run_c4(args, torch, dist, _native, world, rank, local, device, rows):
     out_keys = torch.empty(KEYS_C4, dtype=torch.int64, device=device)
     out = torch.empty((KEYS_C4, 64), dtype=torch.float32, device=device)
 
+    out_keys2 = torch.empty(KEYS_C4, dtype=torch.int64, device=device)
+    out2 = torch.empty((KEYS_C4, 64), dtype=torch.float32, device=device)
+    owned = [0]
+
     def step():
-        return sess.aggregate_into(DA(keys), {"v_input": DA(v)}, {"v": DA(out)}, DA(out_keys))
+        g = sess.aggregate_into(DA(keys), {"v_input": DA(v)}, {"v": DA(out)}, DA(out_keys))
+        if world > 1:
+            # exchange: partial groups travel to the rank that owns their key, which merges them
+            from tensorframes_b200.distributed import exchange_groups
+            rk, (rv,) = exchange_groups(out_keys[:g], [out[:g]])
+            owned[0] = sess.aggregate_into(DA(rk), {"v_input": DA(rv)}, {"v": DA(out2)}, DA(out_keys2))
+        return g
 
     for _ in range(args.warmup):
         n_groups = step()
@@ -418,7 +429,7 @@ def run_c4(args, torch, dist, _native, world, rank, local, device, rows):
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"BASELINE configs[3]: aggregate groupBy int64 key ({n_groups} distinct), reduce_sum "
                                    f"FloatType[?,64], {rows} rows per GPU (config names 5e8; reduced to bound memory)",
-                       "rows_per_gpu": rows, "l2": "inputs larger than L2 (no flush needed)", "exchange": "none (per-GPU blocks)"},
+                       "rows_per_gpu": rows, "l2": "inputs larger than L2 (no flush needed)", "exchange": "none" if world == 1 else "key-owner all_to_all of partial groups + merge aggregate"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": ncu_traffic("c4", rows), "peak_source": peak_src, "kernel": "whole step (5 passes, agg_gather_reduce_kernel dominant)",
                          "algorithmic_bytes_per_launch": rows * 264.0, "frac_of_nominal_8000": achieved / 8000.0},

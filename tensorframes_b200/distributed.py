@@ -54,3 +54,54 @@ def owner_of_key(keys: np.ndarray, world: int) -> np.ndarray:
     x *= np.uint64(0x94D049BB133111EB)
     x ^= x >> np.uint64(31)
     return (x % np.uint64(world)).astype(np.int64)
+
+
+def owner_of_key_torch(keys, world: int):
+    """owner_of_key on a torch int64 tensor (any device), bit-identical to the numpy version:
+    the 64-bit mix is done in wrapping int64 arithmetic with logical shifts emulated by masks."""
+    import torch
+
+    def lsr(x, k):   # logical shift right on int64
+        return (x >> k) & ((1 << (64 - k)) - 1)
+
+    def mul(x, c):   # wrapping multiply by an unsigned 64-bit constant
+        return x * torch.tensor(c - (1 << 64) if c >= (1 << 63) else c, dtype=torch.int64, device=x.device)
+
+    x = keys.clone()
+    x = x ^ lsr(x, 30)
+    x = mul(x, 0xBF58476D1CE4E5B9)
+    x = x ^ lsr(x, 27)
+    x = mul(x, 0x94D049BB133111EB)
+    x = x ^ lsr(x, 31)
+    # unsigned modulo of a value held in int64: fold the top bit back in
+    hi = lsr(x, 1)
+    r = ((hi % world) * 2 + (x & 1)) % world
+    return r
+
+
+def exchange_groups(keys, values: Sequence, dist=None):
+    """The exchange step of aggregate: every rank holds partial groups (keys [G], values[i] [G, cell...]);
+    afterwards every rank holds all partial rows of the keys it owns (owner = mix(key) mod world), ready
+    for one more keyed reduction.  The reference does this with Spark's hash shuffle between the UDAF's
+    partial and final aggregation (impl/DebugRowOps.scala:573-576).  Returns (keys, values) of the
+    received rows; row order is by source rank."""
+    import torch
+    import torch.distributed as td
+    dist = dist or td
+    world = dist.get_world_size()
+    owner = owner_of_key_torch(keys, world)
+    order = torch.argsort(owner, stable=True)
+    send_counts = torch.bincount(owner, minlength=world).to(torch.int64)
+    recv_counts = torch.empty_like(send_counts)
+    dist.all_to_all_single(recv_counts, send_counts)
+    send_splits = send_counts.tolist()
+    recv_splits = recv_counts.tolist()
+    n_recv = int(sum(recv_splits))
+
+    def a2a(t):
+        t = t[order].contiguous()
+        out = torch.empty((n_recv,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        dist.all_to_all_single(out, t, output_split_sizes=recv_splits, input_split_sizes=send_splits)
+        return out
+
+    return a2a(keys), [a2a(v) for v in values]

@@ -68,3 +68,41 @@ def test_reduce_blocks_exchange_two_ranks(tmp_path):
     world = 2
     mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
     assert sorted(os.listdir(tmp_path)) == ["ok0", "ok1"]
+
+
+def _agg_worker(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from tensorframes_b200.distributed import exchange_groups, owner_of_key, owner_of_key_torch, shard_rows
+
+        rng = np.random.default_rng(11)
+        n, n_keys = 6000, 97
+        table = rng.integers(-2**63, 2**63 - 1, n_keys, dtype=np.int64)
+        keys = table[rng.integers(0, n_keys, n)]
+        v = rng.integers(-50, 50, (n, 3)).astype(np.int64)         # integers: the merged sums must be exact
+        assert np.array_equal(owner_of_key_torch(torch.from_numpy(table), world).numpy(), owner_of_key(table, world))
+        lo, hi = shard_rows(n, rank, world)
+
+        def local_aggregate(k, x):      # stands in for tfs_session_aggregate on the rank's GPU
+            uk, inv = np.unique(k, return_inverse=True)
+            out = np.zeros((len(uk), x.shape[1]), dtype=x.dtype)
+            np.add.at(out, inv, x)
+            return uk, out
+
+        pk, pv = local_aggregate(keys[lo:hi], v[lo:hi])                                 # partial groups of this partition
+        rk, (rv,) = exchange_groups(torch.from_numpy(pk), [torch.from_numpy(pv)])      # key-owner exchange
+        fk, fv = local_aggregate(rk.numpy(), rv.numpy())                                # final merge on the owner
+        wk, wv = local_aggregate(keys, v)
+        mine = owner_of_key(wk, world) == rank
+        assert np.array_equal(fk, wk[mine]) and np.array_equal(fv, wv[mine])           # every key once, on its owner
+        open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+def test_aggregate_exchange_two_ranks(tmp_path):
+    world = 2
+    mp.spawn(_agg_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    assert sorted(os.listdir(tmp_path)) == ["ok0", "ok1"]
