@@ -157,7 +157,10 @@ def make_inputs(torch, workload, rows, seed, device):
         return {"y_input": y, "z_input": z}
     if workload == "c4":
         # keys: a table of 1e6 distinct random 64-bit values (not dense ids, so the hash is really exercised)
-        table = torch.randint(-2**62, 2**62, (KEYS_C4,), generator=g, device=device, dtype=torch.int64)
+        # (the key universe is shared by all ranks, as the partitions of one DataFrame would share it)
+        gk = torch.Generator(device=device)
+        gk.manual_seed(4)
+        table = torch.randint(-2**62, 2**62, (KEYS_C4,), generator=gk, device=device, dtype=torch.int64)
         table = torch.unique(table)
         idx = torch.randint(0, table.numel(), (rows,), generator=g, device=device, dtype=torch.int64)
         keys = table[idx]
