@@ -18,6 +18,8 @@
  *     (impl/datatypes.scala:344-347,407-410,468-471,526-529)  tfs_session_run feeds
  *   runner.fetch(n)...feed(n,t)...run()                   tfs_session_run
  *     (impl/DebugRowOps.scala:787-794, 900-917)
+ *   ... the same, once per row (mapRows)                  tfs_session_run_rows
+ *     (impl/DebugRowOps.scala:832-856)
  *   t.numElements(); t.writeTo(buffer)   (fetch)          tfs_session_resolve +
  *     (impl/datatypes.scala:365-370,438-443,488-493,546-551) fetch buffers of _run
  *   TensorFlowUDAF update/merge/evaluate                  tfs_session_aggregate
@@ -151,6 +153,19 @@ int tfs_session_resolve(tfs_session* s, int n_feeds, const tfs_tensor* feeds,
  *     after the host buffers have been written. */
 int tfs_session_run(tfs_session* s, int n_feeds, const tfs_tensor* feeds,
                     int n_fetches, const tfs_tensor* fetches);
+
+/* Row-wise execution = DebugRowOpsImpl.performMapRows (impl/DebugRowOps.scala:819-857), which runs one
+ * Session.run per row.  Here the graph still describes ONE row -- placeholders have the cell's shape
+ * (impl/DebugRowOps.scala:424-428) -- but a whole block of rows is evaluated in one call: every feed is
+ * [n_rows, cell...], every fetch comes back as [n_rows, fetch cell...] (a fetch that does not depend on
+ * any placeholder is replicated per row).  All rows of one call share a cell shape; a caller with
+ * variable-length cells (TFDataOps.convert(Row,...), impl/TFDataOps.scala:86-105) calls once per shape.
+ * Supported per-row graphs: element-wise ops between same-shaped cells, scalars and constants, and
+ * reductions over all axes of a cell; anything else is TFS_ERR_UNSUPPORTED (use the block form). */
+int tfs_session_resolve_rows(tfs_session* s, int n_feeds, const tfs_tensor* feeds,
+                             int n_fetches, tfs_tensor* fetches);
+int tfs_session_run_rows(tfs_session* s, int n_feeds, const tfs_tensor* feeds,
+                         int n_fetches, const tfs_tensor* fetches);
 
 /* Keyed block reduction = the whole TensorFlowUDAF (impl/DebugRowOps.scala:601-695)
  * for one block: rows with equal keys[i] are reduced together by the session's

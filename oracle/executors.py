@@ -11,6 +11,9 @@ Follows /root/reference/src/main/scala/org/tensorframes/ line by line where it m
   reduce_blocks      impl/DebugRowOps.scala:503-526 (+ reducePairBlock :741-750)
   TensorFlowUDAF     impl/DebugRowOps.scala:601-695 (buffer of 10 rows, compaction)
   aggregate          impl/DebugRowOps.scala:547-592
+  map_rows           impl/DebugRowOps.scala:396-477, 819-857 (one Session.run per row; a cell whose first
+                     dimension is unknown takes the row's own length, impl/TFDataOps.scala:86-105)
+  reduce_rows        impl/DebugRowOps.scala:479-501, 930-969 (pairwise fold X_1, X_2 -> X)
   analyze            ExperimentalOperations.scala:68-157
 
 Rows are python tuples, partitions are lists of rows, and the arithmetic is
@@ -293,3 +296,57 @@ def aggregate(partitions, cols: Sequence[Col], key_idx: Sequence[int], graph: by
                 final[key] = udaf.initialize()
             udaf.merge(final[key], buf)
     return [key + tuple(udaf.evaluate(buf)) for key, buf in final.items()]
+
+
+# ---- row-wise ------------------------------------------------------------------------------
+def _cell_array(value, dtype_code):
+    return np.asarray(value, dtype=DT[dtype_code])
+
+
+def map_rows(partitions, cols: Sequence[Col], graph: bytes, feed: Dict[str, str],
+             fetch_info: Dict[str, Tuple[int, Tuple[int, ...]]]):
+    """feed: placeholder name -> column name.  fetch_info: fetch -> (dtype code, cell shape).
+    Returns (column names, partitions of rows): TF columns (sorted by name) first, then the inputs."""
+    by_name = {c.name: i for i, c in enumerate(cols)}
+    for ph, col in feed.items():
+        if col not in by_name:
+            raise Exception(f"Graph input {ph} found, but no column to match it.")
+    fetches = sorted(fetch_info)
+    for f in fetches:
+        if f in by_name:
+            raise Exception(f"TF graph has an output node called '{f}', but this column already exists.")
+    out_parts = []
+    for rows in partitions:
+        out_rows = []
+        for r in rows:                                   # one Session.run per row
+            feeds = {ph: _cell_array(r[by_name[col]], cols[by_name[col]].dtype) for ph, col in feed.items()}
+            outs = evaluate(graph, feeds, fetches)
+            cells = []
+            for f, t in zip(fetches, outs):
+                n_rows, shape = infer_physical_shape(int(t.size), tuple(fetch_info[f][1]), 1)
+                arr = t.reshape(shape)
+                cells.append(arr.tolist() if shape else arr.item())
+            out_rows.append(tuple(cells) + tuple(r))
+        out_parts.append(out_rows)
+    return fetches + [c.name for c in cols], out_parts
+
+
+def perform_reduce_pairwise(rows, cols: Sequence[Col], graph: bytes) -> tuple:
+    assert rows, "Cannot provide empty input"
+    result = tuple(rows[0])
+    names = [c.name for c in cols]
+    for r in rows[1:]:
+        feeds = {}
+        for i, c in enumerate(cols):
+            feeds[c.name + "_1"] = _cell_array(result[i], c.dtype)
+            feeds[c.name + "_2"] = _cell_array(r[i], c.dtype)
+        outs = evaluate(graph, feeds, names)
+        result = tuple(o.tolist() if o.ndim else o.item() for o in outs)
+    return result
+
+
+def reduce_rows(partitions, cols: Sequence[Col], graph: bytes) -> tuple:
+    partials = [perform_reduce_pairwise(rows, cols, graph) for rows in partitions if rows]
+    if not partials:
+        raise ValueError("empty collection")
+    return perform_reduce_pairwise(partials, cols, graph)

@@ -61,6 +61,8 @@ SYMBOLS = {
     "tfs_session_launch_count": (C.c_int64, [C.c_void_p]),
     "tfs_session_resolve": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(Tensor), C.c_int, C.POINTER(Tensor)]),
     "tfs_session_run": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(Tensor), C.c_int, C.POINTER(Tensor)]),
+    "tfs_session_resolve_rows": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(Tensor), C.c_int, C.POINTER(Tensor)]),
+    "tfs_session_run_rows": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(Tensor), C.c_int, C.POINTER(Tensor)]),
     "tfs_session_aggregate": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.POINTER(Tensor), C.c_int,
                                         C.POINTER(Tensor), C.c_int64, C.c_void_p, C.POINTER(C.c_int64)]),
     "tfs_reduce_axis0_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_int64,
@@ -219,25 +221,28 @@ class Session:
                 _fill_tensor(arr[i], name, st.tf_code, a.shape, a.ctypes.data if a.size else None)
         return arr, keep
 
-    def resolve(self, feeds: Dict[str, object], fetches: Sequence[str]) -> List[Tuple[ScalarType, Tuple[int, ...]]]:
+    def resolve(self, feeds: Dict[str, object], fetches: Sequence[str], rows: bool = False) -> List[Tuple[ScalarType, Tuple[int, ...]]]:
         farr, keep = self._feed_array(feeds)
         oarr = (Tensor * max(1, len(fetches)))()
         for i, name in enumerate(fetches):
             _fill_tensor(oarr[i], name, 0, (), None)
-        _check(lib().tfs_session_resolve(self._h, len(feeds), farr, len(fetches), oarr))
+        fn = lib().tfs_session_resolve_rows if rows else lib().tfs_session_resolve
+        _check(fn(self._h, len(feeds), farr, len(fetches), oarr))
         return [(scalar_type_from_tf(oarr[i].dtype), tuple(oarr[i].dims[d] for d in range(oarr[i].rank)))
                 for i in range(len(fetches))]
 
-    def run(self, feeds: Dict[str, object], fetches: Sequence[str]) -> List[np.ndarray]:
-        """Host in, host out: feeds are numpy arrays (or DeviceArray), results are new numpy arrays."""
-        metas = self.resolve(feeds, fetches)
+    def run(self, feeds: Dict[str, object], fetches: Sequence[str], rows: bool = False) -> List[np.ndarray]:
+        """Host in, host out: feeds are numpy arrays (or DeviceArray), results are new numpy arrays.
+        rows=True maps a per-row graph over the leading dimension of the feeds (tfs_session_run_rows)."""
+        metas = self.resolve(feeds, fetches, rows)
         farr, keep = self._feed_array(feeds)
         outs = [np.empty(shape, dtype=st.np_dtype) for st, shape in metas]
         oarr = (Tensor * max(1, len(fetches)))()
         for i, name in enumerate(fetches):
             st, shape = metas[i]
             _fill_tensor(oarr[i], name, st.tf_code, shape, outs[i].ctypes.data if outs[i].size else None)
-        _check(lib().tfs_session_run(self._h, len(feeds), farr, len(fetches), oarr))
+        fn = lib().tfs_session_run_rows if rows else lib().tfs_session_run
+        _check(fn(self._h, len(feeds), farr, len(fetches), oarr))
         return outs
 
     def run_into(self, feeds: Dict[str, object], fetches: Dict[str, object]) -> None:

@@ -1,7 +1,6 @@
 """The python API of the reference, by name: tensorframes/core.py:10-11.
 
-    map_blocks, reduce_blocks, aggregate, analyze, print_schema, block, row
-    (map_rows / reduce_rows: the row-wise variants are SURVEY §8(f) "next" rows)
+    map_blocks, map_rows, reduce_blocks, reduce_rows, aggregate, analyze, print_schema, block, row
 
 The reference's functions take TensorFlow tensors built in the default python-TF
 graph and ship the serialized GraphDef to the JVM (core.py:38-72, 123-135).
@@ -94,9 +93,23 @@ def row(df: TensorFrame, col_name: str, tf_name: str = None):
     return dsl.row(df, col_name, tf_name)
 
 
-def map_rows(fetches, dframe, feed_dict=None):
-    raise NotImplementedError("map_rows is not part of the B200 block path yet (SURVEY.md §8(f) rank 2)")
+def map_rows(fetches, dframe: TensorFrame, feed_dict=None) -> TensorFrame:
+    """Transforms a DataFrame row by row, adding one column per fetch (core.py:175-211).  Placeholders
+    have the shape of one cell; `feed_dict` maps a placeholder name to a column name (default: the
+    column with the placeholder's name).  Rows may hold vectors of different lengths."""
+    fetches = _check_fetches(fetches)
+    for f in fetches:
+        f.freeze()
+    _unique_names(fetches)
+    return default_ops().mapRows(dframe, *fetches, feed_dict=feed_dict)
 
 
-def reduce_rows(fetches, dframe):
-    raise NotImplementedError("reduce_rows is not part of the B200 block path yet (SURVEY.md §8(f) rank 2)")
+def reduce_rows(fetches, dframe: TensorFrame):
+    """Pairwise reduction to a single row: fetch `z` reads placeholders `z_1` and `z_2` (core.py:138-173)."""
+    fetches = _check_fetches(fetches)
+    for f in fetches:
+        f.freeze()
+    _unique_names(fetches)
+    row = default_ops().reduceRows(dframe, *fetches)
+    out = [np.array(row[f.name]) if f.shape.numDims > 0 else row[f.name] for f in fetches]
+    return out[0] if len(out) == 1 else out

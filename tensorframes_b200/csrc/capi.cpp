@@ -145,7 +145,7 @@ int tfs_session_sync(tfs_session* s) {
 
 int64_t tfs_session_launch_count(const tfs_session* s) { return s ? s->s->launches() : 0; }
 
-int tfs_session_resolve(tfs_session* s, int n_feeds, const tfs_tensor* feeds, int n_fetches, tfs_tensor* fetches) {
+static int resolve_impl(tfs_session* s, int n_feeds, const tfs_tensor* feeds, int n_fetches, tfs_tensor* fetches, bool rows) {
   return guarded([&] {
     TFS_CHECK(s, TFS_ERR_INVALID, "null session");
     auto f = args_from(n_feeds, feeds, "feed");
@@ -155,7 +155,7 @@ int tfs_session_resolve(tfs_session* s, int n_feeds, const tfs_tensor* feeds, in
       TFS_CHECK(fetches[i].name != nullptr, TFS_ERR_INVALID, "fetch without a name");
       out[size_t(i)].name = fetches[i].name;
     }
-    s->s->resolve(f, out);
+    s->s->resolve(f, out, rows);
     for (int i = 0; i < n_fetches; ++i) {
       fetches[i].dtype = out[size_t(i)].dtype;
       fetches[i].rank = out[size_t(i)].shape.rank;
@@ -164,13 +164,29 @@ int tfs_session_resolve(tfs_session* s, int n_feeds, const tfs_tensor* feeds, in
   });
 }
 
-int tfs_session_run(tfs_session* s, int n_feeds, const tfs_tensor* feeds, int n_fetches, const tfs_tensor* fetches) {
+int tfs_session_resolve(tfs_session* s, int n_feeds, const tfs_tensor* feeds, int n_fetches, tfs_tensor* fetches) {
+  return resolve_impl(s, n_feeds, feeds, n_fetches, fetches, false);
+}
+
+int tfs_session_resolve_rows(tfs_session* s, int n_feeds, const tfs_tensor* feeds, int n_fetches, tfs_tensor* fetches) {
+  return resolve_impl(s, n_feeds, feeds, n_fetches, fetches, true);
+}
+
+static int run_impl(tfs_session* s, int n_feeds, const tfs_tensor* feeds, int n_fetches, const tfs_tensor* fetches, bool rows) {
   return guarded([&] {
     TFS_CHECK(s, TFS_ERR_INVALID, "null session");
     auto f = args_from(n_feeds, feeds, "feed");
     auto o = args_from(n_fetches, fetches, "fetch");
-    s->s->run(f, o);
+    s->s->run(f, o, rows);
   });
+}
+
+int tfs_session_run(tfs_session* s, int n_feeds, const tfs_tensor* feeds, int n_fetches, const tfs_tensor* fetches) {
+  return run_impl(s, n_feeds, feeds, n_fetches, fetches, false);
+}
+
+int tfs_session_run_rows(tfs_session* s, int n_feeds, const tfs_tensor* feeds, int n_fetches, const tfs_tensor* fetches) {
+  return run_impl(s, n_feeds, feeds, n_fetches, fetches, true);
 }
 
 int tfs_session_aggregate(tfs_session* s, int64_t n_rows, const int64_t* keys, int n_feeds, const tfs_tensor* feeds,

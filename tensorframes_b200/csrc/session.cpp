@@ -52,6 +52,12 @@ struct Session::Plan {
   std::vector<Step> steps;            // execution order
   std::vector<int> step_of;           // by node index, -1 = not computed by a step
   std::vector<char> materialize;      // by node index: output needs a device buffer
+  // row mode (mapRows): the graph describes ONE row; tensors that depend on a placeholder carry an extra
+  // leading dimension of n_batch rows at execution time
+  bool rows = false;
+  int64_t n_batch = 0;
+  std::vector<char> batched;          // by node index
+  std::vector<Shape> cshape;          // by node index: per-row (cell) shape
 };
 
 Session::Session(const Graph& g, int device) : g_(g) { dev_.device = device; }
@@ -141,9 +147,28 @@ void* Session::const_device(int node) {
 // ---------------------------------------------------------------------------
 // Planning
 // ---------------------------------------------------------------------------
+namespace {
+Shape drop_lead(const Shape& s) {
+  Shape r;
+  r.rank = s.rank - 1;
+  for (int i = 0; i < r.rank; ++i) r.d[i] = s.d[i + 1];
+  return r;
+}
+Shape with_lead(int64_t n, const Shape& s) {
+  Shape r;
+  r.rank = s.rank + 1;
+  r.d[0] = n;
+  for (int i = 0; i < s.rank; ++i) r.d[i + 1] = s.d[i];
+  return r;
+}
+}  // namespace
+
 void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<std::string>& fetch_names,
-                         Plan& plan) {
+                         Plan& plan, bool rows) {
   const size_t N = g_.nodes.size();
+  plan.rows = rows;
+  plan.batched.assign(N, 0);
+  plan.cshape.assign(N, Shape());
   plan.shape.assign(N, Shape());
   plan.feed_of.assign(N, -1);
   plan.step_of.assign(N, -1);
@@ -160,8 +185,15 @@ void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<
     TFS_CHECK(feeds[i].dtype == n.dtype, TFS_ERR_INVALID,
               "The type of node '" + n.name + "' (" + dtype_name(n.dtype) +
                   ") is not compatible with the data type of the feed (" + dtype_name(feeds[i].dtype) + ")");
-    const Shape& fs = feeds[i].shape;
-    TFS_CHECK(fs.fully_known(), TFS_ERR_INVALID, "feed '" + n.name + "' has unknown dimensions: " + fs.str());
+    TFS_CHECK(feeds[i].shape.fully_known(), TFS_ERR_INVALID,
+              "feed '" + n.name + "' has unknown dimensions: " + feeds[i].shape.str());
+    if (rows) {
+      TFS_CHECK(feeds[i].shape.rank >= 1, TFS_ERR_INVALID, "row mode: feed '" + n.name + "' needs a leading row dimension");
+      if (i == 0) plan.n_batch = feeds[i].shape.d[0];
+      TFS_CHECK(feeds[i].shape.d[0] == plan.n_batch, TFS_ERR_INVALID, "row mode: feeds differ in their number of rows");
+    }
+    // in row mode the placeholder describes one cell (reference: impl/DebugRowOps.scala:424-428)
+    const Shape fs = rows ? drop_lead(feeds[i].shape) : feeds[i].shape;
     // Shape.checkMorePreciseThan (reference: Shape.scala:54-59)
     if (n.sshape.known_rank()) {
       bool ok = n.sshape.rank == fs.rank;
@@ -199,20 +231,31 @@ void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<
     }
   }
 
-  // concrete shapes
+  // concrete shapes (row mode: per-row shapes first, then the row dimension in front of everything that
+  // depends on a placeholder)
   for (int idx : plan.needed) {
     const Node& n = g_.nodes[size_t(idx)];
     if (n.cls == OpClass::Placeholder) {
       int f = plan.feed_of[size_t(idx)];
       TFS_CHECK(f >= 0, TFS_ERR_INVALID, "placeholder '" + n.name + "' is needed by the fetches but was not fed");
-      plan.shape[size_t(idx)] = feeds[size_t(f)].shape;
+      plan.cshape[size_t(idx)] = rows ? drop_lead(feeds[size_t(f)].shape) : feeds[size_t(f)].shape;
+      plan.batched[size_t(idx)] = rows ? 1 : 0;
     } else {
       std::vector<Shape> in;
-      for (int k : n.in) in.push_back(plan.shape[size_t(k)]);
-      Shape s = infer_shape(g_, n, in);
-      TFS_CHECK(s.fully_known(), TFS_ERR_INVALID, "could not resolve the shape of node '" + n.name + "': " + s.str());
-      plan.shape[size_t(idx)] = s;
+      for (int k : n.in) {
+        in.push_back(plan.cshape[size_t(k)]);
+        if (plan.batched[size_t(k)]) plan.batched[size_t(idx)] = 1;
+      }
+      Shape sh = infer_shape(g_, n, in);
+      TFS_CHECK(sh.fully_known(), TFS_ERR_INVALID, "could not resolve the shape of node '" + n.name + "': " + sh.str());
+      plan.cshape[size_t(idx)] = sh;
+      if (rows && plan.batched[size_t(idx)])
+        TFS_CHECK(n.cls != OpClass::MatMul, TFS_ERR_UNSUPPORTED,
+                  "node '" + n.name + "' (MatMul) is not supported in row mode; use map_blocks");
     }
+    plan.shape[size_t(idx)] = plan.batched[size_t(idx)] ? with_lead(plan.n_batch, plan.cshape[size_t(idx)])
+                                                        : plan.cshape[size_t(idx)];
+    TFS_CHECK(plan.shape[size_t(idx)].rank <= TFS_MAX_RANK, TFS_ERR_UNSUPPORTED, "tensor rank above the supported maximum");
   }
 
   // levels: number of reduce/matmul nodes on the longest path below a node
@@ -274,7 +317,10 @@ void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<
       Step s;
       s.nodes = {idx};
       const Shape& xs = plan.shape[size_t(n.in[0])];
-      std::vector<int> axes = normalize_axes(n, xs.rank);
+      const bool in_batched = plan.batched[size_t(n.in[0])] != 0;
+      std::vector<int> axes = normalize_axes(n, plan.cshape[size_t(n.in[0])].rank);
+      if (in_batched)
+        for (int& a : axes) a += 1;     // the row dimension sits in front of the cell
       const int k = int(axes.size());
       bool leading = true, trailing = true;
       for (int i = 0; i < k; ++i) {
@@ -344,15 +390,17 @@ void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<
     if (plan.step_of[size_t(idx)] >= 0) plan.step_of[size_t(idx)] = remap[size_t(plan.step_of[size_t(idx)])];
 }
 
-void Session::resolve(const std::vector<TensorArg>& feeds, std::vector<TensorArg>& fetches) {
+void Session::resolve(const std::vector<TensorArg>& feeds, std::vector<TensorArg>& fetches, bool rows) {
   Plan plan;
   std::vector<std::string> names;
   for (auto& f : fetches) names.push_back(f.name);
-  build_plan(feeds, names, plan);
+  build_plan(feeds, names, plan, rows);
   for (size_t i = 0; i < fetches.size(); ++i) {
     int idx = plan.fetch_nodes[i];
     fetches[i].dtype = g_.nodes[size_t(idx)].dtype;
-    fetches[i].shape = plan.shape[size_t(idx)];
+    // row mode: one cell per row for every fetch, also for fetches that do not depend on the row
+    fetches[i].shape = (rows && !plan.batched[size_t(idx)]) ? with_lead(plan.n_batch, plan.cshape[size_t(idx)])
+                                                            : plan.shape[size_t(idx)];
   }
 }
 
@@ -644,21 +692,28 @@ bool make_chain(const EltProgram& prog, ChainProgram& ch) {
 // ---------------------------------------------------------------------------
 // Execution
 // ---------------------------------------------------------------------------
-void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorArg>& fetches) {
+void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorArg>& fetches, bool rows) {
   Plan plan;
   std::vector<std::string> names;
   for (auto& f : fetches) names.push_back(f.name);
-  build_plan(feeds, names, plan);
+  build_plan(feeds, names, plan, rows);
+  // row mode: a fetch that does not depend on any placeholder is replicated once per row
+  std::vector<char> bcast(fetches.size(), 0);
+  auto out_numel = [&](size_t i) {
+    const int idx = plan.fetch_nodes[i];
+    return plan.shape[size_t(idx)].numel() * (bcast[i] ? plan.n_batch : 1);
+  };
+  for (size_t i = 0; i < fetches.size(); ++i) bcast[i] = rows && !plan.batched[size_t(plan.fetch_nodes[i])];
   for (size_t i = 0; i < fetches.size(); ++i) {
     int idx = plan.fetch_nodes[i];
     const Node& n = g_.nodes[size_t(idx)];
-    TFS_CHECK(fetches[i].data != nullptr || plan.shape[size_t(idx)].numel() == 0, TFS_ERR_INVALID,
+    TFS_CHECK(fetches[i].data != nullptr || out_numel(i) == 0, TFS_ERR_INVALID,
               "fetch '" + n.name + "' has no output buffer");
     TFS_CHECK(fetches[i].dtype == 0 || fetches[i].dtype == n.dtype, TFS_ERR_INVALID,
               "fetch '" + n.name + "' produces " + dtype_name(n.dtype) + " but the output buffer is declared " +
                   dtype_name(fetches[i].dtype));
     if (fetches[i].shape.known_rank())
-      TFS_CHECK(fetches[i].shape.fully_known() && fetches[i].shape.numel() == plan.shape[size_t(idx)].numel(),
+      TFS_CHECK(fetches[i].shape.fully_known() && fetches[i].shape.numel() == out_numel(i),
                 TFS_ERR_INVALID,
                 "fetch '" + n.name + "' has shape " + plan.shape[size_t(idx)].str() + " but the output buffer is declared " +
                     fetches[i].shape.str());
@@ -697,10 +752,13 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
       // uploaded lazily below
     } else if (plan.materialize[size_t(idx)]) {
       for (size_t i = 0; i < fetches.size() && !dev_ptr[size_t(idx)]; ++i)
-        if (plan.fetch_nodes[i] == idx && fetch_dev[i]) dev_ptr[size_t(idx)] = fetches[i].data;
+        if (plan.fetch_nodes[i] == idx && fetch_dev[i] && !bcast[i]) dev_ptr[size_t(idx)] = fetches[i].data;
       if (!dev_ptr[size_t(idx)]) { ws_off[size_t(idx)] = ws_bytes; ws_bytes += align_up(std::max<size_t>(nbytes(idx), 16)); }
     }
   }
+  std::vector<size_t> bc_off(fetches.size(), SIZE_MAX);
+  for (size_t i = 0; i < fetches.size(); ++i)
+    if (bcast[i] && !fetch_dev[i]) { bc_off[i] = ws_bytes; ws_bytes += align_up(std::max<size_t>(nbytes(plan.fetch_nodes[i]) * size_t(plan.n_batch), 16)); }
   for (const Step& s : plan.steps) {
     if (s.kind == Step::REDUCE_AXIS0) {
       needs_reduce_scratch = true;
@@ -804,6 +862,28 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
     if (bytes == 0) continue;
     void* src = dev_ptr[size_t(idx)];
     TFS_CHECK(src != nullptr, TFS_ERR_INVALID, "internal: fetch '" + g_.nodes[size_t(idx)].name + "' was not produced");
+    if (bcast[i]) {
+      if (plan.n_batch == 0) continue;
+      // replicate the row-independent value once per row: out[flat] = value[flat % numel]
+      void* dst = fetch_dev[i] ? fetches[i].data : static_cast<void*>(ws_ + bc_off[i]);
+      EltProgram prog{};
+      prog.err = err_flag_;
+      const int di = dtype_index(g_.nodes[size_t(idx)].dtype);
+      prog.n_bufs = 2;
+      prog.bufs[0] = BufRef{src, plan.shape[size_t(idx)].numel(), di, 0};
+      prog.bufs[1] = BufRef{dst, 0, di, 0};
+      prog.n_instr = 2;
+      prog.ins[0] = Instr{};
+      prog.ins[0].code = C_LOAD_PER;
+      prog.ins[0].arg = 0;
+      prog.ins[1] = Instr{};
+      prog.ins[1].code = C_STORE;
+      prog.ins[1].arg = 1;
+      launches_ += launch_eltwise(prog, out_numel(i), dtype_size(g_.nodes[size_t(idx)].dtype) == 8, dev_, stream_);
+      if (!fetch_dev[i])
+        TFS_CUDA(cudaMemcpyAsync(fetches[i].data, dst, bytes * size_t(plan.n_batch), cudaMemcpyDeviceToHost, stream_));
+      continue;
+    }
     if (fetch_dev[i]) {
       if (src != fetches[i].data)
         TFS_CUDA(cudaMemcpyAsync(fetches[i].data, src, bytes, cudaMemcpyDeviceToDevice, stream_));

@@ -33,8 +33,10 @@ class Session {
   int64_t launches() const { return launches_; }
 
   // Fills fetches[i].dtype / .shape for the given feed shapes. No CUDA work.
-  void resolve(const std::vector<TensorArg>& feeds, std::vector<TensorArg>& fetches);
-  void run(const std::vector<TensorArg>& feeds, const std::vector<TensorArg>& fetches);
+  // rows = true: the graph describes ONE row (placeholders are cell-shaped) and is mapped over the
+  // leading dimension of the feeds; every fetch comes back with one cell per row (mapRows).
+  void resolve(const std::vector<TensorArg>& feeds, std::vector<TensorArg>& fetches, bool rows = false);
+  void run(const std::vector<TensorArg>& feeds, const std::vector<TensorArg>& fetches, bool rows = false);
   void aggregate(int64_t n_rows, const int64_t* keys, const std::vector<TensorArg>& feeds,
                  const std::vector<TensorArg>& fetches, int64_t max_groups, int64_t* out_keys,
                  int64_t* n_groups);
@@ -42,7 +44,8 @@ class Session {
  private:
   struct Plan;
   void ensure_device();
-  void build_plan(const std::vector<TensorArg>& feeds, const std::vector<std::string>& fetch_names, Plan& plan);
+  void build_plan(const std::vector<TensorArg>& feeds, const std::vector<std::string>& fetch_names, Plan& plan,
+                  bool rows = false);
   void* const_device(int node);
   void reserve_workspace(size_t bytes);
   void check_device_error();

@@ -387,6 +387,14 @@ class TensorFrame:
         from . import ops
         return ops.default_ops().reduceBlocks(self, *fetches)
 
+    def mapRows(self, *fetches, feed_dict=None):
+        from . import ops
+        return ops.default_ops().mapRows(self, *fetches, feed_dict=feed_dict)
+
+    def reduceRows(self, *fetches):
+        from . import ops
+        return ops.default_ops().reduceRows(self, *fetches)
+
 
 class GroupedData:
     def __init__(self, df: TensorFrame, keys: List[str]):

@@ -375,6 +375,167 @@ class B200Ops:
         schema = StructType(tuple(df.schema[k] for k in key_names) + schemas.output.fields)
         return TensorFrame(schema, [part])
 
+    # ---- mapRows (impl/DebugRowOps.scala:396-477, 819-857) ------------------------------
+    def mapRows(self, df: TensorFrame, *fetches, feed_dict: Optional[Dict[str, str]] = None) -> TensorFrame:
+        """Row-wise map: placeholders have the shape of ONE cell and are bound to columns through
+        `feed_dict` (placeholder -> column; default: the column of the same name).  Rows whose cells differ
+        in length (first cell dimension unknown) are allowed.  The device evaluates all rows of a partition
+        that share a cell shape in one call (tfs_session_run_rows) instead of one Session.run per row."""
+        g, h = self._graph_args(fetches)
+        feed_dict = dict(feed_dict or {})
+        with _native.Graph(g) as graph:
+            summary = {s.name: s for s in analyze_graph(graph, h)}
+            inputs = {k: v for k, v in summary.items() if v.isInput}
+            outputs = {k: v for k, v in summary.items() if v.isOutput}
+            fields_by_name = {f.name: f for f in df.schema.fields}
+            cols = ", ".join(df.schema.fieldNames)
+            hint_inputs = dict(h.inputs)
+            hint_inputs.update(feed_dict)
+            binding: Dict[str, str] = {}
+            for inp in inputs.values():
+                fname = hint_inputs.get(inp.name)
+                if fname is None:
+                    raise Exception(f"The graph placeholder {inp.name} was not given a corresponding dataframe field "
+                                    f"name as input:hints: {hint_inputs}")
+                f = fields_by_name.get(fname)
+                if f is None:
+                    raise Exception(f"Graph input {inp.name} found, but no column to match it. Dataframe columns: {cols}")
+                stf = ColumnInformation.of(f).stf
+                if stf is None:
+                    raise Exception(f"Data column {f.name} has not been analyzed yet, cannot run TF on this dataframe")
+                if stf.dataType != inp.scalarType:
+                    raise Exception(f"The type of node '{inp.name}' ({stf.dataType}) is not compatible with the data type "
+                                    f"of the column ({inp.scalarType})")
+                cell = stf.shape.tail
+                if not cell.checkMorePreciseThan(inp.shape):
+                    raise Exception(f"The data column '{f.name}' has shape {stf.shape} (not compatible) with shape"
+                                    f" {inp.shape} requested by the TF graph")
+                binding[inp.name] = fname
+            out_fields = []
+            for out in sorted(outputs.values(), key=lambda o: o.name):
+                if out.name in fields_by_name:
+                    raise Exception(f"TF graph has an output node called '{out.name}', but this column already exists. "
+                                    f"Input columns: {cols}")
+                out_fields.append(ColumnInformation.structField(out.name, out.scalarType, out.shape.prepend(Unknown)))
+            tf_schema = StructType(tuple(out_fields))
+            out_schema = StructType(tf_schema.fields + df.schema.fields)
+            fetch_names = [f.name for f in tf_schema.fields]
+            parts = []
+            with _native.Session(graph, self.device) as session:
+                for part in df.partitions:
+                    n = df._part_len(part)
+                    if n == 0:
+                        continue
+                    # group the rows by the shapes of their fed cells (one group when the columns are dense)
+                    groups: Dict[tuple, List[int]] = {}
+                    dense = all(isinstance(part[c], np.ndarray) for c in binding.values())
+                    if dense or not binding:
+                        groups[()] = list(range(n))
+                    else:
+                        for i in range(n):
+                            key = tuple(np.shape(part[c][i]) for c in binding.values())
+                            groups.setdefault(key, []).append(i)
+                    per_row: Dict[str, List[object]] = {name: [None] * n for name in fetch_names}
+                    for idxs in groups.values():
+                        feeds = {}
+                        for ph, c in binding.items():
+                            col = part[c]
+                            st = ColumnInformation.of(df.schema[c]).stf.dataType
+                            feeds[ph] = (col if isinstance(col, np.ndarray) and len(idxs) == n
+                                         else np.asarray([col[i] for i in idxs], dtype=st.np_dtype))
+                        if feeds:
+                            outs = session.run(feeds, fetch_names, rows=True)
+                        else:   # no placeholder at all: every row gets the graph's constant result
+                            outs = [np.broadcast_to(o, (len(idxs),) + o.shape) for o in session.run({}, fetch_names)]
+                        for name, arr in zip(fetch_names, outs):
+                            for j, i in enumerate(idxs):
+                                per_row[name][i] = arr[j]
+                    new_part: Dict[str, object] = {}
+                    for f in tf_schema.fields:
+                        cells = per_row[f.name]
+                        shapes = {np.shape(c) for c in cells}
+                        new_part[f.name] = np.stack(cells) if len(shapes) == 1 else [np.asarray(c).tolist() for c in cells]
+                    for name in df.schema.fieldNames:
+                        new_part[name] = part[name]
+                    parts.append(new_part)
+        return TensorFrame(out_schema, parts)
+
+    # ---- reduceRows (impl/DebugRowOps.scala:172-262, 479-501, 930-969) ----------------------
+    def reduceRows(self, df: TensorFrame, *fetches) -> Row:
+        """Pairwise reduction: for every column X the graph reads placeholders X_1 and X_2 (one cell each)
+        and produces X.  The reference folds the rows one by one through a session; here each round
+        combines the first half of the remaining rows with the second half in one row-mode call, so n rows
+        take about log2(n) device calls (the order of combination is unspecified in the reference too)."""
+        g, h = self._graph_args(fetches)
+        with _native.Graph(g) as graph:
+            summary = {s.name: s for s in analyze_graph(graph, h)}
+            fields_by_name = {f.name: f for f in df.schema.fields}
+            field_names = ", ".join(sorted(fields_by_name))
+            outputs = {k: v for k, v in summary.items() if v.isOutput}
+            output_names = ", ".join(sorted(outputs))
+            extra = sorted(set(outputs) - set(fields_by_name))
+            if extra:
+                raise Exception(f"Some extra outputs were found in the reducer: {', '.join(extra)}. "
+                                f"Dataframe columns: {field_names}; Outputs: {output_names}")
+            missing = sorted(set(fields_by_name) - set(outputs))
+            if missing:
+                raise Exception(f"Some outputs are missing in the reducer: {', '.join(missing)}. "
+                                f"Dataframe columns: {field_names}; Outputs: {output_names}")
+            inputs = {k: v for k, v in summary.items() if v.isInput}
+            expected = {n + s for n in fields_by_name for s in ("_1", "_2")}
+            extra = sorted(set(inputs) - expected)
+            if extra:
+                raise Exception(f"Extra graph inputs have been found: {', '.join(extra)}. Dataframe columns: {field_names}")
+            missing = sorted(expected - set(inputs))
+            if missing:
+                raise Exception(f"Some inputs are missing in th graph: {', '.join(missing)}. Dataframe columns: {field_names}")
+            names = df.schema.fieldNames
+            for f in df.schema.fields:
+                stf = ColumnInformation.of(f).stf
+                if stf is None:
+                    raise Exception(f"Data column '{f.name}' has not been analyzed yet, cannot run TF on this dataframe")
+                out = summary[f.name]
+                if stf.dataType != out.scalarType:
+                    raise Exception(f"Output '{f.name}' has type {out.scalarType} but the column type is {stf.dataType}")
+                cell = stf.shape.tail
+                if not out.shape.checkMorePreciseThan(cell):
+                    raise Exception(f"Output '{f.name}' has shape {out.shape}, not compatible with the shapesof field "
+                                    f"elements {cell}")
+                for suffix in ("_1", "_2"):
+                    inp = summary[f.name + suffix]
+                    if not cell.checkMorePreciseThan(inp.shape):
+                        raise Exception(f"The data column '{f.name}' has shape {stf.shape} (not compatible) with shape"
+                                        f" {inp.shape} requested by the TF graph")
+                    if stf.dataType != inp.scalarType:
+                        raise Exception(f"The type of node '{inp.name}' ({stf.dataType}) is not compatible with the data"
+                                        f" type of the column ({inp.scalarType})")
+            blocks: Dict[str, List[np.ndarray]] = {n: [] for n in names}
+            for part in df.partitions:
+                n = df._part_len(part)
+                if n == 0:
+                    continue
+                for name in names:
+                    col = part[name]
+                    if not isinstance(col, np.ndarray):
+                        raise Exception(f"Column '{name}' holds ragged cells and cannot be reduced pairwise")
+                    blocks[name].append(col)
+            if not blocks[names[0]]:
+                raise ValueError("empty collection")
+            cur = {name: np.concatenate(blocks[name]) for name in names}
+            with _native.Session(graph, self.device) as session:
+                n = cur[names[0]].shape[0]
+                while n > 1:
+                    half = n // 2
+                    feeds = {}
+                    for name in names:
+                        feeds[name + "_1"] = np.ascontiguousarray(cur[name][:half])
+                        feeds[name + "_2"] = np.ascontiguousarray(cur[name][half:2 * half])
+                    outs = session.run(feeds, names, rows=True)
+                    for name, o in zip(names, outs):
+                        cur[name] = np.concatenate([o, cur[name][2 * half:]]) if n % 2 else o
+                    n = half + (n % 2)
+        return Row.of(names, [_to_python(cur[name][0]) for name in names])
+
     # ---- analysis --------------------------------------------------------------------
     def analyze(self, df: TensorFrame) -> TensorFrame:
         return _analyze(df)

@@ -55,8 +55,10 @@ def build_fetches(case, df):
         env[name] = dsl.placeholder(TYPES[dt], *shape).named(name)
     for col, tf_name in spec.get("block_placeholders", []):
         env[tf_name] = tfs.block(df, col, tf_name=tf_name)
+    for col, tf_name in spec.get("row_placeholders", []):
+        env[tf_name] = tfs.row(df, col, tf_name=tf_name)
     for name, dt, value in spec.get("consts", []):
-        fetch = name in spec["fetches"]
+        fetch = name in spec["fetches"] or name in spec.get("keep_consts", [])
         c = dsl.constant(np.asarray(value, dtype=TYPES[dt].np_dtype))
         env[name] = c.named(name) if fetch else c
     for op in spec.get("ops", []):

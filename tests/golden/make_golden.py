@@ -191,6 +191,94 @@ cases += [
          select=["key", "x"], expected=[["0", 2.0], ["1", 4.0]]),
 ]
 
+# ---------------- mapRows / reduceRows ----------------
+cases += [
+    dict(id="rows_identity", cite="T/BasicOperationsSuite.scala:78-84", kind="map_rows",
+         columns=[["in", "double"]], rows=[[1.0], [2.0]],
+         graph=dict(placeholders=[["in", "double", []]], ops=[["out", "identity", "in"]], fetches=["out"]),
+         select=["in", "out"], expected=[[1.0, 1.0], [2.0, 2.0]]),
+    dict(id="rows_simple_add", cite="T/BasicOperationsSuite.scala:86-98", kind="map_rows",
+         columns=[["a", "double"], ["b", "double"]], rows=[[1.0, 1.1], [2.0, 2.2]],
+         graph=dict(placeholders=[["a", "double", []], ["b", "double", []]], ops=[["out", "add", "a", "b"]], fetches=["out"]),
+         select=["a", "b", "out"], expected=[[1.0, 1.1, 2.1], [2.0, 2.2, 4.2]]),
+    dict(id="rows_identity_known_dim", cite="T/BasicOperationsSuite.scala:100-112", kind="map_rows", analyze=True,
+         columns=[["in", "double"]], rows=[[[1.0]], [[2.0]]],
+         graph=dict(placeholders=[["in", "double", [1]]], ops=[["out", "identity", "in"]], fetches=["out"]),
+         select=["in", "out"], expected=[[[1.0], [1.0]], [[2.0], [2.0]]]),
+    dict(id="rows_identity_unknown_dim", cite="T/BasicOperationsSuite.scala:114-126", kind="map_rows", analyze=True,
+         columns=[["in", "double"]], rows=[[[1.0]], [[2.0]]],
+         graph=dict(placeholders=[["in", "double", [-1]]], ops=[["out", "identity", "in"]], fetches=["out"]),
+         select=["in", "out"], expected=[[[1.0], [1.0]], [[2.0], [2.0]]]),
+    dict(id="rows_identity_variable_sizes", cite="T/BasicOperationsSuite.scala:128-140", kind="map_rows", analyze=True,
+         columns=[["in", "double"]], rows=[[[1.0]], [[2.0, 2.1]]],
+         graph=dict(placeholders=[["in", "double", [-1]]], ops=[["out", "identity", "in"]], fetches=["out"]),
+         select=["in", "out"], expected=[[[1.0], [1.0]], [[2.0, 2.1], [2.0, 2.1]]]),
+    dict(id="rows_add_1dim", cite="T/BasicOperationsSuite.scala:142-155", kind="map_rows", analyze=True,
+         columns=[["a", "double"], ["b", "double"]], rows=[[[1.0], [1.1]], [[2.0], [2.2]]],
+         graph=dict(placeholders=[["a", "double", [1]], ["b", "double", [1]]], ops=[["out", "add", "a", "b"]], fetches=["out"]),
+         select=["a", "b", "out"], expected=[[[1.0], [1.1], [2.1]], [[2.0], [2.2], [4.2]]]),
+    dict(id="rows_add_unknown_rows", cite="T/BasicOperationsSuite.scala:157-172", kind="map_rows", analyze=True,
+         columns=[["a", "double"], ["b", "double"]], rows=[[[1.0, 1.0], [1.1, 1.1]], [[2.0], [2.2]]],
+         graph=dict(placeholders=[["a", "double", [-1]], ["b", "double", [-1]]], ops=[["out", "add", "a", "b"]], fetches=["out"]),
+         select=["a", "b", "out"], expected=[[[1.0, 1.0], [1.1, 1.1], [2.1, 2.1]], [[2.0], [2.2], [4.2]]]),
+    dict(id="rows_const_reduce", cite="T/DSLOperationsSuite.scala:12-19", kind="map_rows",
+         columns=[["a", "int"]], rows=[[1]],
+         graph=dict(consts=[["x", "double", [1.0, 1.0]]], ops=[["out", "reduce_sum", "x", [0]]], fetches=["out"], keep_consts=["x"]),
+         select=["a", "out"], expected=[[1, 2.0]]),
+    dict(id="rows_constant", cite="T/DSLOperationsSuite.scala:21-26", kind="map_rows",
+         columns=[["a", "int"]], rows=[[1]],
+         graph=dict(consts=[["x", "double", 1.0]], fetches=["x"]),
+         select=["a", "x"], expected=[[1, 1.0]]),
+    dict(id="rows_row_extraction", cite="T/DSLOperationsSuite.scala:52-60", kind="map_rows",
+         columns=[["a", "double"]], rows=[[1.0], [2.0]],
+         graph=dict(row_placeholders=[["a", "a"]], consts=[["c", "double", 2.0]], ops=[["b", "add", "a", "c"]], fetches=["b"]),
+         select=["a", "b"], expected=[[1.0, 3.0], [2.0, 4.0]]),
+    dict(id="rows_2tensor_constant_output", cite="T/BasicOperationsSuite.scala:239-246", kind="map_rows", analyze=True,
+         columns=[["x", "int"]], rows=[[1]],
+         graph=dict(consts=[["y", "double", [[1.0]]]], fetches=["y"]),
+         select=["y"], expected=[[[[1.0]]]]),
+    dict(id="py_map_rows_feed_dict", cite="P/core_test.py:64-75", kind="map_rows", feed_dict={"x": "y"},
+         columns=[["y", "double"]], rows=[[float(i)] for i in range(5)],
+         graph=dict(placeholders=[["x", "double", []]], consts=[["c", "double", 3.0]], ops=[["z", "add", "x", "c"]], fetches=["z"]),
+         select=["z", "y"], expected=[[float(i) + 3.0, float(i)] for i in range(5)]),
+    dict(id="reduce_rows_sum_double", cite="T/BasicOperationsSuite.scala:60-67", kind="reduce_rows",
+         columns=[["x", "double"]], rows=[[1.0], [2.0]],
+         graph=dict(placeholders=[["x_1", "double", []], ["x_2", "double", []]], ops=[["x", "add", "x_1", "x_2"]], fetches=["x"]),
+         expected=[3.0]),
+    dict(id="reduce_rows_sum_int", cite="T/BasicOperationsSuite.scala:69-76", kind="reduce_rows",
+         columns=[["x", "int"]], rows=[[1], [2], [3], [4]],
+         graph=dict(placeholders=[["x_1", "int", []], ["x_2", "int", []]], ops=[["x", "add", "x_1", "x_2"]], fetches=["x"]),
+         expected=[10]),
+    dict(id="py_reduce_rows", cite="P/core_test.py:78-90", kind="reduce_rows",
+         columns=[["x", "double"]], rows=[[float(i)] for i in range(5)],
+         graph=dict(placeholders=[["x_1", "double", []], ["x_2", "double", []]], ops=[["x", "add", "x_1", "x_2"]], fetches=["x"]),
+         expected=[10.0]),
+]
+for dt in DTYPES:
+    cases += [
+        dict(id=f"type_rows_identity_known_dim_{dt}", cite="T/type_suites.scala:29-40", kind="map_rows", analyze=True,
+             columns=[["in", dt]], rows=u(dt, [[[1.0]], [[20.0]]]),
+             graph=dict(placeholders=[["in", dt, [1]]], ops=[["out", "identity", "in"]], fetches=["out"]),
+             select=["in", "out"], expected=u(dt, [[[1.0], [1.0]], [[20.0], [20.0]]])),
+        dict(id=f"type_rows_variable_sizes_{dt}", cite="T/type_suites.scala:55-66", kind="map_rows", analyze=True,
+             columns=[["in", dt]], rows=[[u(dt, [1.0])], [u(dt, [20.0, 21.0])]],
+             graph=dict(placeholders=[["in", dt, [-1]]], ops=[["out", "identity", "in"]], fetches=["out"]),
+             select=["in", "out"], expected=[[u(dt, [1.0]), u(dt, [1.0])], [u(dt, [20.0, 21.0]), u(dt, [20.0, 21.0])]]),
+        dict(id=f"type_rows_add_one_row_{dt}", cite="T/type_suites.scala:114-124", kind="map_rows",
+             columns=[["a", dt], ["b", dt]], rows=u(dt, [[10.0, 11.0], [20.0, 22.0]]),
+             graph=dict(placeholders=[["a", dt, []], ["b", dt, []]], ops=[["out", "add", "a", "b"]], fetches=["out"]),
+             select=["a", "b", "out"], expected=u(dt, [[10.0, 11.0, 21.0], [20.0, 22.0, 42.0]])),
+        dict(id=f"type_rows_add_unknown_rows_{dt}", cite="T/type_suites.scala:142-156", kind="map_rows", analyze=True,
+             columns=[["a", dt], ["b", dt]], rows=[[u(dt, [10.0, 10.0]), u(dt, [11.0, 11.0])], [u(dt, [20.0]), u(dt, [22.0])]],
+             graph=dict(placeholders=[["a", dt, [-1]], ["b", dt, [-1]]], ops=[["out", "add", "a", "b"]], fetches=["out"]),
+             select=["a", "b", "out"],
+             expected=[[u(dt, [10.0, 10.0]), u(dt, [11.0, 11.0]), u(dt, [21.0, 21.0])], [u(dt, [20.0]), u(dt, [22.0]), u(dt, [42.0])]]),
+        dict(id=f"type_reduce_rows_sum_{dt}", cite="T/type_suites.scala:98-105", kind="reduce_rows",
+             columns=[["x", dt]], rows=u(dt, [[1.0], [2.0]]),
+             graph=dict(placeholders=[["x_1", dt, []], ["x_2", dt, []]], ops=[["x", "add", "x_1", "x_2"]], fetches=["x"]),
+             expected=u(dt, [3.0])),
+    ]
+
 # ---------------- analyze / schema ----------------
 analyze_cases = [
     dict(id="explain_double", cite="T/ExtraOperationsSuite.scala:15-23", analyze=False,

@@ -31,6 +31,18 @@ def test_executor_case(case):
             idx = [names.index(n) for n in case["select"]]
             rows = [[r[i] for i in idx] for r in rows]
         assert _golden.normalize(rows) == _golden.normalize(case["expected"])
+    elif kind == "map_rows":
+        phs = [n.name for n in graphdef.parse_graph(graph) if n.op == "Placeholder"]
+        feed = {p: case.get("feed_dict", {}).get(p, p) for p in phs}
+        info = {f.name: (f.scalarType.tf_code, tuple(hints.out[f.name].dims)) for f in fetches}
+        names, out_parts = ox.map_rows(parts, cols, graph, feed, info)
+        rows = [r for p in out_parts for r in p]
+        idx = [names.index(n) for n in case["select"]]
+        rows = [[r[i] for i in idx] for r in rows]
+        assert _golden.normalize(rows) == _golden.normalize(case["expected"])
+    elif kind == "reduce_rows":
+        row = ox.reduce_rows(parts, cols, graph)
+        assert list(row) == case["expected"]
     elif kind == "reduce_blocks":
         row = ox.reduce_blocks(parts, cols, graph, [f.name for f in fetches])
         assert list(row) == case["expected"]
