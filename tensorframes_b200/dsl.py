@@ -443,4 +443,20 @@ def hints(nodes: Sequence[Node]) -> ShapeDescription:
     for n in nodes:
         n.freeze(everything=True)
     ins = graph_inputs(nodes)
-    return ShapeDescription({n.name: n.shape for n in nodes}, tuple(n.name for n in nodes), {i: i for i in ins})
+    out = {n.name: n.shape for n in nodes}
+    # like the python front end (core.py:52-72), also send the shape of every placeholder: TF drops the
+    # shape attribute of scalar placeholders, so the hint is the only place it survives
+    seen = set()
+
+    def walk(n: Node):
+        if id(n) in seen:
+            return
+        seen.add(id(n))
+        if n.opName == "Placeholder" and not n.parents:
+            out.setdefault(n.name, n.shape)
+        for p in n._all_parents():
+            walk(p)
+
+    for n in nodes:
+        walk(n)
+    return ShapeDescription(out, tuple(n.name for n in nodes), {i: i for i in ins})
