@@ -34,6 +34,16 @@ bool is_device_pointer(const void* p) {
   return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
 }
 
+bool is_pinned_host_pointer(const void* p) {
+  if (p == nullptr) return false;
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeHost;
+}
+
 struct Step {
   enum Kind { ELT, REDUCE_AXIS0, REDUCE_ROWS, COPY, MATMUL } kind = ELT;
   std::vector<int> nodes;   // ELT: the group (topological order); others: one node
@@ -73,6 +83,9 @@ Session::~Session() {
   if (red_scratch_) cudaFree(red_scratch_);
   if (err_flag_) cudaFree(err_flag_);
   if (err_host_) cudaFreeHost(err_host_);
+  for (int k = 0; k < 2; ++k)
+    if (pipe_stream_[k]) cudaStreamDestroy(pipe_stream_[k]);
+  if (pipe_event_) cudaEventDestroy(pipe_event_);
   if (own_stream_) cudaStreamDestroy(own_stream_);
 }
 
@@ -690,6 +703,125 @@ bool make_chain(const EltProgram& prog, ChainProgram& ch) {
 }  // namespace
 
 // ---------------------------------------------------------------------------
+// Host ingest pipeline (K0) for row-separable map graphs
+// ---------------------------------------------------------------------------
+// A map whose whole graph is ONE fused element-wise group over [n_rows, cell...] can be evaluated chunk by
+// chunk.  When every feed and fetch is a page-locked host buffer (tfs_host_alloc), the block is cut into
+// chunks of rows that go round two streams: while one chunk is being computed, the next one is on its way
+// in over PCIe and the previous one on its way out, so a step costs about max(H2D, D2H) instead of
+// H2D + kernel + D2H.  This replaces the reference's pack -> Tensor.create -> run -> writeTo sequence
+// (impl/TFDataOps.scala:27-59, impl/datatypes.scala:344-347, 365-370), which is fully serial.
+bool Session::run_pipelined(const std::vector<TensorArg>& feeds, const std::vector<TensorArg>& fetches, const Plan& plan) {
+  constexpr size_t kChunkBytes = size_t(32) << 20;    // per-chunk budget of the widest column
+  if (plan.steps.size() != 1 || plan.steps[0].kind != Step::ELT) return false;
+  const Step& st = plan.steps[0];
+  if (st.shape.rank < 1) return false;
+  const int64_t n = st.shape.d[0];
+  for (const TensorArg& f : feeds)
+    if (!is_pinned_host_pointer(f.data)) return false;
+  for (const TensorArg& f : fetches)
+    if (!is_pinned_host_pointer(f.data)) return false;
+  // every fed placeholder and every fetch must be a [n, ...] block of the group's row count
+  size_t max_row_bytes = 0, total_bytes = 0;
+  auto row_bytes = [&](int idx) {
+    const Shape& sh = plan.shape[size_t(idx)];
+    return size_t(sh.numel() / std::max<int64_t>(n, 1)) * size_t(dtype_size(g_.nodes[size_t(idx)].dtype));
+  };
+  for (int idx : plan.needed) {
+    const Node& nd = g_.nodes[size_t(idx)];
+    if (nd.cls == OpClass::Placeholder) {
+      const Shape& sh = plan.shape[size_t(idx)];
+      if (sh.rank < 1 || sh.d[0] != n || sh.numel() != st.shape.numel() * (sh.numel() / std::max<int64_t>(st.shape.numel(), 1))) return false;
+      if (sh.numel() != st.shape.numel()) return false;     // only same-shaped columns (no per-row broadcast)
+      max_row_bytes = std::max(max_row_bytes, row_bytes(idx));
+      total_bytes += size_t(sh.numel()) * size_t(dtype_size(nd.dtype));
+    }
+  }
+  for (int f : plan.fetch_nodes) {
+    if (plan.step_of[size_t(f)] != 0 || plan.shape[size_t(f)] != st.shape) return false;
+    max_row_bytes = std::max(max_row_bytes, row_bytes(f));
+  }
+  if (total_bytes < 4 * kChunkBytes || max_row_bytes == 0) return false;   // small blocks: one shot is as good
+
+  int64_t chunk_rows = int64_t(kChunkBytes / max_row_bytes);
+  chunk_rows = std::max<int64_t>(16, chunk_rows / 16 * 16);    // keeps every chunk start 16-byte aligned
+  const int64_t n_chunks = (n + chunk_rows - 1) / chunk_rows;
+
+  if (!pipe_stream_[0]) {
+    for (int k = 0; k < 2; ++k) TFS_CUDA(cudaStreamCreateWithFlags(&pipe_stream_[k], cudaStreamNonBlocking));
+    TFS_CUDA(cudaEventCreateWithFlags(&pipe_event_, cudaEventDisableTiming));
+  }
+  // chunk plans: one for a full chunk, one for the last (shorter) chunk
+  std::vector<std::string> names;
+  for (auto& f : fetches) names.push_back(f.name);
+  auto chunk_feeds = [&](int64_t rows_in_chunk) {
+    std::vector<TensorArg> cf = feeds;
+    for (auto& f : cf) f.shape.d[0] = rows_in_chunk;
+    return cf;
+  };
+  Plan full_plan, tail_plan;
+  build_plan(chunk_feeds(std::min(chunk_rows, n)), names, full_plan, false);
+  const int64_t tail_rows = n - (n_chunks - 1) * chunk_rows;
+  const bool has_tail = tail_rows != std::min(chunk_rows, n);
+  if (has_tail) build_plan(chunk_feeds(tail_rows), names, tail_plan, false);
+
+  // workspace: two slots, each holding one chunk of every fed column and every fetched column
+  const size_t N = g_.nodes.size();
+  std::vector<size_t> off(N, SIZE_MAX);
+  size_t slot_bytes = 0;
+  for (int idx : plan.needed) {
+    const Node& nd = g_.nodes[size_t(idx)];
+    const bool is_out = std::find(plan.fetch_nodes.begin(), plan.fetch_nodes.end(), idx) != plan.fetch_nodes.end();
+    if (nd.cls == OpClass::Placeholder || is_out || (plan.materialize[size_t(idx)] && nd.cls != OpClass::Const)) {
+      off[size_t(idx)] = slot_bytes;
+      slot_bytes += align_up(row_bytes(idx) * size_t(chunk_rows));
+    }
+  }
+  reserve_workspace(2 * slot_bytes);
+  // constants that are read as tensors
+  std::vector<void*> const_ptr(N, nullptr);
+  for (int idx : plan.needed)
+    if (g_.nodes[size_t(idx)].cls == OpClass::Const && plan.materialize[size_t(idx)]) const_ptr[size_t(idx)] = const_device(idx);
+  // everything enqueued so far on the session stream (constant uploads) precedes the pipeline
+  TFS_CUDA(cudaEventRecord(pipe_event_, stream_));
+  for (int k = 0; k < 2; ++k) TFS_CUDA(cudaStreamWaitEvent(pipe_stream_[k], pipe_event_, 0));
+
+  for (int64_t c = 0; c < n_chunks; ++c) {
+    const int slot = int(c & 1);
+    cudaStream_t sx = pipe_stream_[slot];
+    const int64_t r0 = c * chunk_rows;
+    const int64_t rows_here = std::min(chunk_rows, n - r0);
+    const Plan& cp = (has_tail && c == n_chunks - 1) ? tail_plan : full_plan;
+    std::vector<void*> dev_ptr(N, nullptr);
+    for (int idx : plan.needed) {
+      if (off[size_t(idx)] != SIZE_MAX) dev_ptr[size_t(idx)] = ws_ + size_t(slot) * slot_bytes + off[size_t(idx)];
+      else if (const_ptr[size_t(idx)]) dev_ptr[size_t(idx)] = const_ptr[size_t(idx)];
+    }
+    for (int idx : plan.needed) {
+      if (g_.nodes[size_t(idx)].cls != OpClass::Placeholder) continue;
+      const TensorArg& f = feeds[size_t(plan.feed_of[size_t(idx)])];
+      const size_t rb = row_bytes(idx);
+      TFS_CUDA(cudaMemcpyAsync(dev_ptr[size_t(idx)], static_cast<const char*>(f.data) + size_t(r0) * rb,
+                               size_t(rows_here) * rb, cudaMemcpyHostToDevice, sx));
+    }
+    GroupCompiler gc(g_, cp.shape, dev_ptr, cp.materialize, cp.steps[0]);
+    gc.build(err_flag_);
+    ChainProgram chain;
+    if (make_chain(gc.prog, chain)) launches_ += launch_chain(chain, cp.steps[0].shape.numel(), dev_, sx);
+    else launches_ += launch_eltwise(gc.prog, cp.steps[0].shape.numel(), gc.wide, dev_, sx);
+    for (size_t i = 0; i < fetches.size(); ++i) {
+      const int idx = plan.fetch_nodes[i];
+      const size_t rb = row_bytes(idx);
+      TFS_CUDA(cudaMemcpyAsync(static_cast<char*>(fetches[i].data) + size_t(r0) * rb, dev_ptr[size_t(idx)],
+                               size_t(rows_here) * rb, cudaMemcpyDeviceToHost, sx));
+    }
+  }
+  for (int k = 0; k < 2; ++k) TFS_CUDA(cudaStreamSynchronize(pipe_stream_[k]));
+  check_device_error();
+  return true;
+}
+
+// ---------------------------------------------------------------------------
 // Execution
 // ---------------------------------------------------------------------------
 void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorArg>& fetches, bool rows) {
@@ -719,6 +851,7 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
                     fetches[i].shape.str());
   }
   ensure_device();
+  if (!rows && run_pipelined(feeds, fetches, plan)) return;
   const size_t N = g_.nodes.size();
   std::vector<void*> dev_ptr(N, nullptr);
   auto nbytes = [&](int idx) { return size_t(plan.shape[size_t(idx)].numel()) * size_t(dtype_size(g_.nodes[size_t(idx)].dtype)); };

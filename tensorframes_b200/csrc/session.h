@@ -46,6 +46,7 @@ class Session {
   void ensure_device();
   void build_plan(const std::vector<TensorArg>& feeds, const std::vector<std::string>& fetch_names, Plan& plan,
                   bool rows = false);
+  bool run_pipelined(const std::vector<TensorArg>& feeds, const std::vector<TensorArg>& fetches, const Plan& plan);
   void* const_device(int node);
   void reserve_workspace(size_t bytes);
   void check_device_error();
@@ -55,6 +56,8 @@ class Session {
   bool device_ready_ = false;
   cudaStream_t own_stream_ = nullptr;
   cudaStream_t stream_ = nullptr;
+  cudaStream_t pipe_stream_[2] = {nullptr, nullptr};   // host ingest pipeline (chunked H2D / kernel / D2H)
+  cudaEvent_t pipe_event_ = nullptr;
   char* ws_ = nullptr;
   size_t ws_cap_ = 0;
   void* red_scratch_ = nullptr;

@@ -682,3 +682,32 @@ def test_row_mode_rejects_what_it_cannot_batch():
     with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
         with pytest.raises(_native.UnsupportedError, match="broadcasting"):
             s.run({"x": np.zeros(4), "y": np.zeros((4, 3))}, ["z"], rows=True)
+
+
+# ---- host ingest pipeline (K0): pinned host blocks, chunked H2D / kernel / D2H ------------------------------
+def test_pipelined_host_map_matches_one_shot():
+    n = 20_000_003                                   # 160 MB of f64: well past the pipelining threshold, ragged tail
+    rng = np.random.default_rng(71)
+    xa = _native.PinnedBuffer((n,), np.float64)
+    ya = _native.PinnedBuffer((n,), np.float64)
+    za = _native.PinnedBuffer((n,), np.float32)
+    wa = _native.PinnedBuffer((n,), np.float64)
+    try:
+        xa.array[:] = rng.uniform(-1, 1, n)
+        ya.array[:] = rng.uniform(1, 2, n)
+        with dsl.withGraph():
+            px = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x")
+            py = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("y")
+            z = dsl.cast(dsl.maximum(px * 1.5 + 0.25, 0.0), tfs.FloatType).named("z")      # chain kernel
+            w = ((px + py) * (px - py)).named("w")                                          # interpreter (DAG)
+            g = dsl.build_graph(z, w)
+        with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+            s.run_into({"x": xa.array, "y": ya.array}, {"z": za.array, "w": wa.array})
+            launches = s.launch_count
+        assert launches > 2                              # the block really went through in chunks
+        x, y = xa.array, ya.array
+        assert za.array.tobytes() == np.maximum(x * 1.5 + 0.25, 0.0).astype(np.float32).tobytes()
+        assert wa.array.tobytes() == ((x + y) * (x - y)).tobytes()
+    finally:
+        for b in (xa, ya, za, wa):
+            b.free()
