@@ -711,3 +711,28 @@ def test_pipelined_host_map_matches_one_shot():
     finally:
         for b in (xa, ya, za, wa):
             b.free()
+
+
+def test_blocks_beyond_2_31_elements():
+    """int64 sizes end to end: the reference caps a block at Int.MaxValue scalars (impl/datatypes.scala:74-78);
+    here a 2.2e9-element column is mapped and reduced in one block each (closed-form checks on the device)."""
+    torch = pytest.importorskip("torch")
+    n = 2_200_000_000
+    x = torch.ones(n, dtype=torch.int32, device="cuda")
+    x[n - 1] = 7
+    x[2**31 + 5] = -3
+    y = torch.empty(n, dtype=torch.int32, device="cuda")
+    tot = torch.empty((), dtype=torch.int32, device="cuda")
+    with dsl.withGraph():
+        p = dsl.placeholder(tfs.IntegerType, dsl.Unknown).named("x")
+        g = dsl.build_graph((p * 2 + 1).named("y"), dsl.reduce_sum(p, [0]).named("s"), dsl.reduce_min(p, [0]).named("m"))
+    mn = torch.empty((), dtype=torch.int32, device="cuda")
+    DA = _native.DeviceArray.from_torch
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        s.run_into({"x": DA(x)}, {"y": DA(y), "s": DA(tot), "m": DA(mn)})
+        s.sync()
+    assert int(y[0]) == 3 and int(y[n - 1]) == 15 and int(y[2**31 + 5]) == -5 and int(y[2**31 + 6]) == 3
+    assert bool((y[:1000] == 3).all()) and bool((y[n - 1000:n - 1] == 3).all())
+    expect = (n - 2 + 7 - 3) % (1 << 32)
+    expect = expect - (1 << 32) if expect >= (1 << 31) else expect      # int32 sums wrap, as in TF
+    assert int(tot) == expect and int(mn) == -3
