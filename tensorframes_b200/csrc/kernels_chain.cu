@@ -14,7 +14,6 @@ namespace tfs {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kJ = 4;
 
 #include "arith.inc"
 
@@ -67,57 +66,60 @@ __device__ __forceinline__ void st_tile(T* __restrict__ base, int64_t elem, int 
   }
 }
 
-template <class T, int P>
-__device__ __forceinline__ void apply_slot(const ChainSlot& s, T (&acc)[kJ][P], const int64_t (&elem)[kJ],
-                                           const int (&nvalid)[kJ], int* err) {
-  T b[kJ][P];
-  if (s.operand_buf != nullptr) {
-    const T* base = static_cast<const T*>(s.operand_buf);
-#pragma unroll
-    for (int j = 0; j < kJ; ++j) ld_tile<T, P>(base, elem[j], nvalid[j], b[j]);
-  } else {
-    T imm;
-    memcpy(&imm, &s.imm, sizeof(T));
-#pragma unroll
-    for (int j = 0; j < kJ; ++j)
-#pragma unroll
-      for (int e = 0; e < P; ++e) b[j][e] = imm;
+// one op applied in place to the register tile; OPERAND(j, e) yields the second operand
+#define TFS_SLOT_SWITCH(OPERAND)                                                        \
+  switch (s.op) {                                                                       \
+    case CH_ADD: TFS_SLOT(Arith<T>::add(a, OPERAND))                                    \
+    case CH_SUB: TFS_SLOT(Arith<T>::sub(a, OPERAND))                                    \
+    case CH_RSUB: TFS_SLOT(Arith<T>::sub(OPERAND, a))                                   \
+    case CH_MUL: TFS_SLOT(Arith<T>::mul(a, OPERAND))                                    \
+    case CH_DIV: TFS_SLOT(Arith<T>::div(a, OPERAND, e < nvalid[j], err))                \
+    case CH_RDIV: TFS_SLOT(Arith<T>::div(OPERAND, a, e < nvalid[j], err))               \
+    case CH_MIN: TFS_SLOT(Arith<T>::mn(a, OPERAND))                                     \
+    case CH_RMIN: TFS_SLOT(Arith<T>::mn(OPERAND, a))                                    \
+    case CH_MAX: TFS_SLOT(Arith<T>::mx(a, OPERAND))                                     \
+    case CH_RMAX: TFS_SLOT(Arith<T>::mx(OPERAND, a))                                    \
+    case CH_NEG: TFS_SLOT(Arith<T>::neg(a))                                             \
+    case CH_RELU: TFS_SLOT(Arith<T>::mx(a, T(0)))                                       \
+    case CH_SQUARE: TFS_SLOT(Arith<T>::mul(a, a))                                       \
+    case CH_ABS: TFS_SLOT(Arith<T>::abs(a))                                             \
+    case CH_SQRT: TFS_SLOT(Arith<T>::sqrt(a))                                           \
+    case CH_RECIP: TFS_SLOT(Arith<T>::recip(a))                                         \
+    default: break;                                                                     \
   }
 #define TFS_SLOT(expr)                                \
   _Pragma("unroll") for (int j = 0; j < kJ; ++j)      \
   _Pragma("unroll") for (int e = 0; e < P; ++e) {     \
     const T a = acc[j][e];                            \
-    const T c = b[j][e];                              \
-    (void)c;                                          \
     acc[j][e] = (expr);                               \
   }                                                   \
   break;
-  switch (s.op) {
-    case CH_ADD: TFS_SLOT(Arith<T>::add(a, c))
-    case CH_SUB: TFS_SLOT(Arith<T>::sub(a, c))
-    case CH_RSUB: TFS_SLOT(Arith<T>::sub(c, a))
-    case CH_MUL: TFS_SLOT(Arith<T>::mul(a, c))
-    case CH_DIV: TFS_SLOT(Arith<T>::div(a, c, e < nvalid[j], err))
-    case CH_RDIV: TFS_SLOT(Arith<T>::div(c, a, e < nvalid[j], err))
-    case CH_MIN: TFS_SLOT(Arith<T>::mn(a, c))
-    case CH_RMIN: TFS_SLOT(Arith<T>::mn(c, a))
-    case CH_MAX: TFS_SLOT(Arith<T>::mx(a, c))
-    case CH_RMAX: TFS_SLOT(Arith<T>::mx(c, a))
-    case CH_NEG: TFS_SLOT(Arith<T>::neg(a))
-    case CH_RELU: TFS_SLOT(Arith<T>::mx(a, T(0)))
-    case CH_SQUARE: TFS_SLOT(Arith<T>::mul(a, a))
-    case CH_ABS: TFS_SLOT(Arith<T>::abs(a))
-    case CH_SQRT: TFS_SLOT(Arith<T>::sqrt(a))
-    case CH_RECIP: TFS_SLOT(Arith<T>::recip(a))
-    default: break;
-  }
-#undef TFS_SLOT
-}
 
-template <class T, class OutT>
+template <class T, int P, int kJ, bool BUFOPS>
+__device__ __forceinline__ void apply_slot(const ChainSlot& s, T (&acc)[kJ][P], const int64_t (&elem)[kJ],
+                                           const int (&nvalid)[kJ], int* err) {
+  if (BUFOPS && s.operand_buf != nullptr) {   // second operand: another column, same flat index
+    T b[kJ][P];
+    const T* base = static_cast<const T*>(s.operand_buf);
+#pragma unroll
+    for (int j = 0; j < kJ; ++j) ld_tile<T, P>(base, elem[j], nvalid[j], b[j]);
+    TFS_SLOT_SWITCH(b[j][e])
+  } else {                          // second operand: a scalar constant (or none), kept in one register
+    T imm;
+    memcpy(&imm, &s.imm, sizeof(T));
+    TFS_SLOT_SWITCH(imm)
+  }
+}
+#undef TFS_SLOT
+#undef TFS_SLOT_SWITCH
+
+// BUFOPS = false: no slot reads a second column, so the operand tile is not needed and the thread carries
+// twice as many vectors (8 independent 128-bit loads in flight instead of 4).
+template <class T, class OutT, bool BUFOPS>
 __global__ void __launch_bounds__(kThreads, 3)
 chain_kernel(const __grid_constant__ ChainProgram prog, const int64_t n) {
   constexpr int P = 16 / int(sizeof(T));
+  constexpr int kJ = BUFOPS ? 4 : 8;
   const int64_t n_vec = (n + P - 1) / P;
   constexpr int64_t tile_vecs = int64_t(kThreads) * kJ;
   const int64_t n_tiles = (n_vec + tile_vecs - 1) / tile_vecs;
@@ -138,7 +140,7 @@ chain_kernel(const __grid_constant__ ChainProgram prog, const int64_t n) {
     for (int j = 0; j < kJ; ++j) ld_tile<T, P>(in, elem[j], nvalid[j], acc[j]);
 #pragma unroll
     for (int s = 0; s < kChainSlots; ++s)
-      if (s < prog.n_slots) apply_slot<T, P>(prog.slots[s], acc, elem, nvalid, prog.err);
+      if (s < prog.n_slots) apply_slot<T, P, kJ, BUFOPS>(prog.slots[s], acc, elem, nvalid, prog.err);
 #pragma unroll
     for (int j = 0; j < kJ; ++j) {
       OutT o[P];
@@ -149,22 +151,30 @@ chain_kernel(const __grid_constant__ ChainProgram prog, const int64_t n) {
   }
 }
 
-template <class T, class OutT>
-int launch_chain_t(const ChainProgram& prog, int64_t n, const DeviceInfo& dev, cudaStream_t stream) {
+template <class T, class OutT, bool BUFOPS>
+int launch_chain_v(const ChainProgram& prog, int64_t n, const DeviceInfo& dev, cudaStream_t stream) {
   static int blocks_per_sm = 0;
   if (blocks_per_sm == 0) {
     int b = 0;
-    TFS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, chain_kernel<T, OutT>, kThreads, 0));
+    TFS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, chain_kernel<T, OutT, BUFOPS>, kThreads, 0));
     blocks_per_sm = b > 0 ? b : 1;
   }
   constexpr int P = 16 / int(sizeof(T));
+  constexpr int kJ = BUFOPS ? 4 : 8;
   const int64_t n_vec = (n + P - 1) / P;
   const int64_t n_tiles = (n_vec + int64_t(kThreads) * kJ - 1) / (int64_t(kThreads) * kJ);
   int64_t grid = std::min<int64_t>(int64_t(dev.sm_count) * blocks_per_sm, n_tiles);
   if (grid < 1) grid = 1;
-  chain_kernel<T, OutT><<<(unsigned)grid, kThreads, 0, stream>>>(prog, n);
+  chain_kernel<T, OutT, BUFOPS><<<(unsigned)grid, kThreads, 0, stream>>>(prog, n);
   TFS_CUDA(cudaGetLastError());
   return 1;
+}
+
+template <class T, class OutT>
+int launch_chain_t(const ChainProgram& prog, int64_t n, const DeviceInfo& dev, cudaStream_t stream) {
+  bool bufops = false;
+  for (int s = 0; s < prog.n_slots; ++s) bufops = bufops || prog.slots[s].operand_buf != nullptr;
+  return bufops ? launch_chain_v<T, OutT, true>(prog, n, dev, stream) : launch_chain_v<T, OutT, false>(prog, n, dev, stream);
 }
 
 template <class T>
