@@ -6,11 +6,12 @@
 // four passes, all HBM-bound:
 //
 //   1. insert   every key into an open-addressing table (64-bit CAS on the key slot); the row
-//               remembers its slot and the slot counts its rows          8 B read + 8 B written / row
+//               remembers its slot (u32) next to its own index (u32) and the slot counts its rows
+//                                                                         8 B read + 8 B written / row
 //   2. scan     one pass over the table: segment offset of every slot, dense group id of every
 //               occupied slot, out_keys                                   (table only)
-//   3. sort     rows by slot (stable LSD radix sort of the 64-bit (slot << 32 | row) tags on their slot
-//               bits -- cub::DeviceRadixSort, the one library call on this path, used as plain plumbing)
+//   3. sort     rows by slot (stable LSD radix sort of the (slot, row) u32 pairs on the slot bits --
+//               cub::DeviceRadixSort, the one library call on this path, used as plain plumbing)
 //   4. gather-reduce  one warp per group walks its segment of the sorted row list and gathers
 //               the payload rows -- each a contiguous cell, read with coalesced vector loads --
 //               accumulating in registers; one coalesced store per group.      cell bytes / row
@@ -38,69 +39,89 @@ __device__ __forceinline__ unsigned long long mix64(unsigned long long x) {
   return x;
 }
 
-// L2 eviction priorities: the hash table (slot keys + counts) must stay resident while the key column, the
-// row slots and the row ids stream past it -- without the hints the streams evict it and every probe and
-// every counter update becomes a DRAM access (measured: 10.4 GB instead of 2.2 GB of reads per 1e8 rows).
-__device__ __forceinline__ unsigned long long policy_keep() {
-  unsigned long long p;
-  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
-  return p;
-}
-__device__ __forceinline__ unsigned long long policy_stream() {
-  unsigned long long p;
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
-  return p;
-}
-__device__ __forceinline__ unsigned long long ld_u64_hint(const unsigned long long* p, unsigned long long pol) {
-  unsigned long long v;
-  asm volatile("ld.global.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(v) : "l"(p), "l"(pol) : "memory");
-  return v;
-}
-__device__ __forceinline__ void red_add_u32_hint(unsigned int* p, unsigned int v, unsigned long long pol) {
-  asm volatile("red.global.add.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(p), "r"(v), "l"(pol) : "memory");
-}
-__device__ __forceinline__ void st_u64_hint(unsigned long long* p, unsigned long long v, unsigned long long pol) {
-  asm volatile("st.global.L2::cache_hint.u64 [%0], %1, %2;" ::"l"(p), "l"(v), "l"(pol) : "memory");
-}
-
 // header[0] = occupied slots so far, header[1] = overflow flag, header[2] = number of groups (after the scan)
 // Slot `slots` (one past the table) belongs to the one key value that equals the empty marker.
+//
+// Each thread takes kInsU keys of a CTA tile: the first probes of all of them are in flight together, the
+// (rare) collisions are walked afterwards, and only when the whole warp is done -- __syncwarp -- are the
+// row slots stored.  Without that reconvergence every lane stores as it leaves its own probe loop, the
+// warp's 256 B store turns into 32 partial-sector writes, and L2 has to read every sector back from DRAM
+// to merge them: measured 85 B/row of DRAM reads instead of 8, 9.2 ms instead of 3.0 ms per 2.5e8 rows.
+//
+// SMEM_COUNTS: tables of at most kSmemSlots slots count in shared memory and flush once per CTA; with few
+// distinct keys the global counters are a handful of addresses that every row would hit (13 ms per
+// 2.5e8 rows at 1000 keys, serialised in the L2 atomic units).
+constexpr int kInsU = 2;
+constexpr int kSmemSlots = 8192;
+
+template <bool SMEM_COUNTS>
 __global__ void __launch_bounds__(kThreads)
 agg_insert_kernel(const long long* __restrict__ keys, const int64_t n, unsigned long long* __restrict__ slot_key,
                   unsigned int* __restrict__ counts, const unsigned long long slots, unsigned int* __restrict__ header,
-                  const unsigned int max_groups, unsigned long long* __restrict__ row_tag) {
+                  const unsigned int max_groups, unsigned int* __restrict__ row_slot, unsigned int* __restrict__ row_id) {
+  __shared__ unsigned int sm_counts[SMEM_COUNTS ? kSmemSlots + 1 : 1];
+  if (SMEM_COUNTS) {
+    for (unsigned int j = threadIdx.x; j <= (unsigned int)slots; j += kThreads) sm_counts[j] = 0u;
+    __syncthreads();
+  }
   const unsigned long long mask = slots - 1;
-  const unsigned long long keep = policy_keep(), stream = policy_stream();
-  const int64_t stride = int64_t(gridDim.x) * blockDim.x;
-  for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const unsigned long long k = ld_u64_hint(reinterpret_cast<const unsigned long long*>(keys) + i, stream);
-    unsigned long long h;
-    bool claimed = false;
-    if (k == kEmpty) {
-      h = slots;
-      claimed = atomicCAS(slot_key + h, 0ULL, kEmpty) == 0ULL;   // this slot starts as 0, not as the marker
-    } else {
-      h = mix64(k) & mask;
+  const unsigned long long* ukeys = reinterpret_cast<const unsigned long long*>(keys);
+  const int64_t tile = int64_t(kThreads) * kInsU;
+  const int64_t tiles = (n + tile - 1) / tile;
+  for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x) {   // CTA-uniform trip count
+    const int64_t base = t * tile + threadIdx.x;
+    unsigned long long k[kInsU], h[kInsU], cur[kInsU];
+#pragma unroll
+    for (int u = 0; u < kInsU; ++u) {
+      const int64_t i = base + int64_t(u) * kThreads;
+      k[u] = i < n ? __ldcs(ukeys + i) : 0ULL;
+    }
+#pragma unroll
+    for (int u = 0; u < kInsU; ++u) {
+      h[u] = k[u] == kEmpty ? slots : (mix64(k[u]) & mask);
+      cur[u] = *reinterpret_cast<volatile unsigned long long*>(slot_key + h[u]);
+    }
+    unsigned int claimed = 0;
+#pragma unroll
+    for (int u = 0; u < kInsU; ++u) {
+      if (base + int64_t(u) * kThreads >= n) continue;
+      if (k[u] == kEmpty) {   // the marker-key slot starts as 0, not as the marker
+        if (cur[u] == 0ULL && atomicCAS(slot_key + slots, 0ULL, kEmpty) == 0ULL) ++claimed;
+        continue;
+      }
+      unsigned long long c = cur[u];
       unsigned int probes = 0;
       while (true) {
-        const unsigned long long cur = ld_u64_hint(slot_key + h, keep);
-        if (cur == k) break;
-        if (cur == kEmpty) {
-          const unsigned long long prev = atomicCAS(slot_key + h, kEmpty, k);   // rare: once per distinct key
-          if (prev == kEmpty) { claimed = true; break; }
-          if (prev == k) break;
+        if (c == k[u]) break;
+        if (c == kEmpty) {
+          const unsigned long long prev = atomicCAS(slot_key + h[u], kEmpty, k[u]);   // rare: once per distinct key
+          if (prev == kEmpty) { ++claimed; break; }
+          if (prev == k[u]) break;
         }
-        h = (h + 1) & mask;
+        h[u] = (h[u] + 1) & mask;
         // a table this crowded means more distinct keys than max_groups: look at the overflow flag now and
         // then (not on every probe: the whole grid would hammer one address) and give up when it is set
         if ((++probes & 255u) == 0u && *reinterpret_cast<volatile unsigned int*>(header + 1)) break;
+        c = *reinterpret_cast<volatile unsigned long long*>(slot_key + h[u]);
       }
     }
-    if (claimed && atomicAdd(header, 1u) >= max_groups) header[1] = 1u;
-    // one 64-bit store per row: (slot << 32) | row.  The sort orders these tags by their slot bits and the
-    // row index rides along in the low half.
-    st_u64_hint(row_tag + i, (h << 32) | (unsigned long long)i, stream);
-    red_add_u32_hint(counts + h, 1u, keep);
+    if (claimed != 0u && atomicAdd(header, claimed) + claimed > max_groups) header[1] = 1u;
+    __syncwarp();   // see above: the stores below must leave as whole-warp, whole-sector writes
+#pragma unroll
+    for (int u = 0; u < kInsU; ++u) {
+      const int64_t i = base + int64_t(u) * kThreads;
+      if (i < n) {
+        __stcs(row_slot + i, (unsigned int)h[u]);
+        __stcs(row_id + i, (unsigned int)i);
+        if (SMEM_COUNTS) atomicAdd(sm_counts + h[u], 1u);
+        else atomicAdd(counts + h[u], 1u);
+      }
+    }
+  }
+  if (SMEM_COUNTS) {
+    __syncthreads();
+    for (unsigned int j = threadIdx.x; j <= (unsigned int)slots; j += kThreads)
+      if (sm_counts[j] != 0u) atomicAdd(counts + j, sm_counts[j]);
   }
 }
 
@@ -254,7 +275,7 @@ __device__ __forceinline__ void load_v(const T* p, T (&x)[V]) {
 // kU rows are in flight per row-lane.
 template <class T, int OP, int V>
 __global__ void __launch_bounds__(kThreads)
-agg_gather_reduce_kernel(const T* __restrict__ payload, const int cell, const unsigned long long* __restrict__ perm,
+agg_gather_reduce_kernel(const T* __restrict__ payload, const int cell, const unsigned int* __restrict__ perm,
                          const unsigned int* __restrict__ offsets, const unsigned int* __restrict__ counts,
                          const unsigned int* __restrict__ group_slot, const int64_t n_groups, const int col_lanes,
                          T* __restrict__ out) {
@@ -278,7 +299,7 @@ agg_gather_reduce_kernel(const T* __restrict__ payload, const int cell, const un
         for (; r + (unsigned long long)(kU - 1) * R < hi; r += (unsigned long long)kU * R) {
           unsigned int idx[kU];
 #pragma unroll
-          for (int u = 0; u < kU; ++u) idx[u] = (unsigned int)__ldg(perm + r + (unsigned long long)u * R);
+          for (int u = 0; u < kU; ++u) idx[u] = __ldg(perm + r + (unsigned long long)u * R);
           T x[kU][V];
 #pragma unroll
           for (int u = 0; u < kU; ++u) load_v<T, V>(payload + (int64_t)idx[u] * cell + c0, x[u]);
@@ -289,7 +310,7 @@ agg_gather_reduce_kernel(const T* __restrict__ payload, const int cell, const un
         }
         for (; r < hi; r += R) {
           T x[V];
-          load_v<T, V>(payload + (int64_t)(unsigned int)__ldg(perm + r) * cell + c0, x);
+          load_v<T, V>(payload + (int64_t)__ldg(perm + r) * cell + c0, x);
 #pragma unroll
           for (int e = 0; e < V; ++e) acc[e] = red_op<T, OP>(acc[e], x[e]);
         }
@@ -308,7 +329,7 @@ agg_gather_reduce_kernel(const T* __restrict__ payload, const int cell, const un
 }
 
 template <class T, int OP>
-int launch_gather_t(const T* payload, int64_t cell, const unsigned long long* perm, const unsigned int* offsets,
+int launch_gather_t(const T* payload, int64_t cell, const unsigned int* perm, const unsigned int* offsets,
                     const unsigned int* counts, const unsigned int* group_slot, int64_t n_groups, T* out,
                     const DeviceInfo& dev, cudaStream_t stream) {
   if (n_groups <= 0 || cell <= 0) return 0;
@@ -337,7 +358,7 @@ int launch_gather_t(const T* payload, int64_t cell, const unsigned long long* pe
 }
 
 template <class T>
-int launch_gather_op(int red_op, const void* payload, int64_t cell, const unsigned long long* perm,
+int launch_gather_op(int red_op, const void* payload, int64_t cell, const unsigned int* perm,
                      const unsigned int* offsets, const unsigned int* counts, const unsigned int* group_slot,
                      int64_t n_groups, void* out, const DeviceInfo& dev, cudaStream_t stream) {
   const T* p = static_cast<const T*>(payload);
@@ -363,8 +384,8 @@ int slot_bits(uint64_t slots) {   // bits needed for slot indices 0..slots (incl
 
 size_t sort_temp_bytes(int64_t n_rows, uint64_t slots) {
   size_t bytes = 0;
-  cub::DeviceRadixSort::SortKeys(nullptr, bytes, static_cast<const unsigned long long*>(nullptr),
-                                 static_cast<unsigned long long*>(nullptr), n_rows, 32, 32 + slot_bits(slots));
+  cub::DoubleBuffer<unsigned int> k(nullptr, nullptr), v(nullptr, nullptr);
+  cub::DeviceRadixSort::SortPairs(nullptr, bytes, k, v, n_rows, 0, slot_bits(slots));
   return bytes;
 }
 
@@ -383,8 +404,11 @@ AggLayout agg_layout(int64_t n_rows, int64_t max_groups) {
   L.off_offsets = off; off += up((cap + 2) * 4);
   L.off_group_slot = off; off += up(size_t(max_groups + 1) * 4);
   L.off_tile_sums = off; off += up(size_t((cap + 1 + kScanTile) / kScanTile + 1) * 8);
-  L.off_row_tag = off; off += up(size_t(n_rows) * 8);
-  L.off_perm = off; off += up(size_t(n_rows) * 8);
+  for (int b = 0; b < 2; ++b) {   // ping-pong buffers of the pair sort
+    L.off_row_slot[b] = off; off += up(size_t(n_rows) * 4);
+    L.off_row_id[b] = off; off += up(size_t(n_rows) * 4);
+  }
+  L.off_perm = L.off_row_id[0];   // set by launch_agg_segments to the buffer the sort finished in
   L.sort_temp_bytes = n_rows > 0 ? sort_temp_bytes(n_rows, cap) : 0;
   L.off_sort_temp = off; off += up(L.sort_temp_bytes);
   L.bytes = off;
@@ -399,7 +423,8 @@ int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, ch
   unsigned int* offsets = reinterpret_cast<unsigned int*>(scratch + L.off_offsets);
   unsigned int* group_slot = reinterpret_cast<unsigned int*>(scratch + L.off_group_slot);
   unsigned long long* tile_sums = reinterpret_cast<unsigned long long*>(scratch + L.off_tile_sums);
-  unsigned long long* row_tag = reinterpret_cast<unsigned long long*>(scratch + L.off_row_tag);
+  unsigned int* row_slot = reinterpret_cast<unsigned int*>(scratch + L.off_row_slot[0]);
+  unsigned int* row_id = reinterpret_cast<unsigned int*>(scratch + L.off_row_id[0]);
   const int64_t m = int64_t(L.table_slots) + 1;   // table + the marker-key slot
   TFS_CUDA(cudaMemsetAsync(header, 0, 256, stream));
   TFS_CUDA(cudaMemsetAsync(counts, 0, size_t(m) * 4, stream));
@@ -408,9 +433,14 @@ int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, ch
   TFS_CUDA(cudaMemsetAsync(slot_key + L.table_slots, 0, 8, stream));
   int launches = 1;
   if (n_rows > 0) {
-    agg_insert_kernel<<<(unsigned)grid_for(n_rows, dev), kThreads, 0, stream>>>(
-        reinterpret_cast<const long long*>(keys), n_rows, slot_key, counts, L.table_slots, header,
-        (unsigned int)max_groups, row_tag);
+    const int64_t tiles = (n_rows + int64_t(kThreads) * kInsU - 1) / (int64_t(kThreads) * kInsU);
+    const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(tiles, int64_t(dev.sm_count) * 16));
+    if (L.table_slots <= uint64_t(kSmemSlots))
+      agg_insert_kernel<true><<<grid, kThreads, 0, stream>>>(reinterpret_cast<const long long*>(keys), n_rows, slot_key, counts,
+                                                             L.table_slots, header, (unsigned int)max_groups, row_slot, row_id);
+    else
+      agg_insert_kernel<false><<<grid, kThreads, 0, stream>>>(reinterpret_cast<const long long*>(keys), n_rows, slot_key, counts,
+                                                              L.table_slots, header, (unsigned int)max_groups, row_slot, row_id);
     TFS_CUDA(cudaGetLastError());
     ++launches;
   }
@@ -425,21 +455,24 @@ int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, ch
   return launches + 3;
 }
 
-int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, char* scratch, const AggLayout& L,
+int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, char* scratch, AggLayout& L,
                         const DeviceInfo& dev, cudaStream_t stream) {
   (void)keys; (void)n_groups; (void)dev;
   if (n_rows <= 0) return 0;
-  const unsigned long long* row_tag = reinterpret_cast<const unsigned long long*>(scratch + L.off_row_tag);
-  unsigned long long* sorted = reinterpret_cast<unsigned long long*>(scratch + L.off_perm);
+  cub::DoubleBuffer<unsigned int> slot(reinterpret_cast<unsigned int*>(scratch + L.off_row_slot[0]),
+                                       reinterpret_cast<unsigned int*>(scratch + L.off_row_slot[1]));
+  cub::DoubleBuffer<unsigned int> row(reinterpret_cast<unsigned int*>(scratch + L.off_row_id[0]),
+                                      reinterpret_cast<unsigned int*>(scratch + L.off_row_id[1]));
   size_t temp = L.sort_temp_bytes;
-  TFS_CUDA(cub::DeviceRadixSort::SortKeys(scratch + L.off_sort_temp, temp, row_tag, sorted, n_rows, 32,
-                                          32 + slot_bits(L.table_slots), stream));
+  TFS_CUDA(cub::DeviceRadixSort::SortPairs(scratch + L.off_sort_temp, temp, slot, row, n_rows, 0,
+                                           slot_bits(L.table_slots), stream));
+  L.off_perm = L.off_row_id[row.selector];
   return 1;   // counted as one launch of ours: the sort's internal kernels are library code
 }
 
 int launch_agg_reduce(int dtype, int red_op, const void* payload, int64_t cell, int64_t n_groups, char* scratch,
                       const AggLayout& L, void* out, const DeviceInfo& dev, cudaStream_t stream) {
-  const unsigned long long* perm = reinterpret_cast<const unsigned long long*>(scratch + L.off_perm);
+  const unsigned int* perm = reinterpret_cast<const unsigned int*>(scratch + L.off_perm);
   const unsigned int* offsets = reinterpret_cast<const unsigned int*>(scratch + L.off_offsets);
   const unsigned int* counts = reinterpret_cast<const unsigned int*>(scratch + L.off_counts);
   const unsigned int* group_slot = reinterpret_cast<const unsigned int*>(scratch + L.off_group_slot);

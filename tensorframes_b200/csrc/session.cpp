@@ -1076,7 +1076,7 @@ void Session::aggregate(int64_t n_rows, const int64_t* keys, const std::vector<T
   if (n_rows == 0) return;
   TFS_CHECK(max_groups > 0, TFS_ERR_INVALID, "aggregate: max_groups must be positive for a non-empty block");
 
-  const AggLayout L = agg_layout(n_rows, max_groups);
+  AggLayout L = agg_layout(n_rows, max_groups);
   auto up = [](size_t x) { return align_up(x); };
   // workspace: [agg scratch][out_keys][staged keys][staged feeds][staged outputs]
   size_t off = up(L.bytes);
