@@ -336,7 +336,7 @@ int launch_gather_t(const T* payload, int64_t cell, const unsigned int* perm, co
   constexpr int VMAX = 16 / int(sizeof(T));
   int V = 1;
   const bool aligned16 = (reinterpret_cast<uintptr_t>(payload) & 15) == 0;
-  if (aligned16 && cell % VMAX == 0 && cell >= 32 * VMAX) V = VMAX;
+  if (aligned16 && cell % VMAX == 0 && cell >= 8 * VMAX) V = VMAX;
   else if (aligned16 && VMAX == 4 && cell % 2 == 0 && cell >= 64) V = 2;
   int need = int((cell + V - 1) / V);
   int C = 1;
