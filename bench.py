@@ -434,7 +434,7 @@ def run_c4(args, torch, dist, _native, world, rank, local, device, rows):
                                    f"FloatType[?,64], {rows} rows per GPU (config names 5e8; reduced to bound memory)",
                        "rows_per_gpu": rows, "l2": "inputs larger than L2 (no flush needed)", "exchange": "none" if world == 1 else "key-owner all_to_all of partial groups + merge aggregate"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": ncu_traffic("c4", rows), "peak_source": peak_src, "kernel": "whole step (5 passes, agg_gather_reduce_kernel dominant)",
+                         "traffic": ncu_traffic("c4", rows), "peak_source": peak_src, "kernel": "whole step (insert, table scan, pair sort, gather-reduce; agg_gather_reduce_kernel dominant)",
                          "algorithmic_bytes_per_launch": rows * 264.0, "frac_of_nominal_8000": achieved / 8000.0},
             "e2e": None, "gpu_launches": int(launches), "clocks": clocks.summary(), "cpu_baseline": None}))
     if world > 1:
@@ -508,7 +508,7 @@ def run_c5(args, torch, dist, _native, world, rank, local, device, rows):
             "roofline": {"bound": "tensor", "achieved": tflops, "peak": bf16, "unit": "TFLOP/s", "frac": tflops / bf16,
                          "traffic": ncu_traffic("c5", rows), "peak_source": "measured bf16 sustained; tf32 runs at half of it and "
                          "each fp32 product costs 3 tf32 MMAs, so the attainable ceiling is ~peak/6",
-                         "kernel": "matmul_tc_kernel", "mma_tflops_issued": 3 * tflops,
+                         "kernel": "matmul_tc_pair_kernel", "mma_tflops_issued": 3 * tflops,
                          "hbm_gbs": rows * 2048.0 / step_s / 1e9, "hbm_frac": rows * 2048.0 / step_s / 1e9 / hbm},
             "e2e": None, "gpu_launches": int(launches), "clocks": clocks.summary(), "cpu_baseline": None}))
     if world > 1:
