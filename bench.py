@@ -421,6 +421,74 @@ def run_c4(args, torch, dist, _native, world, rank, local, device, rows):
     ref.index_add_(0, inv[:chk], v[:chk].double())
     if chk == rows:
         assert torch.all((out[:n_groups][order].double() - ref).abs() <= 1e-5 * ref.abs().clamp_min(1e-30))
+    # ---- end to end: host (pinned) key and payload columns through the same C-ABI call ----------------
+    # bounded block (the full 66 GB block would have to be pinned and staged next to the resident one)
+    e2e = None
+    rows_e2e = min(rows, 50_000_000)
+    pinned = []
+    host = {}
+    if not args.no_e2e:
+        try:
+            from tensorframes_b200.shape import LongType
+            pk = _native.PinnedBuffer((rows_e2e,), np.int64); pinned.append(pk)
+            pv = _native.PinnedBuffer((rows_e2e, 64), np.float32); pinned.append(pv)
+            po = _native.PinnedBuffer((KEYS_C4, 64), np.float32); pinned.append(po)
+            pok = _native.PinnedBuffer((KEYS_C4,), np.int64); pinned.append(pok)
+            torch.from_numpy(pk.array).copy_(keys[:rows_e2e])
+            torch.from_numpy(pv.array).copy_(v[:rows_e2e])
+            host = {"keys": pk.array, "v_input": pv.array}
+            hk = _native.DeviceArray(pk.array.ctypes.data, LongType, pk.array.shape, owner=pk.array)
+            hok = _native.DeviceArray(pok.array.ctypes.data, LongType, pok.array.shape, owner=pok.array)
+
+            def e2e_step():
+                if world == 1:
+                    return sess.aggregate_into(hk, {"v_input": pv.array}, {"v": po.array}, hok)   # H2D, passes, D2H, sync
+                from tensorframes_b200.distributed import exchange_groups
+                g = sess.aggregate_into(hk, {"v_input": pv.array}, {"v": DA(out)}, DA(out_keys))
+                rk, (rv,) = exchange_groups(out_keys[:g], [out[:g]])
+                g2 = sess.aggregate_into(DA(rk), {"v_input": DA(rv)}, {"v": DA(out2)}, DA(out_keys2))
+                torch.from_numpy(po.array)[:g2].copy_(out2[:g2])
+                torch.from_numpy(pok.array)[:g2].copy_(out_keys2[:g2])
+                torch.cuda.synchronize()
+                return g2
+
+            k_e2e = max(1, min(args.steps, 3))
+            g_e2e = e2e_step()
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(k_e2e):
+                g_e2e = e2e_step()
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            dt = time.perf_counter() - t0
+            td = torch.tensor([dt], dtype=torch.float64, device=device)
+            if world > 1:
+                dist.all_reduce(td, op=dist.ReduceOp.MAX)
+            e2e = {"value": world * rows_e2e * k_e2e / float(td.item()), "unit": "rows/s", "steps": k_e2e,
+                   "rows_per_gpu": rows_e2e, "h2d_bytes_per_step": int(rows_e2e * 264),
+                   "d2h_bytes_per_step": int(g_e2e * 264)}
+        except Exception as exc:
+            e2e = {"value": None, "unit": "rows/s", "error": str(exc)[:200],
+                   "h2d_bytes_per_step": int(rows_e2e * 264), "d2h_bytes_per_step": 0}
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        from oracle import cpu_baseline as cb
+        cores = cb.cores()
+        hk_np = host["keys"] if host else keys[:rows_e2e].cpu().numpy()
+        hv_np = host["v_input"] if host else v[:rows_e2e].cpu().numpy()
+        probe = min(rows_e2e, 2_000_000)
+        t, _ = cb.timed(cb.aggregate_sum, hk_np[:probe], hv_np[:probe], cores, cores, KEYS_C4)
+        sample = int(min(rows_e2e, max(probe, 12.0 / max(t, 1e-6) * probe / 3)))
+        t, _ = cb.timed(cb.aggregate_sum, hk_np[:sample], hv_np[:sample], cores, cores, KEYS_C4, repeat=3)
+        cpu = {"value": sample / t, "unit": "rows/s", "cores": cores, "kind": "port",
+               "sample": f"first {sample} rows of the same block, {cores} partitions on {cores} threads (per-partition hash "
+                         "aggregation + merge), best of 3; columnar unboxed input, so an upper bound on the JVM reference"}
+    host = {}
+    for pb in pinned:
+        pb.free()
     if rank == 0:
         peak, peak_src = hbm_peak()
         step_s = elapsed_ms / 1e3 / args.steps
@@ -436,7 +504,7 @@ def run_c4(args, torch, dist, _native, world, rank, local, device, rows):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": ncu_traffic("c4", rows), "peak_source": peak_src, "kernel": "whole step (insert, table scan, pair sort, gather-reduce; agg_gather_reduce_kernel dominant)",
                          "algorithmic_bytes_per_launch": rows * 264.0, "frac_of_nominal_8000": achieved / 8000.0},
-            "e2e": None, "gpu_launches": int(launches), "clocks": clocks.summary(), "cpu_baseline": None}))
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks.summary(), "cpu_baseline": cpu}))
     if world > 1:
         dist.destroy_process_group()
 
@@ -487,6 +555,53 @@ def run_c5(args, torch, dist, _native, world, rank, local, device, rows):
     exact = xs @ w.double() + b.double()
     scale = xs.abs() @ w.double().abs() + b.double().abs()
     assert torch.all((y[:65536].double() - exact).abs() <= 1e-5 * scale)
+    # ---- end to end: pinned host block in, pinned host block out (bounded block; PCIe-bound) ---------
+    e2e = None
+    rows_e2e = min(rows, 1 << 22)
+    pinned = []
+    hx = None
+    if not args.no_e2e:
+        try:
+            px = _native.PinnedBuffer((rows_e2e, 256), np.float32); pinned.append(px)
+            py = _native.PinnedBuffer((rows_e2e, 256), np.float32); pinned.append(py)
+            torch.from_numpy(px.array).copy_(x[:rows_e2e])
+            hx = px.array
+            k_e2e = max(1, min(args.steps, 3))
+            sess.run_into({"x": px.array}, {"y": py.array})
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(k_e2e):
+                sess.run_into({"x": px.array}, {"y": py.array})      # H2D + kernel + D2H + sync inside
+            if world > 1:
+                dist.barrier()
+            dt = time.perf_counter() - t0
+            td = torch.tensor([dt], dtype=torch.float64, device=device)
+            if world > 1:
+                dist.all_reduce(td, op=dist.ReduceOp.MAX)
+            assert np.array_equal(py.array[:4096], y[:4096].cpu().numpy())
+            e2e = {"value": world * rows_e2e * k_e2e / float(td.item()), "unit": "rows/s", "steps": k_e2e,
+                   "rows_per_gpu": rows_e2e, "h2d_bytes_per_step": int(rows_e2e * 1024), "d2h_bytes_per_step": int(rows_e2e * 1024)}
+        except Exception as exc:
+            e2e = {"value": None, "unit": "rows/s", "error": str(exc)[:200],
+                   "h2d_bytes_per_step": int(rows_e2e * 1024), "d2h_bytes_per_step": int(rows_e2e * 1024)}
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        from oracle import cpu_baseline as cb
+        cores = cb.cores()
+        xs_np = hx if hx is not None else x[:rows_e2e].cpu().numpy()
+        w_np, b_np = w.cpu().numpy(), b.cpu().numpy()
+        probe = min(rows_e2e, 65536)
+        t, _ = cb.timed(cb.matmul_bias, xs_np[:probe], w_np, b_np, cores, cores)
+        sample = int(min(rows_e2e, max(probe, 12.0 / max(t, 1e-6) * probe / 3)))
+        t, _ = cb.timed(cb.matmul_bias, xs_np[:sample], w_np, b_np, cores, cores, repeat=3)
+        cpu = {"value": sample / t, "unit": "rows/s", "cores": cores, "kind": "port",
+               "sample": f"first {sample} rows of the same block, {cores} partitions on {cores} threads, best of 3; "
+                         "plain C loops (the reference's TF-CPU build calls Eigen's GEMM, which would be faster than this port)"}
+    hx = None
+    for pb in pinned:
+        pb.free()
     if rank == 0:
         peaks = {}
         try:
@@ -510,7 +625,7 @@ def run_c5(args, torch, dist, _native, world, rank, local, device, rows):
                          "each fp32 product costs 3 tf32 MMAs, so the attainable ceiling is ~peak/6",
                          "kernel": "matmul_tc_pair_kernel", "mma_tflops_issued": 3 * tflops,
                          "hbm_gbs": rows * 2048.0 / step_s / 1e9, "hbm_frac": rows * 2048.0 / step_s / 1e9 / hbm},
-            "e2e": None, "gpu_launches": int(launches), "clocks": clocks.summary(), "cpu_baseline": None}))
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks.summary(), "cpu_baseline": cpu}))
     if world > 1:
         dist.destroy_process_group()
 
@@ -546,19 +661,29 @@ def run_reference(args):
     from oracle import cpu_baseline as cb
     wl = args.workload
     cores = cb.cores()
-    rows_full = args.rows or (ROWS_C2 if wl == "c2" else ROWS_C3)
-    rng = np.random.default_rng(2 if wl == "c2" else 3)
+    rows_full = args.rows or {"c2": ROWS_C2, "c3": ROWS_C3, "c4": ROWS_C4, "c5": ROWS_C5}[wl]
+    rng = np.random.default_rng({"c2": 2, "c3": 3, "c4": 4, "c5": 5}[wl])
     # bounded sample: sized so that warmup + steps stay within a few minutes
-    sample = min(rows_full, 20_000_000 if wl == "c2" else 50_000_000)
+    sample = min(rows_full, {"c2": 20_000_000, "c3": 50_000_000, "c4": 4_000_000, "c5": 262_144}[wl])
     if wl == "c2":
         u = rng.random(sample)
         y = np.stack([u, -u], axis=1)
         u = rng.random(sample)
         z = np.stack([u, -u], axis=1)
         fn = lambda: cb.reduce_blocks_sum_min(y, z, cores, cores)
-    else:
+    elif wl == "c3":
         x = rng.random(sample) * 2.0 - 1.0
         fn = lambda: cb.map_blocks_chain(x, 1.5, 0.25, cores, cores)
+    elif wl == "c4":
+        table = np.unique(rng.integers(-2**62, 2**62, KEYS_C4, dtype=np.int64))
+        keys = table[rng.integers(0, table.size, sample)]
+        v = rng.random((sample, 64), dtype=np.float32)
+        fn = lambda: cb.aggregate_sum(keys, v, cores, cores, KEYS_C4)
+    else:
+        w = rng.uniform(-1 / 16, 1 / 16, (256, 256)).astype(np.float32)
+        b = rng.uniform(-1, 1, 256).astype(np.float32)
+        x = rng.random((sample, 256), dtype=np.float32)
+        fn = lambda: cb.matmul_bias(x, w, b, cores, cores)
     for _ in range(args.warmup):
         fn()
     t0 = time.perf_counter()
@@ -571,13 +696,17 @@ def run_reference(args):
             "(Spark + TF-Java are not installable here)")
     line = {
         "impl": "reference",
-        "metric": "rows/s for reduceBlocks (reduce_sum + reduce_min over DoubleType[?,2])" if wl == "c2"
-                  else "rows/s for mapBlocks (fused x*a+b, max(.,0), cast f32 on a float64 column)",
+        "metric": {"c2": "rows/s for reduceBlocks (reduce_sum + reduce_min over DoubleType[?,2])",
+                   "c3": "rows/s for mapBlocks (fused x*a+b, max(.,0), cast f32 on a float64 column)",
+                   "c4": "rows/s for aggregate (groupBy int64 key, reduce_sum over FloatType[?,64])",
+                   "c5": "rows/s for mapBlocks (MatMul FloatType[?,256] x 256x256 + bias)"}[wl],
         "value": value, "unit": "rows/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic",
-        "config": {"workload": ("BASELINE configs[1]: reduce_blocks reduce_sum+reduce_min, DoubleType[?,2], "
-                                if wl == "c2" else "BASELINE configs[2]: map_blocks fused chain, float64 column, ")
+        "dtype": "f64" if wl in ("c2", "c3") else "f32", "data": "synthetic",
+        "config": {"workload": {"c2": "BASELINE configs[1]: reduce_blocks reduce_sum+reduce_min, DoubleType[?,2], ",
+                                "c3": "BASELINE configs[2]: map_blocks fused chain, float64 column, ",
+                                "c4": "BASELINE configs[3]: aggregate groupBy int64 key, reduce_sum FloatType[?,64], ",
+                                "c5": "BASELINE configs[4]: map_blocks matmul FloatType[?,256] x 256x256 + bias, "}[wl]
                                + f"{rows_full} rows per GPU", "rows_per_gpu": rows_full},
         "cpu_baseline": {"value": value, "unit": "rows/s", "cores": cores, "kind": "port", "sample": desc},
         "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},

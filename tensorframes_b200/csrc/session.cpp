@@ -702,6 +702,78 @@ bool make_chain(const EltProgram& prog, ChainProgram& ch) {
 
 }  // namespace
 
+// The constant operand of a tensor-core MatMul, split once per session into tf32 hi / lo parts laid out [N, K].
+std::unordered_map<int, std::pair<float*, float*>>::iterator Session::ensure_tc_weights(const Node& n, const float* b, int64_t Nc,
+                                                                                         int64_t K, cudaStream_t stream) {
+  const int key = n.in[1] * 2 + (n.transpose_b ? 1 : 0);
+  auto it = tc_weights_.find(key);
+  if (it == tc_weights_.end()) {
+    float *hi = nullptr, *lo = nullptr;
+    TFS_CUDA(cudaMalloc(reinterpret_cast<void**>(&hi), matmul_tc_weight_bytes(Nc, K)));
+    TFS_CUDA(cudaMalloc(reinterpret_cast<void**>(&lo), matmul_tc_weight_bytes(Nc, K)));
+    launches_ += launch_split_weights(b, n.transpose_b, K, Nc, hi, lo, stream);
+    it = tc_weights_.emplace(key, std::make_pair(hi, lo)).first;
+  }
+  return it;
+}
+
+// One step of a plan on `stream`; dev_ptr holds the device address of every materialised node.
+void Session::exec_step(const Plan& plan, size_t step_index, std::vector<void*>& dev_ptr, cudaStream_t stream) {
+  const Step& s = plan.steps[step_index];
+  switch (s.kind) {
+    case Step::ELT: {
+      if (s.shape.numel() == 0) break;
+      GroupCompiler gc(g_, plan.shape, dev_ptr, plan.materialize, s);
+      gc.build(err_flag_);
+      ChainProgram chain;
+      if (make_chain(gc.prog, chain)) launches_ += launch_chain(chain, s.shape.numel(), dev_, stream);
+      else launches_ += launch_eltwise(gc.prog, s.shape.numel(), gc.wide, dev_, stream);
+      break;
+    }
+    case Step::REDUCE_AXIS0: {
+      const Node& n = g_.nodes[size_t(s.nodes[0])];
+      if (s.inner > 0)
+        launches_ += launch_reduce_axis0(n.dtype, n.red_op, dev_ptr[size_t(n.in[0])], s.outer, s.inner,
+                                         dev_ptr[size_t(s.nodes[0])], red_scratch_, dev_, stream);
+      break;
+    }
+    case Step::REDUCE_ROWS: {
+      const Node& n = g_.nodes[size_t(s.nodes[0])];
+      launches_ += launch_reduce_rows(n.dtype, n.red_op, dev_ptr[size_t(n.in[0])], s.outer, s.inner,
+                                      dev_ptr[size_t(s.nodes[0])], dev_, stream);
+      break;
+    }
+    case Step::COPY: {
+      const Node& n = g_.nodes[size_t(s.nodes[0])];
+      const size_t bytes = size_t(plan.shape[size_t(s.nodes[0])].numel()) * size_t(dtype_size(n.dtype));
+      if (bytes > 0)
+        TFS_CUDA(cudaMemcpyAsync(dev_ptr[size_t(s.nodes[0])], dev_ptr[size_t(n.in[0])], bytes, cudaMemcpyDeviceToDevice, stream));
+      break;
+    }
+    case Step::MATMUL: {
+      const int mm = s.nodes[0];
+      const Node& n = g_.nodes[size_t(mm)];
+      const Shape& as = plan.shape[size_t(n.in[0])];
+      const Shape& os = plan.shape[size_t(mm)];
+      const int64_t M = os.d[0], Nc = os.d[1], K = n.transpose_a ? as.d[0] : as.d[1];
+      const float* a = static_cast<const float*>(dev_ptr[size_t(n.in[0])]);
+      const float* b = static_cast<const float*>(dev_ptr[size_t(n.in[1])]);
+      const float* bias = s.bias_node >= 0 ? static_cast<const float*>(dev_ptr[size_t(s.bias_node)]) : nullptr;
+      float* out = static_cast<float*>(dev_ptr[size_t(s.out_node >= 0 ? s.out_node : mm)]);
+      if (M * Nc == 0) break;
+      const bool const_b = g_.nodes[size_t(n.in[1])].cls == OpClass::Const;
+      static const bool force_simt = [] { const char* e = std::getenv("TFS_MATMUL_IMPL"); return e && std::string(e) == "simt"; }();
+      if (!force_simt && const_b && matmul_tc_supported(a, out, M, Nc, K, n.transpose_a)) {
+        auto it = ensure_tc_weights(n, b, Nc, K, stream);
+        launches_ += launch_matmul_tc(a, it->second.first, it->second.second, bias, out, M, Nc, K, dev_, stream);
+      } else {
+        launches_ += launch_matmul_simt(a, b, bias, out, M, Nc, K, n.transpose_a, n.transpose_b, dev_, stream);
+      }
+      break;
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------
 // Host ingest pipeline (K0) for row-separable map graphs
 // ---------------------------------------------------------------------------
@@ -713,32 +785,47 @@ bool make_chain(const EltProgram& prog, ChainProgram& ch) {
 // (impl/TFDataOps.scala:27-59, impl/datatypes.scala:344-347, 365-370), which is fully serial.
 bool Session::run_pipelined(const std::vector<TensorArg>& feeds, const std::vector<TensorArg>& fetches, const Plan& plan) {
   constexpr size_t kChunkBytes = size_t(32) << 20;    // per-chunk budget of the widest column
-  if (plan.steps.size() != 1 || plan.steps[0].kind != Step::ELT) return false;
+  if (plan.steps.size() != 1) return false;
   const Step& st = plan.steps[0];
-  if (st.shape.rank < 1) return false;
-  const int64_t n = st.shape.d[0];
+  const bool is_mm = st.kind == Step::MATMUL;
+  if (st.kind != Step::ELT && !is_mm) return false;
+  int64_t n = 0;
+  if (is_mm) {
+    // x[n, K] (a fed placeholder, not transposed) times a constant matrix (+ constant bias): rows are independent
+    const Node& mm = g_.nodes[size_t(st.nodes[0])];
+    if (mm.transpose_a || g_.nodes[size_t(mm.in[0])].cls != OpClass::Placeholder ||
+        g_.nodes[size_t(mm.in[1])].cls != OpClass::Const)
+      return false;
+    if (st.bias_node >= 0 && g_.nodes[size_t(st.bias_node)].cls != OpClass::Const) return false;
+    n = plan.shape[size_t(st.nodes[0])].d[0];
+  } else {
+    if (st.shape.rank < 1) return false;
+    n = st.shape.d[0];
+  }
   for (const TensorArg& f : feeds)
     if (!is_pinned_host_pointer(f.data)) return false;
   for (const TensorArg& f : fetches)
     if (!is_pinned_host_pointer(f.data)) return false;
-  // every fed placeholder and every fetch must be a [n, ...] block of the group's row count
+  // every fed placeholder and every fetch must be a [n, ...] block of the step's row count
   size_t max_row_bytes = 0, total_bytes = 0;
   auto row_bytes = [&](int idx) {
     const Shape& sh = plan.shape[size_t(idx)];
     return size_t(sh.numel() / std::max<int64_t>(n, 1)) * size_t(dtype_size(g_.nodes[size_t(idx)].dtype));
   };
+  const int out_node = is_mm ? (st.out_node >= 0 ? st.out_node : st.nodes[0]) : -1;
   for (int idx : plan.needed) {
     const Node& nd = g_.nodes[size_t(idx)];
     if (nd.cls == OpClass::Placeholder) {
       const Shape& sh = plan.shape[size_t(idx)];
-      if (sh.rank < 1 || sh.d[0] != n || sh.numel() != st.shape.numel() * (sh.numel() / std::max<int64_t>(st.shape.numel(), 1))) return false;
-      if (sh.numel() != st.shape.numel()) return false;     // only same-shaped columns (no per-row broadcast)
+      if (sh.rank < 1 || sh.d[0] != n) return false;
+      if (!is_mm && sh.numel() != st.shape.numel()) return false;     // only same-shaped columns (no per-row broadcast)
       max_row_bytes = std::max(max_row_bytes, row_bytes(idx));
       total_bytes += size_t(sh.numel()) * size_t(dtype_size(nd.dtype));
     }
   }
   for (int f : plan.fetch_nodes) {
-    if (plan.step_of[size_t(f)] != 0 || plan.shape[size_t(f)] != st.shape) return false;
+    if (plan.step_of[size_t(f)] != 0) return false;
+    if (is_mm ? f != out_node : plan.shape[size_t(f)] != st.shape) return false;
     max_row_bytes = std::max(max_row_bytes, row_bytes(f));
   }
   if (total_bytes < 4 * kChunkBytes || max_row_bytes == 0) return false;   // small blocks: one shot is as good
@@ -782,6 +869,14 @@ bool Session::run_pipelined(const std::vector<TensorArg>& feeds, const std::vect
   std::vector<void*> const_ptr(N, nullptr);
   for (int idx : plan.needed)
     if (g_.nodes[size_t(idx)].cls == OpClass::Const && plan.materialize[size_t(idx)]) const_ptr[size_t(idx)] = const_device(idx);
+  if (is_mm) {
+    // the tf32 hi/lo split of the constant matrix is cached per session: make sure it exists (on the session
+    // stream) before two pipeline streams would both try to create it
+    const Node& mm = g_.nodes[size_t(st.nodes[0])];
+    const Shape& os = plan.shape[size_t(st.nodes[0])];
+    const Shape& as = plan.shape[size_t(mm.in[0])];
+    ensure_tc_weights(mm, static_cast<const float*>(const_ptr[size_t(mm.in[1])]), os.d[1], as.d[1], stream_);
+  }
   // everything enqueued so far on the session stream (constant uploads) precedes the pipeline
   TFS_CUDA(cudaEventRecord(pipe_event_, stream_));
   for (int k = 0; k < 2; ++k) TFS_CUDA(cudaStreamWaitEvent(pipe_stream_[k], pipe_event_, 0));
@@ -804,11 +899,7 @@ bool Session::run_pipelined(const std::vector<TensorArg>& feeds, const std::vect
       TFS_CUDA(cudaMemcpyAsync(dev_ptr[size_t(idx)], static_cast<const char*>(f.data) + size_t(r0) * rb,
                                size_t(rows_here) * rb, cudaMemcpyHostToDevice, sx));
     }
-    GroupCompiler gc(g_, cp.shape, dev_ptr, cp.materialize, cp.steps[0]);
-    gc.build(err_flag_);
-    ChainProgram chain;
-    if (make_chain(gc.prog, chain)) launches_ += launch_chain(chain, cp.steps[0].shape.numel(), dev_, sx);
-    else launches_ += launch_eltwise(gc.prog, cp.steps[0].shape.numel(), gc.wide, dev_, sx);
+    exec_step(cp, 0, dev_ptr, sx);
     for (size_t i = 0; i < fetches.size(); ++i) {
       const int idx = plan.fetch_nodes[i];
       const size_t rb = row_bytes(idx);
@@ -926,67 +1017,7 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
   }
 
   // steps
-  for (const Step& s : plan.steps) {
-    switch (s.kind) {
-      case Step::ELT: {
-        if (s.shape.numel() == 0) break;
-        GroupCompiler gc(g_, plan.shape, dev_ptr, plan.materialize, s);
-        gc.build(err_flag_);
-        ChainProgram chain;
-        if (make_chain(gc.prog, chain)) launches_ += launch_chain(chain, s.shape.numel(), dev_, stream_);
-        else launches_ += launch_eltwise(gc.prog, s.shape.numel(), gc.wide, dev_, stream_);
-        break;
-      }
-      case Step::REDUCE_AXIS0: {
-        const Node& n = g_.nodes[size_t(s.nodes[0])];
-        if (s.inner > 0)
-          launches_ += launch_reduce_axis0(n.dtype, n.red_op, dev_ptr[size_t(n.in[0])], s.outer, s.inner,
-                                           dev_ptr[size_t(s.nodes[0])], red_scratch_, dev_, stream_);
-        break;
-      }
-      case Step::REDUCE_ROWS: {
-        const Node& n = g_.nodes[size_t(s.nodes[0])];
-        launches_ += launch_reduce_rows(n.dtype, n.red_op, dev_ptr[size_t(n.in[0])], s.outer, s.inner,
-                                        dev_ptr[size_t(s.nodes[0])], dev_, stream_);
-        break;
-      }
-      case Step::COPY: {
-        const Node& n = g_.nodes[size_t(s.nodes[0])];
-        if (nbytes(s.nodes[0]) > 0)
-          TFS_CUDA(cudaMemcpyAsync(dev_ptr[size_t(s.nodes[0])], dev_ptr[size_t(n.in[0])], nbytes(s.nodes[0]),
-                                   cudaMemcpyDeviceToDevice, stream_));
-        break;
-      }
-      case Step::MATMUL: {
-        const int mm = s.nodes[0];
-        const Node& n = g_.nodes[size_t(mm)];
-        const Shape& as = plan.shape[size_t(n.in[0])];
-        const Shape& os = plan.shape[size_t(mm)];
-        const int64_t M = os.d[0], Nc = os.d[1], K = n.transpose_a ? as.d[0] : as.d[1];
-        const float* a = static_cast<const float*>(dev_ptr[size_t(n.in[0])]);
-        const float* b = static_cast<const float*>(dev_ptr[size_t(n.in[1])]);
-        const float* bias = s.bias_node >= 0 ? static_cast<const float*>(dev_ptr[size_t(s.bias_node)]) : nullptr;
-        float* out = static_cast<float*>(dev_ptr[size_t(s.out_node >= 0 ? s.out_node : mm)]);
-        if (M * Nc == 0) break;
-        const bool const_b = g_.nodes[size_t(n.in[1])].cls == OpClass::Const;
-        static const bool force_simt = [] { const char* e = std::getenv("TFS_MATMUL_IMPL"); return e && std::string(e) == "simt"; }();
-        if (!force_simt && const_b && matmul_tc_supported(a, out, M, Nc, K, n.transpose_a)) {
-          auto it = tc_weights_.find(n.in[1] * 2 + (n.transpose_b ? 1 : 0));
-          if (it == tc_weights_.end()) {   // split the constant once per session: [N, K] K-major hi / lo parts
-            float *hi = nullptr, *lo = nullptr;
-            TFS_CUDA(cudaMalloc(reinterpret_cast<void**>(&hi), matmul_tc_weight_bytes(Nc, K)));
-            TFS_CUDA(cudaMalloc(reinterpret_cast<void**>(&lo), matmul_tc_weight_bytes(Nc, K)));
-            launches_ += launch_split_weights(b, n.transpose_b, K, Nc, hi, lo, stream_);
-            it = tc_weights_.emplace(n.in[1] * 2 + (n.transpose_b ? 1 : 0), std::make_pair(hi, lo)).first;
-          }
-          launches_ += launch_matmul_tc(a, it->second.first, it->second.second, bias, out, M, Nc, K, dev_, stream_);
-        } else {
-          launches_ += launch_matmul_simt(a, b, bias, out, M, Nc, K, n.transpose_a, n.transpose_b, dev_, stream_);
-        }
-        break;
-      }
-    }
-  }
+  for (size_t k = 0; k < plan.steps.size(); ++k) exec_step(plan, k, dev_ptr, stream_);
 
   // results
   for (size_t i = 0; i < fetches.size(); ++i) {

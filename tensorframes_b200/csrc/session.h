@@ -46,6 +46,9 @@ class Session {
   void ensure_device();
   void build_plan(const std::vector<TensorArg>& feeds, const std::vector<std::string>& fetch_names, Plan& plan,
                   bool rows = false);
+  std::unordered_map<int, std::pair<float*, float*>>::iterator ensure_tc_weights(const Node& n, const float* b, int64_t Nc, int64_t K,
+                                                                                 cudaStream_t stream);
+  void exec_step(const Plan& plan, size_t step_index, std::vector<void*>& dev_ptr, cudaStream_t stream);
   bool run_pipelined(const std::vector<TensorArg>& feeds, const std::vector<TensorArg>& fetches, const Plan& plan);
   void* const_device(int node);
   void reserve_workspace(size_t bytes);
