@@ -160,6 +160,51 @@ def evaluate(graph_bytes: bytes, feeds: Dict[str, np.ndarray], fetches: Sequence
             dims = [int(v) for v in np.asarray(ev(n.inputs[0])).reshape(-1)]
             val = ev(n.inputs[1])
             out = np.full(dims, val, dtype=val.dtype)
+        elif op in ("OnesLike", "ZerosLike"):
+            a = ev(n.inputs[0])
+            out = np.ones_like(a) if op == "OnesLike" else np.zeros_like(a)
+        elif op == "Shape":
+            a = ev(n.inputs[0])
+            out = np.asarray(a.shape, dtype=DT[attr(n, "out_type", "type", default=3)])
+        elif op == "StridedSlice":
+            # x[b:e:s] / x[i] on vectors, as python TF emits for tf.shape(x)[0]
+            a = ev(n.inputs[0])
+            b, e, st = (np.asarray(ev(i)).reshape(-1) for i in n.inputs[1:4])
+            if a.ndim != 1 or len(b) != 1:
+                raise OracleError(f"node {name}: only one-dimensional StridedSlice is in the subset")
+            if attr(n, "ellipsis_mask", "i", default=0) or attr(n, "new_axis_mask", "i", default=0):
+                raise OracleError(f"node {name}: ellipsis / new-axis masks are not in the subset")
+            if attr(n, "shrink_axis_mask", "i", default=0) & 1:
+                out = np.asarray(a[int(b[0])])
+            else:
+                lo = None if attr(n, "begin_mask", "i", default=0) & 1 else int(b[0])
+                hi = None if attr(n, "end_mask", "i", default=0) & 1 else int(e[0])
+                out = a[lo:hi:int(st[0])]
+        elif op == "Pack":
+            out = np.stack([ev(i) for i in n.inputs], axis=int(attr(n, "axis", "i", default=0)))
+        elif op == "ExpandDims":
+            out = np.expand_dims(ev(n.inputs[0]), int(np.asarray(ev(n.inputs[1])).reshape(-1)[0]))
+        elif op == "Tile":
+            a = ev(n.inputs[0])
+            reps = [int(v) for v in np.asarray(ev(n.inputs[1])).reshape(-1)]
+            if len(reps) != a.ndim:
+                raise OracleError(f"node {name}: multiples must have one entry per dimension")
+            out = np.tile(a, reps)
+        elif op in ("ArgMin", "ArgMax"):
+            a = ev(n.inputs[0])
+            ax = int(np.asarray(ev(n.inputs[1])).reshape(-1)[0])
+            idx = np.argmin(a, axis=ax) if op == "ArgMin" else np.argmax(a, axis=ax)   # first extreme wins, like Eigen
+            out = idx.astype(DT[attr(n, "output_type", "type", default=9)])
+        elif op == "UnsortedSegmentSum":
+            data, ids = ev(n.inputs[0]), np.asarray(ev(n.inputs[1]))
+            k = int(np.asarray(ev(n.inputs[2])).reshape(-1)[0])
+            if ids.ndim != 1 or ids.shape[0] != data.shape[0]:
+                raise OracleError(f"node {name}: segment_ids must be a vector over the rows of data")
+            if ids.size and (ids.min() < 0 or ids.max() >= k):
+                raise OracleError(f"node {name}: segment ids out of range")
+            out = np.zeros((k,) + data.shape[1:], dtype=data.dtype)
+            for i in range(data.shape[0]):          # row order, one accumulation per row: the CPU kernel's order
+                out[ids[i]] = out[ids[i]] + data[i]
         else:
             raise OracleError(f"op {op} is not in the subset")
         cache[name] = np.asarray(out)

@@ -246,6 +246,11 @@ bool attr_bool(const Node& n, const char* key, bool dflt) {
   return a ? a->b : dflt;
 }
 
+int64_t attr_int(const Node& n, const char* key, int64_t dflt) {
+  const Attr* a = get_attr(n, key, Attr::I);
+  return a ? a->i : dflt;
+}
+
 struct OpDesc { const char* name; OpClass cls; int code; };
 const OpDesc kOps[] = {
     {"Placeholder", OpClass::Placeholder, 0},
@@ -259,6 +264,16 @@ const OpDesc kOps[] = {
     {"Reciprocal", OpClass::Unary, E_RECIP},
     {"Inv", OpClass::Unary, E_RECIP},
     {"Cast", OpClass::Unary, E_CAST},
+    {"OnesLike", OpClass::Unary, E_ONES_LIKE},
+    {"ZerosLike", OpClass::Unary, E_ZEROS_LIKE},
+    {"Shape", OpClass::ShapeOf, 0},
+    {"StridedSlice", OpClass::StridedSlice, 0},
+    {"Pack", OpClass::Pack, 0},
+    {"ExpandDims", OpClass::ExpandDims, 0},
+    {"Tile", OpClass::Tile, 0},
+    {"ArgMin", OpClass::ArgMinMax, 1},
+    {"ArgMax", OpClass::ArgMinMax, 0},
+    {"UnsortedSegmentSum", OpClass::SegmentSum, 0},
     {"Add", OpClass::Binary, E_ADD},
     {"BiasAdd", OpClass::Binary, E_ADD},
     {"Sub", OpClass::Binary, E_SUB},
@@ -335,7 +350,62 @@ std::vector<int> normalize_axes(const Node& n, int rank) {
   return std::vector<int>(s.begin(), s.end());
 }
 
-Shape infer_shape(const Graph& g, const Node& n, const std::vector<Shape>& in) {
+namespace {
+int norm_axis(const Node& n, int axis, int rank_plus, const char* what) {
+  const int x = axis < 0 ? axis + rank_plus : axis;
+  TFS_CHECK(x >= 0 && x < rank_plus, TFS_ERR_INVALID,
+            "node '" + n.name + "' (" + n.op + "): " + what + " " + std::to_string(axis) + " out of range");
+  return x;
+}
+}  // namespace
+
+bool infer_int_value(const Graph& g, const Node& n, const std::vector<Shape>& in, const IntVals& vals, std::vector<int64_t>& out) {
+  (void)g;
+  out.clear();
+  switch (n.cls) {
+    case OpClass::Const:
+      if ((n.dtype != TFS_INT32 && n.dtype != TFS_INT64) || n.value.shape.rank > 1 || n.value.numel() > 64) return false;
+      out = const_ints(n.value);
+      return true;
+    case OpClass::ShapeOf:
+      if (!in[0].known_rank()) return false;
+      for (int i = 0; i < in[0].rank; ++i) out.push_back(in[0].d[i]);
+      return true;
+    case OpClass::StridedSlice: {
+      // 1-D integer vectors only: x[b:e:s] or x[i] (shrink)
+      if (!vals[0] || !vals[1] || !vals[2] || !vals[3]) return false;
+      const std::vector<int64_t>& x = *vals[0];
+      TFS_CHECK(vals[1]->size() == 1 && vals[2]->size() == 1 && vals[3]->size() == 1, TFS_ERR_UNSUPPORTED,
+                "node '" + n.name + "' (StridedSlice): only slices of one-dimensional shape vectors are supported");
+      const int64_t len = int64_t(x.size());
+      int64_t b = (*vals[1])[0], e = (*vals[2])[0], st = (*vals[3])[0];
+      TFS_CHECK(st == 1, TFS_ERR_UNSUPPORTED, "node '" + n.name + "' (StridedSlice): only stride 1 is supported");
+      if (b < 0) b += len;
+      if (n.ss_shrink_mask & 1) {
+        TFS_CHECK(b >= 0 && b < len, TFS_ERR_INVALID, "node '" + n.name + "' (StridedSlice): index out of range");
+        out.push_back(x[size_t(b)]);
+        return true;
+      }
+      if (e < 0) e += len;
+      if (n.ss_begin_mask & 1) b = 0;
+      if (n.ss_end_mask & 1) e = len;
+      b = std::max<int64_t>(0, std::min(b, len));
+      e = std::max<int64_t>(b, std::min(e, len));
+      for (int64_t i = b; i < e; ++i) out.push_back(x[size_t(i)]);
+      return true;
+    }
+    case OpClass::Pack:
+      for (size_t k = 0; k < n.in.size(); ++k) {
+        if (!vals[k] || vals[k]->size() != 1) return false;
+        out.push_back((*vals[k])[0]);
+      }
+      return true;
+    default:
+      return false;
+  }
+}
+
+Shape infer_shape(const Graph& g, const Node& n, const std::vector<Shape>& in, const IntVals& vals) {
   switch (n.cls) {
     case OpClass::Placeholder: {
       const Attr* a = get_attr(n, "shape", Attr::SHAPE);
@@ -383,9 +453,77 @@ Shape infer_shape(const Graph& g, const Node& n, const std::vector<Shape>& in) {
       }
       return out;
     }
+    case OpClass::ShapeOf: {
+      Shape out; out.rank = 1;
+      out.d[0] = in[0].known_rank() ? in[0].rank : -1;
+      return out;
+    }
+    case OpClass::StridedSlice:
+    case OpClass::Pack: {
+      // (the run-time planner insists on the value; at import an unknown one only leaves the length open)
+      std::vector<int64_t> v;
+      const bool known = infer_int_value(g, n, in, vals, v);
+      Shape out;
+      if (n.cls == OpClass::StridedSlice && (n.ss_shrink_mask & 1)) { out.rank = 0; return out; }
+      out.rank = 1;
+      out.d[0] = known ? int64_t(v.size()) : (n.cls == OpClass::Pack ? int64_t(n.in.size()) : -1);
+      return out;
+    }
+    case OpClass::ExpandDims: {
+      const Shape& x = in[0];
+      if (!x.known_rank()) return Shape();
+      TFS_CHECK(x.rank + 1 <= TFS_MAX_RANK, TFS_ERR_UNSUPPORTED, "node '" + n.name + "' (ExpandDims): rank too large");
+      const int ax = norm_axis(n, n.axis, x.rank + 1, "dim");
+      Shape out; out.rank = x.rank + 1;
+      for (int i = 0, j = 0; i < out.rank; ++i) out.d[i] = (i == ax) ? 1 : x.d[j++];
+      return out;
+    }
+    case OpClass::Tile: {
+      const Shape& x = in[0];
+      if (!x.known_rank()) return Shape();
+      Shape out; out.rank = x.rank;
+      for (int i = 0; i < x.rank; ++i) out.d[i] = -1;
+      if (vals[1]) {
+        TFS_CHECK(int(vals[1]->size()) == x.rank, TFS_ERR_INVALID,
+                  "node '" + n.name + "' (Tile): multiples has " + std::to_string(vals[1]->size()) + " entries for an input of rank " +
+                      std::to_string(x.rank));
+        for (int i = 0; i < x.rank; ++i) {
+          const int64_t m = (*vals[1])[size_t(i)];
+          TFS_CHECK(m >= -1, TFS_ERR_INVALID, "node '" + n.name + "' (Tile): negative multiple");
+          out.d[i] = (m < 0 || x.d[i] < 0) ? -1 : m * x.d[i];
+        }
+      }
+      return out;
+    }
+    case OpClass::ArgMinMax: {
+      const Shape& x = in[0];
+      if (!x.known_rank()) return Shape();
+      TFS_CHECK(x.rank >= 1, TFS_ERR_INVALID, "node '" + n.name + "' (" + n.op + "): input must have at least one dimension");
+      const int ax = norm_axis(n, n.axis, x.rank, "dimension");
+      Shape out; out.rank = 0;
+      for (int i = 0; i < x.rank; ++i)
+        if (i != ax) out.d[out.rank++] = x.d[i];
+      return out;
+    }
+    case OpClass::SegmentSum: {
+      const Shape &x = in[0], &ids = in[1];
+      if (!x.known_rank() || !ids.known_rank()) return Shape();
+      TFS_CHECK(ids.rank == 1 && x.rank >= 1, TFS_ERR_UNSUPPORTED,
+                "node '" + n.name + "' (UnsortedSegmentSum): segment_ids must be a vector over the rows of data");
+      TFS_CHECK(x.d[0] < 0 || ids.d[0] < 0 || x.d[0] == ids.d[0], TFS_ERR_INVALID,
+                "node '" + n.name + "' (UnsortedSegmentSum): data has " + std::to_string(x.d[0]) + " rows, segment_ids " +
+                    std::to_string(ids.d[0]));
+      Shape out = x;
+      out.d[0] = (vals[2] && vals[2]->size() == 1) ? (*vals[2])[0] : -1;
+      return out;
+    }
   }
   return Shape();
 }
+
+namespace {
+int desc_code_of(const Node& n) { return n.op == "ArgMin" ? 1 : 0; }
+}  // namespace
 
 Graph import_graphdef(const uint8_t* data, size_t len) {
   Graph g;
@@ -421,9 +559,15 @@ Graph import_graphdef(const uint8_t* data, size_t len) {
     size_t want = 0;
     switch (n.cls) {
       case OpClass::Placeholder: case OpClass::Const: want = 0; break;
-      case OpClass::Unary: want = 1; break;
+      case OpClass::Unary: case OpClass::ShapeOf: want = 1; break;
+      case OpClass::StridedSlice: want = 4; break;
+      case OpClass::SegmentSum: want = 3; break;
+      case OpClass::Pack: want = n.in.size(); break;
       default: want = 2;
     }
+    if (n.cls == OpClass::Pack)
+      TFS_CHECK(!n.in.empty() && int64_t(n.in.size()) == attr_int(n, "N", int64_t(n.in.size())), TFS_ERR_INVALID,
+                "node '" + n.name + "' (Pack): attr N differs from the number of inputs");
     TFS_CHECK(n.in.size() == want, TFS_ERR_INVALID,
               "node '" + n.name + "' (" + n.op + "): expected " + std::to_string(want) + " inputs, found " +
                   std::to_string(n.in.size()));
@@ -486,7 +630,8 @@ Graph import_graphdef(const uint8_t* data, size_t len) {
                   "node '" + n.name + "' (" + n.op + "): attr T is " + dtype_name(n.dtype) + " but the inputs are " +
                       dtype_name(in_dtype(0)) + " and " + dtype_name(in_dtype(1)));
         if (n.cls == OpClass::MatMul) {
-          TFS_CHECK(n.dtype == TFS_FLOAT, TFS_ERR_UNSUPPORTED, "node '" + n.name + "' (MatMul): only float32 is supported");
+          TFS_CHECK(n.dtype == TFS_FLOAT || n.dtype == TFS_DOUBLE, TFS_ERR_UNSUPPORTED,
+                    "node '" + n.name + "' (MatMul): only float32 and float64 are supported");
           n.transpose_a = attr_bool(n, "transpose_a", false);
           n.transpose_b = attr_bool(n, "transpose_b", false);
         }
@@ -501,6 +646,52 @@ Graph import_graphdef(const uint8_t* data, size_t len) {
         n.keep_dims = attr_bool(n, "keep_dims", false);
         break;
       }
+      case OpClass::ShapeOf: {
+        auto ot = n.attrs.find("out_type");
+        n.dtype = (ot != n.attrs.end() && ot->second.kind == Attr::TYPE) ? ot->second.type : TFS_INT32;
+        TFS_CHECK(n.dtype == TFS_INT32 || n.dtype == TFS_INT64, TFS_ERR_INVALID, "node '" + n.name + "' (Shape): out_type must be int32 or int64");
+        break;
+      }
+      case OpClass::StridedSlice:
+        n.dtype = in_dtype(0);
+        n.ss_begin_mask = int(attr_int(n, "begin_mask", 0));
+        n.ss_end_mask = int(attr_int(n, "end_mask", 0));
+        n.ss_shrink_mask = int(attr_int(n, "shrink_axis_mask", 0));
+        TFS_CHECK(attr_int(n, "ellipsis_mask", 0) == 0 && attr_int(n, "new_axis_mask", 0) == 0, TFS_ERR_UNSUPPORTED,
+                  "node '" + n.name + "' (StridedSlice): ellipsis / new-axis slicing is not supported");
+        break;
+      case OpClass::Pack:
+        n.dtype = in_dtype(0);
+        for (size_t k = 1; k < n.in.size(); ++k)
+          TFS_CHECK(in_dtype(k) == n.dtype, TFS_ERR_INVALID, "node '" + n.name + "' (Pack): inputs differ in dtype");
+        TFS_CHECK(attr_int(n, "axis", 0) == 0, TFS_ERR_UNSUPPORTED, "node '" + n.name + "' (Pack): only axis 0 is supported");
+        break;
+      case OpClass::ExpandDims:
+      case OpClass::ArgMinMax: {
+        const Node& ax = g.nodes[size_t(n.in[1])];
+        TFS_CHECK(ax.cls == OpClass::Const && (ax.dtype == TFS_INT32 || ax.dtype == TFS_INT64) && ax.value.numel() == 1,
+                  TFS_ERR_UNSUPPORTED, "node '" + n.name + "' (" + n.op + "): the axis must be an integer scalar Const");
+        n.axis = int(const_ints(ax.value)[0]);
+        if (n.cls == OpClass::ExpandDims) {
+          n.dtype = in_dtype(0);
+        } else {
+          auto ot = n.attrs.find("output_type");
+          n.dtype = (ot != n.attrs.end() && ot->second.kind == Attr::TYPE) ? ot->second.type : TFS_INT64;
+          TFS_CHECK(n.dtype == TFS_INT32 || n.dtype == TFS_INT64, TFS_ERR_INVALID,
+                    "node '" + n.name + "' (" + n.op + "): output_type must be int32 or int64");
+          n.arg_min = desc_code_of(n) == 1;
+        }
+        break;
+      }
+      case OpClass::Tile:
+        n.dtype = in_dtype(0);
+        TFS_CHECK(in_dtype(1) == TFS_INT32 || in_dtype(1) == TFS_INT64, TFS_ERR_INVALID, "node '" + n.name + "' (Tile): multiples must be integers");
+        break;
+      case OpClass::SegmentSum:
+        n.dtype = in_dtype(0);
+        TFS_CHECK(in_dtype(1) == TFS_INT32 || in_dtype(1) == TFS_INT64, TFS_ERR_INVALID,
+                  "node '" + n.name + "' (UnsortedSegmentSum): segment_ids must be int32 or int64");
+        break;
       case OpClass::Fill: {
         n.dtype = attr_type(n, "T");
         TFS_CHECK(n.dtype == in_dtype(1), TFS_ERR_INVALID, "node '" + n.name + "' (Fill): attr T differs from the value dtype");
@@ -511,8 +702,13 @@ Graph import_graphdef(const uint8_t* data, size_t len) {
       }
     }
     std::vector<Shape> in_shapes;
-    for (int k : n.in) in_shapes.push_back(g.nodes[size_t(k)].sshape);
-    n.sshape = infer_shape(g, n, in_shapes);
+    IntVals in_vals;
+    for (int k : n.in) {
+      in_shapes.push_back(g.nodes[size_t(k)].sshape);
+      in_vals.push_back(g.nodes[size_t(k)].has_ival ? &g.nodes[size_t(k)].ival : nullptr);
+    }
+    n.has_ival = infer_int_value(g, n, in_shapes, in_vals, n.ival);
+    n.sshape = infer_shape(g, n, in_shapes, in_vals);
   }
   return g;
 }

@@ -44,12 +44,21 @@ enum class OpClass {
   Reduce,   // Sum, Min, Max with Const reduction_indices
   MatMul,
   Fill,
+  // shape plumbing of the k-means / geometric-mean snippets (tensorframes_snippets/kmeans_demo.py:26-43, 76-79, 136-144)
+  ShapeOf,       // Shape: int vector known once the input shape is
+  StridedSlice,  // on such int vectors only (tf.shape(x)[0])
+  Pack,          // stack of int scalars -> int vector (tf.stack([n, 1]))
+  ExpandDims,
+  Tile,
+  ArgMinMax,     // ArgMin / ArgMax along one axis
+  SegmentSum,    // UnsortedSegmentSum(data, segment_ids, num_segments)
 };
 
 // Element-wise opcodes; shared with the device interpreter (program.h mirrors these values).
 enum EltOp : int {
   E_IDENTITY = 0, E_NEG, E_RELU, E_SQUARE, E_ABS, E_SQRT, E_RECIP, E_CAST,
   E_ADD, E_SUB, E_MUL, E_DIV, E_MIN, E_MAX,
+  E_ONES_LIKE, E_ZEROS_LIKE,   // unary by arity only: the operand gives the shape, its data is never read
 };
 enum RedOp : int { R_SUM = 0, R_MIN = 1, R_MAX = 2 };
 
@@ -69,6 +78,13 @@ struct Node {
   bool keep_dims = false;          // Reduce
   bool transpose_a = false, transpose_b = false;  // MatMul
   TensorValue value;               // Const
+  int axis = 0;                    // ExpandDims dim / ArgMinMax dimension (as written, may be negative)
+  bool arg_min = true;             // ArgMinMax
+  int ss_begin_mask = 0, ss_end_mask = 0, ss_shrink_mask = 0;   // StridedSlice
+  // Small integer tensors whose VALUE follows from shapes and constants (Shape, StridedSlice, Pack, int Consts):
+  // statically known entries, -1 where the value depends on a dimension not known at import.
+  bool has_ival = false;
+  std::vector<int64_t> ival;
 };
 
 struct Graph {
@@ -81,9 +97,18 @@ struct Graph {
 // Parses + validates + statically analyses a binary GraphDef. Throws tfs::Error.
 Graph import_graphdef(const uint8_t* data, size_t len);
 
-// Shape of node `n`'s output given the shapes of its inputs (dims may be -1).
+// Integer value of an input as far as it is known (nullptr: not an integer-valued node).
+using IntVals = std::vector<const std::vector<int64_t>*>;
+
+// Shape of node `n`'s output given the shapes of its inputs (dims may be -1) and, for the ops whose output
+// shape depends on an input VALUE (Fill dims, Tile multiples, UnsortedSegmentSum num_segments), those values.
 // Used with static shapes at import and with concrete shapes at run time.
-Shape infer_shape(const Graph& g, const Node& n, const std::vector<Shape>& in_shapes);
+Shape infer_shape(const Graph& g, const Node& n, const std::vector<Shape>& in_shapes, const IntVals& in_vals);
+
+// Integer value of node `n` (Shape / StridedSlice / Pack / small int Const) from its inputs' shapes and values;
+// false when `n` is not such a node. Entries are -1 where unknown.
+bool infer_int_value(const Graph& g, const Node& n, const std::vector<Shape>& in_shapes, const IntVals& in_vals,
+                     std::vector<int64_t>& out);
 
 // Normalised, sorted, de-duplicated reduction axes for an input of `rank`.
 std::vector<int> normalize_axes(const Node& n, int rank);

@@ -38,9 +38,20 @@ int launch_reduce_axis0(int dtype, int red_op, const void* in, int64_t outer, in
 int launch_reduce_rows(int dtype, int red_op, const void* in, int64_t outer, int64_t inner, void* out,
                        const DeviceInfo& dev, cudaStream_t stream);
 
-// K4: out[M, N] = op(a) * op(b) (+ bias[N]); float32. The SIMT kernel takes any shape.
-int launch_matmul_simt(const float* a, const float* b, const float* bias, float* out, int64_t M, int64_t N, int64_t K,
+// K4: out[M, N] = op(a) * op(b) (+ bias[N]); float32 or float64 (dtype). The SIMT kernel takes any shape.
+int launch_matmul_simt(int dtype, const void* a, const void* b, const void* bias, void* out, int64_t M, int64_t N, int64_t K,
                        bool ta, bool tb, const DeviceInfo& dev, cudaStream_t stream);
+
+// Shape-changing steps (kernels_shape.cu). Tile copies elem_size-byte elements (4 or 8).
+int launch_tile(int elem_size, const void* in, const Shape& in_shape, void* out, const Shape& out_shape, const DeviceInfo& dev,
+                cudaStream_t stream);
+// out[o, i] = arg extreme over a of in[o, a, i]; ties -> smallest index. out_dtype: TFS_INT32 or TFS_INT64.
+int launch_argminmax(int dtype, int out_dtype, bool is_min, const void* in, int64_t outer, int64_t len, int64_t inner, void* out,
+                     const DeviceInfo& dev, cudaStream_t stream);
+int launch_widen_ids(const int* in, int64_t n, int64_t* out, const DeviceInfo& dev, cudaStream_t stream);
+// out[keys[g], :] = sums[g, :] for g < groups; keys outside [0, segments) set *err to 2.
+int launch_segment_scatter(int dtype, const void* sums, const int64_t* keys, int64_t groups, int64_t cell, int64_t segments,
+                           void* out, int32_t* err, const DeviceInfo& dev, cudaStream_t stream);
 
 // tcgen05 path for x[M, K] * w[K, N] (+ bias): K % 32 == 0, N % 16 == 0, N <= 256, x not transposed.
 // w is passed pre-split into tf32-exact hi / lo parts laid out [N, K] (launch_split_weights).

@@ -15,11 +15,20 @@ size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
 bool is_elt(const Node& n) {
   return n.cls == OpClass::Unary || n.cls == OpClass::Binary || n.cls == OpClass::Fill;
 }
-bool is_compute_barrier(const Node& n) { return n.cls == OpClass::Reduce || n.cls == OpClass::MatMul; }
+// nodes whose value is a small integer vector computed on the host from shapes (no kernel unless someone reads it as data)
+bool is_host_value(const Node& n) {
+  return n.cls == OpClass::ShapeOf || n.cls == OpClass::StridedSlice || n.cls == OpClass::Pack;
+}
+bool is_like_fill(const Node& n) { return n.cls == OpClass::Unary && (n.elt_op == E_ONES_LIKE || n.elt_op == E_ZEROS_LIKE); }
+bool is_compute_barrier(const Node& n) {
+  return n.cls == OpClass::Reduce || n.cls == OpClass::MatMul || n.cls == OpClass::ExpandDims || n.cls == OpClass::Tile ||
+         n.cls == OpClass::ArgMinMax || n.cls == OpClass::SegmentSum || is_host_value(n);
+}
 
 // data operands of an element-wise node (Fill's dims input is a static attribute, not data)
 std::vector<int> elt_operands(const Node& n) {
   if (n.cls == OpClass::Fill) return {n.in[1]};
+  if (is_like_fill(n)) return {};            // OnesLike / ZerosLike take only the operand's shape
   return n.in;
 }
 
@@ -45,10 +54,11 @@ bool is_pinned_host_pointer(const void* p) {
 }
 
 struct Step {
-  enum Kind { ELT, REDUCE_AXIS0, REDUCE_ROWS, COPY, MATMUL } kind = ELT;
+  enum Kind { ELT, REDUCE_AXIS0, REDUCE_ROWS, COPY, MATMUL, HOSTVAL, TILE, ARGMINMAX, SEGSUM } kind = ELT;
   std::vector<int> nodes;   // ELT: the group (topological order); others: one node
   Shape shape;              // ELT: iteration shape
-  int64_t outer = 0, inner = 0;  // reductions
+  int64_t outer = 0, inner = 0;  // reductions, ARGMINMAX
+  int64_t len = 0;               // ARGMINMAX: length of the searched axis; SEGSUM: number of segments
   int out_node = -1, bias_node = -1;  // MATMUL with a fused "+ bias[N]" epilogue: the Add node and its bias operand
 };
 
@@ -68,6 +78,8 @@ struct Session::Plan {
   int64_t n_batch = 0;
   std::vector<char> batched;          // by node index
   std::vector<Shape> cshape;          // by node index: per-row (cell) shape
+  std::vector<std::vector<int64_t>> ival;   // by node index: integer value of shape-derived nodes (has_ival)
+  std::vector<char> has_ival;
 };
 
 Session::Session(const Graph& g, int device) : g_(g) { dev_.device = device; }
@@ -81,6 +93,7 @@ Session::~Session() {
   for (auto& kv : tc_weights_) { cudaFree(kv.second.first); cudaFree(kv.second.second); }
   if (ws_) cudaFree(ws_);
   if (red_scratch_) cudaFree(red_scratch_);
+  if (seg_scratch_) cudaFree(seg_scratch_);
   if (err_flag_) cudaFree(err_flag_);
   if (err_host_) cudaFreeHost(err_host_);
   for (int k = 0; k < 2; ++k)
@@ -125,10 +138,11 @@ void Session::check_device_error() {
   TFS_CUDA(cudaMemcpyAsync(err_host_, err_flag_, sizeof(int32_t), cudaMemcpyDeviceToHost, stream_));
   TFS_CUDA(cudaStreamSynchronize(stream_));
   if (*err_host_ != 0) {
+    const int32_t code = *err_host_;
     *err_host_ = 0;
     TFS_CUDA(cudaMemsetAsync(err_flag_, 0, sizeof(int32_t), stream_));
     TFS_CUDA(cudaStreamSynchronize(stream_));
-    fail(TFS_ERR_RUNTIME, "Integer division by zero");
+    fail(TFS_ERR_RUNTIME, code == 2 ? "UnsortedSegmentSum: segment ids out of range" : "Integer division by zero");
   }
 }
 
@@ -186,6 +200,8 @@ void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<
   plan.feed_of.assign(N, -1);
   plan.step_of.assign(N, -1);
   plan.materialize.assign(N, 0);
+  plan.ival.assign(N, {});
+  plan.has_ival.assign(N, 0);
 
   for (size_t i = 0; i < feeds.size(); ++i) {
     int idx = g_.find(feeds[i].name);
@@ -255,16 +271,29 @@ void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<
       plan.batched[size_t(idx)] = rows ? 1 : 0;
     } else {
       std::vector<Shape> in;
+      IntVals vals;
       for (int k : n.in) {
         in.push_back(plan.cshape[size_t(k)]);
-        if (plan.batched[size_t(k)]) plan.batched[size_t(idx)] = 1;
+        vals.push_back(plan.has_ival[size_t(k)] ? &plan.ival[size_t(k)] : nullptr);
+        // a Shape node reads the operand's shape, not its rows
+        if (plan.batched[size_t(k)] && !is_host_value(n)) plan.batched[size_t(idx)] = 1;
       }
-      Shape sh = infer_shape(g_, n, in);
+      plan.has_ival[size_t(idx)] = infer_int_value(g_, n, in, vals, plan.ival[size_t(idx)]) ? 1 : 0;
+      if (is_host_value(n))
+        TFS_CHECK(plan.has_ival[size_t(idx)], TFS_ERR_UNSUPPORTED,
+                  "node '" + n.name + "' (" + n.op + "): supported only on integer shape vectors (Shape, Const, Pack, StridedSlice)");
+      if (n.cls == OpClass::Tile)
+        TFS_CHECK(vals[1] != nullptr, TFS_ERR_UNSUPPORTED, "node '" + n.name + "' (Tile): multiples must follow from shapes and constants");
+      if (n.cls == OpClass::SegmentSum)
+        TFS_CHECK(vals[2] != nullptr && vals[2]->size() == 1 && (*vals[2])[0] >= 0, TFS_ERR_UNSUPPORTED,
+                  "node '" + n.name + "' (UnsortedSegmentSum): num_segments must be a non-negative scalar that follows from shapes and constants");
+      Shape sh = infer_shape(g_, n, in, vals);
       TFS_CHECK(sh.fully_known(), TFS_ERR_INVALID, "could not resolve the shape of node '" + n.name + "': " + sh.str());
       plan.cshape[size_t(idx)] = sh;
       if (rows && plan.batched[size_t(idx)])
-        TFS_CHECK(n.cls != OpClass::MatMul, TFS_ERR_UNSUPPORTED,
-                  "node '" + n.name + "' (MatMul) is not supported in row mode; use map_blocks");
+        TFS_CHECK(n.cls != OpClass::MatMul && n.cls != OpClass::Tile && n.cls != OpClass::ArgMinMax &&
+                      n.cls != OpClass::SegmentSum && n.cls != OpClass::ExpandDims,
+                  TFS_ERR_UNSUPPORTED, "node '" + n.name + "' (" + n.op + ") is not supported in row mode; use map_blocks");
     }
     plan.shape[size_t(idx)] = plan.batched[size_t(idx)] ? with_lead(plan.n_batch, plan.cshape[size_t(idx)])
                                                         : plan.cshape[size_t(idx)];
@@ -363,6 +392,30 @@ void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<
       s.nodes = {idx};
       plan.steps.push_back(s);
       plan.step_of[size_t(idx)] = int(plan.steps.size()) - 1;
+    } else if (is_host_value(n) || n.cls == OpClass::ExpandDims || n.cls == OpClass::Tile || n.cls == OpClass::ArgMinMax ||
+               n.cls == OpClass::SegmentSum) {
+      Step s;
+      s.nodes = {idx};
+      if (is_host_value(n)) {
+        s.kind = Step::HOSTVAL;
+      } else if (n.cls == OpClass::ExpandDims) {
+        s.kind = Step::COPY;                  // same bytes, one more unit dimension
+      } else if (n.cls == OpClass::Tile) {
+        s.kind = Step::TILE;
+      } else if (n.cls == OpClass::ArgMinMax) {
+        s.kind = Step::ARGMINMAX;
+        const Shape& xs = plan.shape[size_t(n.in[0])];
+        int ax = n.axis < 0 ? n.axis + xs.rank : n.axis;
+        s.outer = s.inner = 1;
+        for (int i = 0; i < xs.rank; ++i) (i < ax ? s.outer : s.inner) *= (i == ax ? 1 : xs.d[i]);
+        s.len = xs.d[ax];
+        TFS_CHECK(s.len >= 1 || xs.numel() == 0, TFS_ERR_INVALID, "node '" + n.name + "' (" + n.op + "): the searched axis is empty");
+      } else {
+        s.kind = Step::SEGSUM;
+        s.len = plan.ival[size_t(n.in[2])][0];
+      }
+      plan.steps.push_back(s);
+      plan.step_of[size_t(idx)] = int(plan.steps.size()) - 1;
     }
   }
 
@@ -375,6 +428,8 @@ void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<
     const Node& n = g_.nodes[size_t(idx)];
     std::vector<int> operands = is_elt(n) ? elt_operands(n) : std::vector<int>{n.in[0]};
     if (n.cls == OpClass::MatMul) operands = n.in;
+    if (n.cls == OpClass::SegmentSum) operands = {n.in[0], n.in[1]};
+    if (is_host_value(n)) operands.clear();
     if (fused_from[size_t(idx)] >= 0) operands = {fused_from[size_t(idx)], fused_bias[size_t(fused_from[size_t(idx)])]};
     for (int k : operands) {
       int sk = plan.step_of[size_t(k)];
@@ -584,7 +639,17 @@ struct GroupCompiler {
     TFS_CHECK(!done.count(n), TFS_ERR_INVALID, "internal: element-wise node computed twice");
     const Node& nd = node(n);
     std::vector<int> ops = elt_operands(nd);
-    if (nd.cls == OpClass::Fill || nd.cls == OpClass::Unary) {
+    if (is_like_fill(nd)) {
+      uint64_t imm = 0;
+      if (nd.elt_op == E_ONES_LIKE) {
+        switch (nd.dtype) {
+          case TFS_FLOAT: { const float one = 1.f; memcpy(&imm, &one, 4); break; }
+          case TFS_DOUBLE: { const double one = 1.0; memcpy(&imm, &one, 8); break; }
+          default: imm = 1;
+        }
+      }
+      emit(C_LOAD_IMM, 0, imm);
+    } else if (nd.cls == OpClass::Fill || nd.cls == OpClass::Unary) {
       into_acc(ops[0]);
       if (nd.cls == OpClass::Unary && nd.elt_op == E_CAST) {
         if (di(ops[0]) != di(n)) emit(C_CAST + di(ops[0]) * 4 + di(n));
@@ -750,24 +815,106 @@ void Session::exec_step(const Plan& plan, size_t step_index, std::vector<void*>&
         TFS_CUDA(cudaMemcpyAsync(dev_ptr[size_t(s.nodes[0])], dev_ptr[size_t(n.in[0])], bytes, cudaMemcpyDeviceToDevice, stream));
       break;
     }
+    case Step::HOSTVAL: {
+      const int idx = s.nodes[0];
+      if (!plan.materialize[size_t(idx)] || plan.ival[size_t(idx)].empty()) break;   // read as a value by the planner only
+      const Node& n = g_.nodes[size_t(idx)];
+      const std::vector<int64_t>& v = plan.ival[size_t(idx)];
+      if (n.dtype == TFS_INT64) {
+        TFS_CUDA(cudaMemcpyAsync(dev_ptr[size_t(idx)], v.data(), v.size() * 8, cudaMemcpyHostToDevice, stream));
+      } else {
+        std::vector<int32_t> v32(v.begin(), v.end());
+        TFS_CUDA(cudaMemcpyAsync(dev_ptr[size_t(idx)], v32.data(), v32.size() * 4, cudaMemcpyHostToDevice, stream));
+      }
+      // (pageable source: the copy has been staged when the call returns, so the vectors may go)
+      break;
+    }
+    case Step::TILE: {
+      const int idx = s.nodes[0];
+      const Node& n = g_.nodes[size_t(idx)];
+      launches_ += launch_tile(dtype_size(n.dtype), dev_ptr[size_t(n.in[0])], plan.shape[size_t(n.in[0])], dev_ptr[size_t(idx)],
+                               plan.shape[size_t(idx)], dev_, stream);
+      break;
+    }
+    case Step::ARGMINMAX: {
+      const int idx = s.nodes[0];
+      const Node& n = g_.nodes[size_t(idx)];
+      if (s.outer * s.inner > 0)
+        launches_ += launch_argminmax(g_.nodes[size_t(n.in[0])].dtype, n.dtype, n.arg_min, dev_ptr[size_t(n.in[0])], s.outer, s.len,
+                                      s.inner, dev_ptr[size_t(idx)], dev_, stream);
+      break;
+    }
+    case Step::SEGSUM: {
+      // UnsortedSegmentSum = the keyed block reduction (K3) with the segment ids as keys, then a scatter of the
+      // per-group sums to out[id, :]; segments without rows stay zero.
+      const int idx = s.nodes[0];
+      const Node& n = g_.nodes[size_t(idx)];
+      const Shape& xs = plan.shape[size_t(n.in[0])];
+      const int64_t n_rows = xs.rank ? xs.d[0] : 0, segments = s.len;
+      const int64_t cell = n_rows > 0 ? xs.numel() / n_rows : plan.shape[size_t(idx)].numel() / std::max<int64_t>(segments, 1);
+      const size_t es = size_t(dtype_size(n.dtype));
+      const size_t out_bytes = size_t(segments) * size_t(cell) * es;
+      if (out_bytes > 0) TFS_CUDA(cudaMemsetAsync(dev_ptr[size_t(idx)], 0, out_bytes, stream));
+      if (n_rows == 0 || cell == 0 || segments == 0) {
+        TFS_CHECK(n_rows == 0 || segments > 0, TFS_ERR_RUNTIME, "UnsortedSegmentSum: segment ids out of range (num_segments is 0)");
+        break;
+      }
+      TFS_CHECK(n_rows < (int64_t(1) << 32), TFS_ERR_UNSUPPORTED, "UnsortedSegmentSum: blocks of 2^32 rows or more are not supported");
+      const int64_t max_groups = std::min(n_rows, segments);
+      const AggLayout L0 = agg_layout(n_rows, max_groups);
+      AggLayout L = L0;
+      const size_t off_keys64 = align_up(L.bytes);
+      const size_t off_out_keys = off_keys64 + align_up(size_t(n_rows) * 8);
+      const size_t off_sums = off_out_keys + align_up(size_t(max_groups) * 8);
+      const size_t need = off_sums + align_up(size_t(max_groups) * size_t(cell) * es);
+      if (need > seg_scratch_cap_) {
+        TFS_CUDA(cudaStreamSynchronize(stream));
+        if (seg_scratch_) TFS_CUDA(cudaFree(seg_scratch_));
+        seg_scratch_ = nullptr;
+        seg_scratch_cap_ = 0;
+        TFS_CUDA(cudaMalloc(reinterpret_cast<void**>(&seg_scratch_), need + need / 8));
+        seg_scratch_cap_ = need + need / 8;
+      }
+      char* scratch = seg_scratch_;
+      const int64_t* keys = static_cast<const int64_t*>(dev_ptr[size_t(n.in[1])]);
+      if (g_.nodes[size_t(n.in[1])].dtype == TFS_INT32) {
+        launches_ += launch_widen_ids(static_cast<const int*>(dev_ptr[size_t(n.in[1])]), n_rows,
+                                      reinterpret_cast<int64_t*>(scratch + off_keys64), dev_, stream);
+        keys = reinterpret_cast<const int64_t*>(scratch + off_keys64);
+      }
+      int64_t* d_out_keys = reinterpret_cast<int64_t*>(scratch + off_out_keys);
+      launches_ += launch_agg_build(keys, n_rows, max_groups, scratch, L, d_out_keys, dev_, stream);
+      unsigned int header[4] = {0, 0, 0, 0};
+      TFS_CUDA(cudaMemcpyAsync(header, scratch + L.off_header, sizeof(header), cudaMemcpyDeviceToHost, stream));
+      TFS_CUDA(cudaStreamSynchronize(stream));
+      TFS_CHECK(header[1] == 0 && int64_t(header[2]) <= max_groups, TFS_ERR_RUNTIME,
+                "UnsortedSegmentSum: segment ids out of range [0, " + std::to_string(segments) + ")");
+      const int64_t n_groups = header[2];
+      launches_ += launch_agg_segments(keys, n_rows, n_groups, scratch, L, dev_, stream);
+      launches_ += launch_agg_reduce(n.dtype, R_SUM, dev_ptr[size_t(n.in[0])], cell, n_groups, scratch, L, scratch + off_sums, dev_, stream);
+      launches_ += launch_segment_scatter(n.dtype, scratch + off_sums, d_out_keys, n_groups, cell, segments, dev_ptr[size_t(idx)],
+                                          err_flag_, dev_, stream);
+      break;
+    }
     case Step::MATMUL: {
       const int mm = s.nodes[0];
       const Node& n = g_.nodes[size_t(mm)];
       const Shape& as = plan.shape[size_t(n.in[0])];
       const Shape& os = plan.shape[size_t(mm)];
       const int64_t M = os.d[0], Nc = os.d[1], K = n.transpose_a ? as.d[0] : as.d[1];
-      const float* a = static_cast<const float*>(dev_ptr[size_t(n.in[0])]);
-      const float* b = static_cast<const float*>(dev_ptr[size_t(n.in[1])]);
-      const float* bias = s.bias_node >= 0 ? static_cast<const float*>(dev_ptr[size_t(s.bias_node)]) : nullptr;
-      float* out = static_cast<float*>(dev_ptr[size_t(s.out_node >= 0 ? s.out_node : mm)]);
+      const void* a = dev_ptr[size_t(n.in[0])];
+      const void* b = dev_ptr[size_t(n.in[1])];
+      const void* bias = s.bias_node >= 0 ? dev_ptr[size_t(s.bias_node)] : nullptr;
+      void* out = dev_ptr[size_t(s.out_node >= 0 ? s.out_node : mm)];
       if (M * Nc == 0) break;
       const bool const_b = g_.nodes[size_t(n.in[1])].cls == OpClass::Const;
       static const bool force_simt = [] { const char* e = std::getenv("TFS_MATMUL_IMPL"); return e && std::string(e) == "simt"; }();
-      if (!force_simt && const_b && matmul_tc_supported(a, out, M, Nc, K, n.transpose_a)) {
-        auto it = ensure_tc_weights(n, b, Nc, K, stream);
-        launches_ += launch_matmul_tc(a, it->second.first, it->second.second, bias, out, M, Nc, K, dev_, stream);
+      if (n.dtype == TFS_FLOAT && !force_simt && const_b && matmul_tc_supported(a, out, M, Nc, K, n.transpose_a)) {
+        auto it = ensure_tc_weights(n, static_cast<const float*>(b), Nc, K, stream);
+        launches_ += launch_matmul_tc(static_cast<const float*>(a), it->second.first, it->second.second, static_cast<const float*>(bias),
+                                      static_cast<float*>(out), M, Nc, K, dev_, stream);
       } else {
-        launches_ += launch_matmul_simt(a, b, bias, out, M, Nc, K, n.transpose_a, n.transpose_b, dev_, stream);
+        launches_ += launch_matmul_simt(n.dtype, a, b, bias, out, M, Nc, K, n.transpose_a, n.transpose_b, dev_, stream);
       }
       break;
     }

@@ -65,6 +65,8 @@ class Session {
   size_t ws_cap_ = 0;
   void* red_scratch_ = nullptr;
   size_t red_scratch_cap_ = 0;
+  char* seg_scratch_ = nullptr;        // UnsortedSegmentSum: keyed-reduction scratch, grown on demand
+  size_t seg_scratch_cap_ = 0;
   int32_t* err_flag_ = nullptr;       // device
   int32_t* err_host_ = nullptr;       // pinned
   std::unordered_map<int, void*> const_dev_;

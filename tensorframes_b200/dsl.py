@@ -30,6 +30,8 @@ __all__ = [
     "Unknown", "Node", "scope", "withGraph", "placeholder", "constant", "zeros", "ones", "fill",
     "identity", "add", "sub", "mul", "div", "neg", "cast", "minimum", "maximum", "relu",
     "reduce_sum", "reduce_min", "reduce_max", "matmul", "block", "row", "build_graph", "hints",
+    "square", "reciprocal", "inv", "sqrt", "abs_", "ones_like", "zeros_like", "shape", "strided_index", "stack",
+    "expand_dims", "tile", "argmin", "argmax", "unsorted_segment_sum",
 ]
 
 
@@ -94,6 +96,9 @@ class Node:
         self.extraAttr = dict(extra_attr)
         self._path: Optional[str] = None
         self._created_parents: List[Node] = []
+        # value of small integer nodes that follows from shapes and constants (Unknown where it does not):
+        # what lets tile / unsorted_segment_sum give their outputs a static shape, as TF's shape inference does
+        self.ivalue: Optional[List[int]] = None
 
     @property
     def frozen(self) -> bool:
@@ -129,8 +134,14 @@ class Node:
     def named(self, new_name: str) -> "Node":
         c = Node(new_name, self.opName, self.scalarType, self.shape, self.parents, self.internalParents,
                  self.isOp, self.extraAttr, creation_path=self.creationPath)
+        c.ivalue = self.ivalue
         c.freeze()
         return c
+
+    def __getitem__(self, index: int) -> "Node":
+        """x[i] on an integer vector such as shape(x): a StridedSlice with shrink_axis_mask = 1, what python TF
+        emits for tf.shape(points)[0] (tensorframes_snippets/kmeans_demo.py:26)."""
+        return strided_index(self, index)
 
     def node_defs(self) -> List[bytes]:
         self.freeze()
@@ -253,8 +264,11 @@ def placeholder(dtype: ScalarType, *shape: int) -> Node:
 def constant(x, dtype: Optional[ScalarType] = None) -> Node:
     """tf.constant (dsl/package.scala:50-53, DslImpl.build_constant DslImpl.scala:77-82)."""
     st, sh, arr = _dense(x, dtype)
-    return _build("Const", is_op=False, shape=sh, dtype=st,
-                  extra_attrs={"value": AttrValue.of_tensor(st, sh, arr)})
+    n = _build("Const", is_op=False, shape=sh, dtype=st,
+               extra_attrs={"value": AttrValue.of_tensor(st, sh, arr)})
+    if st in (IntegerType, LongType) and arr.ndim <= 1 and arr.size <= 64:
+        n.ivalue = [int(v) for v in arr.reshape(-1)]
+    return n
 
 
 def fill(dims, value) -> Node:
@@ -362,6 +376,102 @@ def matmul(a: Node, b: Node, transpose_a: bool = False, transpose_b: bool = Fals
     return _build("MatMul", parents=[a, b], shape=Shape(m, n),
                   extra_attrs={"transpose_a": AttrValue.of_bool(transpose_a),
                                "transpose_b": AttrValue.of_bool(transpose_b)})
+
+
+# --- the k-means / geometric-mean snippets' vocabulary (tensorframes_snippets/kmeans_demo.py, geom_mean.py) ---------
+def square(x: Node) -> Node: return _build("Square", parents=[x])
+def reciprocal(x: Node) -> Node: return _build("Reciprocal", parents=[x])
+def inv(x: Node) -> Node: return _build("Inv", parents=[x])            # tf.inv, the TF 1.0 name geom_mean.py uses
+def sqrt(x: Node) -> Node: return _build("Sqrt", parents=[x])
+def abs_(x: Node) -> Node: return _build("Abs", parents=[x])
+def ones_like(x: Node) -> Node: return _build("OnesLike", parents=[x])
+def zeros_like(x: Node) -> Node: return _build("ZerosLike", parents=[x])
+
+
+def shape(x: Node) -> Node:
+    """tf.shape: the int32 vector of x's dimensions, known once the block's shape is."""
+    n = Node(None, "Shape", IntegerType, Shape(x.shape.numDims), [x], lambda _p: [], True,
+             {"T": AttrValue.of_type(x.scalarType), "out_type": AttrValue.of_type(IntegerType)})
+    n.ivalue = [int(d) for d in x.shape.dims]
+    return n
+
+
+def strided_index(x: Node, index: int) -> Node:
+    assert x.shape.numDims == 1 and x.scalarType in (IntegerType, LongType), "only integer vectors can be indexed"
+    i = int(index)
+
+    def internal(p: str) -> List[Node]:
+        return [constant(np.asarray([i], dtype=np.int32)).named(p + "/stack"),
+                constant(np.asarray([i + 1], dtype=np.int32)).named(p + "/stack_1"),
+                constant(np.asarray([1], dtype=np.int32)).named(p + "/stack_2")]
+
+    n = Node(None, "StridedSlice", x.scalarType, Shape.empty(), [x], internal, True,
+             {"Index": AttrValue.of_type(IntegerType), "begin_mask": AttrValue.of_int(0), "end_mask": AttrValue.of_int(0),
+              "ellipsis_mask": AttrValue.of_int(0), "new_axis_mask": AttrValue.of_int(0),
+              "shrink_axis_mask": AttrValue.of_int(1)})
+    if x.ivalue is not None and -len(x.ivalue) <= i < len(x.ivalue):
+        n.ivalue = [x.ivalue[i]]
+    return n
+
+
+def stack(values: Sequence) -> Node:
+    """tf.stack of integer scalars (python ints become int32 Consts): a Pack along axis 0."""
+    lifted = [v if isinstance(v, Node) else constant(np.int32(v)) for v in values]
+    assert lifted and all(v.shape.numDims == 0 for v in lifted), "only scalars can be stacked"
+    n = _build("Pack", parents=lifted, shape=Shape(len(lifted)),
+               extra_attrs={"N": AttrValue.of_int(len(lifted)), "axis": AttrValue.of_int(0)})
+    if all(v.ivalue is not None and len(v.ivalue) == 1 for v in lifted):
+        n.ivalue = [v.ivalue[0] for v in lifted]
+    return n
+
+
+def expand_dims(x: Node, dim: int) -> Node:
+    r = x.shape.numDims
+    ax = dim + r + 1 if dim < 0 else dim
+    assert 0 <= ax <= r, (dim, x.shape)
+    dims = list(x.shape.dims)
+    dims.insert(ax, 1)
+
+    def internal(p: str) -> List[Node]:
+        return [constant(np.int32(dim)).named(p + "/dim")]
+
+    return Node(None, "ExpandDims", x.scalarType, Shape(dims), [x], internal, True, {"Tdim": AttrValue.of_type(IntegerType)})
+
+
+def tile(x: Node, multiples) -> Node:
+    m = multiples if isinstance(multiples, Node) else constant(np.asarray(list(multiples), dtype=np.int32))
+    assert m.shape.numDims == 1
+    known = m.ivalue if m.ivalue is not None and len(m.ivalue) == x.shape.numDims else [Unknown] * x.shape.numDims
+    dims = [Unknown if (k == Unknown or d == Unknown) else k * d for k, d in zip(known, x.shape.dims)]
+    return _build("Tile", parents=[x, m], shape=Shape(dims), dtype=x.scalarType,
+                  extra_attrs={"Tmultiples": AttrValue.of_type(m.scalarType)})
+
+
+def _arg_reduce(op_name: str, x: Node, dimension: int) -> Node:
+    r = x.shape.numDims
+    ax = dimension + r if dimension < 0 else dimension
+    assert 0 <= ax < r, (dimension, x.shape)
+
+    def internal(p: str) -> List[Node]:
+        return [constant(np.int32(dimension)).named(p + "/dimension")]
+
+    return Node(None, op_name, LongType, Shape([d for i, d in enumerate(x.shape.dims) if i != ax]), [x], internal, True,
+                {"T": AttrValue.of_type(x.scalarType), "Tidx": AttrValue.of_type(IntegerType),
+                 "output_type": AttrValue.of_type(LongType)})
+
+
+def argmin(x: Node, dimension: int) -> Node: return _arg_reduce("ArgMin", x, dimension)
+def argmax(x: Node, dimension: int) -> Node: return _arg_reduce("ArgMax", x, dimension)
+
+
+def unsorted_segment_sum(data: Node, segment_ids: Node, num_segments) -> Node:
+    ns = num_segments if isinstance(num_segments, Node) else constant(np.int32(num_segments))
+    assert segment_ids.shape.numDims == 1 and ns.shape.numDims == 0
+    k = ns.ivalue[0] if ns.ivalue else Unknown
+    return _build("UnsortedSegmentSum", parents=[data, segment_ids, ns], dtype=data.scalarType,
+                  shape=Shape([k] + list(data.shape.dims[1:])),
+                  extra_attrs={"Tindices": AttrValue.of_type(segment_ids.scalarType),
+                               "Tnumsegments": AttrValue.of_type(ns.scalarType)})
 
 
 def _extract_placeholder(df, col_name: str, tf_name: Optional[str], block_: bool,

@@ -297,6 +297,100 @@ class TensorFrame:
             parts.append({name: np.ascontiguousarray(np.asarray(arr)[lo:hi]) for name, arr in columns.items()})
         return TensorFrame(StructType(tuple(fields)), parts)
 
+    @staticmethod
+    def from_arrow(data, num_partitions: Optional[int] = None) -> "TensorFrame":
+        """Arrow table / record batches -> frame, without copying numeric columns.
+
+        One record batch becomes one partition (Arrow chunk <-> Spark partition), unless `num_partitions`
+        asks for a contiguous re-split.  Primitive float64/float32/int32/int64 arrays map to scalar columns,
+        (nested) FixedSizeList<primitive> arrays to [n, cell...] blocks viewed over Arrow's own value buffer --
+        already the row-major packing TFDataOps.convert produces (impl/TFDataOps.scala:27-59) -- and List<>
+        arrays to blocks when every row has the same length, else to ragged per-row cells.  String columns
+        (group keys) become Python lists.  Nulls are rejected: the reference's tensors cannot hold them
+        (all its columns are declared nullable = false)."""
+        import pyarrow as pa
+        if isinstance(data, pa.Table):
+            batches, arrow_schema = data.to_batches(), data.schema
+        elif isinstance(data, pa.RecordBatch):
+            batches, arrow_schema = [data], data.schema
+        else:
+            batches = list(data)
+            if not batches:
+                raise ValueError("from_arrow needs at least one record batch (or a table, which carries its schema)")
+            arrow_schema = batches[0].schema
+        if num_partitions:   # contiguous, zero-copy re-split of the combined table
+            tbl = pa.Table.from_batches(batches, schema=arrow_schema).combine_chunks()
+            empty = pa.RecordBatch.from_arrays([pa.array([], type=f.type) for f in arrow_schema], schema=arrow_schema)
+            batches = []
+            for p in range(num_partitions):
+                lo, hi = (tbl.num_rows * p) // num_partitions, (tbl.num_rows * (p + 1)) // num_partitions
+                piece = tbl.slice(lo, hi - lo).to_batches() if hi > lo else []
+                batches.append(piece[0] if piece else empty)
+
+        def sql_of(t):
+            if pa.types.is_fixed_size_list(t) or pa.types.is_list(t) or pa.types.is_large_list(t):
+                return ArrayType(sql_of(t.value_type), False)
+            if pa.types.is_string(t) or pa.types.is_large_string(t):
+                return StringType
+            try:
+                st = scalar_type_from_numpy(np.dtype(t.to_pandas_dtype()))
+            except (NotImplementedError, TypeError):
+                st = None
+            if st is None:
+                raise TypeError(f"Arrow type {t} is not supported (float64, float32, int32, int64, lists of them, string)")
+            return st
+
+        def column_of(arr, name):
+            if arr.null_count:
+                raise ValueError(f"column {name} holds nulls; tensor columns cannot")
+            t = arr.type
+            if pa.types.is_string(t) or pa.types.is_large_string(t):
+                return arr.to_pylist()
+            dims = []
+            while pa.types.is_fixed_size_list(t):
+                dims.append(t.list_size)
+                arr = arr.flatten()
+                t = arr.type
+                if arr.null_count:
+                    raise ValueError(f"column {name} holds nulls; tensor columns cannot")
+            if pa.types.is_list(t) or pa.types.is_large_list(t):
+                if dims:
+                    raise TypeError(f"column {name}: variable-length lists inside fixed-size lists are not supported")
+                offsets = arr.offsets.to_numpy(zero_copy_only=True)
+                values = arr.values
+                if pa.types.is_list(values.type) or pa.types.is_fixed_size_list(values.type) or values.null_count:
+                    return [np.asarray(v) for v in arr.to_pylist()]
+                flat = values.to_numpy(zero_copy_only=True)
+                lens = np.diff(offsets)
+                if len(lens) and np.all(lens == lens[0]):
+                    return flat[offsets[0]:offsets[-1]].reshape(len(lens), int(lens[0]))
+                return [flat[offsets[i]:offsets[i + 1]] for i in range(len(lens))]
+            flat = arr.to_numpy(zero_copy_only=True)
+            n = len(flat) // int(np.prod(dims, dtype=np.int64)) if dims else len(flat)
+            return flat.reshape((n, *dims)) if dims else flat
+
+        fields = tuple(StructField(f.name, sql_of(f.type), nullable=False) for f in arrow_schema)
+        parts = [{f.name: column_of(b.column(i), f.name) for i, f in enumerate(arrow_schema)} for b in batches]
+        return TensorFrame(StructType(fields), parts)
+
+    def to_arrow(self):
+        """The frame as an Arrow table, one record batch per partition; dense [n, cell...] blocks become nested
+        FixedSizeList columns over the same memory, ragged cells List columns."""
+        import pyarrow as pa
+
+        def array_of(col, dt):
+            if isinstance(col, np.ndarray) and col.dtype != object:
+                flat = pa.array(np.ascontiguousarray(col).reshape(-1))
+                for d in reversed(col.shape[1:]):
+                    flat = pa.FixedSizeListArray.from_arrays(flat, int(d))
+                return flat
+            return pa.array([_to_python(v) for v in col])
+
+        names = self.schema.fieldNames
+        batches = [pa.RecordBatch.from_arrays([array_of(part[n], self.schema[n].dataType) for n in names], names=names)
+                   for part in self.partitions]
+        return pa.Table.from_batches(batches) if batches else pa.table({n: [] for n in names})
+
     # -- basic relational surface --
     @property
     def columns(self) -> List[str]:

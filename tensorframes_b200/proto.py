@@ -97,6 +97,10 @@ class AttrValue:
         return AttrValue(_vi(5, 1 if b else 0), f"b:{b}")
 
     @staticmethod
+    def of_int(v: int) -> "AttrValue":
+        return AttrValue(_vi(3, int(v)), f"i:{int(v)}")
+
+    @staticmethod
     def of_tensor(dtype: ScalarType, shape: Shape, values, use_content: bool = False) -> "AttrValue":
         return AttrValue(_ld(8, tensor_proto(dtype, shape, np.asarray(values), use_content)),
                          f"tensor:{dtype.name}{shape}")

@@ -745,6 +745,28 @@ def test_pipelined_host_matmul_matches_device_run():
         ya.free()
 
 
+def test_arrow_columns_through_map_blocks_and_aggregate():
+    """Arrow record batches in, Arrow table out: FixedSizeList blocks go to the device as they are."""
+    pa = pytest.importorskip("pyarrow")
+    from tensorframes_b200.frame import TensorFrame
+    n = 1000
+    rng = np.random.default_rng(73)
+    v = rng.uniform(-1, 1, (n, 4))
+    key = rng.integers(0, 7, n)
+    tbl = pa.table({"key": pa.array(key), "v": pa.FixedSizeListArray.from_arrays(pa.array(v.reshape(-1)), 4)})
+    df = TensorFrame.from_arrow(pa.Table.from_batches(tbl.slice(0, 300).to_batches() + tbl.slice(300).to_batches()))
+    with dsl.withGraph():
+        p = tfs.block(df, "v")
+        out = tfs.map_blocks((p * 2.0 + 1.0).named("w"), df).to_arrow()
+    assert np.asarray(out.column("w").to_pylist()).tobytes() == (v * 2.0 + 1.0).tobytes()
+    with dsl.withGraph():
+        p = tfs.block(df, "v", tf_name="v_input")
+        agg = tfs.aggregate(dsl.reduce_sum(p, [0]).named("v"), df.groupBy("key")).to_arrow()
+    got = {k: np.asarray(r) for k, r in zip(agg.column("key").to_pylist(), agg.column("v").to_pylist())}
+    for k in range(7):
+        np.testing.assert_allclose(got[k], v[key == k].sum(axis=0), rtol=1e-12, atol=1e-12)
+
+
 def test_blocks_beyond_2_31_elements():
     """int64 sizes end to end: the reference caps a block at Int.MaxValue scalars (impl/datatypes.scala:74-78);
     here a 2.2e9-element column is mapped and reduced in one block each (closed-form checks on the device)."""

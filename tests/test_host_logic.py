@@ -250,3 +250,51 @@ def test_python_api_names():
     for name in ["reduce_rows", "map_rows", "reduce_blocks", "map_blocks", "analyze", "print_schema", "aggregate",
                  "block", "row"]:
         assert callable(getattr(tfs, name))
+
+
+# ---- Arrow ingestion / egress (columnar hand-over without per-row work) ----------
+def test_from_arrow_is_zero_copy_and_keeps_chunks_as_partitions():
+    pa = pytest.importorskip("pyarrow")
+    from tensorframes_b200.frame import TensorFrame, ArrayType
+    n = 10
+    x = np.arange(n, dtype=np.float64)
+    v = np.arange(n * 6, dtype=np.float32).reshape(n, 2, 3)
+    fsl = pa.FixedSizeListArray.from_arrays(pa.FixedSizeListArray.from_arrays(pa.array(v.reshape(-1)), 3), 2)
+    key = pa.array([f"k{i % 3}" for i in range(n)])
+    tbl = pa.table({"x": pa.array(x), "v": fsl, "key": key})
+    two = pa.Table.from_batches(tbl.slice(0, 4).to_batches() + tbl.slice(4).to_batches())
+    df = TensorFrame.from_arrow(two)
+    assert len(df.partitions) == 2 and df.count() == n
+    assert df.schema["x"].dataType == tfs.DoubleType
+    assert isinstance(df.schema["v"].dataType, ArrayType) and isinstance(df.schema["v"].dataType.elementType, ArrayType)
+    got = np.concatenate([p["v"] for p in df.partitions])
+    assert got.dtype == np.float32 and got.shape == (n, 2, 3) and np.array_equal(got, v)
+    # the blocks are views over Arrow's own value buffer
+    values_buf = two.column("v").chunk(1).flatten().flatten().buffers()[1]
+    lo = values_buf.address
+    assert lo <= df.partitions[1]["v"].ctypes.data < lo + values_buf.size
+    assert df.partitions[0]["key"] == ["k0", "k1", "k2", "k0"]
+    # contiguous re-split
+    df3 = TensorFrame.from_arrow(two, num_partitions=3)
+    assert [len(p["x"]) for p in df3.partitions] == [3, 3, 4]
+    assert np.array_equal(np.concatenate([p["x"] for p in df3.partitions]), x)
+    # and back
+    back = df.to_arrow()
+    assert back.num_rows == n and back.column("v").type == fsl.type
+    assert back.column("x").to_pylist() == x.tolist() and back.column("key").to_pylist() == key.to_pylist()
+    assert np.array_equal(np.asarray(back.column("v").to_pylist(), dtype=np.float32), v)
+
+
+def test_from_arrow_lists_and_rejections():
+    pa = pytest.importorskip("pyarrow")
+    from tensorframes_b200.frame import TensorFrame
+    same = pa.array([[1, 2], [3, 4], [5, 6]], type=pa.list_(pa.int32()))
+    ragged = pa.array([[1.0], [2.0, 3.0], []], type=pa.list_(pa.float64()))
+    df = TensorFrame.from_arrow(pa.table({"a": same, "b": ragged}))
+    a, b = df.partitions[0]["a"], df.partitions[0]["b"]
+    assert isinstance(a, np.ndarray) and a.shape == (3, 2) and a.dtype == np.int32
+    assert isinstance(b, list) and [c.tolist() for c in b] == [[1.0], [2.0, 3.0], []]
+    with pytest.raises(ValueError, match="nulls"):
+        TensorFrame.from_arrow(pa.table({"x": pa.array([1.0, None])}))
+    with pytest.raises(TypeError, match="not supported"):
+        TensorFrame.from_arrow(pa.table({"x": pa.array([True, False])}))
