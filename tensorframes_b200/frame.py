@@ -369,7 +369,17 @@ class TensorFrame:
             n = len(flat) // int(np.prod(dims, dtype=np.int64)) if dims else len(flat)
             return flat.reshape((n, *dims)) if dims else flat
 
-        fields = tuple(StructField(f.name, sql_of(f.type), nullable=False) for f in arrow_schema)
+        def field_of(f):
+            # a FixedSizeList type states the cell shape: such columns arrive analysed (metadata [?, dims...])
+            t, dims = f.type, []
+            while pa.types.is_fixed_size_list(t):
+                dims.append(t.list_size)
+                t = t.value_type
+            if dims and not (pa.types.is_list(t) or pa.types.is_large_list(t) or pa.types.is_string(t) or pa.types.is_large_string(t)):
+                return ColumnInformation.structField(f.name, sql_of(t), Shape([Unknown] + dims))
+            return StructField(f.name, sql_of(f.type), nullable=False)
+
+        fields = tuple(field_of(f) for f in arrow_schema)
         parts = [{f.name: column_of(b.column(i), f.name) for i, f in enumerate(arrow_schema)} for b in batches]
         return TensorFrame(StructType(fields), parts)
 
