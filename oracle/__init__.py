@@ -18,7 +18,10 @@ every known-answer vector the reference's own tests and README hold for this pat
 (tests/golden/reference_vectors.json, made by tests/golden/make_golden.py):
 Identity, Add, Const, Sum, the trimmed maps, reduce_blocks, aggregate, analyze, and
 the two GraphDef fixtures.  Ops with no reference test -- Sub, Mul, Div, Neg, Cast,
-Minimum, Maximum, Relu, reduce_min (README only), reduce_max, MatMul -- are PARITY
-UNPINNED: they follow the published TF op definitions (IEEE-754 round-to-nearest
-arithmetic, C++ static_cast casts, truncating integer division).
+Minimum, Maximum, Relu, reduce_min (README only), reduce_max, MatMul, and the k-means /
+geometric-mean snippet vocabulary (Square, Inv, OnesLike, ZerosLike, Shape, StridedSlice,
+Pack, ExpandDims, Tile, ArgMin, ArgMax, UnsortedSegmentSum; the snippets print, they hold
+no expected values) -- are PARITY UNPINNED: they follow the published TF op definitions
+(IEEE-754 round-to-nearest arithmetic, C++ static_cast casts, truncating integer division,
+first-extreme-wins arg reductions, row-order segment sums).
 """
