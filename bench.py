@@ -244,8 +244,10 @@ def run_ours(args):
     with ClockSampler(local) as clocks:
         barrier()
         start.record(stream)
+        t_host0 = time.perf_counter()
         for _ in range(args.steps):
             step(True)
+        host_enqueue_ms = (time.perf_counter() - t_host0) * 1e3 / args.steps   # CPU time to enqueue one step
         end.record(stream)
         barrier()
     elapsed_ms = start.elapsed_time(end)
@@ -355,6 +357,7 @@ def run_ours(args):
             "gpu_launches": int(launches),
             "clocks": clocks.summary(),
             "cpu_baseline": cpu,
+            "host_enqueue_ms_per_step": host_enqueue_ms,
         }
         print(json.dumps(line))
     if world > 1:

@@ -29,12 +29,18 @@ def gather_partials(partials: Sequence, dist=None) -> List:
     import torch.distributed as td
     dist = dist or td
     world = dist.get_world_size()
-    out = []
-    for p in partials:
-        flat = torch.empty(world * p.numel(), dtype=p.dtype, device=p.device)
-        dist.all_gather_into_tensor(flat, p.contiguous().reshape(-1))   # flat form works on NCCL and gloo alike
-        out.append(flat.reshape((world,) + tuple(p.shape)))
-    return out
+    flats = [torch.empty(world * p.numel(), dtype=p.dtype, device=p.device) for p in partials]
+    srcs = [p.contiguous().reshape(-1) for p in partials]     # flat form works on NCCL and gloo alike
+    coalesce = getattr(dist, "_coalescing_manager", None)
+    if coalesce is not None and len(partials) > 1 and partials[0].is_cuda:
+        # one NCCL group = one launch for all fetches: the rows are a few bytes, so the step is pure launch latency
+        with coalesce(device=partials[0].device):
+            for flat, src in zip(flats, srcs):
+                dist.all_gather_into_tensor(flat, src)
+    else:
+        for flat, src in zip(flats, srcs):
+            dist.all_gather_into_tensor(flat, src)
+    return [flat.reshape((world,) + tuple(p.shape)) for flat, p in zip(flats, partials)]
 
 
 def combine_reduce_blocks(partials: Sequence, names: Sequence[str], run_graph: Callable[[Dict[str, object]], List]):
