@@ -65,19 +65,21 @@ int launch_matmul_tc(const float* x, const float* w_hi, const float* w_lo, const
 struct AggLayout {
   uint64_t table_slots;
   size_t off_header, off_slot_key, off_counts, off_offsets, off_group_slot, off_tile_sums, off_perm, off_sort_temp;
+  size_t off_group_slot_tab, off_keys_tab;   // groups in table order, before they are sorted by key
   size_t off_row_slot[2], off_row_id[2];   // (slot, row) u32 pairs, ping-pong buffers of the sort
   size_t sort_temp_bytes;
   size_t bytes;
 };
 AggLayout agg_layout(int64_t n_rows, int64_t max_groups);
 // passes 1-2: hash-insert the keys (each row records its slot, each slot counts its rows), then scan the
-// table: segment offsets, dense group ids, out_keys[gid]. header (first 16 bytes of scratch):
+// table: segment offsets, dense group ids and keys in table order. header (first 16 bytes of scratch):
 // [0] = occupied slots, [1] = overflow flag (more than max_groups distinct keys), [2] = number of groups.
 int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, char* scratch, const AggLayout& L,
-                     int64_t* out_keys_dev, const DeviceInfo& dev, cudaStream_t stream);
-// pass 3: stable sort of the rows by slot -> row permutation (sets L.off_perm).
+                     const DeviceInfo& dev, cudaStream_t stream);
+// pass 3: groups sorted by key -> out_keys_dev[0..n_groups) ascending (the table order depends on probe races);
+// stable sort of the rows by slot -> row permutation (sets L.off_perm).
 int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, char* scratch, AggLayout& L,
-                        const DeviceInfo& dev, cudaStream_t stream);
+                        int64_t* out_keys_dev, const DeviceInfo& dev, cudaStream_t stream);
 // pass 4: out[g, :] = reduce over the rows of group g of payload[row, :].
 int launch_agg_reduce(int dtype, int red_op, const void* payload, int64_t cell, int64_t n_groups, char* scratch,
                       const AggLayout& L, void* out, const DeviceInfo& dev, cudaStream_t stream);

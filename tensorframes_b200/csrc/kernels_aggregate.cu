@@ -18,8 +18,10 @@
 //
 // The payload (the dominant traffic: 256 B/row at BASELINE config 4) is read exactly once and
 // no accumulator table is read-modify-written, unlike a scatter-add formulation.  Keys are
-// compared bit-exactly.  Groups come out in table order and, the sort being stable, the rows of
-// a group are folded in block order: results are run-to-run deterministic, floats included.
+// compared bit-exactly.  Which slot a key lands in depends on who wins a contended probe, so the
+// table order of the groups is not reproducible; the (few) groups are therefore sorted by key before
+// the gather, and -- the row sort being stable -- the rows of a group are folded in block order:
+// output order and values are run-to-run deterministic, floats included.
 #include <cub/device/device_radix_sort.cuh>
 
 #include <cstdlib>
@@ -403,6 +405,8 @@ AggLayout agg_layout(int64_t n_rows, int64_t max_groups) {
   L.off_counts = off; off += up((cap + 1) * 4);
   L.off_offsets = off; off += up((cap + 2) * 4);
   L.off_group_slot = off; off += up(size_t(max_groups + 1) * 4);
+  L.off_group_slot_tab = off; off += up(size_t(max_groups + 1) * 4);     // table order, before the sort by key
+  L.off_keys_tab = off; off += up(size_t(max_groups + 1) * 8);
   L.off_tile_sums = off; off += up(size_t((cap + 1 + kScanTile) / kScanTile + 1) * 8);
   for (int b = 0; b < 2; ++b) {   // ping-pong buffers of the pair sort
     L.off_row_slot[b] = off; off += up(size_t(n_rows) * 4);
@@ -410,18 +414,26 @@ AggLayout agg_layout(int64_t n_rows, int64_t max_groups) {
   }
   L.off_perm = L.off_row_id[0];   // set by launch_agg_segments to the buffer the sort finished in
   L.sort_temp_bytes = n_rows > 0 ? sort_temp_bytes(n_rows, cap) : 0;
+  {
+    size_t b = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, b, static_cast<const long long*>(nullptr), static_cast<long long*>(nullptr),
+                                    static_cast<const unsigned int*>(nullptr), static_cast<unsigned int*>(nullptr),
+                                    std::max<int64_t>(max_groups, 1));
+    L.sort_temp_bytes = std::max(L.sort_temp_bytes, b);
+  }
   L.off_sort_temp = off; off += up(L.sort_temp_bytes);
   L.bytes = off;
   return L;
 }
 
 int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, char* scratch, const AggLayout& L,
-                     int64_t* out_keys_dev, const DeviceInfo& dev, cudaStream_t stream) {
+                     const DeviceInfo& dev, cudaStream_t stream) {
   unsigned int* header = reinterpret_cast<unsigned int*>(scratch + L.off_header);
   unsigned long long* slot_key = reinterpret_cast<unsigned long long*>(scratch + L.off_slot_key);
   unsigned int* counts = reinterpret_cast<unsigned int*>(scratch + L.off_counts);
   unsigned int* offsets = reinterpret_cast<unsigned int*>(scratch + L.off_offsets);
-  unsigned int* group_slot = reinterpret_cast<unsigned int*>(scratch + L.off_group_slot);
+  unsigned int* group_slot = reinterpret_cast<unsigned int*>(scratch + L.off_group_slot_tab);
+  long long* keys_tab = reinterpret_cast<long long*>(scratch + L.off_keys_tab);
   unsigned long long* tile_sums = reinterpret_cast<unsigned long long*>(scratch + L.off_tile_sums);
   unsigned int* row_slot = reinterpret_cast<unsigned int*>(scratch + L.off_row_slot[0]);
   unsigned int* row_id = reinterpret_cast<unsigned int*>(scratch + L.off_row_id[0]);
@@ -449,16 +461,25 @@ int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, ch
   TFS_CUDA(cudaGetLastError());
   scan_tile_offsets_kernel<<<1, 1024, 0, stream>>>(tile_sums, tiles, header);
   TFS_CUDA(cudaGetLastError());
-  scan_apply_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(counts, m, tile_sums, slot_key, offsets, group_slot,
-                                                            reinterpret_cast<long long*>(out_keys_dev), (unsigned int)max_groups);
+  scan_apply_kernel<<<(unsigned)tiles, kThreads, 0, stream>>>(counts, m, tile_sums, slot_key, offsets, group_slot, keys_tab,
+                                                            (unsigned int)max_groups);
   TFS_CUDA(cudaGetLastError());
   return launches + 3;
 }
 
 int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, char* scratch, AggLayout& L,
-                        const DeviceInfo& dev, cudaStream_t stream) {
-  (void)keys; (void)n_groups; (void)dev;
+                        int64_t* out_keys_dev, const DeviceInfo& dev, cudaStream_t stream) {
+  (void)keys; (void)dev;
   if (n_rows <= 0) return 0;
+  // groups by key (signed order): out_keys ascending, group_slot permuted alongside
+  if (n_groups > 0) {
+    size_t temp = L.sort_temp_bytes;
+    TFS_CUDA(cub::DeviceRadixSort::SortPairs(scratch + L.off_sort_temp, temp, reinterpret_cast<const long long*>(scratch + L.off_keys_tab),
+                                             reinterpret_cast<long long*>(out_keys_dev),
+                                             reinterpret_cast<const unsigned int*>(scratch + L.off_group_slot_tab),
+                                             reinterpret_cast<unsigned int*>(scratch + L.off_group_slot), n_groups, 0, 64, stream));
+  }
+  // rows by slot, stable
   cub::DoubleBuffer<unsigned int> slot(reinterpret_cast<unsigned int*>(scratch + L.off_row_slot[0]),
                                        reinterpret_cast<unsigned int*>(scratch + L.off_row_slot[1]));
   cub::DoubleBuffer<unsigned int> row(reinterpret_cast<unsigned int*>(scratch + L.off_row_id[0]),
@@ -467,7 +488,7 @@ int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, c
   TFS_CUDA(cub::DeviceRadixSort::SortPairs(scratch + L.off_sort_temp, temp, slot, row, n_rows, 0,
                                            slot_bits(L.table_slots), stream));
   L.off_perm = L.off_row_id[row.selector];
-  return 1;   // counted as one launch of ours: the sort's internal kernels are library code
+  return 1;   // counted as one launch of ours: the sorts' internal kernels are library code
 }
 
 int launch_agg_reduce(int dtype, int red_op, const void* payload, int64_t cell, int64_t n_groups, char* scratch,

@@ -883,14 +883,14 @@ void Session::exec_step(const Plan& plan, size_t step_index, std::vector<void*>&
         keys = reinterpret_cast<const int64_t*>(scratch + off_keys64);
       }
       int64_t* d_out_keys = reinterpret_cast<int64_t*>(scratch + off_out_keys);
-      launches_ += launch_agg_build(keys, n_rows, max_groups, scratch, L, d_out_keys, dev_, stream);
+      launches_ += launch_agg_build(keys, n_rows, max_groups, scratch, L, dev_, stream);
       unsigned int header[4] = {0, 0, 0, 0};
       TFS_CUDA(cudaMemcpyAsync(header, scratch + L.off_header, sizeof(header), cudaMemcpyDeviceToHost, stream));
       TFS_CUDA(cudaStreamSynchronize(stream));
       TFS_CHECK(header[1] == 0 && int64_t(header[2]) <= max_groups, TFS_ERR_RUNTIME,
                 "UnsortedSegmentSum: segment ids out of range [0, " + std::to_string(segments) + ")");
       const int64_t n_groups = header[2];
-      launches_ += launch_agg_segments(keys, n_rows, n_groups, scratch, L, dev_, stream);
+      launches_ += launch_agg_segments(keys, n_rows, n_groups, scratch, L, d_out_keys, dev_, stream);
       launches_ += launch_agg_reduce(n.dtype, R_SUM, dev_ptr[size_t(n.in[0])], cell, n_groups, scratch, L, scratch + off_sums, dev_, stream);
       launches_ += launch_segment_scatter(n.dtype, scratch + off_sums, d_out_keys, n_groups, cell, segments, dev_ptr[size_t(idx)],
                                           err_flag_, dev_, stream);
@@ -1277,7 +1277,7 @@ void Session::aggregate(int64_t n_rows, const int64_t* keys, const std::vector<T
     TFS_CUDA(cudaMemcpyAsync(ws_ + off_keys, keys, size_t(n_rows) * 8, cudaMemcpyHostToDevice, stream_));
     d_keys = reinterpret_cast<const int64_t*>(ws_ + off_keys);
   }
-  launches_ += launch_agg_build(d_keys, n_rows, max_groups, scratch, L, d_out_keys, dev_, stream_);
+  launches_ += launch_agg_build(d_keys, n_rows, max_groups, scratch, L, dev_, stream_);
   // the number of groups sizes every later launch: one small readback
   unsigned int header[4] = {0, 0, 0, 0};
   TFS_CUDA(cudaMemcpyAsync(header, scratch + L.off_header, sizeof(header), cudaMemcpyDeviceToHost, stream_));
@@ -1285,7 +1285,7 @@ void Session::aggregate(int64_t n_rows, const int64_t* keys, const std::vector<T
   TFS_CHECK(header[1] == 0 && int64_t(header[2]) <= max_groups, TFS_ERR_INVALID,
             "aggregate: the block holds more than max_groups = " + std::to_string(max_groups) + " distinct keys");
   const int64_t n_groups = header[2];
-  launches_ += launch_agg_segments(d_keys, n_rows, n_groups, scratch, L, dev_, stream_);
+  launches_ += launch_agg_segments(d_keys, n_rows, n_groups, scratch, L, d_out_keys, dev_, stream_);
   for (size_t k = 0; k < items.size(); ++k) {
     const Node& n = g_.nodes[size_t(items[k].node)];
     const size_t es = size_t(dtype_size(n.dtype));

@@ -385,6 +385,77 @@ def test_full_size_properties_on_device():
     assert torch.equal(dz, want)
 
 
+def test_full_size_aggregate_closed_form():
+    """BASELINE config 4 at the bench's block size (2.5e8 rows, 1e6 int64 keys, FloatType[?,64]): small-integer
+    payloads make every group sum exact in float32, so the result has a closed form that needs no CPU pass."""
+    torch = pytest.importorskip("torch")
+    n, n_keys, cell = 250_000_000, 1_000_000, 64
+    i = torch.arange(n, dtype=torch.int64, device="cuda")
+    gid = (i * 7919) % n_keys                                   # 7919 is coprime to 1e6: every key gets exactly n / n_keys rows
+    keys = gid * 0x9E3779B97F4A7C15 + 12345                     # wrapping multiply by an odd constant: a bijection on int64
+    v = ((i % 5).to(torch.float32)[:, None] + torch.arange(cell, dtype=torch.float32, device="cuda")[None, :] % 3).contiguous()
+    per = n // n_keys
+    g = aggregate_graph(tfs.FloatType, (cell,), "sum")
+    out = torch.empty((n_keys, cell), dtype=torch.float32, device="cuda")
+    out_keys = torch.empty(n_keys, dtype=torch.int64, device="cuda")
+    DA = _native.DeviceArray.from_torch
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        s.set_stream(torch.cuda.current_stream().cuda_stream)
+        n_groups = s.aggregate_into(DA(keys), {"v_input": DA(v)}, {"v": DA(out)}, DA(out_keys))
+        again = torch.empty_like(out)
+        again_keys = torch.empty_like(out_keys)
+        assert s.aggregate_into(DA(keys), {"v_input": DA(v)}, {"v": DA(again)}, DA(again_keys)) == n_keys
+    assert n_groups == n_keys
+    assert torch.equal(out_keys, again_keys) and torch.equal(out, again)          # run-to-run deterministic, order included
+    want_keys = torch.sort(torch.arange(n_keys, dtype=torch.int64, device="cuda") * 0x9E3779B97F4A7C15 + 12345).values
+    assert torch.equal(out_keys, want_keys)                                        # groups come out in key order
+    # rows of key g are i = g * inv(7919) + t * n_keys; n_keys is a multiple of 5, so (i % 5) is the same for all of them
+    first = torch.full((n_keys,), -1, dtype=torch.int64, device="cuda")
+    first[gid[:n_keys]] = i[:n_keys] % 5                       # the first n_keys rows hit every key once
+    want = (first[:, None].to(torch.float32) + (torch.arange(cell, device="cuda") % 3).to(torch.float32)[None, :]) * per
+    inv = torch.empty(n_keys, dtype=torch.int64, device="cuda")
+    got_gid = ((out_keys - 12345) * pow(0x9E3779B97F4A7C15, -1, 1 << 64)) % n_keys
+    inv[got_gid] = torch.arange(n_keys, device="cuda")
+    assert torch.equal(out[inv], want)
+    # checksum of checksums: the group sums add up to the column sums
+    col = torch.zeros(cell, dtype=torch.float64, device="cuda")
+    for a in range(0, n, 25_000_000):                          # chunked: the f64 copy of the whole payload would not fit
+        col += v[a:a + 25_000_000].sum(0, dtype=torch.float64)
+    assert torch.equal(out.sum(0, dtype=torch.float64), col)
+
+
+def test_full_size_matmul_exact_on_small_integers():
+    """BASELINE config 5 at full size (2^24 rows): integers below 2^10 are exact in TF32 and their dot products in the
+    fp32 accumulator, so the tensor-core path must be bit-exact against integer arithmetic."""
+    torch = pytest.importorskip("torch")
+    n, k, m = 1 << 24, 256, 256
+    rng = np.random.default_rng(55)
+    w = rng.integers(-8, 9, (k, m)).astype(np.float32)
+    b = rng.integers(-100, 101, m).astype(np.float32)
+    i = torch.arange(n, dtype=torch.int32, device="cuda")
+    x = (((i[:, None] * 31 + torch.arange(k, dtype=torch.int32, device="cuda")[None, :] * 17) % 23) - 11).to(torch.float32).contiguous()
+    y = torch.empty((n, m), dtype=torch.float32, device="cuda")
+    with dsl.withGraph():
+        px = dsl.placeholder(tfs.FloatType, dsl.Unknown, k).named("x")
+        g = dsl.build_graph((dsl.matmul(px, dsl.constant(w)) + dsl.constant(b)).named("y"))
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        s.set_stream(torch.cuda.current_stream().cuda_stream)
+        s.run_into({"x": _native.DeviceArray.from_torch(x)}, {"y": _native.DeviceArray.from_torch(y)})
+        s.sync()
+    wt, bt = torch.from_numpy(w).cuda(), torch.from_numpy(b).cuda()
+    for lo in (0, n // 2 - 100_000, n - 300_000):              # slices at both ends and the middle (incl. the last partial tile)
+        hi = min(n, lo + 300_000)
+        want = (x[lo:hi].double() @ wt.double() + bt.double()).to(torch.float32)
+        assert torch.equal(y[lo:hi], want)
+    # linearity over the whole block: column sums of y follow from the column sums of x
+    xs = torch.zeros(k, dtype=torch.float64, device="cuda")
+    ys = torch.zeros(m, dtype=torch.float64, device="cuda")
+    for a in range(0, n, 1 << 21):
+        xs += x[a:a + (1 << 21)].sum(0, dtype=torch.float64)
+        ys += y[a:a + (1 << 21)].sum(0, dtype=torch.float64)
+    assert torch.equal(ys, (xs @ wt.double()) + n * bt.double())
+
+
 # ---- operators: partitions, empties, trimming -------------------------------------------------------
 def test_map_blocks_partitions_and_empty_partition():
     df = TensorFrame.from_columns({"x": np.arange(10, dtype=np.float64)}, num_partitions=3)
