@@ -838,6 +838,77 @@ def test_arrow_columns_through_map_blocks_and_aggregate():
         np.testing.assert_allclose(got[k], v[key == k].sum(axis=0), rtol=1e-12, atol=1e-12)
 
 
+@pytest.mark.parametrize("m_rows,k,n_cols", [(1, 32, 16), (129, 64, 48), (257, 32, 256), (1000, 96, 80), (4099, 256, 256)])
+def test_tensor_core_matmul_stays_inside_its_output(m_rows, k, n_cols):
+    """Ragged last tiles and partial column boxes: the TMA stores must clip exactly at [M, N].  The output sits
+    between two guard bands that have to come back untouched."""
+    torch = pytest.importorskip("torch")
+    rng = np.random.default_rng(m_rows)
+    w = rng.uniform(-0.5, 0.5, (k, n_cols)).astype(np.float32)
+    x = torch.from_numpy(rng.uniform(-1, 1, (m_rows, k)).astype(np.float32)).cuda()
+    guard = 4096
+    buf = torch.full((guard + m_rows * n_cols + guard,), 12345.0, dtype=torch.float32, device="cuda")
+    y = buf[guard:guard + m_rows * n_cols].view(m_rows, n_cols)
+    with dsl.withGraph():
+        px = dsl.placeholder(tfs.FloatType, dsl.Unknown, k).named("x")
+        g = dsl.build_graph(dsl.matmul(px, dsl.constant(w)).named("y"))
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        s.set_stream(torch.cuda.current_stream().cuda_stream)
+        s.run_into({"x": _native.DeviceArray.from_torch(x)}, {"y": _native.DeviceArray(y.data_ptr(), tfs.FloatType, (m_rows, n_cols), owner=buf)})
+        s.sync()
+    assert torch.all(buf[:guard] == 12345.0) and torch.all(buf[guard + m_rows * n_cols:] == 12345.0)
+    exact = x.double() @ torch.from_numpy(w).cuda().double()
+    scale = x.double().abs() @ torch.from_numpy(w).cuda().double().abs()
+    assert torch.all((y.double() - exact).abs() <= 1e-5 * scale.clamp_min(1e-30))
+
+
+def test_keyed_and_shape_steps_stay_inside_their_outputs():
+    torch = pytest.importorskip("torch")
+    rng = np.random.default_rng(99)
+    n, cell, n_keys = 10_007, 12, 37
+    keys = torch.from_numpy(rng.integers(0, n_keys, n)).cuda()
+    v = torch.from_numpy(rng.integers(-5, 6, (n, cell)).astype(np.float32)).cuda()
+    guard = 1024
+    obuf = torch.full((guard + n_keys * cell + guard,), -7.0, dtype=torch.float32, device="cuda")
+    kbuf = torch.full((guard + n_keys + guard,), -7, dtype=torch.int64, device="cuda")
+    DA = _native.DeviceArray
+    g = aggregate_graph(tfs.FloatType, (cell,), "sum")
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        s.set_stream(torch.cuda.current_stream().cuda_stream)
+        ng = s.aggregate_into(DA.from_torch(keys), {"v_input": DA.from_torch(v)},
+                              {"v": DA(obuf[guard:].data_ptr(), tfs.FloatType, (n_keys, cell), owner=obuf)},
+                              DA(kbuf[guard:].data_ptr(), tfs.LongType, (n_keys,), owner=kbuf))
+    assert ng == n_keys
+    assert torch.all(obuf[:guard] == -7.0) and torch.all(obuf[guard + n_keys * cell:] == -7.0)
+    assert torch.all(kbuf[:guard] == -7) and torch.all(kbuf[guard + n_keys:] == -7)
+    assert kbuf[guard:guard + n_keys].tolist() == list(range(n_keys))
+    want = torch.zeros((n_keys, cell), dtype=torch.float32, device="cuda").index_add_(0, keys, v)
+    assert torch.equal(obuf[guard:guard + n_keys * cell].view(n_keys, cell), want)        # small integers: exact
+    # tile / argmin / segment sum into guarded buffers
+    with dsl.withGraph():
+        p = dsl.placeholder(tfs.FloatType, dsl.Unknown, cell).named("v")
+        ids = dsl.placeholder(tfs.LongType, dsl.Unknown).named("ids")
+        fetches = [dsl.tile(p, [1, 3]).named("t"), dsl.argmin(p, 1).named("a"), dsl.unsorted_segment_sum(p, ids, n_keys).named("s")]
+        g2 = dsl.build_graph(*fetches)
+    shapes = {"t": ((n, 3 * cell), torch.float32, tfs.FloatType), "a": ((n,), torch.int64, tfs.LongType),
+              "s": ((n_keys, cell), torch.float32, tfs.FloatType)}
+    bufs, outs = {}, {}
+    for nm, (sh, tdt, st) in shapes.items():
+        numel = int(np.prod(sh))
+        b = torch.full((guard + numel + guard,), 99, dtype=tdt, device="cuda")
+        bufs[nm] = (b, numel)
+        outs[nm] = DA(b[guard:].data_ptr(), st, sh, owner=b)
+    with _native.Graph(g2) as gr, _native.Session(gr, 0) as s:
+        s.set_stream(torch.cuda.current_stream().cuda_stream)
+        s.run_into({"v": DA.from_torch(v), "ids": DA.from_torch(keys)}, outs)
+        s.sync()
+    for nm, (b, numel) in bufs.items():
+        assert torch.all(b[:guard] == 99) and torch.all(b[guard + numel:] == 99), nm
+    assert torch.equal(bufs["t"][0][guard:guard + n * 3 * cell].view(n, 3 * cell), v.repeat(1, 3))
+    assert torch.equal(bufs["a"][0][guard:guard + n], v.argmin(dim=1))
+    assert torch.equal(bufs["s"][0][guard:guard + n_keys * cell].view(n_keys, cell), want)
+
+
 def test_blocks_beyond_2_31_elements():
     """int64 sizes end to end: the reference caps a block at Int.MaxValue scalars (impl/datatypes.scala:74-78);
     here a 2.2e9-element column is mapped and reduced in one block each (closed-form checks on the device)."""
