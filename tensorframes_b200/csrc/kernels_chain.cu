@@ -13,7 +13,7 @@
 namespace tfs {
 namespace {
 
-constexpr int kThreads = 256;
+constexpr int kThreads = kChainThreads;
 
 #include "arith.inc"
 
@@ -98,11 +98,25 @@ __device__ __forceinline__ void st_tile(T* __restrict__ base, int64_t elem, int 
 template <class T, int P, int kJ, bool BUFOPS>
 __device__ __forceinline__ void apply_slot(const ChainSlot& s, T (&acc)[kJ][P], const int64_t (&elem)[kJ],
                                            const int (&nvalid)[kJ], int* err) {
-  if (BUFOPS && s.operand_buf != nullptr) {   // second operand: another column, same flat index
+  if (BUFOPS && s.operand_buf != nullptr) {   // second operand: another column, same flat index ...
     T b[kJ][P];
     const T* base = static_cast<const T*>(s.operand_buf);
+    if (s.period != 0u) {
+      // ... or a row vector broadcast down the block.  The period divides the tile span, so the position inside
+      // the vector depends only on the thread's place in the tile; it is a multiple of P, so a vector never wraps.
 #pragma unroll
-    for (int j = 0; j < kJ; ++j) ld_tile<T, P>(base, elem[j], nvalid[j], b[j]);
+      for (int j = 0; j < kJ; ++j) {
+        const unsigned int at = (unsigned int)((j * kThreads + threadIdx.x) * P) % s.period;
+        using V = typename VecOf<T, P>::type;
+        const V t = __ldg(reinterpret_cast<const V*>(base + at));
+        const T* tv = reinterpret_cast<const T*>(&t);
+#pragma unroll
+        for (int e = 0; e < P; ++e) b[j][e] = tv[e];
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < kJ; ++j) ld_tile<T, P>(base, elem[j], nvalid[j], b[j]);
+    }
     TFS_SLOT_SWITCH(b[j][e])
   } else {                          // second operand: a scalar constant (or none), kept in one register
     T imm;
@@ -119,7 +133,7 @@ template <class T, class OutT, bool BUFOPS>
 __global__ void __launch_bounds__(kThreads, 3)
 chain_kernel(const __grid_constant__ ChainProgram prog, const int64_t n) {
   constexpr int P = 16 / int(sizeof(T));
-  constexpr int kJ = BUFOPS ? 4 : 8;
+  constexpr int kJ = BUFOPS ? kChainVecsPerThread : 2 * kChainVecsPerThread;
   const int64_t n_vec = (n + P - 1) / P;
   constexpr int64_t tile_vecs = int64_t(kThreads) * kJ;
   const int64_t n_tiles = (n_vec + tile_vecs - 1) / tile_vecs;
@@ -160,7 +174,7 @@ int launch_chain_v(const ChainProgram& prog, int64_t n, const DeviceInfo& dev, c
     blocks_per_sm = b > 0 ? b : 1;
   }
   constexpr int P = 16 / int(sizeof(T));
-  constexpr int kJ = BUFOPS ? 4 : 8;
+  constexpr int kJ = BUFOPS ? kChainVecsPerThread : 2 * kChainVecsPerThread;
   const int64_t n_vec = (n + P - 1) / P;
   const int64_t n_tiles = (n_vec + int64_t(kThreads) * kJ - 1) / (int64_t(kThreads) * kJ);
   int64_t grid = std::min<int64_t>(int64_t(dev.sm_count) * blocks_per_sm, n_tiles);

@@ -97,16 +97,46 @@ __device__ __forceinline__ void load_vec(const BufRef& b, int64_t elem, int nval
   }
 }
 
+// Operand broadcast along the rows (a [cell] vector against a [n, cell] block): element i reads b[i % period].
+// One modulo per VECTOR (32-bit when the index allows), then either one cached vector load -- BufRef.pad is set by
+// the host when the period is a multiple of the vector width and the buffer is 16-byte aligned, so a vector never
+// wraps -- or per-element loads with a wrap test.
 template <int ES, int P>
 __device__ __forceinline__ void load_periodic(const BufRef& b, int64_t elem, int nvalid,
                                               typename Slot<ES>::type (&x)[P]) {
   using S = typename Slot<ES>::type;
+  const int64_t period = b.period;
+  const int64_t i0 = ((elem | period) >> 32) == 0 ? int64_t((unsigned int)elem % (unsigned int)period) : elem % period;
+  const bool wide_elems = ES == 8 && (b.dt & 1);
+  if (b.pad != 0 && nvalid == P) {
+    if (wide_elems) {
+      if (P == 2) {
+        const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2*>(static_cast<const unsigned long long*>(b.ptr) + i0));
+        x[0] = S(v.x);
+        x[P - 1] = S(v.y);
+        return;
+      }
+    } else if (P == 4) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(static_cast<const unsigned int*>(b.ptr) + i0));
+      x[0] = S(v.x);
+      x[1 % P] = S(v.y);
+      x[2 % P] = S(v.z);
+      x[3 % P] = S(v.w);
+      return;
+    } else if (P == 2) {
+      const uint2 v = __ldg(reinterpret_cast<const uint2*>(static_cast<const unsigned int*>(b.ptr) + i0));
+      x[0] = S(v.x);
+      x[P - 1] = S(v.y);
+      return;
+    }
+  }
 #pragma unroll
   for (int e = 0; e < P; ++e) {
     S v = 0;
     if (e < nvalid) {
-      int64_t i = (elem + e) % b.period;
-      if (ES == 8 && (b.dt & 1)) v = S(__ldg(static_cast<const unsigned long long*>(b.ptr) + i));
+      int64_t i = i0 + e;
+      if (i >= period) i = period >= P ? i - period : i % period;
+      if (wide_elems) v = S(__ldg(static_cast<const unsigned long long*>(b.ptr) + i));
       else v = S(__ldg(static_cast<const unsigned int*>(b.ptr) + i));
     }
     x[e] = v;

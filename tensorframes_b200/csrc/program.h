@@ -82,8 +82,13 @@ struct ChainSlot {
   const void* operand_buf;  // second operand column (same dtype, same flat index), or null: use imm
   uint64_t imm;
   uint8_t op;
-  uint8_t pad[7];
+  uint8_t pad[3];
+  uint32_t period;          // != 0: operand_buf holds `period` elements broadcast along the rows (x * w + b with row
+                            // vectors); it divides the tile span and is a multiple of the vector width (make_chain)
 };
+// geometry of the chain kernel's column-operand variant, shared with make_chain's eligibility test
+constexpr int kChainThreads = 256;
+constexpr int kChainVecsPerThread = 4;
 struct ChainProgram {
   const void* in;
   void* out;

@@ -538,7 +538,9 @@ struct GroupCompiler {
     b.ptr = p;
     b.period = period;
     b.dt = di(n);
-    b.pad = 0;
+    // periodic operands: 1 = a vector of the kernel's width never wraps and is aligned (see load_periodic)
+    const int64_t lanes = wide ? 2 : 4;
+    b.pad = (period > 0 && period % lanes == 0 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) ? 1 : 0;
     return prog.n_bufs++;
   }
 
@@ -721,14 +723,23 @@ bool make_chain(const EltProgram& prog, ChainProgram& ch) {
   static const uint8_t kUn[U_COUNT] = {CH_NEG, CH_RELU, CH_SQUARE, CH_ABS, CH_SQRT, CH_RECIP};
   const void* pending = nullptr;   // operand fetched by a C_FETCH_BUF awaiting its C_BIN_X
   bool have_pending = false, cast_seen = false;
+  uint32_t pending_period = 0;
   for (int pc = 1; pc < prog.n_instr - 1; ++pc) {
     const Instr& in_ = prog.ins[pc];
     const int c = in_.code;
     if (cast_seen) return false;                       // a cast may only end the chain
-    if (c == C_FETCH_BUF) {
+    if (c == C_FETCH_BUF || c == C_FETCH_PER) {
       if (have_pending) return false;
       const BufRef& b = prog.bufs[in_.arg];
       if (b.dt != dt || !aligned(b.ptr)) return false;
+      pending_period = 0;
+      if (c == C_FETCH_PER) {
+        // a row vector: its length must be a multiple of the vector width and divide the tile span
+        const int64_t lanes = 16 / ((dt & 1) ? 8 : 4);
+        const int64_t span = int64_t(kChainThreads) * kChainVecsPerThread * lanes;
+        if (b.period <= 0 || b.period % lanes != 0 || span % b.period != 0) return false;
+        pending_period = uint32_t(b.period);
+      }
       pending = b.ptr;
       have_pending = true;
       continue;
@@ -739,6 +750,7 @@ bool make_chain(const EltProgram& prog, ChainProgram& ch) {
       if (!have_pending || (k % 8) / 2 != dt) return false;
       slot.op = (k & 1) ? kRev[k / 8] : kFwd[k / 8];
       slot.operand_buf = pending;
+      slot.period = pending_period;
       have_pending = false;
     } else if (c >= C_BIN_IMM && c < C_BIN_IMM + B_COUNT * 8) {
       const int k = c - C_BIN_IMM;

@@ -609,6 +609,35 @@ def test_chain_fast_path_bit_exact(dt):
             assert got.dtype == want.dtype and got.tobytes() == want.tobytes(), (dt, n, name)
 
 
+@pytest.mark.parametrize("dt,cell", [("f4", 64), ("f4", 4), ("f8", 16), ("f8", 2), ("f4", 6), ("f8", 3), ("i4", 8), ("f4", 1024), ("f4", 2048)])
+def test_row_vector_operands_bit_exact(dt, cell):
+    """x * w + b with [cell] row vectors against a [n, cell] block (per-feature scaling): the chain kernel takes the
+    vectors as periodic operands when the cell is a multiple of the vector width and divides its tile, the
+    interpreter otherwise.  Both must give numpy's separately rounded result bit for bit."""
+    st = {"f4": tfs.FloatType, "f8": tfs.DoubleType, "i4": tfs.IntegerType}[dt]
+    npdt = np.dtype("<" + dt)
+    rng = np.random.default_rng(cell)
+    n = 5003
+    if dt == "i4":
+        x = rng.integers(-1000, 1000, (n, cell)).astype(npdt)
+        w = rng.integers(-50, 50, cell).astype(npdt)
+        b = rng.integers(-1000, 1000, cell).astype(npdt)
+    else:
+        x = rng.uniform(-2, 2, (n, cell)).astype(npdt)
+        w = rng.uniform(-2, 2, cell).astype(npdt)
+        b = rng.uniform(-2, 2, cell).astype(npdt)
+    with dsl.withGraph():
+        p = dsl.placeholder(st, dsl.Unknown, cell).named("x")
+        z = dsl.relu(p * dsl.constant(w) + dsl.constant(b)).named("z")
+        r = (dsl.constant(b) - p).named("r")                   # vector on the left: the reversed ops
+        g = dsl.build_graph(z, r)
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        got_z, got_r = s.run({"x": x}, ["z", "r"])
+    want_z = np.maximum((x * w).astype(npdt) + b, npdt.type(0)).astype(npdt)
+    assert got_z.tobytes() == want_z.tobytes()
+    assert got_r.tobytes() == (b - x).astype(npdt).tobytes()
+
+
 def test_chain_fast_path_unaligned_device_pointers():
     torch = pytest.importorskip("torch")
     n = 50001
