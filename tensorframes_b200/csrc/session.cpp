@@ -1,6 +1,8 @@
 // Session: planning and execution. See session.h.
 #include "session.h"
 
+#include <mutex>
+
 #include <algorithm>
 #include <cstdlib>
 #include <map>
@@ -82,6 +84,46 @@ struct Session::Plan {
   std::vector<char> has_ival;
 };
 
+// ---------------------------------------------------------------------------
+// Per-device pools.  The reference opens a Graph + Session for every partition (impl/DebugRowOps.scala:783-802), so
+// a drop-in caller creates and destroys sessions at that rate: creation must not cost device allocations.  What a
+// session needs on every run -- an error flag on the device with its pinned host mirror, and a modest workspace -- is
+// borrowed from these pools and handed back by the destructor; the device properties are read once.
+// ---------------------------------------------------------------------------
+namespace {
+constexpr int kMaxDevices = 64;
+constexpr size_t kPooledWorkspaceMax = size_t(64) << 20;   // larger workspaces are freed, not parked
+constexpr size_t kPooledWorkspaces = 4;
+
+struct ErrSlot { int32_t* dev; int32_t* host; };
+struct DevicePool {
+  std::mutex mu;
+  bool probed = false;
+  int cc_major = 0, sm_count = 0;
+  std::vector<ErrSlot> free_slots;
+  std::vector<std::pair<char*, size_t>> free_ws;
+};
+DevicePool g_pools[kMaxDevices];
+
+ErrSlot borrow_err_slot(DevicePool& p) {
+  std::lock_guard<std::mutex> lock(p.mu);
+  if (p.free_slots.empty()) {   // a batch of 32 slots, 256 bytes apart on the device, one cache line apart on the host
+    constexpr int kBatch = 32;
+    char* d = nullptr;
+    char* h = nullptr;
+    TFS_CUDA(cudaMalloc(reinterpret_cast<void**>(&d), kBatch * kAlign));
+    TFS_CUDA(cudaMemset(d, 0, kBatch * kAlign));
+    TFS_CUDA(cudaMallocHost(reinterpret_cast<void**>(&h), kBatch * 64));
+    memset(h, 0, kBatch * 64);
+    for (int i = 0; i < kBatch; ++i)
+      p.free_slots.push_back(ErrSlot{reinterpret_cast<int32_t*>(d + size_t(i) * kAlign), reinterpret_cast<int32_t*>(h + size_t(i) * 64)});
+  }
+  ErrSlot s = p.free_slots.back();
+  p.free_slots.pop_back();
+  return s;
+}
+}  // namespace
+
 Session::Session(const Graph& g, int device) : g_(g) { dev_.device = device; }
 
 Session::~Session() {
@@ -91,11 +133,23 @@ Session::~Session() {
   if (stream_ != own_stream_) cudaStreamSynchronize(own_stream_);
   for (auto& kv : const_dev_) cudaFree(kv.second);
   for (auto& kv : tc_weights_) { cudaFree(kv.second.first); cudaFree(kv.second.second); }
+  DevicePool& pool = g_pools[dev_.device];
+  {
+    std::lock_guard<std::mutex> lock(pool.mu);
+    if (ws_ && ws_cap_ <= kPooledWorkspaceMax && pool.free_ws.size() < kPooledWorkspaces) {
+      pool.free_ws.emplace_back(ws_, ws_cap_);
+      ws_ = nullptr;
+    }
+    if (err_flag_) {
+      *err_host_ = 0;
+      cudaMemsetAsync(err_flag_, 0, sizeof(int32_t), own_stream_);     // the next borrower finds a clean flag
+      cudaStreamSynchronize(own_stream_);
+      pool.free_slots.push_back(ErrSlot{err_flag_, err_host_});
+    }
+  }
   if (ws_) cudaFree(ws_);
   if (red_scratch_) cudaFree(red_scratch_);
   if (seg_scratch_) cudaFree(seg_scratch_);
-  if (err_flag_) cudaFree(err_flag_);
-  if (err_host_) cudaFreeHost(err_host_);
   for (int k = 0; k < 2; ++k)
     if (pipe_stream_[k]) cudaStreamDestroy(pipe_stream_[k]);
   if (pipe_event_) cudaEventDestroy(pipe_event_);
@@ -113,18 +167,25 @@ void Session::ensure_device() {
             "device ordinal " + std::to_string(dev_.device) + " out of range (" + std::to_string(count) + " devices)");
   TFS_CUDA(cudaSetDevice(dev_.device));
   if (device_ready_) return;
-  cudaDeviceProp prop{};
-  TFS_CUDA(cudaGetDeviceProperties(&prop, dev_.device));
-  TFS_CHECK(prop.major >= 10, TFS_ERR_CUDA,
-            std::string("device '") + prop.name + "' is sm_" + std::to_string(prop.major) + std::to_string(prop.minor) +
-                "; this library is built for sm_100a (B200) only");
-  dev_.sm_count = prop.multiProcessorCount;
+  TFS_CHECK(dev_.device < kMaxDevices, TFS_ERR_UNSUPPORTED, "device ordinal above the supported maximum");
+  DevicePool& pool = g_pools[dev_.device];
+  {
+    std::lock_guard<std::mutex> lock(pool.mu);
+    if (!pool.probed) {       // (cudaGetDeviceProperties costs milliseconds; two attributes are all that is needed)
+      TFS_CUDA(cudaDeviceGetAttribute(&pool.cc_major, cudaDevAttrComputeCapabilityMajor, dev_.device));
+      TFS_CUDA(cudaDeviceGetAttribute(&pool.sm_count, cudaDevAttrMultiProcessorCount, dev_.device));
+      pool.probed = true;
+    }
+  }
+  TFS_CHECK(pool.cc_major >= 10, TFS_ERR_CUDA,
+            "device " + std::to_string(dev_.device) + " has compute capability " + std::to_string(pool.cc_major) +
+                ".x; this library is built for sm_100a (B200) only");
+  dev_.sm_count = pool.sm_count;
   TFS_CUDA(cudaStreamCreateWithFlags(&own_stream_, cudaStreamNonBlocking));
   if (!stream_) stream_ = own_stream_;
-  TFS_CUDA(cudaMalloc(reinterpret_cast<void**>(&err_flag_), kAlign));
-  TFS_CUDA(cudaMemset(err_flag_, 0, kAlign));
-  TFS_CUDA(cudaMallocHost(reinterpret_cast<void**>(&err_host_), sizeof(int32_t)));
-  *err_host_ = 0;
+  const ErrSlot slot = borrow_err_slot(pool);
+  err_flag_ = slot.dev;
+  err_host_ = slot.host;
   device_ready_ = true;
 }
 
@@ -148,11 +209,23 @@ void Session::check_device_error() {
 
 void Session::reserve_workspace(size_t bytes) {
   if (bytes <= ws_cap_) return;
+  if (!ws_ && bytes <= kPooledWorkspaceMax) {     // a parked workspace of a finished session
+    DevicePool& pool = g_pools[dev_.device];
+    std::lock_guard<std::mutex> lock(pool.mu);
+    for (size_t i = 0; i < pool.free_ws.size(); ++i) {
+      if (pool.free_ws[i].second >= bytes) {
+        ws_ = pool.free_ws[i].first;
+        ws_cap_ = pool.free_ws[i].second;
+        pool.free_ws.erase(pool.free_ws.begin() + long(i));
+        return;
+      }
+    }
+  }
   TFS_CUDA(cudaStreamSynchronize(stream_));
   if (ws_) TFS_CUDA(cudaFree(ws_));
   ws_ = nullptr;
   ws_cap_ = 0;
-  size_t cap = align_up(bytes + bytes / 8);
+  size_t cap = std::max(align_up(bytes + bytes / 8), size_t(1) << 20);   // at least 1 MiB, so a parked one is reusable
   TFS_CUDA(cudaMalloc(reinterpret_cast<void**>(&ws_), cap));
   ws_cap_ = cap;
 }
