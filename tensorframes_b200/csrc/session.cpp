@@ -82,6 +82,7 @@ struct Session::Plan {
   std::vector<Shape> cshape;          // by node index: per-row (cell) shape
   std::vector<std::vector<int64_t>> ival;   // by node index: integer value of shape-derived nodes (has_ival)
   std::vector<char> has_ival;
+  bool may_raise = false;             // some step can set the device error flag (integer division, segment ids)
 };
 
 // ---------------------------------------------------------------------------
@@ -371,6 +372,12 @@ void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<
     plan.shape[size_t(idx)] = plan.batched[size_t(idx)] ? with_lead(plan.n_batch, plan.cshape[size_t(idx)])
                                                         : plan.cshape[size_t(idx)];
     TFS_CHECK(plan.shape[size_t(idx)].rank <= TFS_MAX_RANK, TFS_ERR_UNSUPPORTED, "tensor rank above the supported maximum");
+  }
+
+  for (int idx : plan.needed) {
+    const Node& n = g_.nodes[size_t(idx)];
+    const bool int_div = n.cls == OpClass::Binary && n.elt_op == E_DIV && (n.dtype == TFS_INT32 || n.dtype == TFS_INT64);
+    if (int_div || n.cls == OpClass::SegmentSum) plan.may_raise = true;
   }
 
   // levels: number of reduce/matmul nodes on the longest path below a node
@@ -1140,7 +1147,7 @@ bool Session::run_pipelined(const std::vector<TensorArg>& feeds, const std::vect
     }
   }
   for (int k = 0; k < 2; ++k) TFS_CUDA(cudaStreamSynchronize(pipe_stream_[k]));
-  check_device_error();
+  if (plan.may_raise) check_device_error();
   return true;
 }
 
@@ -1287,7 +1294,12 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
       TFS_CUDA(cudaMemcpyAsync(fetches[i].data, src, bytes, cudaMemcpyDeviceToHost, stream_));
     }
   }
-  if (any_host) check_device_error();
+  // results on the host: the caller may read them as soon as this returns, so a raised flag must fail the call now
+  // (device-resident results are checked by tfs_session_sync); graphs that cannot raise skip the round trip
+  if (any_host) {
+    if (plan.may_raise) check_device_error();
+    else TFS_CUDA(cudaStreamSynchronize(stream_));     // pinned destinations are written asynchronously
+  }
 }
 
 // ---------------------------------------------------------------------------
