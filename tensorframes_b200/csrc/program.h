@@ -73,20 +73,32 @@ struct EltProgram {
 };
 
 // ---- linear-chain fast path (kernels_chain.cu) --------------------------------------------
-constexpr int kChainSlots = 6;
+constexpr int kChainSlots = 8;
 enum : uint8_t {
   CH_NOP = 0, CH_ADD, CH_SUB, CH_RSUB, CH_MUL, CH_DIV, CH_RDIV, CH_MIN, CH_RMIN, CH_MAX, CH_RMAX,
   CH_NEG, CH_RELU, CH_SQUARE, CH_ABS, CH_SQRT, CH_RECIP,
+  CH_LOAD,   // acc = operand (general variant only)
+};
+// where a slot's second operand comes from
+enum : uint8_t {
+  CK_IMM = 0,   // scalar constant in `imm`
+  CK_COL,       // another column: operand_buf at the same flat index
+  CK_ROWVEC,    // operand_buf holds `period` elements broadcast along the rows (x * w + b with row vectors); the
+                // period divides the tile span and is a multiple of the vector width (make_chain checks)
+  CK_TMP,       // the saved tile
+  CK_SELF,      // the accumulator itself (x + x)
 };
 struct ChainSlot {
-  const void* operand_buf;  // second operand column (same dtype, same flat index), or null: use imm
+  const void* operand_buf;  // CK_COL / CK_ROWVEC
+  void* store_buf;          // != null: after the op the accumulator is also written to this column (a second fetch)
   uint64_t imm;
   uint8_t op;
-  uint8_t pad[3];
-  uint32_t period;          // != 0: operand_buf holds `period` elements broadcast along the rows (x * w + b with row
-                            // vectors); it divides the tile span and is a multiple of the vector width (make_chain)
+  uint8_t kind;
+  uint8_t save;             // after the op: saved tile = accumulator
+  uint8_t pad;
+  uint32_t period;
 };
-// geometry of the chain kernel's column-operand variant, shared with make_chain's eligibility test
+// geometry of the chain kernel's general variant, shared with make_chain's eligibility test
 constexpr int kChainThreads = 256;
 constexpr int kChainVecsPerThread = 4;
 struct ChainProgram {

@@ -780,8 +780,10 @@ struct GroupCompiler {
   }
 };
 
-// Recognises a compiled group that is a linear chain (see kernels_chain.cu) and rewrites it for
-// the straight-line kernel.  Returns false when the program needs the general interpreter.
+// Recognises a compiled group the straight-line kernel can run (see kernels_chain.cu) and rewrites it for that
+// kernel: one input column, then slots whose operand is a constant, another column, a row vector, the single saved
+// tile or the accumulator itself; reloads, one saved tile, extra output columns of the same dtype, an optional
+// final cast.  Returns false when the program needs the general interpreter.
 bool make_chain(const EltProgram& prog, ChainProgram& ch) {
   if (prog.n_instr < 2) return false;
   const Instr& first = prog.ins[0];
@@ -798,60 +800,140 @@ bool make_chain(const EltProgram& prog, ChainProgram& ch) {
   ch.dt = uint8_t(in.dt);
   ch.out_dt = ch.dt;
   const int dt = in.dt;
+  const int64_t lanes = 16 / ((dt & 1) ? 8 : 4);
+  const int64_t span = int64_t(kChainThreads) * kChainVecsPerThread * lanes;
   static const uint8_t kFwd[B_COUNT] = {CH_ADD, CH_SUB, CH_MUL, CH_DIV, CH_MIN, CH_MAX};
   static const uint8_t kRev[B_COUNT] = {CH_ADD, CH_RSUB, CH_MUL, CH_RDIV, CH_RMIN, CH_RMAX};
   static const uint8_t kUn[U_COUNT] = {CH_NEG, CH_RELU, CH_SQUARE, CH_ABS, CH_SQRT, CH_RECIP};
-  const void* pending = nullptr;   // operand fetched by a C_FETCH_BUF awaiting its C_BIN_X
-  bool have_pending = false, cast_seen = false;
-  uint32_t pending_period = 0;
-  for (int pc = 1; pc < prog.n_instr - 1; ++pc) {
-    const Instr& in_ = prog.ins[pc];
-    const int c = in_.code;
-    if (cast_seen) return false;                       // a cast may only end the chain
-    if (c == C_FETCH_BUF || c == C_FETCH_PER) {
-      if (have_pending) return false;
-      const BufRef& b = prog.bufs[in_.arg];
-      if (b.dt != dt || !aligned(b.ptr)) return false;
-      pending_period = 0;
-      if (c == C_FETCH_PER) {
-        // a row vector: its length must be a multiple of the vector width and divide the tile span
-        const int64_t lanes = 16 / ((dt & 1) ? 8 : 4);
-        const int64_t span = int64_t(kChainThreads) * kChainVecsPerThread * lanes;
-        if (b.period <= 0 || b.period % lanes != 0 || span % b.period != 0) return false;
-        pending_period = uint32_t(b.period);
-      }
-      pending = b.ptr;
-      have_pending = true;
-      continue;
+
+  struct Operand { uint8_t kind = CK_IMM; const void* buf = nullptr; uint32_t period = 0; uint64_t imm = 0; };
+  // a column / row-vector operand the kernel can read as whole vectors
+  auto column_operand = [&](const Instr& ins, bool periodic, Operand& o) {
+    const BufRef& b = prog.bufs[ins.arg];
+    if (b.dt != dt || !aligned(b.ptr)) return false;
+    o = Operand{};
+    o.buf = b.ptr;
+    if (periodic) {
+      if (b.period <= 0 || b.period % lanes != 0 || span % b.period != 0) return false;
+      o.kind = CK_ROWVEC;
+      o.period = uint32_t(b.period);
+    } else {
+      o.kind = CK_COL;
     }
+    return true;
+  };
+  auto push = [&](const ChainSlot& slot) {
+    if (ch.n_slots >= kChainSlots) return false;
+    ch.slots[ch.n_slots++] = slot;
+    return true;
+  };
+  auto slot_with = [](uint8_t op, const Operand& o) {
     ChainSlot slot{};
+    slot.op = op;
+    slot.kind = o.kind;
+    slot.operand_buf = o.buf;
+    slot.period = o.period;
+    slot.imm = o.imm;
+    return slot;
+  };
+  // the slot a save / store attaches to: the last one, or a no-op placed right after the initial load
+  auto last_slot = [&]() -> ChainSlot* {
+    if (ch.n_slots == 0) {
+      ChainSlot nop{};
+      nop.op = CH_NOP;
+      nop.kind = CK_IMM;
+      if (!push(nop)) return nullptr;
+    }
+    return &ch.slots[ch.n_slots - 1];
+  };
+
+  Operand pending;
+  bool have_pending = false, cast_seen = false;
+  for (int pc = 1; pc < prog.n_instr - 1; ++pc) {
+    const Instr& ins = prog.ins[pc];
+    const int c = ins.code;
+    if (cast_seen) return false;                       // a cast may only end the chain
+    Operand o;
+    switch (c) {
+      case C_FETCH_BUF:
+      case C_FETCH_PER:
+        if (have_pending || !column_operand(ins, c == C_FETCH_PER, pending)) return false;
+        have_pending = true;
+        continue;
+      case C_FETCH_TMP:
+        if (have_pending || ins.arg != 0) return false;    // one saved tile
+        pending = Operand{};
+        pending.kind = CK_TMP;
+        have_pending = true;
+        continue;
+      case C_FETCH_ACC:
+        if (have_pending) return false;
+        pending = Operand{};
+        pending.kind = CK_SELF;
+        have_pending = true;
+        continue;
+      case C_LOAD_BUF:
+      case C_LOAD_PER:
+        if (have_pending || !column_operand(ins, c == C_LOAD_PER, o) || !push(slot_with(CH_LOAD, o))) return false;
+        continue;
+      case C_LOAD_TMP:
+        if (have_pending || ins.arg != 0) return false;
+        o.kind = CK_TMP;
+        if (!push(slot_with(CH_LOAD, o))) return false;
+        continue;
+      case C_LOAD_IMM:
+        if (have_pending) return false;
+        o.kind = CK_IMM;
+        o.imm = ins.imm;
+        if (!push(slot_with(CH_LOAD, o))) return false;
+        continue;
+      case C_STTMP: {
+        if (have_pending || ins.arg != 0) return false;
+        ChainSlot* sl = last_slot();
+        if (!sl || sl->store_buf != nullptr) return false;   // (a slot saves before it stores; keep the program order)
+        sl->save = 1;
+        continue;
+      }
+      case C_STORE: {                                        // a further output column, in the chain's dtype
+        const BufRef& b = prog.bufs[ins.arg];
+        if (have_pending || b.dt != dt || !aligned(b.ptr)) return false;
+        ChainSlot* sl = last_slot();
+        if (!sl) return false;
+        if (sl->store_buf != nullptr) {                      // two stores in a row: a no-op slot carries the second
+          ChainSlot nop{};
+          nop.op = CH_NOP;
+          nop.kind = CK_IMM;
+          if (!push(nop)) return false;
+          sl = &ch.slots[ch.n_slots - 1];
+        }
+        sl->store_buf = b.ptr;
+        continue;
+      }
+      default: break;
+    }
     if (c >= C_BIN_X && c < C_BIN_X + B_COUNT * 8) {
       const int k = c - C_BIN_X;
       if (!have_pending || (k % 8) / 2 != dt) return false;
-      slot.op = (k & 1) ? kRev[k / 8] : kFwd[k / 8];
-      slot.operand_buf = pending;
-      slot.period = pending_period;
+      if (!push(slot_with((k & 1) ? kRev[k / 8] : kFwd[k / 8], pending))) return false;
       have_pending = false;
     } else if (c >= C_BIN_IMM && c < C_BIN_IMM + B_COUNT * 8) {
       const int k = c - C_BIN_IMM;
       if (have_pending || (k % 8) / 2 != dt) return false;
-      slot.op = (k & 1) ? kRev[k / 8] : kFwd[k / 8];
-      slot.imm = in_.imm;
+      o.kind = CK_IMM;
+      o.imm = ins.imm;
+      if (!push(slot_with((k & 1) ? kRev[k / 8] : kFwd[k / 8], o))) return false;
     } else if (c >= C_UNARY && c < C_UNARY + U_COUNT * 4) {
       const int k = c - C_UNARY;
       if (have_pending || k % 4 != dt) return false;
-      slot.op = kUn[k / 4];
+      if (!push(slot_with(kUn[k / 4], Operand{}))) return false;
     } else if (c >= C_CAST && c < C_CAST + 16) {
       const int k = c - C_CAST;
       if (have_pending || k / 4 != dt) return false;
       ch.out_dt = uint8_t(k % 4);
       cast_seen = true;
-      continue;
     } else {
       return false;
     }
-    if (ch.n_slots >= kChainSlots) return false;
-    ch.slots[ch.n_slots++] = slot;
   }
   if (have_pending) return false;
   return out.dt == ch.out_dt;

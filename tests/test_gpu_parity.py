@@ -337,6 +337,7 @@ def test_device_pointer_path_matches_host_path():
         dy = torch.from_numpy(y).cuda()
         dz = torch.empty(n, dtype=torch.float32, device="cuda")
         ds = torch.empty(2, dtype=torch.float64, device="cuda")
+        torch.cuda.synchronize()      # inputs were produced on torch's stream; the session runs on its own (a NULL handle selects it)
         s.set_stream(torch.cuda.current_stream().cuda_stream)
         s.run_into({"x": _native.DeviceArray.from_torch(dx.contiguous()) if dx.data_ptr() % 16 == 0 else
                     _native.DeviceArray(dx.data_ptr(), tfs.DoubleType, (n,), owner=dx),
@@ -363,6 +364,7 @@ def test_full_size_properties_on_device():
     ds = torch.empty(2, dtype=torch.float64, device="cuda")
     dm = torch.empty(2, dtype=torch.float64, device="cuda")
     with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        torch.cuda.synchronize()      # inputs were produced on torch's stream; the session runs on its own (a NULL handle selects it)
         s.set_stream(torch.cuda.current_stream().cuda_stream)
         s.run_into({"y_input": _native.DeviceArray.from_torch(y), "z_input": _native.DeviceArray.from_torch(y)},
                    {"y": _native.DeviceArray.from_torch(ds), "z": _native.DeviceArray.from_torch(dm)})
@@ -378,6 +380,7 @@ def test_full_size_properties_on_device():
         px = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x")
         g = dsl.build_graph(dsl.cast(dsl.maximum(px * 1.5 + 0.25, 0.0), tfs.FloatType).named("z"))
     with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        torch.cuda.synchronize()      # inputs were produced on torch's stream; the session runs on its own (a NULL handle selects it)
         s.set_stream(torch.cuda.current_stream().cuda_stream)
         s.run_into({"x": _native.DeviceArray.from_torch(x)}, {"z": _native.DeviceArray.from_torch(dz)})
         s.sync()
@@ -400,6 +403,7 @@ def test_full_size_aggregate_closed_form():
     out_keys = torch.empty(n_keys, dtype=torch.int64, device="cuda")
     DA = _native.DeviceArray.from_torch
     with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        torch.cuda.synchronize()      # inputs were produced on torch's stream; the session runs on its own (a NULL handle selects it)
         s.set_stream(torch.cuda.current_stream().cuda_stream)
         n_groups = s.aggregate_into(DA(keys), {"v_input": DA(v)}, {"v": DA(out)}, DA(out_keys))
         again = torch.empty_like(out)
@@ -439,6 +443,7 @@ def test_full_size_matmul_exact_on_small_integers():
         px = dsl.placeholder(tfs.FloatType, dsl.Unknown, k).named("x")
         g = dsl.build_graph((dsl.matmul(px, dsl.constant(w)) + dsl.constant(b)).named("y"))
     with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        torch.cuda.synchronize()      # inputs were produced on torch's stream; the session runs on its own (a NULL handle selects it)
         s.set_stream(torch.cuda.current_stream().cuda_stream)
         s.run_into({"x": _native.DeviceArray.from_torch(x)}, {"y": _native.DeviceArray.from_torch(y)})
         s.sync()
@@ -636,6 +641,38 @@ def test_row_vector_operands_bit_exact(dt, cell):
     want_z = np.maximum((x * w).astype(npdt) + b, npdt.type(0)).astype(npdt)
     assert got_z.tobytes() == want_z.tobytes()
     assert got_r.tobytes() == (b - x).astype(npdt).tobytes()
+
+
+@pytest.mark.parametrize("dt", ["f4", "f8", "i4", "i8"])
+def test_straight_line_kernel_small_dags_bit_exact(dt):
+    """Graphs the general variant of the straight-line kernel takes over from the interpreter: a saved tile
+    ((x+y)*(x-y)), a reload with a second fetch (y2 = x*2, z = x+3), the accumulator as its own operand (x+x), a
+    column on the left of a non-commutative op.  Ragged sizes exercise the tails."""
+    st = {"f4": tfs.FloatType, "f8": tfs.DoubleType, "i4": tfs.IntegerType, "i8": tfs.LongType}[dt]
+    npdt = np.dtype("<" + dt)
+    rng = np.random.default_rng(7)
+    for n in (1, 5, 4099, 70_001):
+        if npdt.kind == "i":
+            x = rng.integers(-1000, 1000, n).astype(npdt)
+            y = rng.integers(1, 1000, n).astype(npdt)
+        else:
+            x = rng.uniform(-2, 2, n).astype(npdt)
+            y = rng.uniform(1, 2, n).astype(npdt)
+        two, three = npdt.type(2), npdt.type(3)
+        with dsl.withGraph():
+            px = dsl.placeholder(st, dsl.Unknown).named("x")
+            py = dsl.placeholder(st, dsl.Unknown).named("y")
+            c2, c3 = dsl.constant(two), dsl.constant(three)
+            fetches = [((px + py) * (px - py)).named("a"), (px * c2).named("b"), (px + c3).named("c"), (px + px).named("d"),
+                       (py - px).named("e"), ((px - py) * (px - py)).named("f")]
+            g = dsl.build_graph(*fetches)
+        with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+            got = s.run({"x": x, "y": y}, [f.name for f in fetches])
+        with np.errstate(over="ignore"):
+            want = [((x + y).astype(npdt) * (x - y).astype(npdt)).astype(npdt), (x * two).astype(npdt), (x + three).astype(npdt),
+                    (x + x).astype(npdt), (y - x).astype(npdt), ((x - y).astype(npdt) * (x - y).astype(npdt)).astype(npdt)]
+        for f, w, gt in zip(fetches, want, got):
+            assert gt.tobytes() == w.tobytes(), (f.name, n)
 
 
 def test_chain_fast_path_unaligned_device_pointers():
@@ -882,6 +919,7 @@ def test_tensor_core_matmul_stays_inside_its_output(m_rows, k, n_cols):
         px = dsl.placeholder(tfs.FloatType, dsl.Unknown, k).named("x")
         g = dsl.build_graph(dsl.matmul(px, dsl.constant(w)).named("y"))
     with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        torch.cuda.synchronize()      # inputs were produced on torch's stream; the session runs on its own (a NULL handle selects it)
         s.set_stream(torch.cuda.current_stream().cuda_stream)
         s.run_into({"x": _native.DeviceArray.from_torch(x)}, {"y": _native.DeviceArray(y.data_ptr(), tfs.FloatType, (m_rows, n_cols), owner=buf)})
         s.sync()
@@ -903,6 +941,7 @@ def test_keyed_and_shape_steps_stay_inside_their_outputs():
     DA = _native.DeviceArray
     g = aggregate_graph(tfs.FloatType, (cell,), "sum")
     with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        torch.cuda.synchronize()      # inputs were produced on torch's stream; the session runs on its own (a NULL handle selects it)
         s.set_stream(torch.cuda.current_stream().cuda_stream)
         ng = s.aggregate_into(DA.from_torch(keys), {"v_input": DA.from_torch(v)},
                               {"v": DA(obuf[guard:].data_ptr(), tfs.FloatType, (n_keys, cell), owner=obuf)},
@@ -928,6 +967,7 @@ def test_keyed_and_shape_steps_stay_inside_their_outputs():
         bufs[nm] = (b, numel)
         outs[nm] = DA(b[guard:].data_ptr(), st, sh, owner=b)
     with _native.Graph(g2) as gr, _native.Session(gr, 0) as s:
+        torch.cuda.synchronize()      # inputs were produced on torch's stream; the session runs on its own (a NULL handle selects it)
         s.set_stream(torch.cuda.current_stream().cuda_stream)
         s.run_into({"v": DA.from_torch(v), "ids": DA.from_torch(keys)}, outs)
         s.sync()
@@ -953,6 +993,7 @@ def test_blocks_beyond_2_31_elements():
         g = dsl.build_graph((p * 2 + 1).named("y"), dsl.reduce_sum(p, [0]).named("s"), dsl.reduce_min(p, [0]).named("m"))
     mn = torch.empty((), dtype=torch.int32, device="cuda")
     DA = _native.DeviceArray.from_torch
+    torch.cuda.synchronize()      # x was filled on torch's stream; the session runs on its own
     with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
         s.run_into({"x": DA(x)}, {"y": DA(y), "s": DA(tot), "m": DA(mn)})
         s.sync()
