@@ -323,7 +323,12 @@ def run_ours(args):
                 sess.run_into(host_in, host_out)      # H2D + kernels + D2H + sync inside
                 if wl == "c2" and world > 1:
                     parts = [torch.from_numpy(host_out[n]).to(device) for n in names]
-                    combine_reduce_blocks(parts, names, merge)
+                    if overlap:      # the merge session lives on the side stream: order it after the copies above
+                        side.wait_stream(torch.cuda.current_stream())
+                        with torch.cuda.stream(side):
+                            combine_reduce_blocks(parts, names, merge)
+                    else:
+                        combine_reduce_blocks(parts, names, merge)
                     torch.cuda.synchronize()
 
             e2e_step()
