@@ -288,11 +288,14 @@ def run_ours(args):
     # parity spot check on the device (the tests hold the real parity checks)
     if wl == "c2":
         res = merged_t if world > 1 else outs_t
-        if world == 1:
-            y = feeds_t["y_input"]
-            ref_sum = y.sum(dim=0)
-            assert torch.all((res["y"] - ref_sum).abs() <= 1e-12 * y.abs().sum(dim=0)), (res["y"], ref_sum)
-            assert torch.equal(res["z"], feeds_t["z_input"].min(dim=0).values)
+        y = feeds_t["y_input"]
+        ref_sum, ref_abs, ref_min = y.sum(dim=0), y.abs().sum(dim=0), feeds_t["z_input"].min(dim=0).values
+        if world > 1:       # the merged row must be the reduction over every rank's partition
+            dist.all_reduce(ref_sum)
+            dist.all_reduce(ref_abs)
+            dist.all_reduce(ref_min, op=dist.ReduceOp.MIN)
+        assert torch.all((res["y"] - ref_sum).abs() <= 1e-12 * ref_abs), (res["y"], ref_sum)
+        assert torch.equal(res["z"], ref_min)
     else:
         n_chk = min(rows, 1 << 24)
         x = feeds_t["x"][:n_chk]
