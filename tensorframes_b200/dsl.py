@@ -175,6 +175,10 @@ def _lift(x, like: Node) -> Node:
     """Implicit conversion of python scalars / sequences to constants (dsl/Implicits.scala)."""
     if isinstance(x, Node):
         return x
+    if type(x) in (int, float):
+        # a bare python number takes the dtype of the tensor it meets, as python TF's operator overloads do
+        # (x_float32 * 1.5 is a float32 product); arrays and sequences keep their own dtype
+        return constant(like.scalarType.np_dtype.type(x))
     return constant(x)
 
 

@@ -298,3 +298,20 @@ def test_from_arrow_lists_and_rejections():
         TensorFrame.from_arrow(pa.table({"x": pa.array([1.0, None])}))
     with pytest.raises(TypeError, match="not supported"):
         TensorFrame.from_arrow(pa.table({"x": pa.array([True, False])}))
+
+
+def test_python_scalars_take_the_tensor_dtype():
+    """x_float32 * 1.5 stays float32 (python TF's operator overloads convert the scalar); arrays keep their dtype."""
+    with dsl.withGraph():
+        x = dsl.placeholder(tfs.FloatType, Unknown).named("x")
+        z = (2 - x * 1.5).named("z")
+        g = dsl.build_graph(z)
+    assert z.scalarType is tfs.FloatType
+    nodes = {n.name: n for n in graphdef.parse_graph(g)}
+    consts = [n for n in nodes.values() if n.op == "Const"]
+    assert len(consts) == 2 and all(n.attr["dtype"] == ("type", 1) for n in consts)
+    with dsl.withGraph():
+        i = dsl.placeholder(tfs.LongType, Unknown).named("i")
+        assert (i + 3).scalarType is tfs.LongType
+        with pytest.raises(AssertionError, match="should be the same"):
+            i + np.float64(3.0)           # a typed numpy scalar is not converted
