@@ -978,6 +978,45 @@ def test_keyed_and_shape_steps_stay_inside_their_outputs():
     assert torch.equal(bufs["s"][0][guard:guard + n_keys * cell].view(n_keys, cell), want)
 
 
+def test_sessions_on_concurrent_threads():
+    """The reference runs N task threads in one JVM (local[N]), each with its own Graph + Session per partition:
+    distinct handles must work concurrently, creation / destruction included (the per-device pools are shared)."""
+    import threading
+    rng = np.random.default_rng(17)
+    n_threads, rounds = 6, 12
+    xs = [rng.uniform(-1, 1, 50_000 + 37 * t) for t in range(n_threads)]
+    keys = [rng.integers(0, 50, len(x)) for x in xs]
+    with dsl.withGraph():
+        px = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x")
+        g_map = dsl.build_graph(((px + 1.0) * (px - 1.0)).named("z"), dsl.reduce_sum(px, [0]).named("s"))
+    g_agg = aggregate_graph(tfs.DoubleType, (), "sum")
+    errors = []
+
+    def work(t):
+        try:
+            x, k = xs[t], keys[t]
+            want_z = (x + 1.0) * (x - 1.0)
+            for _ in range(rounds):
+                with _native.Graph(g_map) as gr, _native.Session(gr, 0) as s:
+                    z, tot = s.run({"x": x}, ["z", "s"])
+                assert z.tobytes() == want_z.tobytes()
+                assert abs(tot - x.sum()) <= 1e-12 * np.abs(x).sum()
+                with _native.Graph(g_agg) as gr, _native.Session(gr, 0) as s:
+                    got_k, (got_v,) = s.aggregate(k, {"v_input": x}, ["v"], max_groups=64)
+                assert got_k.tolist() == sorted(set(k.tolist()))
+                ref = np.array([x[k == kk].sum() for kk in got_k])
+                assert np.all(np.abs(got_v - ref) <= 1e-12 * np.abs(x).sum())
+        except Exception as exc:      # surfaced in the main thread below
+            errors.append((t, repr(exc)))
+
+    threads = [threading.Thread(target=work, args=(t,)) for t in range(n_threads)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors
+
+
 def test_blocks_beyond_2_31_elements():
     """int64 sizes end to end: the reference caps a block at Int.MaxValue scalars (impl/datatypes.scala:74-78);
     here a 2.2e9-element column is mapped and reduced in one block each (closed-form checks on the device)."""
