@@ -3,6 +3,8 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <atomic>
+
 #include "common.h"
 #include "graph.h"
 #include "program.h"
@@ -14,6 +16,16 @@ inline void cuda_check(cudaError_t e, const char* what) {
     fail(TFS_ERR_CUDA, std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")");
 }
 #define TFS_CUDA(call) ::tfs::cuda_check((call), #call)
+
+// Function attributes (the opt-in to more than 48 KB of dynamic shared memory) belong to a device: a launcher sets them
+// the first time it runs on each device.  One flag word per call site; setting twice is harmless, so a lost race is too.
+struct PerDeviceOnce {
+  std::atomic<uint64_t> done{0};
+  bool first(int device) {
+    const uint64_t bit = uint64_t(1) << (device & 63);
+    return (done.fetch_or(bit) & bit) == 0;
+  }
+};
 
 struct DeviceInfo {
   int device = 0;

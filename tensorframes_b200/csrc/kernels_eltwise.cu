@@ -370,12 +370,12 @@ eltwise_kernel(const __grid_constant__ EltProgram prog, const int64_t n) {
 
 template <int ES, int P>
 int launch_variant(const EltProgram& prog, int64_t n, const DeviceInfo& dev, cudaStream_t stream) {
-  static int blocks_per_sm = 0;  // same for every device of a homogeneous box
-  if (blocks_per_sm == 0) {
+  // same for every device of a homogeneous box; initialised once, thread-safely
+  static const int blocks_per_sm = [] {
     int b = 0;
     TFS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, eltwise_kernel<ES, P>, kThreads, 0));
-    blocks_per_sm = b > 0 ? b : 1;
-  }
+    return b > 0 ? b : 1;
+  }();
   const int64_t n_vec = (n + P - 1) / P;
   const int64_t n_tiles = (n_vec + int64_t(kThreads) * kJ - 1) / (int64_t(kThreads) * kJ);
   int64_t grid = int64_t(dev.sm_count) * blocks_per_sm;

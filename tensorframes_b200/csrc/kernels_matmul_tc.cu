@@ -595,14 +595,13 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  if (!fn) {
+  static const EncodeTiledFn fn = [] {
     void* p = nullptr;
     cudaDriverEntryPointQueryResult q;
     TFS_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
     TFS_CHECK(p != nullptr && q == cudaDriverEntryPointSuccess, TFS_ERR_CUDA, "cuTensorMapEncodeTiled is not available in this driver");
-    fn = reinterpret_cast<EncodeTiledFn>(p);
-  }
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
   return fn;
 }
 
@@ -639,15 +638,15 @@ int launch_split_weights(const float* w, bool transposed, int64_t K, int64_t N, 
 
 int launch_matmul_tc(const float* x, const float* w_hi, const float* w_lo, const float* bias, float* out, int64_t M,
                      int64_t N, int64_t K, const DeviceInfo& dev, cudaStream_t stream) {
-  static bool attr_set = false;
-  static bool single_cta = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr;
+  if (attr.first(dev.device)) {
     TFS_CUDA(cudaFuncSetAttribute(matmul_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kSmemBytes)));
     TFS_CUDA(cudaFuncSetAttribute(matmul_tc_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kSmemBytes2)));
-    const char* impl = std::getenv("TFS_MATMUL_IMPL");   // "tc1": the single-CTA kernel, kept for A/B measurements
-    single_cta = impl != nullptr && std::string(impl) == "tc1";
-    attr_set = true;
   }
+  static const bool single_cta = [] {
+    const char* impl = std::getenv("TFS_MATMUL_IMPL");   // "tc1": the single-CTA kernel, kept for A/B measurements
+    return impl != nullptr && std::string(impl) == "tc1";
+  }();
   const CUtensorMap map_x = make_map(x, uint64_t(M), uint64_t(K), kBlockM);
   if (single_cta) {
     const CUtensorMap map_whi = make_map(w_hi, uint64_t(N), uint64_t(K), uint32_t(N));
