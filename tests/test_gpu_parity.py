@@ -1017,6 +1017,38 @@ def test_sessions_on_concurrent_threads():
     assert not errors, errors
 
 
+@pytest.mark.skipif(_native.device_count() < 2, reason="needs two GPUs in one process")
+def test_two_devices_in_one_process():
+    """A session is bound to the device it was created for; one process may drive several (pools, function
+    attributes and constant uploads are per device)."""
+    rng = np.random.default_rng(23)
+    x = rng.uniform(-1, 1, (300_000, 64)).astype(np.float32)
+    w = rng.uniform(-0.2, 0.2, (64, 32)).astype(np.float32)
+    y2 = rng.uniform(0, 1, (2_000_000, 2))
+    keys = rng.integers(0, 100, len(x))
+    with dsl.withGraph():
+        px = dsl.placeholder(tfs.FloatType, dsl.Unknown, 64).named("x")
+        g_mm = dsl.build_graph(dsl.relu(dsl.matmul(px, dsl.constant(w))).named("y"))
+    with dsl.withGraph():
+        py = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("y_input")
+        g_red = dsl.build_graph(dsl.reduce_sum(py, [0]).named("y"))
+    g_agg = aggregate_graph(tfs.FloatType, (64,), "max")
+    results = []
+    for dev in (0, 1, 0):
+        with _native.Graph(g_mm) as gr, _native.Session(gr, dev) as s:
+            (mm,) = s.run({"x": x}, ["y"])
+        with _native.Graph(g_red) as gr, _native.Session(gr, dev) as s:
+            (red,) = s.run({"y_input": y2}, ["y"])
+        with _native.Graph(g_agg) as gr, _native.Session(gr, dev) as s:
+            k, (v,) = s.aggregate(keys, {"v_input": x}, ["v"], max_groups=128)
+        results.append((mm, red, k, v))
+    for mm, red, k, v in results[1:]:
+        assert mm.tobytes() == results[0][0].tobytes() and red.tobytes() == results[0][1].tobytes()
+        assert k.tobytes() == results[0][2].tobytes() and v.tobytes() == results[0][3].tobytes()
+    exact = np.maximum(x.astype(np.float64) @ w.astype(np.float64), 0)
+    assert np.all(np.abs(results[0][0] - exact) <= 1e-5 * (np.abs(x).astype(np.float64) @ np.abs(w).astype(np.float64)))
+
+
 def test_blocks_beyond_2_31_elements():
     """int64 sizes end to end: the reference caps a block at Int.MaxValue scalars (impl/datatypes.scala:74-78);
     here a 2.2e9-element column is mapped and reduced in one block each (closed-form checks on the device)."""
