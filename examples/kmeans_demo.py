@@ -4,7 +4,7 @@
 Each iteration is one trimmed map_blocks (distances to the centroids, nearest centroid, per-block segment sums of
 the points -- all on the GPU, one pre-aggregated row per partition) and one reduce_blocks over those rows.
 
-    python examples/kmeans_demo.py [n_points] [n_features] [k] [n_partitions]
+    python examples/kmeans_demo.py [n_points] [n_features] [k] [n_partitions] [--host]
 """
 import os
 import sys
@@ -73,14 +73,17 @@ def kmeanstf(df, init_centers, num_iters=5):
 
 
 def main():
-    n = int(sys.argv[1]) if len(sys.argv) > 1 else 2_000_000
-    m = int(sys.argv[2]) if len(sys.argv) > 2 else 16
-    k = int(sys.argv[3]) if len(sys.argv) > 3 else 10
-    parts = int(sys.argv[4]) if len(sys.argv) > 4 else 4
+    args = [a for a in sys.argv[1:] if not a.startswith("--")]
+    n = int(args[0]) if len(args) > 0 else 2_000_000
+    m = int(args[1]) if len(args) > 1 else 16
+    k = int(args[2]) if len(args) > 2 else 10
+    parts = int(args[3]) if len(args) > 3 else 4
     rng = np.random.default_rng(0)
     true = rng.uniform(-10, 10, (k, m))
     x = true[rng.integers(0, k, n)] + rng.normal(0, 1.0, (n, m))
     df = tfs.analyze(TensorFrame.from_columns({"features": x}, num_partitions=parts))
+    if "--host" not in sys.argv:
+        df = df.to_device(0)          # the points stay in HBM across iterations; only the [k, m] sums come back
     init = x[rng.choice(n, k, replace=False)].copy()
     centers, ds = kmeanstf(df, init, num_iters=8)
     assert all(b <= a * (1 + 1e-12) for a, b in zip(ds, ds[1:])), "k-means must not increase the total distance"

@@ -245,6 +245,21 @@ class Session:
         _check(fn(self._h, len(feeds), farr, len(fetches), oarr))
         return outs
 
+    def run_torch(self, feeds: Dict[str, object], fetches: Sequence[str], device: int):
+        """Device in, device out: feeds are torch CUDA tensors (numpy arrays are accepted too and uploaded by the
+        call), results are new torch tensors on `device`.  torch only owns the memory; the work is the same
+        tfs_session_run.  Inputs produced on torch's current stream are ordered before the run, and the results are
+        complete when this returns."""
+        import torch
+        torch.cuda.current_stream(device).synchronize()
+        wrapped = {k: (DeviceArray.from_torch(v.contiguous()) if hasattr(v, "is_cuda") else v) for k, v in feeds.items()}
+        metas = self.resolve(wrapped, fetches)
+        tdt = {"float64": torch.float64, "float32": torch.float32, "int32": torch.int32, "int64": torch.int64}
+        outs = [torch.empty(tuple(shape), dtype=tdt[st.np_dtype.name], device=f"cuda:{device}") for st, shape in metas]
+        self.run_into(wrapped, {name: DeviceArray.from_torch(o) for name, o in zip(fetches, outs)})
+        self.sync()
+        return outs
+
     def run_into(self, feeds: Dict[str, object], fetches: Dict[str, object]) -> None:
         """Run with caller-provided output buffers (numpy arrays or DeviceArray). Device-only calls
         return as soon as the work is enqueued; use sync()."""

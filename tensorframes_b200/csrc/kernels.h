@@ -93,7 +93,10 @@ int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, ch
 int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, char* scratch, AggLayout& L,
                         int64_t* out_keys_dev, const DeviceInfo& dev, cudaStream_t stream);
 // pass 4: out[g, :] = reduce over the rows of group g of payload[row, :].
-int launch_agg_reduce(int dtype, int red_op, const void* payload, int64_t cell, int64_t n_groups, char* scratch,
-                      const AggLayout& L, void* out, const DeviceInfo& dev, cudaStream_t stream);
+// split_scratch (agg_split_scratch_bytes, may be null): partial rows when few large groups are cut into pieces.
+size_t agg_split_scratch_bytes(int64_t cell, const DeviceInfo& dev);
+int launch_agg_reduce(int dtype, int red_op, const void* payload, int64_t cell, int64_t n_groups, int64_t n_rows, char* scratch,
+                      const AggLayout& L, void* out, void* split_scratch, size_t split_bytes, const DeviceInfo& dev,
+                      cudaStream_t stream);
 
 }  // namespace tfs

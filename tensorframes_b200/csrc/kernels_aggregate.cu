@@ -272,24 +272,29 @@ __device__ __forceinline__ void load_v(const T* p, T (&x)[V]) {
   }
 }
 
-// One warp per group.  The warp is split into R row-lanes x C col-lanes (R * C = 32, C a power
-// of two >= ceil(cell / V) when the cell fits, else C = 32 with a loop over column chunks).
-// kU rows are in flight per row-lane.
+// One warp per work item = (group, part): normally one part per group; when there are few, large groups
+// (k-means: 10 segments, a low-cardinality groupBy) every group's segment is cut into `parts` equal pieces so
+// that the whole chip has work, the pieces go to a partial buffer and fold_parts_kernel combines them in order.
+// The warp is split into R row-lanes x C col-lanes (R * C = 32, C a power of two >= ceil(cell / V) when the
+// cell fits, else C = 32 with a loop over column chunks).  kU rows are in flight per row-lane.
 template <class T, int OP, int V>
 __global__ void __launch_bounds__(kThreads)
 agg_gather_reduce_kernel(const T* __restrict__ payload, const int cell, const unsigned int* __restrict__ perm,
                          const unsigned int* __restrict__ offsets, const unsigned int* __restrict__ counts,
                          const unsigned int* __restrict__ group_slot, const int64_t n_groups, const int col_lanes,
-                         T* __restrict__ out) {
+                         const int parts, T* __restrict__ out) {
   constexpr int kU = 8;
   const int lane = threadIdx.x & 31;
   const int64_t warp = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
   const int C = col_lanes, R = 32 / C;
   const int cl = lane % C, rl = lane / C;
-  for (int64_t g = warp; g < n_groups; g += warps) {
-    const unsigned int slot = group_slot[g];
-    const unsigned long long lo = offsets[slot], hi = lo + counts[slot];
+  const int64_t n_items = n_groups * parts;
+  for (int64_t g = warp; g < n_items; g += warps) {          // g indexes the output row: the group, or (group, part)
+    const unsigned int slot = group_slot[g / parts];
+    const unsigned long long part = (unsigned long long)(g % parts), cnt = counts[slot];
+    const unsigned long long lo = offsets[slot] + cnt * part / (unsigned long long)parts;
+    const unsigned long long hi = offsets[slot] + cnt * (part + 1) / (unsigned long long)parts;
     for (int cbase = 0; cbase < cell; cbase += C * V) {   // warp-uniform trip count
       const int c0 = cbase + cl * V;
       const bool active = c0 < cell;
@@ -330,10 +335,26 @@ agg_gather_reduce_kernel(const T* __restrict__ payload, const int cell, const un
   }
 }
 
+int64_t grid_for(int64_t n, const DeviceInfo& dev);
+
+// out[g, c] = fold over part of partial[(g * parts + part), c], in part order
+template <class T, int OP>
+__global__ void __launch_bounds__(kThreads)
+fold_parts_kernel(const T* __restrict__ partial, const int64_t n_groups, const int64_t cell, const int parts, T* __restrict__ out) {
+  const int64_t n = n_groups * cell;
+  const int64_t stride = int64_t(gridDim.x) * blockDim.x;
+  for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const int64_t g = i / cell, c = i % cell;
+    T acc = partial[(g * parts) * cell + c];
+    for (int p = 1; p < parts; ++p) acc = red_op<T, OP>(acc, partial[(g * parts + p) * cell + c]);
+    out[i] = acc;
+  }
+}
+
 template <class T, int OP>
 int launch_gather_t(const T* payload, int64_t cell, const unsigned int* perm, const unsigned int* offsets,
-                    const unsigned int* counts, const unsigned int* group_slot, int64_t n_groups, T* out,
-                    const DeviceInfo& dev, cudaStream_t stream) {
+                    const unsigned int* counts, const unsigned int* group_slot, int64_t n_groups, int64_t n_rows, T* out,
+                    void* split_scratch, size_t split_bytes, const DeviceInfo& dev, cudaStream_t stream) {
   if (n_groups <= 0 || cell <= 0) return 0;
   constexpr int VMAX = 16 / int(sizeof(T));
   int V = 1;
@@ -343,32 +364,47 @@ int launch_gather_t(const T* payload, int64_t cell, const unsigned int* perm, co
   int need = int((cell + V - 1) / V);
   int C = 1;
   while (C < need && C < 32) C <<= 1;
+  // few large groups: cut every segment into `parts` pieces so that about 32 warps per SM have work
+  const int64_t target = int64_t(dev.sm_count) * 32;
+  int parts = 1;
+  if (split_scratch != nullptr && n_groups < target && n_rows / n_groups >= 2048) {
+    int64_t p = std::min<int64_t>((target + n_groups - 1) / n_groups, 1024);
+    p = std::min<int64_t>(p, n_rows / n_groups / 256);                       // at least 256 rows per piece
+    p = std::min<int64_t>(p, int64_t(split_bytes / (size_t(n_groups) * size_t(cell) * sizeof(T))));
+    if (p > 1) parts = int(p);
+  }
+  T* dst = parts > 1 ? static_cast<T*>(split_scratch) : out;
   const int64_t warps_per_cta = kThreads / 32;
-  int64_t grid = std::min<int64_t>((n_groups + warps_per_cta - 1) / warps_per_cta, int64_t(dev.sm_count) * 16);
+  const int64_t items = n_groups * parts;
+  int64_t grid = std::min<int64_t>((items + warps_per_cta - 1) / warps_per_cta, int64_t(dev.sm_count) * 16);
   if (grid < 1) grid = 1;
   const int icell = int(cell);
   if (V == 4) {
     if constexpr (VMAX == 4)
-      agg_gather_reduce_kernel<T, OP, 4><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, counts, group_slot, n_groups, C, out);
+      agg_gather_reduce_kernel<T, OP, 4><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, counts, group_slot, n_groups, C, parts, dst);
   } else if (V == 2) {
-    agg_gather_reduce_kernel<T, OP, 2><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, counts, group_slot, n_groups, C, out);
+    agg_gather_reduce_kernel<T, OP, 2><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, counts, group_slot, n_groups, C, parts, dst);
   } else {
-    agg_gather_reduce_kernel<T, OP, 1><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, counts, group_slot, n_groups, C, out);
+    agg_gather_reduce_kernel<T, OP, 1><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, counts, group_slot, n_groups, C, parts, dst);
   }
   TFS_CUDA(cudaGetLastError());
-  return 1;
+  if (parts == 1) return 1;
+  fold_parts_kernel<T, OP><<<(unsigned)grid_for(n_groups * cell, dev), kThreads, 0, stream>>>(dst, n_groups, cell, parts, out);
+  TFS_CUDA(cudaGetLastError());
+  return 2;
 }
 
 template <class T>
 int launch_gather_op(int red_op, const void* payload, int64_t cell, const unsigned int* perm,
                      const unsigned int* offsets, const unsigned int* counts, const unsigned int* group_slot,
-                     int64_t n_groups, void* out, const DeviceInfo& dev, cudaStream_t stream) {
+                     int64_t n_groups, int64_t n_rows, void* out, void* split_scratch, size_t split_bytes, const DeviceInfo& dev,
+                     cudaStream_t stream) {
   const T* p = static_cast<const T*>(payload);
   T* o = static_cast<T*>(out);
   switch (red_op) {
-    case R_SUM: return launch_gather_t<T, R_SUM>(p, cell, perm, offsets, counts, group_slot, n_groups, o, dev, stream);
-    case R_MIN: return launch_gather_t<T, R_MIN>(p, cell, perm, offsets, counts, group_slot, n_groups, o, dev, stream);
-    default: return launch_gather_t<T, R_MAX>(p, cell, perm, offsets, counts, group_slot, n_groups, o, dev, stream);
+    case R_SUM: return launch_gather_t<T, R_SUM>(p, cell, perm, offsets, counts, group_slot, n_groups, n_rows, o, split_scratch, split_bytes, dev, stream);
+    case R_MIN: return launch_gather_t<T, R_MIN>(p, cell, perm, offsets, counts, group_slot, n_groups, n_rows, o, split_scratch, split_bytes, dev, stream);
+    default: return launch_gather_t<T, R_MAX>(p, cell, perm, offsets, counts, group_slot, n_groups, n_rows, o, split_scratch, split_bytes, dev, stream);
   }
 }
 
@@ -491,17 +527,26 @@ int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, c
   return 1;   // counted as one launch of ours: the sorts' internal kernels are library code
 }
 
-int launch_agg_reduce(int dtype, int red_op, const void* payload, int64_t cell, int64_t n_groups, char* scratch,
-                      const AggLayout& L, void* out, const DeviceInfo& dev, cudaStream_t stream) {
+size_t agg_split_scratch_bytes(int64_t cell, const DeviceInfo& dev) {
+  // room for the partial rows of split groups: at most 2 x (32 warps per SM) work items of one cell each;
+  // very wide cells go without (one warp per group then)
+  const size_t bytes = size_t(2) * size_t(dev.sm_count) * 32 * size_t(std::max<int64_t>(cell, 1)) * 8;
+  return bytes <= (size_t(256) << 20) ? bytes : 0;
+}
+
+int launch_agg_reduce(int dtype, int red_op, const void* payload, int64_t cell, int64_t n_groups, int64_t n_rows, char* scratch,
+                      const AggLayout& L, void* out, void* split_scratch, size_t split_bytes, const DeviceInfo& dev,
+                      cudaStream_t stream) {
   const unsigned int* perm = reinterpret_cast<const unsigned int*>(scratch + L.off_perm);
   const unsigned int* offsets = reinterpret_cast<const unsigned int*>(scratch + L.off_offsets);
   const unsigned int* counts = reinterpret_cast<const unsigned int*>(scratch + L.off_counts);
   const unsigned int* group_slot = reinterpret_cast<const unsigned int*>(scratch + L.off_group_slot);
+  if (split_bytes == 0) split_scratch = nullptr;
   switch (dtype) {
-    case TFS_FLOAT: return launch_gather_op<float>(red_op, payload, cell, perm, offsets, counts, group_slot, n_groups, out, dev, stream);
-    case TFS_DOUBLE: return launch_gather_op<double>(red_op, payload, cell, perm, offsets, counts, group_slot, n_groups, out, dev, stream);
-    case TFS_INT32: return launch_gather_op<int>(red_op, payload, cell, perm, offsets, counts, group_slot, n_groups, out, dev, stream);
-    case TFS_INT64: return launch_gather_op<long long>(red_op, payload, cell, perm, offsets, counts, group_slot, n_groups, out, dev, stream);
+    case TFS_FLOAT: return launch_gather_op<float>(red_op, payload, cell, perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
+    case TFS_DOUBLE: return launch_gather_op<double>(red_op, payload, cell, perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
+    case TFS_INT32: return launch_gather_op<int>(red_op, payload, cell, perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
+    case TFS_INT64: return launch_gather_op<long long>(red_op, payload, cell, perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
   }
   fail(TFS_ERR_UNSUPPORTED, "aggregate: unsupported dtype");
 }

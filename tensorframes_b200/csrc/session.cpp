@@ -1040,7 +1040,9 @@ void Session::exec_step(const Plan& plan, size_t step_index, std::vector<void*>&
       const size_t off_keys64 = align_up(L.bytes);
       const size_t off_out_keys = off_keys64 + align_up(size_t(n_rows) * 8);
       const size_t off_sums = off_out_keys + align_up(size_t(max_groups) * 8);
-      const size_t need = off_sums + align_up(size_t(max_groups) * size_t(cell) * es);
+      const size_t off_split = off_sums + align_up(size_t(max_groups) * size_t(cell) * es);
+      const size_t split_bytes = agg_split_scratch_bytes(cell, dev_);
+      const size_t need = off_split + align_up(split_bytes);
       if (need > seg_scratch_cap_) {
         TFS_CUDA(cudaStreamSynchronize(stream));
         if (seg_scratch_) TFS_CUDA(cudaFree(seg_scratch_));
@@ -1065,7 +1067,8 @@ void Session::exec_step(const Plan& plan, size_t step_index, std::vector<void*>&
                 "UnsortedSegmentSum: segment ids out of range [0, " + std::to_string(segments) + ")");
       const int64_t n_groups = header[2];
       launches_ += launch_agg_segments(keys, n_rows, n_groups, scratch, L, d_out_keys, dev_, stream);
-      launches_ += launch_agg_reduce(n.dtype, R_SUM, dev_ptr[size_t(n.in[0])], cell, n_groups, scratch, L, scratch + off_sums, dev_, stream);
+      launches_ += launch_agg_reduce(n.dtype, R_SUM, dev_ptr[size_t(n.in[0])], cell, n_groups, n_rows, scratch, L, scratch + off_sums,
+                                     scratch + off_split, split_bytes, dev_, stream);
       launches_ += launch_segment_scatter(n.dtype, scratch + off_sums, d_out_keys, n_groups, cell, segments, dev_ptr[size_t(idx)],
                                           err_flag_, dev_, stream);
       break;
@@ -1438,6 +1441,10 @@ void Session::aggregate(int64_t n_rows, const int64_t* keys, const std::vector<T
   // workspace: [agg scratch][out_keys][staged keys][staged feeds][staged outputs]
   size_t off = up(L.bytes);
   const size_t off_out_keys = off; off += up(size_t(max_groups) * 8);
+  int64_t widest = 1;
+  for (const Item& it : items) widest = std::max(widest, it.cell);
+  const size_t split_bytes = agg_split_scratch_bytes(widest, dev_);
+  const size_t off_split = off; off += up(split_bytes);
   const bool keys_dev = is_device_pointer(keys);
   size_t off_keys = 0;
   if (!keys_dev) { off_keys = off; off += up(size_t(n_rows) * 8); }
@@ -1474,7 +1481,8 @@ void Session::aggregate(int64_t n_rows, const int64_t* keys, const std::vector<T
       payload = ws_ + off_feed[k];
     }
     void* out = off_out[k] != SIZE_MAX ? static_cast<void*>(ws_ + off_out[k]) : fetches[items[k].fetch].data;
-    launches_ += launch_agg_reduce(n.dtype, n.red_op, payload, items[k].cell, n_groups, scratch, L, out, dev_, stream_);
+    launches_ += launch_agg_reduce(n.dtype, n.red_op, payload, items[k].cell, n_groups, n_rows, scratch, L, out, ws_ + off_split,
+                                   split_bytes, dev_, stream_);
     if (off_out[k] != SIZE_MAX && n_groups * items[k].cell > 0)
       TFS_CUDA(cudaMemcpyAsync(fetches[items[k].fetch].data, out, size_t(n_groups) * items[k].cell * es,
                                cudaMemcpyDeviceToHost, stream_));

@@ -202,8 +202,14 @@ def _to_python(v):
 Column = Union[np.ndarray, list]
 
 
+def is_device_column(c) -> bool:
+    """A dense block that lives in GPU memory (a torch CUDA tensor): TensorFrame.to_device puts columns there and
+    map_blocks keeps its outputs there, so a chain of operators does not cross PCIe between steps."""
+    return type(c).__module__.split(".")[0] == "torch" and bool(getattr(c, "is_cuda", False))
+
+
 def _column_len(c: Column) -> int:
-    return int(c.shape[0]) if isinstance(c, np.ndarray) else len(c)
+    return int(c.shape[0]) if (isinstance(c, np.ndarray) or is_device_column(c)) else len(c)
 
 
 def _infer_sql_type(value):
@@ -446,12 +452,25 @@ class TensorFrame:
             parts.append(part)
         return TensorFrame(self.schema, parts)
 
+    def to_device(self, device: int = 0) -> "TensorFrame":
+        """Dense numeric columns move to GPU memory (torch owns the allocations); ragged and string columns stay.
+        Operators keep device-resident inputs and outputs where they are: 180 GB of HBM hold a lot of partitions."""
+        import torch
+        parts = [{n: (torch.from_numpy(np.ascontiguousarray(c)).to(f"cuda:{device}")
+                      if isinstance(c, np.ndarray) and scalar_type_from_numpy(c.dtype) is not None else c)
+                  for n, c in p.items()} for p in self.partitions]
+        return TensorFrame(self.schema, parts)
+
+    def to_host(self) -> "TensorFrame":
+        parts = [{n: (c.cpu().numpy() if is_device_column(c) else c) for n, c in p.items()} for p in self.partitions]
+        return TensorFrame(self.schema, parts)
+
     def collect(self) -> List[Row]:
         names = self.columns
         out = []
         for p in self.partitions:
             n = self._part_len(p)
-            cols = [p[name] for name in names]
+            cols = [p[name].cpu().numpy() if is_device_column(p[name]) else p[name] for name in names]
             for i in range(n):
                 out.append(Row.of(names, [_to_python(c[i]) for c in cols]))
         return out
@@ -540,6 +559,8 @@ def analyze_data(x) -> Optional[Shape]:
 def _partition_shape(col: Column) -> Optional[Shape]:
     """Block shape of one partition's column: merged cell shape with the row count in front."""
     n = _column_len(col)
+    if is_device_column(col):
+        return Shape(tuple(col.shape))
     if isinstance(col, np.ndarray):
         return Shape(col.shape) if scalar_type_from_numpy(col.dtype) is not None else None
     merged = analyze_data(col[0])

@@ -22,7 +22,7 @@ import numpy as np
 
 from . import _native, dsl
 from .frame import (ColumnInformation, GroupedData, Row, SparkTFColInfo, StructField, StructType, TensorFrame,
-                    analyze as _analyze, explain as _explain, _to_python)
+                    analyze as _analyze, explain as _explain, is_device_column, _to_python)
 from .shape import ScalarType, Shape, ShapeDescription, Unknown
 
 
@@ -180,6 +180,23 @@ def reduce_blocks_schema(schema: StructType, graph: _native.Graph, hints: ShapeD
     return ReduceBlockSchema(map_input, idx, output_schema, reduce_input)
 
 
+def _has_device_columns(df: TensorFrame) -> bool:
+    return any(is_device_column(c) for p in df.partitions for c in p.values())
+
+
+def _numel(arr) -> int:
+    return int(arr.numel()) if is_device_column(arr) else int(arr.size)
+
+
+def _as_feed(col):
+    """A device-resident block as the C ABI wants it (pointer + dtype + shape); host blocks pass through."""
+    if is_device_column(col):
+        import torch
+        torch.cuda.current_stream(col.device).synchronize()      # produced on torch's stream, read on the session's
+        return _native.DeviceArray.from_torch(col.contiguous())
+    return col
+
+
 class B200Ops:
     """OperationsInterface (Operations.scala:20-135) executed on a B200 through libtfsb200."""
 
@@ -215,7 +232,7 @@ class B200Ops:
         if cell.hasUnknown:
             raise AssertionError(f"Shape {cell} has unknown values.")
         col = part[name]
-        if not isinstance(col, np.ndarray):
+        if not isinstance(col, np.ndarray) and not is_device_column(col):
             raise Exception(f"Column '{name}' holds ragged or non-numeric cells and cannot be packed as a block")
         if tuple(col.shape[1:]) != cell.dims:
             raise Exception(f"Column '{name}' cells have shape {Shape(col.shape[1:])} but the metadata says {cell}")
@@ -272,12 +289,14 @@ class B200Ops:
                     if n == 0:          # empty partitions never reach the runtime (:380-390, :777-779)
                         continue
                     feeds = {name: self._dense_block(df, part, name, n) for name in input_names}
-                    outs = session.run(feeds, fetch_names)
+                    # blocks that live on the device stay there, and so do the columns computed from them
+                    on_device = any(is_device_column(v) for v in feeds.values())
+                    outs = session.run_torch(feeds, fetch_names, self.device) if on_device else session.run(feeds, fetch_names)
                     new_part: Dict[str, object] = {}
                     rows_seen = []
                     for f, arr in zip(tf_schema.fields, outs):
                         info = ColumnInformation.of(f).stf
-                        n_rows, cell = infer_physical_shape(int(arr.size), info.shape.tail, n if append_input else None)
+                        n_rows, cell = infer_physical_shape(_numel(arr), info.shape.tail, n if append_input else None)
                         rows_seen.append(n_rows)
                         if cell.numDims > 2:
                             raise ValueError(f"Operations for tensors of order {cell.numDims + 1} are not supported")
@@ -305,8 +324,8 @@ class B200Ops:
                     n = df._part_len(part)
                     if n == 0:
                         continue
-                    feeds = {name + "_input": self._dense_block(df, part, name, n) for name in out_names}
-                    partials.append(session.run(feeds, out_names))
+                    feeds = {name + "_input": _as_feed(self._dense_block(df, part, name, n)) for name in out_names}
+                    partials.append(session.run(feeds, out_names))      # the partial row is small: it comes to the host
                 if not partials:
                     raise ValueError("empty collection")  # RDD.reduce on an empty RDD (:524)
                 result = partials[0]
@@ -326,7 +345,8 @@ class B200Ops:
     # ---- aggregate (impl/DebugRowOps.scala:547-592, TensorFlowUDAF :601-695) ------------
     def aggregate(self, grouped: GroupedData, *fetches) -> TensorFrame:
         g, h = self._graph_args(fetches)
-        df = grouped.df
+        # (grouping builds key ids on the host: device-resident frames come back for this operator)
+        df = grouped.df.to_host() if _has_device_columns(grouped.df) else grouped.df
         with _native.Graph(g) as graph:
             schemas = reduce_blocks_schema(df.schema, graph, h)
             out_names = [f.name for f in schemas.output.fields]
@@ -384,6 +404,8 @@ class B200Ops:
         `feed_dict` (placeholder -> column; default: the column of the same name).  Rows whose cells differ
         in length (first cell dimension unknown) are allowed.  The device evaluates all rows of a partition
         that share a cell shape in one call (tfs_session_run_rows) instead of one Session.run per row."""
+        if _has_device_columns(df):          # row operators pack on the host
+            df = df.to_host()
         g, h = self._graph_args(fetches)
         feed_dict = dict(feed_dict or {})
         with _native.Graph(g) as graph:
@@ -469,6 +491,8 @@ class B200Ops:
         and produces X.  The reference folds the rows one by one through a session; here each round
         combines the first half of the remaining rows with the second half in one row-mode call, so n rows
         take about log2(n) device calls (the order of combination is unspecified in the reference too)."""
+        if _has_device_columns(df):          # row operators pack on the host
+            df = df.to_host()
         g, h = self._graph_args(fetches)
         with _native.Graph(g) as graph:
             summary = {s.name: s for s in analyze_graph(graph, h)}

@@ -1073,3 +1073,69 @@ def test_blocks_beyond_2_31_elements():
     expect = (n - 2 + 7 - 3) % (1 << 32)
     expect = expect - (1 << 32) if expect >= (1 << 31) else expect      # int32 sums wrap, as in TF
     assert int(tot) == expect and int(mn) == -3
+
+
+def test_device_resident_frame_keeps_columns_in_hbm():
+    """TensorFrame.to_device: blocks live in GPU memory, map_blocks reads and writes them there, reduce_blocks reads
+    them there; results are the host path's, bit for bit."""
+    torch = pytest.importorskip("torch")
+    from tensorframes_b200.frame import is_device_column
+    rng = np.random.default_rng(41)
+    x = rng.uniform(-1, 1, (100_003, 8))
+    key = rng.integers(0, 11, len(x))
+    host = tfs.analyze(TensorFrame.from_columns({"key": key, "x": x}, num_partitions=3))
+    dev = host.to_device(0)
+    assert all(is_device_column(p["x"]) for p in dev.partitions)
+
+    def pipeline(df):
+        with dsl.withGraph():
+            p = tfs.block(df, "x")
+            df2 = tfs.map_blocks([dsl.relu(p * 2.0 - 0.5).named("y"), dsl.reduce_sum(dsl.square(p), [1]).named("n2")], df)
+        with dsl.withGraph():
+            q = tfs.block(df2, "y")
+            df3 = tfs.map_blocks((q + q).named("z"), df2)
+        with dsl.withGraph():
+            zi = tfs.block(df3, "z", tf_name="z_input")
+            ni = tfs.block(df3, "n2", tf_name="n2_input")
+            red = tfs.reduce_blocks([dsl.reduce_sum(zi, [0]).named("z"), dsl.reduce_max(ni, [0]).named("n2")], df3)
+        with dsl.withGraph():
+            zi = tfs.block(df3, "z", tf_name="z_input")
+            agg = tfs.aggregate(dsl.reduce_sum(zi, [0]).named("z"), df3.groupBy("key"))
+        return df3, red, agg
+
+    h3, h_red, h_agg = pipeline(host)
+    d3, d_red, d_agg = pipeline(dev)
+    assert all(is_device_column(p[c]) for p in d3.partitions for c in ("x", "y", "n2", "z"))      # nothing came back
+    back = d3.to_host()
+    for ph, pd in zip(h3.partitions, back.partitions):
+        for c in ("z", "y", "n2", "x", "key"):
+            assert np.asarray(pd[c]).tobytes() == np.asarray(ph[c]).tobytes(), c
+    for a, b in zip(d_red, h_red):
+        assert np.asarray(a).tobytes() == np.asarray(b).tobytes()
+    rows_d = sorted(d_agg.collect(), key=lambda r: r.key)
+    rows_h = sorted(h_agg.collect(), key=lambda r: r.key)
+    assert [r.key for r in rows_d] == [r.key for r in rows_h]
+    for a, b in zip(rows_d, rows_h):
+        assert np.asarray(a.z).tobytes() == np.asarray(b.z).tobytes()
+    for a, b in zip(d3.collect()[:3], h3.collect()[:3]):
+        assert np.asarray(a.z).tobytes() == np.asarray(b.z).tobytes() and a.key == b.key
+
+
+@pytest.mark.parametrize("n_keys,cell", [(1, 16), (10, 16), (300, 5), (4000, 64)])
+def test_aggregate_few_large_groups_split_across_warps(n_keys, cell):
+    """Few, large groups: every segment is cut into pieces so the whole chip works on it, and the pieces are folded
+    in order.  Small-integer payloads make the sums exact whatever the association; min is association-free."""
+    rng = np.random.default_rng(n_keys)
+    n = 3_000_017
+    keys = rng.integers(0, n_keys, n)
+    v = rng.integers(-8, 9, (n, cell)).astype(np.float32)
+    for op in ("sum", "min"):
+        g = aggregate_graph(tfs.FloatType, (cell,), op)
+        with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+            k1, (o1,) = s.aggregate(keys, {"v_input": v}, ["v"], max_groups=n_keys)
+            k2, (o2,) = s.aggregate(keys, {"v_input": v}, ["v"], max_groups=n_keys)
+        assert k1.tolist() == sorted(set(keys.tolist())) and o1.tobytes() == o2.tobytes()
+        order = np.argsort(keys, kind="stable")
+        bounds = np.searchsorted(keys[order], k1)
+        ref = (np.add if op == "sum" else np.minimum).reduceat(v[order].astype(np.float64), bounds, axis=0)
+        assert np.array_equal(o1.astype(np.float64), ref)
