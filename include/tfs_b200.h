@@ -42,6 +42,12 @@
  *    session must not run two calls at the same time (the reference uses one
  *    Session per task thread, impl/DebugRowOps.scala:783).
  *  - there is no CPU execution path: every run needs a CUDA device.
+ *  - several GPUs: one session per device (any mix of processes and threads).  The library moves no data between
+ *    devices; the exchange steps of the reference stay where they are -- RDD.reduce / the UDAF's shuffle on the JVM
+ *    side (impl/DebugRowOps.scala:524-525, 573-576), torch.distributed in this repository's harness -- and their
+ *    merge halves are the same two entry points on the gathered data: tfs_session_run on the stacked
+ *    [n_partitions, cell...] partial rows (reducePairBlock, :741-750) and tfs_session_aggregate on the
+ *    concatenated (key, partial row) pairs (TensorFlowUDAF.merge, :659-672).
  */
 #ifndef TFS_B200_H
 #define TFS_B200_H
