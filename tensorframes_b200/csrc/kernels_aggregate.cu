@@ -107,8 +107,11 @@ agg_insert_kernel(const long long* __restrict__ keys, const int64_t n, unsigned 
         c = *reinterpret_cast<volatile unsigned long long*>(slot_key + h[u]);
       }
     }
-    if (claimed != 0u && atomicAdd(header, claimed) + claimed > max_groups) header[1] = 1u;
     __syncwarp();   // see above: the stores below must leave as whole-warp, whole-sector writes
+    // one counter update per warp: a million first occurrences would otherwise queue on this one address
+    const unsigned int warp_claimed = __reduce_add_sync(0xffffffffu, claimed);
+    if ((threadIdx.x & 31) == 0 && warp_claimed != 0u && atomicAdd(header, warp_claimed) + warp_claimed > max_groups)
+      header[1] = 1u;
 #pragma unroll
     for (int u = 0; u < kInsU; ++u) {
       const int64_t i = base + int64_t(u) * kThreads;
