@@ -99,4 +99,9 @@ int launch_agg_reduce(int dtype, int red_op, const void* payload, int64_t cell, 
                       const AggLayout& L, void* out, void* split_scratch, size_t split_bytes, const DeviceInfo& dev,
                       cudaStream_t stream);
 
+// K0 (host_staging.cpp): copies of at least 64 MiB between PAGEABLE host memory and the device go through a pinned
+// ring filled / drained by a few host threads; `stream` is ordered after the copy.
+bool staged_copy_pays(size_t bytes);
+void staged_copy(int device, void* dst, const void* src, size_t bytes, bool to_device, cudaStream_t stream);
+
 }  // namespace tfs

@@ -51,6 +51,8 @@ class Session {
   void exec_step(const Plan& plan, size_t step_index, std::vector<void*>& dev_ptr, cudaStream_t stream);
   bool run_pipelined(const std::vector<TensorArg>& feeds, const std::vector<TensorArg>& fetches, const Plan& plan);
   void* const_device(int node);
+  void copy_in(void* dst_dev, const void* src_host, size_t bytes);     // host -> device on stream_
+  void copy_out(void* dst_host, const void* src_dev, size_t bytes);    // device -> host on stream_
   void reserve_workspace(size_t bytes);
   void check_device_error();
 

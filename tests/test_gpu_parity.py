@@ -1139,3 +1139,31 @@ def test_aggregate_few_large_groups_split_across_warps(n_keys, cell):
         bounds = np.searchsorted(keys[order], k1)
         ref = (np.add if op == "sum" else np.minimum).reduceat(v[order].astype(np.float64), bounds, axis=0)
         assert np.array_equal(o1.astype(np.float64), ref)
+
+
+def test_large_pageable_blocks_take_the_staged_copies():
+    """numpy arrays (pageable memory) of 64 MiB and more go through the pinned staging ring in both directions;
+    ragged sizes, two columns in, two out, plus the keyed path."""
+    rng = np.random.default_rng(77)
+    n = 12_000_017                                      # 96 MB per f64 column, not a multiple of the 8 MiB chunk
+    x = rng.uniform(-1, 1, n)
+    y = rng.uniform(1, 2, n)
+    with dsl.withGraph():
+        px = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x")
+        py = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("y")
+        g = dsl.build_graph(((px + py) * (px - py)).named("a"), (px * 2.0).named("b"), dsl.reduce_sum(py, [0]).named("s"))
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        a, b, tot = s.run({"x": x, "y": y}, ["a", "b", "s"])
+        a2, b2, _ = s.run({"x": x, "y": y}, ["a", "b", "s"])                # the ring is reused
+    assert a.tobytes() == ((x + y) * (x - y)).tobytes() and b.tobytes() == (x * 2.0).tobytes()
+    assert a2.tobytes() == a.tobytes() and b2.tobytes() == b.tobytes()
+    assert abs(tot - y.sum()) <= 1e-12 * np.abs(y).sum()
+    keys = rng.integers(0, 1000, n)
+    v = rng.integers(-4, 5, (n, 2)).astype(np.float32)              # 96 MB of keys, 96 MB of payload
+    gagg = aggregate_graph(tfs.FloatType, (2,), "sum")
+    with _native.Graph(gagg) as gr, _native.Session(gr, 0) as s:
+        k, (o,) = s.aggregate(keys, {"v_input": v}, ["v"], max_groups=1000)
+    assert k.tolist() == list(range(1000))
+    ref = np.zeros((1000, 2))
+    np.add.at(ref, keys, v.astype(np.float64))
+    assert np.array_equal(o.astype(np.float64), ref)
