@@ -295,3 +295,19 @@ def test_float64_matmul_with_transposes():
         ab, ba = sess.run({"a": a, "b": b}, ["ab", "ba"])
     scale = np.abs(a) @ np.abs(b).T
     assert np.all(np.abs(ab - a @ b.T) <= 1e-12 * scale) and np.all(np.abs(ba - b @ a.T) <= 1e-12 * scale.T)
+
+
+@pytest.mark.gpu
+def test_kmeans_graphs_on_an_empty_block():
+    """Zero rows: every step degenerates to an empty launch, the segment sums are zero rows of the right shape."""
+    _, centers = data(n=16)
+    k, m = centers.shape
+    x = np.zeros((0, m))
+    g, fetches = step1_graph(centers, m)
+    g2, fetches2 = step2_graph(centers, m)
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        idx, cnt, md = s.run({"features": x}, [f.name for f in fetches])
+    assert idx.shape == (0,) and idx.dtype == np.int64 and cnt.shape == (0,) and md.shape == (0,)
+    with _native.Graph(g2) as gr, _native.Session(gr, 0) as s:
+        pts, cts, dist = s.run({"features": x}, [f.name for f in fetches2])
+    assert pts.shape == (1, k, m) and not pts.any() and cts.shape == (1, k) and not cts.any() and dist.tolist() == [0.0]
