@@ -72,6 +72,15 @@ def ncu_traffic(workload, rows=None):
         return None
 
 
+def ncu_extra(workload, key):
+    """Another figure of the committed ncu capture of the workload's dominant kernel (profiles/traffic.json), or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(workload, {}).get(key)
+    except Exception:
+        return None
+
+
 class ClockSampler:
     """SM clock + throttle reasons during the timed region (NVML)."""
 
@@ -662,7 +671,8 @@ def run_c5(args, torch, dist, _native, world, rank, local, device, rows):
                          "traffic": ncu_traffic("c5", rows), "peak_source": "measured bf16 sustained; tf32 runs at half of it and "
                          "each fp32 product costs 3 tf32 MMAs, so the attainable ceiling is ~peak/6",
                          "kernel": "matmul_tc_pair_kernel", "mma_tflops_issued": 3 * tflops,
-                         "hbm_gbs": rows * 2048.0 / step_s / 1e9, "hbm_frac": rows * 2048.0 / step_s / 1e9 / hbm},
+                         "hbm_gbs": rows * 2048.0 / step_s / 1e9, "hbm_frac": rows * 2048.0 / step_s / 1e9 / hbm,
+                         "ncu_tensor_pipe_active_pct_of_elapsed": ncu_extra("c5", "tensor_pipe_active_pct_of_elapsed")},
             "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks.summary(), "cpu_baseline": cpu}))
     if world > 1:
         dist.destroy_process_group()
