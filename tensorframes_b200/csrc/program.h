@@ -108,7 +108,8 @@ struct ChainProgram {
   int32_t n_slots;
   uint8_t dt;       // dtype index the chain computes in
   uint8_t out_dt;   // dtype index of the output (differs when the chain ends in a Cast)
-  uint8_t pad[2];
+  uint8_t in_dt;    // dtype index of the input column (differs when the chain starts with a Cast; then out_dt == dt)
+  uint8_t pad[1];
   ChainSlot slots[kChainSlots];
 };
 

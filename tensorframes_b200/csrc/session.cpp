@@ -810,9 +810,20 @@ bool make_chain(const EltProgram& prog, ChainProgram& ch) {
   ch.in = in.ptr;
   ch.out = out.ptr;
   ch.err = prog.err;
-  ch.dt = uint8_t(in.dt);
+  ch.in_dt = uint8_t(in.dt);
+  int dt = in.dt;
+  int first_pc = 1;
+  if (prog.n_instr > 2) {           // a leading Cast: the chain computes in the cast's target dtype
+    const int c1 = prog.ins[1].code;
+    // (to float or double only: int targets and saved-tile programs stay with the interpreter, which keeps the build small)
+    if (c1 >= C_CAST && c1 < C_CAST + 16 && (c1 - C_CAST) / 4 == in.dt && (c1 - C_CAST) % 4 != in.dt &&
+        ((c1 - C_CAST) % 4 == DI_F32 || (c1 - C_CAST) % 4 == DI_F64)) {
+      dt = (c1 - C_CAST) % 4;
+      first_pc = 2;
+    }
+  }
+  ch.dt = uint8_t(dt);
   ch.out_dt = ch.dt;
-  const int dt = in.dt;
   const int64_t lanes = 16 / ((dt & 1) ? 8 : 4);
   const int64_t span = int64_t(kChainThreads) * kChainVecsPerThread * lanes;
   static const uint8_t kFwd[B_COUNT] = {CH_ADD, CH_SUB, CH_MUL, CH_DIV, CH_MIN, CH_MAX};
@@ -862,10 +873,10 @@ bool make_chain(const EltProgram& prog, ChainProgram& ch) {
 
   Operand pending;
   bool have_pending = false, cast_seen = false;
-  for (int pc = 1; pc < prog.n_instr - 1; ++pc) {
+  for (int pc = first_pc; pc < prog.n_instr - 1; ++pc) {
     const Instr& ins = prog.ins[pc];
     const int c = ins.code;
-    if (cast_seen) return false;                       // a cast may only end the chain
+    if (cast_seen) return false;                       // a cast may only start or end the chain
     Operand o;
     switch (c) {
       case C_FETCH_BUF:
@@ -949,6 +960,11 @@ bool make_chain(const EltProgram& prog, ChainProgram& ch) {
     }
   }
   if (have_pending) return false;
+  if (ch.in_dt != ch.dt) {
+    if (ch.out_dt != ch.dt) return false;     // a cast at both ends: the interpreter takes it
+    for (int k = 0; k < ch.n_slots; ++k)
+      if (ch.slots[k].save || ch.slots[k].kind == CK_TMP) return false;
+  }
   return out.dt == ch.out_dt;
 }
 

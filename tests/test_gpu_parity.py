@@ -1167,3 +1167,27 @@ def test_large_pageable_blocks_take_the_staged_copies():
     ref = np.zeros((1000, 2))
     np.add.at(ref, keys, v.astype(np.float64))
     assert np.array_equal(o.astype(np.float64), ref)
+
+
+@pytest.mark.parametrize("src,dst", [("i4", "f8"), ("i8", "f8"), ("f4", "f8"), ("f8", "f4"), ("i4", "f4"), ("i8", "f4")])
+def test_chains_that_start_with_a_cast_bit_exact(src, dst):
+    """tf.to_double(x) followed by arithmetic (the geometric-mean snippet's shape): the straight-line kernel reads the
+    column in its own dtype and computes in the cast's target."""
+    names = {"f4": tfs.FloatType, "f8": tfs.DoubleType, "i4": tfs.IntegerType, "i8": tfs.LongType}
+    s_np, d_np = np.dtype("<" + src), np.dtype("<" + dst)
+    rng = np.random.default_rng(5)
+    for n in (3, 4097, 100_003):
+        x = (rng.integers(1, 1000, n) if s_np.kind == "i" else rng.uniform(1, 2, n)).astype(s_np)
+        y = rng.uniform(1, 2, n).astype(d_np)
+        with dsl.withGraph():
+            px = dsl.placeholder(names[src], dsl.Unknown).named("x")
+            py = dsl.placeholder(names[dst], dsl.Unknown).named("y")
+            c = dsl.cast(px, names[dst])
+            g = dsl.build_graph(dsl.reciprocal(c * 0.5 + 1.0).named("a"), (dsl.cast(px, names[dst]) - py).named("b"))
+        with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+            a, b = s.run({"x": x, "y": y}, ["a", "b"])
+        xc = x.astype(d_np)
+        one = d_np.type(1)
+        want_a = (one / ((xc * d_np.type(0.5)).astype(d_np) + one).astype(d_np)).astype(d_np)
+        assert a.dtype == d_np and a.tobytes() == want_a.tobytes(), n
+        assert b.tobytes() == (xc - y).astype(d_np).tobytes(), n
