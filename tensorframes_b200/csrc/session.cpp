@@ -4,6 +4,7 @@
 #include <mutex>
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <map>
 #include <set>
@@ -994,7 +995,12 @@ void Session::exec_step(const Plan& plan, size_t step_index, std::vector<void*>&
       GroupCompiler gc(g_, plan.shape, dev_ptr, plan.materialize, s);
       gc.build(err_flag_);
       ChainProgram chain;
-      if (make_chain(gc.prog, chain)) launches_ += launch_chain(chain, s.shape.numel(), dev_, stream);
+      const bool straight = make_chain(gc.prog, chain);
+      static const bool trace = [] { const char* e = std::getenv("TFS_TRACE"); return e && *e && *e != '0'; }();
+      if (trace)
+        fprintf(stderr, "tfs: element-wise group of %zu nodes, %d instructions -> %s\n", s.nodes.size(), gc.prog.n_instr,
+                straight ? "straight-line kernel" : "interpreter");
+      if (straight) launches_ += launch_chain(chain, s.shape.numel(), dev_, stream);
       else launches_ += launch_eltwise(gc.prog, s.shape.numel(), gc.wide, dev_, stream);
       break;
     }
