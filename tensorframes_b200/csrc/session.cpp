@@ -1101,7 +1101,7 @@ void Session::exec_step(const Plan& plan, size_t step_index, std::vector<void*>&
       TFS_CHECK(header[1] == 0 && int64_t(header[2]) <= max_groups, TFS_ERR_RUNTIME,
                 "UnsortedSegmentSum: segment ids out of range [0, " + std::to_string(segments) + ")");
       const int64_t n_groups = header[2];
-      launches_ += launch_agg_segments(keys, n_rows, n_groups, scratch, L, d_out_keys, dev_, stream);
+      launches_ += launch_agg_segments(keys, n_rows, n_groups, scratch, L, d_out_keys, true, true, dev_, stream);
       launches_ += launch_agg_reduce(n.dtype, R_SUM, dev_ptr[size_t(n.in[0])], cell, n_groups, n_rows, scratch, L, scratch + off_sums,
                                      scratch + off_split, split_bytes, dev_, stream);
       launches_ += launch_segment_scatter(n.dtype, scratch + off_sums, d_out_keys, n_groups, cell, segments, dev_ptr[size_t(idx)],
@@ -1480,6 +1480,21 @@ void Session::aggregate(int64_t n_rows, const int64_t* keys, const std::vector<T
   for (const Item& it : items) widest = std::max(widest, it.cell);
   const size_t split_bytes = agg_split_scratch_bytes(widest, dev_);
   const size_t off_split = off; off += up(split_bytes);
+  // scalar payloads (at most two of them) ride through their own sort instead of being gathered
+  std::vector<char> carried(items.size(), 0);
+  size_t carried_bytes = 0;
+  {
+    size_t n_scalar = 0;
+    for (const Item& it : items) n_scalar += it.cell == 1 ? 1 : 0;
+    static const bool off_switch = [] { const char* e = std::getenv("TFS_AGG_CARRY"); return e && std::string(e) == "off"; }();
+    if (n_scalar > 0 && n_scalar <= 2 && n_rows >= (int64_t(1) << 16) && !off_switch)
+      for (size_t k = 0; k < items.size(); ++k)
+        if (items[k].cell == 1) {
+          carried[k] = 1;
+          carried_bytes = std::max(carried_bytes, agg_carried_bytes(n_rows, dtype_size(g_.nodes[size_t(items[k].node)].dtype), L));
+        }
+  }
+  const size_t off_carried = off; off += up(carried_bytes);
   const bool keys_dev = is_device_pointer(keys);
   size_t off_keys = 0;
   if (!keys_dev) { off_keys = off; off += up(size_t(n_rows) * 8); }
@@ -1506,8 +1521,15 @@ void Session::aggregate(int64_t n_rows, const int64_t* keys, const std::vector<T
   TFS_CHECK(header[1] == 0 && int64_t(header[2]) <= max_groups, TFS_ERR_INVALID,
             "aggregate: the block holds more than max_groups = " + std::to_string(max_groups) + " distinct keys");
   const int64_t n_groups = header[2];
-  launches_ += launch_agg_segments(d_keys, n_rows, n_groups, scratch, L, d_out_keys, dev_, stream_);
-  for (size_t k = 0; k < items.size(); ++k) {
+  bool any_gather = false;
+  for (size_t k = 0; k < items.size(); ++k) any_gather = any_gather || !carried[k];
+  launches_ += launch_agg_segments(d_keys, n_rows, n_groups, scratch, L, d_out_keys, true, false, dev_, stream_);   // groups by key
+  // carried fetches first: they read the unsorted slot column, which the row sort below recycles
+  for (int pass = 0; pass < 2; ++pass) {
+   if (pass == 1 && any_gather)
+     launches_ += launch_agg_segments(d_keys, n_rows, n_groups, scratch, L, d_out_keys, false, true, dev_, stream_);  // rows by slot
+   for (size_t k = 0; k < items.size(); ++k) {
+    if ((pass == 0) != (carried[k] != 0)) continue;
     const Node& n = g_.nodes[size_t(items[k].node)];
     const size_t es = size_t(dtype_size(n.dtype));
     const void* payload = feeds[size_t(items[k].feed)].data;
@@ -1516,11 +1538,16 @@ void Session::aggregate(int64_t n_rows, const int64_t* keys, const std::vector<T
       payload = ws_ + off_feed[k];
     }
     void* out = off_out[k] != SIZE_MAX ? static_cast<void*>(ws_ + off_out[k]) : fetches[items[k].fetch].data;
-    launches_ += launch_agg_reduce(n.dtype, n.red_op, payload, items[k].cell, n_groups, n_rows, scratch, L, out, ws_ + off_split,
-                                   split_bytes, dev_, stream_);
+    if (carried[k])
+      launches_ += launch_agg_reduce_carried(n.dtype, n.red_op, payload, n_groups, n_rows, scratch, L, out, ws_ + off_carried,
+                                             carried_bytes, ws_ + off_split, split_bytes, dev_, stream_);
+    else
+      launches_ += launch_agg_reduce(n.dtype, n.red_op, payload, items[k].cell, n_groups, n_rows, scratch, L, out, ws_ + off_split,
+                                     split_bytes, dev_, stream_);
     if (off_out[k] != SIZE_MAX && n_groups * items[k].cell > 0)
       TFS_CUDA(cudaMemcpyAsync(fetches[items[k].fetch].data, out, size_t(n_groups) * items[k].cell * es,
                                cudaMemcpyDeviceToHost, stream_));
+   }
   }
   if (n_groups > 0) {
     const bool ok_dev = is_device_pointer(out_keys);

@@ -1191,3 +1191,37 @@ def test_chains_that_start_with_a_cast_bit_exact(src, dst):
         want_a = (one / ((xc * d_np.type(0.5)).astype(d_np) + one).astype(d_np)).astype(d_np)
         assert a.dtype == d_np and a.tobytes() == want_a.tobytes(), n
         assert b.tobytes() == (xc - y).astype(d_np).tobytes(), n
+
+
+@pytest.mark.parametrize("dt", list(T))
+@pytest.mark.parametrize("op", list(RED))
+def test_aggregate_scalar_payloads_ride_through_the_sort(dt, op):
+    """groupBy(key).sum(x) with one value per row: blocks of 2^16 rows and more sort the values along with the slots
+    instead of gathering them; a second, wide fetch in the same call still takes the gather path."""
+    st = T[dt]
+    rng = np.random.default_rng(3)
+    n, n_keys = 300_007, 5000
+    table = rng.integers(-2**62, 2**62, n_keys, dtype=np.int64)
+    keys = table[rng.integers(0, n_keys, n)]
+    if st.np_dtype.kind == "i":
+        x = rng.integers(-1000, 1000, n).astype(st.np_dtype)
+        w = rng.integers(-1000, 1000, (n, 3)).astype(st.np_dtype)
+    else:
+        x = rng.uniform(-1, 1, n).astype(st.np_dtype)
+        w = rng.uniform(-1, 1, (n, 3)).astype(st.np_dtype)
+    with dsl.withGraph():
+        px = dsl.placeholder(st, dsl.Unknown).named("x_input")
+        pw = dsl.placeholder(st, dsl.Unknown, 3).named("w_input")
+        g = dsl.build_graph(RED[op](px, [0]).named("x"), RED[op](pw, [0]).named("w"))
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        k1, (x1, w1) = s.aggregate(keys, {"x_input": x, "w_input": w}, ["x", "w"], max_groups=n_keys)
+        k2, (x2, w2) = s.aggregate(keys, {"x_input": x, "w_input": w}, ["x", "w"], max_groups=n_keys)
+    assert x1.tobytes() == x2.tobytes() and w1.tobytes() == w2.tobytes() and k1.tolist() == sorted(set(keys.tolist()))
+    for got, data in ((x1, x), (w1, w)):
+        want_keys, want, absum = numpy_group_reduce(keys, data, op)
+        assert k1.tolist() == want_keys.tolist()
+        if st.np_dtype.kind == "i" or op != "sum":
+            assert np.array_equal(got, want)
+        else:
+            tol = 1e-12 if st.np_dtype.itemsize == 8 else 1e-5
+            assert np.all(np.abs(got.astype(np.float64) - want.astype(np.float64)) <= tol * absum)
