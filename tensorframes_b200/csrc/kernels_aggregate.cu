@@ -280,7 +280,7 @@ __device__ __forceinline__ void load_v(const T* p, T (&x)[V]) {
 // that the whole chip has work, the pieces go to a partial buffer and fold_parts_kernel combines them in order.
 // The warp is split into R row-lanes x C col-lanes (R * C = 32, C a power of two >= ceil(cell / V) when the
 // cell fits, else C = 32 with a loop over column chunks).  kU rows are in flight per row-lane.
-template <class T, int OP, int V>
+template <class T, int OP, int V, bool PERM>
 __global__ void __launch_bounds__(kThreads)
 agg_gather_reduce_kernel(const T* __restrict__ payload, const int cell, const unsigned int* __restrict__ perm,
                          const unsigned int* __restrict__ offsets, const unsigned int* __restrict__ counts,
@@ -310,7 +310,7 @@ agg_gather_reduce_kernel(const T* __restrict__ payload, const int cell, const un
           unsigned int idx[kU];
 #pragma unroll
           for (int u = 0; u < kU; ++u)
-            idx[u] = perm ? __ldg(perm + r + (unsigned long long)u * R) : (unsigned int)(r + (unsigned long long)u * R);
+            idx[u] = PERM ? __ldg(perm + r + (unsigned long long)u * R) : (unsigned int)(r + (unsigned long long)u * R);
           T x[kU][V];
 #pragma unroll
           for (int u = 0; u < kU; ++u) load_v<T, V>(payload + (int64_t)idx[u] * cell + c0, x[u]);
@@ -321,7 +321,7 @@ agg_gather_reduce_kernel(const T* __restrict__ payload, const int cell, const un
         }
         for (; r < hi; r += R) {
           T x[V];
-          load_v<T, V>(payload + (int64_t)(perm ? __ldg(perm + r) : (unsigned int)r) * cell + c0, x);
+          load_v<T, V>(payload + (int64_t)(PERM ? __ldg(perm + r) : (unsigned int)r) * cell + c0, x);
 #pragma unroll
           for (int e = 0; e < V; ++e) acc[e] = red_op<T, OP>(acc[e], x[e]);
         }
@@ -383,13 +383,15 @@ int launch_gather_t(const T* payload, int64_t cell, const unsigned int* perm, co
   int64_t grid = std::min<int64_t>((items + warps_per_cta - 1) / warps_per_cta, int64_t(dev.sm_count) * 16);
   if (grid < 1) grid = 1;
   const int icell = int(cell);
-  if (V == 4) {
+  if (perm == nullptr) {       // values already in segment order (carried through the sort): scalar cells only
+    agg_gather_reduce_kernel<T, OP, 1, false><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, counts, group_slot, n_groups, C, parts, dst);
+  } else if (V == 4) {
     if constexpr (VMAX == 4)
-      agg_gather_reduce_kernel<T, OP, 4><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, counts, group_slot, n_groups, C, parts, dst);
+      agg_gather_reduce_kernel<T, OP, 4, true><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, counts, group_slot, n_groups, C, parts, dst);
   } else if (V == 2) {
-    agg_gather_reduce_kernel<T, OP, 2><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, counts, group_slot, n_groups, C, parts, dst);
+    agg_gather_reduce_kernel<T, OP, 2, true><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, counts, group_slot, n_groups, C, parts, dst);
   } else {
-    agg_gather_reduce_kernel<T, OP, 1><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, counts, group_slot, n_groups, C, parts, dst);
+    agg_gather_reduce_kernel<T, OP, 1, true><<<(unsigned)grid, kThreads, 0, stream>>>(payload, icell, perm, offsets, counts, group_slot, n_groups, C, parts, dst);
   }
   TFS_CUDA(cudaGetLastError());
   if (parts == 1) return 1;
