@@ -13,11 +13,13 @@ cell-sized partial rows and the merge run).
   value      rows/s, whole job, inputs resident in HBM, timed with CUDA events on the launch stream
   e2e        the same metric through the C ABI with HOST (pinned) column buffers: H2D of the block
              and D2H of the result row are inside the timed region
-  roofline   the dominant kernel (reduce_axis0_flat_kernel) against the measured HBM peak
+  roofline   the dominant kernel (reduce_axis0_tma_kernel) against the measured HBM peak
   cpu_baseline / --impl reference   oracle/cpu_ref.c, the restatement of the reference's
              per-block algorithm, on the host cores (the real Spark + TF-CPU stack is not installable here)
 
---workload c3 measures map_blocks on the fused chain of BASELINE config 3 instead.
+--workload c3 | c4 | c5 measure the other BASELINE configs the same way: map_blocks on the fused chain (chain_kernel),
+the keyed aggregate (insert / sort / gather passes) and the tcgen05 MatMul (matmul_tc_pair_kernel; roofline.bound =
+"tensor").  With N > 1 the reduce exchange of a block runs on a second stream and overlaps the next block's kernels.
 """
 import argparse
 import json
