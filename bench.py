@@ -225,16 +225,17 @@ def run_ours(args):
     outs = {k: DA(v) for k, v in outs_t.items()}
     names = list(outs_t)
     # N > 1: the exchange of a block (all_gather of the partial rows + merge run) goes on a second stream with its own
-    # session, so it overlaps the next block's reduction kernels; the partial rows are double-buffered for that
+    # session, so it overlaps the next block's reduction kernels; the partial rows are kept in a small ring of buffers for that
     overlap = wl == "c2" and world > 1
     if overlap:
         side = torch.cuda.Stream(device=device)
         merge_sess = _native.Session(graph, local)
         merge_sess.set_stream(side.cuda_stream)
-        part_t = [outs_t, {k: torch.empty_like(v) for k, v in outs_t.items()}]
+        depth = max(2, env_int("TFS_BENCH_EXCHANGE_DEPTH", 4))      # partial-row buffers in flight
+        part_t = [outs_t] + [{k: torch.empty_like(v) for k, v in outs_t.items()} for _ in range(depth - 1)]
         part = [{k: DA(v) for k, v in p.items()} for p in part_t]
-        reduced_ev = [torch.cuda.Event(), torch.cuda.Event()]
-        exchanged_ev = [torch.cuda.Event(), torch.cuda.Event()]
+        reduced_ev = [torch.cuda.Event() for _ in range(depth)]
+        exchanged_ev = [torch.cuda.Event() for _ in range(depth)]
         step_no = [0]
 
     def merge(feeds_stacked):
@@ -248,9 +249,9 @@ def run_ours(args):
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(stream)
         if overlap:
-            b = step_no[0] & 1
+            b = step_no[0] % depth
             step_no[0] += 1
-            stream.wait_event(exchanged_ev[b])          # the exchange that last read this buffer pair (two blocks ago)
+            stream.wait_event(exchanged_ev[b])          # the exchange that last read this buffer set (`depth` blocks ago)
             sess.run_into(feeds, part[b])
         else:
             sess.run_into(feeds, outs)
