@@ -95,8 +95,8 @@ int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, c
 // pass 4: out[g, :] = reduce over the rows of group g of payload[row, :].
 // Scalar payloads: the values ride through their own stable slot sort and are reduced sequentially (no random gather).
 // Call after launch_agg_segments(..., sort_rows = false) or before a launch_agg_segments that sorts rows.
-size_t agg_carried_bytes(int64_t n_rows, int elem_size, const AggLayout& L);
-int launch_agg_reduce_carried(int dtype, int red_op, const void* payload, int64_t n_groups, int64_t n_rows, char* scratch,
+size_t agg_carried_bytes(int64_t n_rows, int row_bytes, const AggLayout& L);   // row_bytes: 4 or 8
+int launch_agg_reduce_carried(int dtype, int red_op, const void* payload, int64_t cell, int64_t n_groups, int64_t n_rows, char* scratch,
                               const AggLayout& L, void* out, char* carried, size_t carried_bytes, void* split_scratch,
                               size_t split_bytes, const DeviceInfo& dev, cudaStream_t stream);
 // split_scratch (agg_split_scratch_bytes, may be null): partial rows when few large groups are cut into pieces.

@@ -365,6 +365,7 @@ int launch_gather_t(const T* payload, int64_t cell, const unsigned int* perm, co
   const bool aligned16 = (reinterpret_cast<uintptr_t>(payload) & 15) == 0;
   if (aligned16 && cell % VMAX == 0 && cell >= 8 * VMAX) V = VMAX;
   else if (aligned16 && VMAX == 4 && cell % 2 == 0 && cell >= 64) V = 2;
+  if (perm == nullptr) V = 1;          // carried values: the scalar-load instantiation serves the (tiny) cell
   int need = int((cell + V - 1) / V);
   int C = 1;
   while (C < need && C < 32) C <<= 1;
@@ -555,10 +556,11 @@ size_t agg_carried_bytes(int64_t n_rows, int elem_size, const AggLayout& L) {
   return ((size_t(n_rows) * size_t(elem_size) + 255) / 256 * 256) + temp;
 }
 
-int launch_agg_reduce_carried(int dtype, int red_op, const void* payload, int64_t n_groups, int64_t n_rows, char* scratch,
+int launch_agg_reduce_carried(int dtype, int red_op, const void* payload, int64_t cell, int64_t n_groups, int64_t n_rows, char* scratch,
                               const AggLayout& L, void* out, char* carried, size_t carried_bytes, void* split_scratch,
                               size_t split_bytes, const DeviceInfo& dev, cudaStream_t stream) {
-  const int es = dtype_size(dtype);
+  const int es = dtype_size(dtype) * int(cell);      // bytes per row: 4 or 8
+  TFS_CHECK(es == 4 || es == 8, TFS_ERR_INVALID, "internal: carried rows must be 4 or 8 bytes");
   const size_t values_bytes = (size_t(n_rows) * size_t(es) + 255) / 256 * 256;
   TFS_CHECK(carried_bytes >= values_bytes, TFS_ERR_INVALID, "internal: carried-sort scratch too small");
   size_t temp = carried_bytes - values_bytes;
@@ -577,10 +579,10 @@ int launch_agg_reduce_carried(int dtype, int red_op, const void* payload, int64_
   if (split_bytes == 0) split_scratch = nullptr;
   const unsigned int* no_perm = nullptr;      // the values are already in segment order
   switch (dtype) {
-    case TFS_FLOAT: return 1 + launch_gather_op<float>(red_op, carried, 1, no_perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
-    case TFS_DOUBLE: return 1 + launch_gather_op<double>(red_op, carried, 1, no_perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
-    case TFS_INT32: return 1 + launch_gather_op<int>(red_op, carried, 1, no_perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
-    case TFS_INT64: return 1 + launch_gather_op<long long>(red_op, carried, 1, no_perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
+    case TFS_FLOAT: return 1 + launch_gather_op<float>(red_op, carried, cell, no_perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
+    case TFS_DOUBLE: return 1 + launch_gather_op<double>(red_op, carried, cell, no_perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
+    case TFS_INT32: return 1 + launch_gather_op<int>(red_op, carried, cell, no_perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
+    case TFS_INT64: return 1 + launch_gather_op<long long>(red_op, carried, cell, no_perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
   }
   fail(TFS_ERR_UNSUPPORTED, "aggregate: unsupported dtype");
 }

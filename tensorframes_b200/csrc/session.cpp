@@ -1485,13 +1485,14 @@ void Session::aggregate(int64_t n_rows, const int64_t* keys, const std::vector<T
   size_t carried_bytes = 0;
   {
     size_t n_scalar = 0;
-    for (const Item& it : items) n_scalar += it.cell == 1 ? 1 : 0;
+    auto row_bytes = [&](const Item& it) { return it.cell * int64_t(dtype_size(g_.nodes[size_t(it.node)].dtype)); };
+    for (const Item& it : items) n_scalar += row_bytes(it) <= 8 ? 1 : 0;
     static const bool off_switch = [] { const char* e = std::getenv("TFS_AGG_CARRY"); return e && std::string(e) == "off"; }();
     if (n_scalar > 0 && n_scalar <= 2 && n_rows >= (int64_t(1) << 16) && !off_switch)
       for (size_t k = 0; k < items.size(); ++k)
-        if (items[k].cell == 1) {
+        if (row_bytes(items[k]) <= 8) {          // one f64 / i64, or up to two f32 / i32 per row
           carried[k] = 1;
-          carried_bytes = std::max(carried_bytes, agg_carried_bytes(n_rows, dtype_size(g_.nodes[size_t(items[k].node)].dtype), L));
+          carried_bytes = std::max(carried_bytes, agg_carried_bytes(n_rows, int(row_bytes(items[k])), L));
         }
   }
   const size_t off_carried = off; off += up(carried_bytes);
@@ -1539,7 +1540,7 @@ void Session::aggregate(int64_t n_rows, const int64_t* keys, const std::vector<T
     }
     void* out = off_out[k] != SIZE_MAX ? static_cast<void*>(ws_ + off_out[k]) : fetches[items[k].fetch].data;
     if (carried[k])
-      launches_ += launch_agg_reduce_carried(n.dtype, n.red_op, payload, n_groups, n_rows, scratch, L, out, ws_ + off_carried,
+      launches_ += launch_agg_reduce_carried(n.dtype, n.red_op, payload, items[k].cell, n_groups, n_rows, scratch, L, out, ws_ + off_carried,
                                              carried_bytes, ws_ + off_split, split_bytes, dev_, stream_);
     else
       launches_ += launch_agg_reduce(n.dtype, n.red_op, payload, items[k].cell, n_groups, n_rows, scratch, L, out, ws_ + off_split,

@@ -1195,22 +1195,24 @@ def test_chains_that_start_with_a_cast_bit_exact(src, dst):
 
 @pytest.mark.parametrize("dt", list(T))
 @pytest.mark.parametrize("op", list(RED))
-def test_aggregate_scalar_payloads_ride_through_the_sort(dt, op):
-    """groupBy(key).sum(x) with one value per row: blocks of 2^16 rows and more sort the values along with the slots
-    instead of gathering them; a second, wide fetch in the same call still takes the gather path."""
+@pytest.mark.parametrize("xcell", [(), (2,)])
+def test_aggregate_scalar_payloads_ride_through_the_sort(dt, op, xcell):
+    """groupBy(key).sum(x) with at most 8 bytes per row (a scalar, or two 4-byte values): blocks of 2^16 rows and more
+    sort the values along with the slots instead of gathering them; a second, wide fetch in the same call still
+    takes the gather path."""
     st = T[dt]
     rng = np.random.default_rng(3)
     n, n_keys = 300_007, 5000
     table = rng.integers(-2**62, 2**62, n_keys, dtype=np.int64)
     keys = table[rng.integers(0, n_keys, n)]
     if st.np_dtype.kind == "i":
-        x = rng.integers(-1000, 1000, n).astype(st.np_dtype)
+        x = rng.integers(-1000, 1000, (n,) + xcell).astype(st.np_dtype)
         w = rng.integers(-1000, 1000, (n, 3)).astype(st.np_dtype)
     else:
-        x = rng.uniform(-1, 1, n).astype(st.np_dtype)
+        x = rng.uniform(-1, 1, (n,) + xcell).astype(st.np_dtype)
         w = rng.uniform(-1, 1, (n, 3)).astype(st.np_dtype)
     with dsl.withGraph():
-        px = dsl.placeholder(st, dsl.Unknown).named("x_input")
+        px = dsl.placeholder(st, dsl.Unknown, *xcell).named("x_input")
         pw = dsl.placeholder(st, dsl.Unknown, 3).named("w_input")
         g = dsl.build_graph(RED[op](px, [0]).named("x"), RED[op](pw, [0]).named("w"))
     with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
