@@ -83,7 +83,9 @@ void staged_copy(int device, void* dst, const void* src, size_t bytes, bool to_d
       char* slot = r.pinned + (size_t(w) * kSlotsPerWorker + size_t(s)) * kChunk;
       const size_t off = c * kChunk, len = std::min(kChunk, bytes - off);
       if (to_device) {
-        if (k >= size_t(kSlotsPerWorker)) e = cudaEventSynchronize(r.slot_free[w][s]);   // its previous DMA has read it
+        // the DMA that last read this slot -- earlier in this call or at the end of the previous one -- must be done
+        // (an event that was never recorded is complete)
+        e = cudaEventSynchronize(r.slot_free[w][s]);
         if (e != cudaSuccess) break;
         std::memcpy(slot, static_cast<const char*>(src) + off, len);
         e = cudaMemcpyAsync(static_cast<char*>(dst) + off, slot, len, cudaMemcpyHostToDevice, r.stream[w]);

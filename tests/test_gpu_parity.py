@@ -1227,3 +1227,33 @@ def test_aggregate_scalar_payloads_ride_through_the_sort(dt, op, xcell):
         else:
             tol = 1e-12 if st.np_dtype.itemsize == 8 else 1e-5
             assert np.all(np.abs(got.astype(np.float64) - want.astype(np.float64)) <= tol * absum)
+
+
+def test_staged_copies_from_concurrent_threads():
+    """Several task threads pushing large pageable blocks at once: the staging ring is shared per device and taken in
+    turn; results must be intact and nothing may deadlock."""
+    import threading
+    rng = np.random.default_rng(91)
+    n = 9_000_011                                          # 72 MB per f64 column: above the staging threshold
+    xs = [rng.uniform(-1, 1, n) for _ in range(3)]
+    with dsl.withGraph():
+        px = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x")
+        g = dsl.build_graph((px * 3.0 - 1.0).named("z"), dsl.reduce_max(px, [0]).named("m"))
+    errors = []
+
+    def work(t):
+        try:
+            for _ in range(3):
+                with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+                    z, m = s.run({"x": xs[t]}, ["z", "m"])
+                assert z.tobytes() == (xs[t] * 3.0 - 1.0).tobytes() and m == xs[t].max()
+        except Exception as exc:
+            errors.append((t, repr(exc)))
+
+    threads = [threading.Thread(target=work, args=(t,)) for t in range(3)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join(timeout=300)
+    assert not any(th.is_alive() for th in threads), "a staged copy did not return"
+    assert not errors, errors
