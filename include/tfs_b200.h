@@ -130,7 +130,9 @@ void tfs_session_free(tfs_session* s);
 /* Run on a caller-provided cudaStream_t instead of the session's own stream.
  * NULL restores the own stream -- so the legacy default stream (handle 0) cannot be
  * selected; pass a created stream, cudaStreamLegacy or cudaStreamPerThread.  Lets a
- * caller time with events on the stream the kernels run on. */
+ * caller time with events on the stream the kernels run on.
+ * The session's own stream is non-blocking: it does not wait for the legacy default stream.  Device-resident feeds
+ * must therefore be complete before a call, or be produced on the stream handed over here. */
 int tfs_session_set_stream(tfs_session* s, void* cuda_stream);
 /* Wait for everything enqueued by this session; reports deferred device-side
  * errors (TFS_ERR_RUNTIME) of asynchronous runs. */
