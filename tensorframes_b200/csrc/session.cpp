@@ -761,12 +761,17 @@ struct GroupCompiler {
         emit(C_BIN_X + sub * 8 + dt * 2);
       } else if (needs_compute(a) && needs_compute(b)) {
         compute(a, true);
-        int t = alloc_tmp();
-        emit(C_STTMP, t);
-        compute(b, true);
-        emit(C_FETCH_TMP, t);                   // acc holds b, x holds a: result = op(x, acc)
-        emit(C_BIN_X + sub * 8 + dt * 2 + 1);
-        tmp_busy[t] = false;
+        if (!needs_compute(b)) {
+          // evaluating a already produced b (a shared sub-expression, now parked in a temporary): b is a leaf here
+          binary_with(n, b, false);
+        } else {
+          int t = alloc_tmp();
+          emit(C_STTMP, t);
+          compute(b, true);
+          emit(C_FETCH_TMP, t);                   // acc holds b, x holds a: result = op(x, acc)
+          emit(C_BIN_X + sub * 8 + dt * 2 + 1);
+          tmp_busy[t] = false;
+        }
       } else if (needs_compute(b)) {
         compute(b, true);
         binary_with(n, a, true);

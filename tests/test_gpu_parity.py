@@ -1257,3 +1257,70 @@ def test_staged_copies_from_concurrent_threads():
         th.join(timeout=300)
     assert not any(th.is_alive() for th in threads), "a staged copy did not return"
     assert not errors, errors
+
+
+def _random_expression(rng, leaves, depth):
+    """A random element-wise expression over the given leaf nodes (no division: no NaN / inf to argue about)."""
+    if depth == 0 or rng.random() < 0.25:
+        return leaves[rng.integers(0, len(leaves))]
+    kind = rng.integers(0, 9)
+    a = _random_expression(rng, leaves, depth - 1)
+    if kind == 0:
+        return dsl.neg(a)
+    if kind == 1:
+        return dsl.relu(a)
+    if kind == 2:
+        return dsl.square(a)
+    if kind == 3:
+        return dsl.abs_(a)
+    b = _random_expression(rng, leaves, depth - 1)
+    return [dsl.add, dsl.sub, dsl.mul, dsl.minimum, dsl.maximum][kind % 5](a, b)
+
+
+@pytest.mark.parametrize("seed", range(160))
+def test_random_elementwise_graphs_match_the_oracle(seed):
+    """Randomised graphs over two columns, a row vector and scalars, with one to three fetches, optional casts in
+    front and behind: whatever mix of straight-line kernel and interpreter the planner picks, the bits must be the
+    oracle's.  (Fixed seeds: the suite stays deterministic.)"""
+    rng = np.random.default_rng(1000 + seed)
+    dts = [("f4", tfs.FloatType), ("f8", tfs.DoubleType), ("i4", tfs.IntegerType), ("i8", tfs.LongType)]
+    name, st = dts[seed % 4]
+    npdt = np.dtype("<" + name)
+    cell = [1, 4, 6, 64][rng.integers(0, 4)]
+    n = int(rng.choice([1, 37, 1025, 50_001]))
+
+    def values(shape):
+        if npdt.kind == "i":
+            return rng.integers(-9, 10, shape).astype(npdt)
+        return (rng.integers(-64, 65, shape) / 8.0).astype(npdt)        # exactly representable: products stay finite
+
+    x, y, vec = values((n, cell)), values((n, cell)), values((cell,))
+    feeds = {"x": x, "y": y}
+    with dsl.withGraph():
+        px = dsl.placeholder(st, dsl.Unknown, cell).named("x")
+        py = dsl.placeholder(st, dsl.Unknown, cell).named("y")
+        lead = px
+        if rng.random() < 0.3:                                           # a chain that starts with a cast
+            src_name, src_st = dts[(seed + 1) % 4]
+            ps = dsl.placeholder(src_st, dsl.Unknown, cell).named("s")
+            feeds["s"] = rng.integers(-9, 10, (n, cell)).astype(np.dtype("<" + src_name))
+            lead = dsl.cast(ps, st)
+        leaves = [lead, px, py, dsl.constant(vec), dsl.constant(npdt.type(2)), dsl.constant(npdt.type(-3))]
+        fetches = []
+        for k in range(int(rng.integers(1, 4))):
+            e = _random_expression(rng, leaves, int(rng.integers(1, 5)))
+            if e in leaves:
+                e = dsl.add(e, lead)
+            if rng.random() < 0.3:
+                e = dsl.cast(e, dts[int(rng.integers(0, 4))][1])
+            fetches.append(e.named(f"out{k}"))
+        g = dsl.build_graph(*fetches)
+    names = [f.name for f in fetches]
+    with np.errstate(all="ignore"):
+        want = tf_ops.evaluate(g, feeds, names)
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        present = {nm for nm, _ in gr.nodes()}
+        got = s.run({k: v for k, v in feeds.items() if k in present}, names)      # a column the expression never picked is not fed
+    for nm, w, gt in zip(names, want, got):
+        w = np.broadcast_to(w, gt.shape) if w.shape != gt.shape else w
+        assert gt.dtype == w.dtype and gt.tobytes() == np.ascontiguousarray(w).tobytes(), (seed, nm)
