@@ -1324,3 +1324,48 @@ def test_random_elementwise_graphs_match_the_oracle(seed):
     for nm, w, gt in zip(names, want, got):
         w = np.broadcast_to(w, gt.shape) if w.shape != gt.shape else w
         assert gt.dtype == w.dtype and gt.tobytes() == np.ascontiguousarray(w).tobytes(), (seed, nm)
+
+
+@pytest.mark.parametrize("seed", range(60))
+def test_random_graphs_with_reductions_match_the_oracle(seed):
+    """Random expressions feeding Sum / Min / Max over the rows or the cells, and element-wise nodes that read a
+    reduction back (x - min(x), a row vector computed at run time): several fused groups and reduction steps in
+    one plan.  Small integer values keep every sum exact in all four dtypes."""
+    rng = np.random.default_rng(5000 + seed)
+    dts = [("f4", tfs.FloatType), ("f8", tfs.DoubleType), ("i4", tfs.IntegerType), ("i8", tfs.LongType)]
+    name, st = dts[seed % 4]
+    npdt = np.dtype("<" + name)
+    cell = [2, 4, 5, 64][rng.integers(0, 4)]
+    n = int(rng.choice([1, 33, 2049, 20_001]))
+    x = rng.integers(-3, 4, (n, cell)).astype(npdt)
+    y = rng.integers(-3, 4, (n, cell)).astype(npdt)
+    reducers = [dsl.reduce_sum, dsl.reduce_min, dsl.reduce_max]
+    with dsl.withGraph():
+        px = dsl.placeholder(st, dsl.Unknown, cell).named("x")
+        py = dsl.placeholder(st, dsl.Unknown, cell).named("y")
+        leaves = [px, py, dsl.constant(npdt.type(2))]
+        fetches = []
+        for k in range(int(rng.integers(1, 4))):
+            e = _random_expression(rng, leaves, int(rng.integers(1, 3)))
+            if e in leaves or e.shape.numDims < 2:          # constants only: give it the block's shape
+                e = dsl.add(e, px)
+            kind = rng.integers(0, 4)
+            if kind == 0:
+                e = reducers[rng.integers(0, 3)](e, [0])                          # block reduction -> [cell]
+            elif kind == 1:
+                e = reducers[rng.integers(0, 3)](e, [1])                          # per-row reduction -> [n]
+            elif kind == 2:
+                e = dsl.sub(e, reducers[rng.integers(1, 3)](e, [0]))              # read a reduction back, broadcast
+            else:
+                e = reducers[rng.integers(0, 3)](dsl.mul(e, e), None)             # everything -> scalar
+            fetches.append(e.named(f"out{k}"))
+        g = dsl.build_graph(*fetches)
+    names = [f.name for f in fetches]
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        present = {nm for nm, _ in gr.nodes()}
+        feeds = {k: v for k, v in {"x": x, "y": y}.items() if k in present}
+        got = s.run(feeds, names)
+    want = tf_ops.evaluate(g, feeds, names)
+    for nm, w, gt in zip(names, want, got):
+        assert gt.dtype == w.dtype and gt.shape == w.shape, (seed, nm, gt.dtype, w.dtype, gt.shape, w.shape)
+        assert gt.tobytes() == np.ascontiguousarray(w).tobytes(), (seed, nm, gt.reshape(-1)[:6], np.asarray(w).reshape(-1)[:6])
