@@ -1369,3 +1369,45 @@ def test_random_graphs_with_reductions_match_the_oracle(seed):
     for nm, w, gt in zip(names, want, got):
         assert gt.dtype == w.dtype and gt.shape == w.shape, (seed, nm, gt.dtype, w.dtype, gt.shape, w.shape)
         assert gt.tobytes() == np.ascontiguousarray(w).tobytes(), (seed, nm, gt.reshape(-1)[:6], np.asarray(w).reshape(-1)[:6])
+
+
+@pytest.mark.parametrize("seed", range(48))
+def test_random_aggregates_match_numpy(seed):
+    """Random keyed reductions: block sizes either side of the carried-values and split-groups thresholds, one to
+    three fetches of different cells, keys from a handful to one per row, the empty-marker key value included.
+    Small integer payloads make sums exact in every dtype."""
+    rng = np.random.default_rng(9000 + seed)
+    st = list(T.values())[seed % 4]
+    npdt = st.np_dtype
+    n = int(rng.choice([1, 7, 1000, 70_000, 300_001]))
+    n_keys = int(rng.choice([1, 3, 50, 4000, max(1, n)]))
+    table = rng.integers(-2**63, 2**63 - 1, n_keys, dtype=np.int64)
+    if rng.random() < 0.3:
+        table[0] = np.int64(-2**63)                       # the value the hash table uses as its empty marker
+    table = np.unique(table)
+    keys = table[rng.integers(0, len(table), n)]
+    cells = [(), (1,), (2,), (3,), (16,), (64,), (5, 3)]
+    ops = list(RED)
+    feeds, fetch_nodes, want = {}, [], {}
+    with dsl.withGraph():
+        for k in range(int(rng.integers(1, 4))):
+            cell = cells[rng.integers(0, len(cells))]
+            op = ops[rng.integers(0, len(ops))]
+            v = rng.integers(-4, 5, (n,) + cell).astype(npdt)
+            p = dsl.placeholder(st, dsl.Unknown, *cell).named(f"c{k}_input")
+            fetch_nodes.append(RED[op](p, [0]).named(f"c{k}"))
+            feeds[f"c{k}_input"] = v
+            want[f"c{k}"] = (v, op)
+        g = dsl.build_graph(*fetch_nodes)
+    names = [f.name for f in fetch_nodes]
+    uniq = np.unique(keys)
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        got_keys, outs = s.aggregate(keys, feeds, names, max_groups=len(uniq))
+    assert got_keys.tolist() == uniq.tolist()
+    order = np.argsort(keys, kind="stable")
+    bounds = np.searchsorted(keys[order], uniq)
+    for nm, got in zip(names, outs):
+        v, op = want[nm]
+        fn = {"sum": np.add, "min": np.minimum, "max": np.maximum}[op]
+        ref = fn.reduceat(v[order].astype(np.int64), bounds, axis=0)
+        assert got.shape == ref.shape and np.array_equal(got.astype(np.int64), ref), (seed, nm, op, v.shape)
