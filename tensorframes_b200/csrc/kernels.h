@@ -50,6 +50,10 @@ int launch_reduce_axis0(int dtype, int red_op, const void* in, int64_t outer, in
 int launch_reduce_rows(int dtype, int red_op, const void* in, int64_t outer, int64_t inner, void* out,
                        const DeviceInfo& dev, cudaStream_t stream);
 
+// Middle axes: in[outer, len, inner] along len into out[outer, inner].
+int launch_reduce_mid(int dtype, int red_op, const void* in, int64_t outer, int64_t len, int64_t inner, void* out,
+                      const DeviceInfo& dev, cudaStream_t stream);
+
 // K4: out[M, N] = op(a) * op(b) (+ bias[N]); float32 or float64 (dtype). The SIMT kernel takes any shape.
 int launch_matmul_simt(int dtype, const void* a, const void* b, const void* bias, void* out, int64_t M, int64_t N, int64_t K,
                        bool ta, bool tb, const DeviceInfo& dev, cudaStream_t stream);

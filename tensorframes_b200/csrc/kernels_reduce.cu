@@ -356,6 +356,24 @@ reduce_rows_kernel(const T* __restrict__ in, const int64_t outer, const int64_t 
   }
 }
 
+// Middle-axis reduction: in[outer, len, inner] -> out[outer, inner] (mapRows over matrix cells: axis 0 of the cell is
+// the middle axis of the block).  One thread per output element, neighbouring threads on neighbouring `inner`
+// positions so every step of the fold is a coalesced read; the fold order is the axis order.
+template <class T, int OP>
+__global__ void __launch_bounds__(kMaxThreads)
+reduce_mid_kernel(const T* __restrict__ in, const int64_t outer, const int64_t len, const int64_t inner, T* __restrict__ out) {
+  using R = Red<T, OP>;
+  const int64_t n = outer * inner;
+  const int64_t stride = int64_t(gridDim.x) * blockDim.x;
+  for (int64_t t = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; t < n; t += stride) {
+    const int64_t o = t / inner, i = t % inner;
+    const T* p = in + o * len * inner + i;
+    T s = R::identity();
+    for (int64_t a = 0; a < len; ++a) s = R::op(s, __ldcs(p + a * inner));
+    out[t] = s;
+  }
+}
+
 int64_t gcd64(int64_t a, int64_t b) { while (b) { int64_t t = a % b; a = b; b = t; } return a; }
 
 struct FlatGeom { bool ok; int P, L, q, threads; int grid; };
@@ -490,6 +508,37 @@ int launch_reduce_axis0(int dtype, int red_op, const void* in, int64_t outer, in
     case TFS_FLOAT: return launch_axis0_op<float>(red_op, in, outer, inner, out, scratch, dev, stream);
     case TFS_INT32: return launch_axis0_op<int>(red_op, in, outer, inner, out, scratch, dev, stream);
     case TFS_INT64: return launch_axis0_op<long long>(red_op, in, outer, inner, out, scratch, dev, stream);
+  }
+  fail(TFS_ERR_UNSUPPORTED, "reduce: unsupported dtype");
+}
+
+namespace {
+template <class T>
+int launch_mid_op(int red_op, const void* in, int64_t outer, int64_t len, int64_t inner, void* out, const DeviceInfo& dev,
+                  cudaStream_t stream) {
+  const T* i = static_cast<const T*>(in);
+  T* o = static_cast<T*>(out);
+  const int threads = kMaxThreads;
+  int64_t grid = std::min<int64_t>((outer * inner + threads - 1) / threads, int64_t(dev.sm_count) * 8);
+  if (grid < 1) grid = 1;
+  switch (red_op) {
+    case R_SUM: reduce_mid_kernel<T, R_SUM><<<(unsigned)grid, threads, 0, stream>>>(i, outer, len, inner, o); break;
+    case R_MIN: reduce_mid_kernel<T, R_MIN><<<(unsigned)grid, threads, 0, stream>>>(i, outer, len, inner, o); break;
+    default: reduce_mid_kernel<T, R_MAX><<<(unsigned)grid, threads, 0, stream>>>(i, outer, len, inner, o); break;
+  }
+  TFS_CUDA(cudaGetLastError());
+  return 1;
+}
+}  // namespace
+
+int launch_reduce_mid(int dtype, int red_op, const void* in, int64_t outer, int64_t len, int64_t inner, void* out,
+                      const DeviceInfo& dev, cudaStream_t stream) {
+  if (outer * inner <= 0) return 0;
+  switch (dtype) {
+    case TFS_DOUBLE: return launch_mid_op<double>(red_op, in, outer, len, inner, out, dev, stream);
+    case TFS_FLOAT: return launch_mid_op<float>(red_op, in, outer, len, inner, out, dev, stream);
+    case TFS_INT32: return launch_mid_op<int>(red_op, in, outer, len, inner, out, dev, stream);
+    case TFS_INT64: return launch_mid_op<long long>(red_op, in, outer, len, inner, out, dev, stream);
   }
   fail(TFS_ERR_UNSUPPORTED, "reduce: unsupported dtype");
 }

@@ -57,7 +57,7 @@ bool is_pinned_host_pointer(const void* p) {
 }
 
 struct Step {
-  enum Kind { ELT, REDUCE_AXIS0, REDUCE_ROWS, COPY, MATMUL, HOSTVAL, TILE, ARGMINMAX, SEGSUM } kind = ELT;
+  enum Kind { ELT, REDUCE_AXIS0, REDUCE_ROWS, REDUCE_MID, COPY, MATMUL, HOSTVAL, TILE, ARGMINMAX, SEGSUM } kind = ELT;
   std::vector<int> nodes;   // ELT: the group (topological order); others: one node
   Shape shape;              // ELT: iteration shape
   int64_t outer = 0, inner = 0;  // reductions, ARGMINMAX
@@ -474,9 +474,13 @@ void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<
         s.outer = s.inner = 1;
         for (int i = 0; i < xs.rank; ++i) (i < xs.rank - k ? s.outer : s.inner) *= xs.d[i];
       } else {
-        fail(TFS_ERR_UNSUPPORTED, "node '" + n.name + "' (" + n.op +
-                                      "): only reductions over leading or trailing axes are supported, input shape " +
-                                      xs.str());
+        bool contiguous = true;
+        for (int i = 1; i < k; ++i) contiguous = contiguous && axes[size_t(i)] == axes[size_t(i - 1)] + 1;
+        TFS_CHECK(contiguous, TFS_ERR_UNSUPPORTED,
+                  "node '" + n.name + "' (" + n.op + "): the reduced axes must be adjacent, input shape " + xs.str());
+        s.kind = Step::REDUCE_MID;            // [outer, len, inner] along len
+        s.outer = s.len = s.inner = 1;
+        for (int i = 0; i < xs.rank; ++i) (i < axes[0] ? s.outer : (i <= axes[size_t(k - 1)] ? s.len : s.inner)) *= xs.d[i];
       }
       plan.steps.push_back(s);
       plan.step_of[size_t(idx)] = int(plan.steps.size()) - 1;
@@ -1020,6 +1024,12 @@ void Session::exec_step(const Plan& plan, size_t step_index, std::vector<void*>&
       const Node& n = g_.nodes[size_t(s.nodes[0])];
       launches_ += launch_reduce_rows(n.dtype, n.red_op, dev_ptr[size_t(n.in[0])], s.outer, s.inner,
                                       dev_ptr[size_t(s.nodes[0])], dev_, stream);
+      break;
+    }
+    case Step::REDUCE_MID: {
+      const Node& n = g_.nodes[size_t(s.nodes[0])];
+      launches_ += launch_reduce_mid(n.dtype, n.red_op, dev_ptr[size_t(n.in[0])], s.outer, s.len, s.inner,
+                                     dev_ptr[size_t(s.nodes[0])], dev_, stream);
       break;
     }
     case Step::COPY: {

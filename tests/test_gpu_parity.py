@@ -1411,3 +1411,66 @@ def test_random_aggregates_match_numpy(seed):
         fn = {"sum": np.add, "min": np.minimum, "max": np.maximum}[op]
         ref = fn.reduceat(v[order].astype(np.int64), bounds, axis=0)
         assert got.shape == ref.shape and np.array_equal(got.astype(np.int64), ref), (seed, nm, op, v.shape)
+
+
+@pytest.mark.parametrize("seed", range(40))
+def test_random_row_mode_graphs_match_the_oracle_row_by_row(seed):
+    """mapRows semantics: the graph describes ONE row; the device maps it over the block in one call.  The oracle
+    evaluates it row by row, as the reference does (impl/DebugRowOps.scala:819-857)."""
+    rng = np.random.default_rng(7000 + seed)
+    dts = [("f4", tfs.FloatType), ("f8", tfs.DoubleType), ("i4", tfs.IntegerType), ("i8", tfs.LongType)]
+    name, st = dts[seed % 4]
+    npdt = np.dtype("<" + name)
+    cell = [(), (3,), (4,), (2, 3)][rng.integers(0, 4)]
+    n = int(rng.choice([1, 5, 37]))
+    x = rng.integers(-3, 4, (n,) + cell).astype(npdt)
+    y = rng.integers(-3, 4, (n,) + cell).astype(npdt)
+    with dsl.withGraph():
+        px = dsl.placeholder(st, *cell).named("x")
+        py = dsl.placeholder(st, *cell).named("y")
+        leaves = [px, py, dsl.constant(npdt.type(2))]
+        fetches = []
+        for k in range(int(rng.integers(1, 3))):
+            e = _random_expression(rng, leaves, int(rng.integers(1, 4)))
+            if e in leaves or e.shape.numDims < len(cell):
+                e = dsl.add(e, px)
+            if cell and rng.random() < 0.5:
+                red = [dsl.reduce_sum, dsl.reduce_min, dsl.reduce_max][rng.integers(0, 3)]
+                e = red(e, [0]) if rng.random() < 0.5 else red(e, None)
+            fetches.append(e.named(f"out{k}"))
+        g = dsl.build_graph(*fetches)
+    names = [f.name for f in fetches]
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        present = {nm for nm, _ in gr.nodes()}
+        feeds = {k: v for k, v in {"x": x, "y": y}.items() if k in present}
+        got = s.run(feeds, names, rows=True)
+    for i in range(n):
+        want = tf_ops.evaluate(g, {k: v[i] for k, v in feeds.items()}, names)
+        for nm, w, gt in zip(names, want, got):
+            assert gt.shape[0] == n and gt[i].shape == w.shape, (seed, nm, gt.shape, w.shape)
+            assert gt[i].tobytes() == np.ascontiguousarray(w).tobytes(), (seed, nm, i)
+
+
+@pytest.mark.parametrize("dt", list(T))
+def test_middle_axis_reductions(dt):
+    """Sum / Min / Max over an axis that is neither first nor last (adjacent axes may be reduced together)."""
+    st = T[dt]
+    rng = np.random.default_rng(12)
+    x = rng.integers(-5, 6, (301, 5, 7)).astype(st.np_dtype)
+    x4 = rng.integers(-5, 6, (19, 3, 4, 6)).astype(st.np_dtype)
+    with dsl.withGraph():
+        p = dsl.placeholder(st, dsl.Unknown, 5, 7).named("x")
+        p4 = dsl.placeholder(st, dsl.Unknown, 3, 4, 6).named("x4")
+        g = dsl.build_graph(dsl.reduce_sum(p, [1]).named("s"), dsl.reduce_min(p, [1]).named("mn"),
+                            dsl.reduce_max(p4, [1, 2]).named("mx"), dsl.reduce_sum(p4, [2]).named("s2"))
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        got = s.run({"x": x, "x4": x4}, ["s", "mn", "mx", "s2"])
+        with pytest.raises(_native.UnsupportedError, match="adjacent"):
+            with dsl.withGraph():
+                q = dsl.placeholder(st, dsl.Unknown, 3, 4, 6).named("x4")
+                bad = dsl.build_graph(dsl.reduce_sum(q, [1, 3]).named("b"))
+            with _native.Graph(bad) as gb, _native.Session(gb, 0) as sb:
+                sb.run({"x4": x4}, ["b"])
+    want = [x.sum(1, dtype=st.np_dtype), x.min(1), x4.max((1, 2)), x4.sum(2, dtype=st.np_dtype)]
+    for gt, w in zip(got, want):
+        assert gt.shape == w.shape and np.array_equal(gt, w)
