@@ -1474,3 +1474,44 @@ def test_middle_axis_reductions(dt):
     want = [x.sum(1, dtype=st.np_dtype), x.min(1), x4.max((1, 2)), x4.sum(2, dtype=st.np_dtype)]
     for gt, w in zip(got, want):
         assert gt.shape == w.shape and np.array_equal(gt, w)
+
+
+@pytest.mark.parametrize("seed", range(48))
+def test_random_matmuls_exact_on_small_integers(seed):
+    """Random MatMul shapes, transposes, constant or fed right-hand sides, optional bias and relu, float32 and
+    float64: tensor-core, pipelined and SIMT paths.  Small integers make every product and sum exact, so all of them
+    must agree with integer arithmetic bit for bit."""
+    rng = np.random.default_rng(11000 + seed)
+    st = [tfs.FloatType, tfs.DoubleType][seed % 2]
+    npdt = st.np_dtype
+    m = int(rng.choice([1, 2, 127, 129, 1000, 4097]))
+    k = int(rng.choice([1, 3, 17, 32, 64, 96, 100, 256]))
+    n = int(rng.choice([1, 5, 16, 48, 100, 256]))
+    ta, tb = bool(rng.random() < 0.2), bool(rng.random() < 0.3)
+    const_b = bool(rng.random() < 0.7)
+    a = rng.integers(-3, 4, (k, m) if ta else (m, k)).astype(npdt)
+    b = rng.integers(-3, 4, (n, k) if tb else (k, n)).astype(npdt)
+    bias = rng.integers(-9, 10, n).astype(npdt)
+    use_bias, use_relu = bool(rng.random() < 0.6), bool(rng.random() < 0.3)
+    feeds = {"a": a}
+    with dsl.withGraph():
+        pa = dsl.placeholder(st, *( (k, dsl.Unknown) if ta else (dsl.Unknown, k) )).named("a")
+        if const_b:
+            nb = dsl.constant(b)
+        else:
+            nb = dsl.placeholder(st, *b.shape).named("b")
+            feeds["b"] = b
+        y = dsl.matmul(pa, nb, transpose_a=ta, transpose_b=tb)
+        if use_bias:
+            y = y + dsl.constant(bias)
+        if use_relu:
+            y = dsl.relu(y)
+        g = dsl.build_graph(y.named("y"))
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        (got,) = s.run(feeds, ["y"])
+    want = (a.T if ta else a).astype(np.int64) @ (b.T if tb else b).astype(np.int64)
+    if use_bias:
+        want = want + bias.astype(np.int64)
+    if use_relu:
+        want = np.maximum(want, 0)
+    assert got.dtype == npdt and got.shape == want.shape and np.array_equal(got.astype(np.int64), want), (seed, m, k, n, ta, tb, const_b)
