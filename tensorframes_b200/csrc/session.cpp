@@ -998,11 +998,18 @@ std::unordered_map<int, std::pair<float*, float*>>::iterator Session::ensure_tc_
 // One step of a plan on `stream`; dev_ptr holds the device address of every materialised node.
 void Session::exec_step(const Plan& plan, size_t step_index, std::vector<void*>& dev_ptr, cudaStream_t stream) {
   const Step& s = plan.steps[step_index];
+  // A node that is needed only for its SHAPE (the operand of OnesLike / ZerosLike / Shape) has no buffer: its step
+  // has nothing to write and is skipped.
+  if (s.kind != Step::ELT && s.kind != Step::HOSTVAL) {
+    const int out_node = (s.kind == Step::MATMUL && s.out_node >= 0) ? s.out_node : s.nodes[0];
+    if (!plan.materialize[size_t(out_node)]) return;
+  }
   switch (s.kind) {
     case Step::ELT: {
       if (s.shape.numel() == 0) break;
       GroupCompiler gc(g_, plan.shape, dev_ptr, plan.materialize, s);
       gc.build(err_flag_);
+      if (gc.prog.n_instr == 0) break;          // every member is needed for its shape only
       ChainProgram chain;
       const bool straight = make_chain(gc.prog, chain);
       static const bool trace = [] { const char* e = std::getenv("TFS_TRACE"); return e && *e && *e != '0'; }();

@@ -311,3 +311,43 @@ def test_kmeans_graphs_on_an_empty_block():
     with _native.Graph(g2) as gr, _native.Session(gr, 0) as s:
         pts, cts, dist = s.run({"features": x}, [f.name for f in fetches2])
     assert pts.shape == (1, k, m) and not pts.any() and cts.shape == (1, k) and not cts.any() and dist.tolist() == [0.0]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", range(40))
+def test_random_shape_op_graphs_match_the_oracle(seed):
+    """Tile / ExpandDims / ArgMin / ArgMax / UnsortedSegmentSum / Shape arithmetic on random shapes and dtypes, fed
+    into each other and into element-wise ops."""
+    rng = np.random.default_rng(13000 + seed)
+    dts = [("f4", tfs.FloatType), ("f8", tfs.DoubleType), ("i4", tfs.IntegerType), ("i8", tfs.LongType)]
+    name, st = dts[seed % 4]
+    npdt = np.dtype("<" + name)
+    n = int(rng.choice([1, 6, 257, 5001]))
+    c = int(rng.choice([1, 3, 8, 33]))
+    x = rng.integers(-5, 6, (n, c)).astype(npdt)
+    n_seg = int(rng.choice([1, 4, 70]))
+    ids = rng.integers(0, n_seg, n).astype([np.int32, np.int64][seed % 2])
+    with dsl.withGraph():
+        p = dsl.placeholder(st, dsl.Unknown, c).named("x")
+        pid = dsl.placeholder([tfs.IntegerType, tfs.LongType][seed % 2], dsl.Unknown).named("ids")
+        rows = dsl.shape(p)[0]
+        reps = int(rng.integers(1, 4))
+        fetches = [
+            dsl.tile(p, [reps, int(rng.integers(1, 3))]).named("t0"),
+            dsl.tile(dsl.expand_dims(dsl.reduce_sum(p, [0]), 0), dsl.stack([rows, 1])).named("t1"),        # a row vector per row
+            (p - dsl.tile(dsl.expand_dims(dsl.reduce_max(p, [1]), 1), dsl.stack([1, c]))).named("t2"),    # x - rowmax
+            dsl.argmin(p, 1).named("a1"), dsl.argmax(p, 0).named("a0"),
+            dsl.unsorted_segment_sum(p, pid, n_seg).named("seg"),
+            dsl.unsorted_segment_sum(dsl.ones_like(dsl.reduce_sum(p, [1])), pid, n_seg).named("cnt"),
+            dsl.expand_dims(dsl.reduce_min(p, [0]), int(rng.integers(0, 2))).named("e"),
+            dsl.stack([rows, c, 7]).named("shp"),
+        ]
+        g = dsl.build_graph(*fetches)
+    names = [f.name for f in fetches]
+    feeds = {"x": x, "ids": ids}
+    want = tf_ops.evaluate(g, feeds, names)
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        got = s.run(feeds, names)
+    for nm, w, gt in zip(names, want, got):
+        assert gt.dtype == w.dtype and gt.shape == w.shape, (seed, nm, gt.dtype, w.dtype, gt.shape, w.shape)
+        assert gt.tobytes() == np.ascontiguousarray(w).tobytes(), (seed, nm)
