@@ -1515,3 +1515,48 @@ def test_random_matmuls_exact_on_small_integers(seed):
     if use_relu:
         want = np.maximum(want, 0)
     assert got.dtype == npdt and got.shape == want.shape and np.array_equal(got.astype(np.int64), want), (seed, m, k, n, ta, tb, const_b)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_random_graphs_through_the_pinned_pipeline(seed):
+    """The chunked H2D / kernel / D2H pipeline on random two-column graphs with ragged row counts: results must be
+    the one-shot (pageable) run's bits, fetch by fetch."""
+    rng = np.random.default_rng(17000 + seed)
+    st, npdt = [(tfs.DoubleType, np.float64), (tfs.FloatType, np.float32), (tfs.LongType, np.int64)][seed % 3]
+    cell = [1, 4, 16][rng.integers(0, 3)]
+    n = (int(rng.integers(9_000_000, 11_000_000)) * 8 // np.dtype(npdt).itemsize) // cell
+    bufs = []
+    try:
+        xa = _native.PinnedBuffer((n, cell), npdt); bufs.append(xa)
+        ya = _native.PinnedBuffer((n, cell), npdt); bufs.append(ya)
+        xa.array[:] = rng.integers(-50, 51, (n, cell)).astype(npdt)
+        ya.array[:] = rng.integers(1, 9, (n, cell)).astype(npdt)
+        vec = rng.integers(-3, 4, cell).astype(npdt)
+        with dsl.withGraph():
+            px = dsl.placeholder(st, dsl.Unknown, cell).named("x")
+            py = dsl.placeholder(st, dsl.Unknown, cell).named("y")
+            leaves = [px, py, dsl.constant(vec), dsl.constant(npdt(2))]
+            fetches = []
+            for k in range(int(rng.integers(1, 3))):
+                e = _random_expression(rng, leaves, int(rng.integers(1, 4)))
+                if e in leaves or e.shape.numDims < 2:
+                    e = dsl.add(e, px)
+                fetches.append(e.named(f"out{k}"))
+            g = dsl.build_graph(*fetches)
+        names = [f.name for f in fetches]
+        outs = {}
+        for nm in names:
+            b = _native.PinnedBuffer((n, cell), npdt); bufs.append(b)
+            outs[nm] = b.array
+        with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+            present = {nm for nm, _ in gr.nodes()}
+            pinned_feeds = {k: v for k, v in {"x": xa.array, "y": ya.array}.items() if k in present}
+            s.run_into(pinned_feeds, outs)
+            launches = s.launch_count
+            pageable = s.run({k: np.array(v) for k, v in pinned_feeds.items()}, names)
+        assert launches >= 1
+        for nm, ref in zip(names, pageable):
+            assert outs[nm].tobytes() == ref.tobytes(), (seed, nm)
+    finally:
+        for b in bufs:
+            b.free()
