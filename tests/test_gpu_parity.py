@@ -1560,3 +1560,48 @@ def test_random_graphs_through_the_pinned_pipeline(seed):
     finally:
         for b in bufs:
             b.free()
+
+
+@pytest.mark.parametrize("seed", range(30))
+def test_random_frames_through_the_operators_match_the_oracle_executors(seed):
+    """Random partitioned frames (empty partitions, a string column along for the ride, scalar or vector cells)
+    through map_blocks, reduce_blocks and aggregate, against the row-by-row restatement of the reference's
+    executors (oracle/executors.py: performMap, reduceBlocks with its pairwise merge, TensorFlowUDAF)."""
+    from oracle import executors as ox
+    rng = np.random.default_rng(19000 + seed)
+    st = [tfs.DoubleType, tfs.LongType][seed % 2]        # what from_rows infers for python floats / ints
+    npdt = st.np_dtype
+    cell = [(), (3,), (2, 2)][rng.integers(0, 3)]
+    n = int(rng.choice([1, 4, 23, 200]))
+    n_parts = int(rng.integers(1, 6))
+    x = rng.integers(-4, 5, (n,) + cell).astype(npdt)
+    key = rng.integers(0, 4, n).astype(np.int64)
+    tag = np.array([f"r{i % 3}" for i in range(n)], dtype=object)
+    rows = [(int(key[i]), tag[i], x[i].tolist() if cell else x[i].item()) for i in range(n)]
+    df = tfs.analyze(TensorFrame.from_rows(rows, ["key", "tag", "x"], num_partitions=n_parts))
+    parts, cols = _golden.oracle_inputs(None, df)
+    # map_blocks: z = f(x), appended in front of the input columns
+    with dsl.withGraph():
+        p = tfs.block(df, "x")
+        z = _random_expression(rng, [p, dsl.constant(npdt.type(2))], int(rng.integers(1, 4)))
+        if z.shape.numDims < 1 + len(cell) or z is p:
+            z = dsl.add(z, p)
+        z = z.named("z")
+        out = tfs.map_blocks(z, df)
+        g = dsl.build_graph(z)
+    names, want_parts = ox.map_blocks(parts, cols, g, ["x"], {"z": (st.tf_code, (dsl.Unknown,) + cell)})
+    assert out.columns == names
+    assert _golden.normalize(out.collect()) == _golden.normalize([r for pr in want_parts for r in pr])
+    # reduce_blocks and aggregate on the numeric column
+    with dsl.withGraph():
+        xi = tfs.block(df, "x", tf_name="x_input")
+        red = [dsl.reduce_sum, dsl.reduce_min, dsl.reduce_max][rng.integers(0, 3)](xi, [0]).named("x")
+        got_red = tfs.reduce_blocks(red, df.select("x"))
+        got_agg = tfs.aggregate(red, df.select("key", "x").groupBy("key"))
+        g2 = dsl.build_graph(red)
+    sel_parts, sel_cols = _golden.oracle_inputs(None, df.select("x"))
+    want_red = ox.reduce_blocks(sel_parts, sel_cols, g2, ["x"])
+    assert np.array_equal(np.asarray(got_red), np.asarray(want_red[0]))
+    kparts, kcols = _golden.oracle_inputs(None, df.select("key", "x"))
+    want_agg = ox.aggregate(kparts, kcols, [0], g2, ["x"])
+    assert _golden.normalize(got_agg.collect()) == _golden.normalize(want_agg)
