@@ -1607,3 +1607,25 @@ def test_random_frames_through_the_operators_match_the_oracle_executors(seed):
     kparts, kcols = _golden.oracle_inputs(None, df.select("key", "x"))
     want_agg = ox.aggregate(kparts, kcols, [0], g2, ["x"])
     assert _golden.normalize(got_agg.collect()) == _golden.normalize(want_agg)
+
+
+@pytest.mark.parametrize("seed", range(40))
+def test_random_reduction_shapes(seed):
+    """Block reductions over random [outer, inner...] shapes: narrow and wide cells, outer from 1 to 1e6, every dtype
+    and op; the flat, TMA-staged, column and row kernels all get their turn."""
+    rng = np.random.default_rng(23000 + seed)
+    dt = list(T)[seed % 4]
+    st = T[dt]
+    op = list(RED)[rng.integers(0, 3)]
+    outer = int(rng.choice([1, 2, 31, 1000, 65_537, 1_000_003]))
+    inner = int(rng.choice([1, 2, 3, 7, 64, 100, 257, 2048, 5000]))
+    if outer * inner > 40_000_000:
+        outer = max(1, 40_000_000 // inner)
+    x = rng.integers(-3, 4, (outer, inner)).astype(st.np_dtype)
+    with dsl.withGraph():
+        p = dsl.placeholder(st, dsl.Unknown, inner).named("x")
+        g = dsl.build_graph(RED[op](p, [0]).named("c"), RED[op](p, [1]).named("r"), RED[op](p, None).named("a"))
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        c, r, a = s.run({"x": x}, ["c", "r", "a"])
+    fn = {"sum": lambda v, ax: v.sum(ax, dtype=st.np_dtype), "min": lambda v, ax: v.min(ax), "max": lambda v, ax: v.max(ax)}[op]
+    assert np.array_equal(c, fn(x, 0)) and np.array_equal(r, fn(x, 1)) and np.array_equal(a, fn(x, None)), (seed, dt, op, outer, inner)
