@@ -1629,3 +1629,51 @@ def test_random_reduction_shapes(seed):
         c, r, a = s.run({"x": x}, ["c", "r", "a"])
     fn = {"sum": lambda v, ax: v.sum(ax, dtype=st.np_dtype), "min": lambda v, ax: v.min(ax), "max": lambda v, ax: v.max(ax)}[op]
     assert np.array_equal(c, fn(x, 0)) and np.array_equal(r, fn(x, 1)) and np.array_equal(a, fn(x, None)), (seed, dt, op, outer, inner)
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_damaged_graphs_plan_and_run_without_faults(seed):
+    """1500 byte-level mutations per seed of valid graphs (constants, attributes, node names, wire types all get
+    hit).  The ones that still import are planned and every node is fetched: an answer or a status are both fine; a
+    device fault (which would poison this process) or a crash is not.  A healthy graph must run right afterwards."""
+    import _mutate
+    graphs = _mutate.seed_graphs()
+    rng = np.random.default_rng(31000 + seed)
+    ran = refused = 0
+    for it in range(1500):
+        g = _mutate.mutate(rng, graphs[it % len(graphs)], structural=False)
+        try:
+            gr = _native.Graph(g)
+        except _native.NativeError:
+            continue
+        try:
+            feeds, fetches = {}, []
+            for name, op in gr.nodes():
+                dt, shape, is_ph, _ = gr.node_info(name)
+                if not is_ph:
+                    fetches.append(name)
+                    continue
+                if shape is None:
+                    raise ValueError("placeholder of unknown rank")
+                dims = [16 if d < 0 else d for d in shape.dims]
+                if int(np.prod(dims)) > 1 << 20:
+                    raise ValueError("placeholder too large to feed")
+                feeds[name] = rng.integers(0, 5, dims).astype(dt.np_dtype)
+            with _native.Session(gr, 0) as s:
+                for f in fetches:
+                    try:
+                        s.run(feeds, [f])
+                        ran += 1
+                    except _native.NativeError:
+                        refused += 1
+        except (_native.NativeError, ValueError, UnicodeDecodeError, AttributeError):
+            refused += 1
+        finally:
+            gr.close()
+    assert ran > 1000 and refused > 0
+    import torch
+    torch.cuda.synchronize()
+    x = np.arange(12, dtype=np.float32).reshape(3, 4)
+    with _native.Graph(graphs[2]) as gr, _native.Session(gr, 0) as s:
+        (got,) = s.run({"x": x}, ["s"])
+    assert np.array_equal(got, x.sum(0))

@@ -1,5 +1,7 @@
 """Host-side logic that needs no GPU: the DSL and its GraphDef bytes, graph analysis through the
 C ABI (no CUDA call), schema validation with the reference's error behaviour, analyze/explain."""
+import ctypes
+
 import numpy as np
 import pytest
 
@@ -143,6 +145,29 @@ def test_native_rejects_bad_graphs():
         proto.node_def("c", "Add", ["a", "b"], {"T": proto.AttrValue.of_type(tfs.FloatType)})])
     with pytest.raises(_native.NativeError):
         _native.Graph(mixed)
+
+
+def test_damaged_graph_bytes_end_in_a_status_code():
+    """2000 byte-level mutations (bit flips, truncations, insertions) of valid graphs: import either succeeds, and
+    every node can then be described, or fails with a status; nothing may crash the process."""
+    import _mutate
+    graphs = _mutate.seed_graphs()
+    rng = np.random.default_rng(11)
+    imported = 0
+    for it in range(2000):
+        g = _mutate.mutate(rng, graphs[it % len(graphs)], structural=True)
+        try:
+            G = _native.Graph(g)
+        except _native.NativeError as e:
+            assert str(e)
+            continue
+        imported += 1
+        h, lib = G.handle, _native.lib()
+        for k in range(lib.tfs_graph_num_nodes(h)):
+            info = _native.NodeInfo()
+            lib.tfs_graph_node_info(h, lib.tfs_graph_node_name(h, k), ctypes.byref(info))
+        G.close()
+    assert 50 < imported < 1500
 
 
 def test_analyze_graph_hints_override():
