@@ -61,3 +61,23 @@ def test_run_without_gpu_fails_loudly():
         with pytest.raises(_native.NativeError) as e:
             s.run({"x": np.arange(10.0)}, ["z"])
         assert e.value.code == _native.TFS_ERR_CUDA and "no CPU execution path" in str(e.value)
+
+
+def test_product_never_touches_the_oracle():
+    """oracle/ is the checker: nothing under tensorframes_b200/ (Python or native source) or examples/ may name it,
+    and importing the package must not pull it in."""
+    import subprocess
+    import sys
+    offenders = []
+    for top in ("tensorframes_b200", "examples"):
+        for dirpath, _, files in os.walk(os.path.join(ROOT, top)):
+            for f in files:
+                if f.endswith((".py", ".cu", ".cpp", ".h", ".inc", ".c")):
+                    text = open(os.path.join(dirpath, f), errors="replace").read()
+                    if re.search(r"\boracle\b", text):
+                        offenders.append(os.path.join(dirpath, f))
+    assert not offenders, offenders
+    code = "import sys; import tensorframes_b200; from tensorframes_b200 import ops, distributed, frame; " \
+           "print([m for m in sys.modules if m == 'oracle' or m.startswith('oracle.')])"
+    out = subprocess.run([sys.executable, "-c", code], cwd=ROOT, capture_output=True, text=True, check=True).stdout
+    assert out.strip() == "[]", out
