@@ -31,6 +31,9 @@ int guarded(F&& f) {
   } catch (const std::exception& e) {
     g_last_error = std::string("unexpected: ") + e.what();
     return TFS_ERR_RUNTIME;
+  } catch (...) {                     // nothing may unwind into a C / JNI caller
+    g_last_error = "unexpected: unknown exception";
+    return TFS_ERR_RUNTIME;
   }
 }
 

@@ -270,6 +270,7 @@ Shape drop_lead(const Shape& s) {
   return r;
 }
 Shape with_lead(int64_t n, const Shape& s) {
+  TFS_CHECK(s.rank < TFS_MAX_RANK, TFS_ERR_UNSUPPORTED, "tensor rank above the supported maximum");
   Shape r;
   r.rank = s.rank + 1;
   r.d[0] = n;
@@ -386,6 +387,15 @@ void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<
     plan.shape[size_t(idx)] = plan.batched[size_t(idx)] ? with_lead(plan.n_batch, plan.cshape[size_t(idx)])
                                                         : plan.cshape[size_t(idx)];
     TFS_CHECK(plan.shape[size_t(idx)].rank <= TFS_MAX_RANK, TFS_ERR_UNSUPPORTED, "tensor rank above the supported maximum");
+    // sizes are int64 throughout (the reference stops at Int.MaxValue elements, impl/datatypes.scala:74-78), but a
+    // product of dimensions must still be a number: 2^62 bytes is far beyond any device
+    int64_t elems = 1;
+    bool fits = true;
+    for (int d = 0; d < plan.shape[size_t(idx)].rank && fits; ++d) {
+      if (plan.shape[size_t(idx)].d[d] == 0) { elems = 0; break; }
+      fits = !__builtin_mul_overflow(elems, plan.shape[size_t(idx)].d[d], &elems) && elems < (int64_t(1) << 59);
+    }
+    TFS_CHECK(fits, TFS_ERR_INVALID, "node '" + n.name + "': " + plan.shape[size_t(idx)].str() + " has too many elements");
   }
 
   for (int idx : plan.needed) {

@@ -81,3 +81,24 @@ def test_product_never_touches_the_oracle():
            "print([m for m in sys.modules if m == 'oracle' or m.startswith('oracle.')])"
     out = subprocess.run([sys.executable, "-c", code], cwd=ROOT, capture_output=True, text=True, check=True).stdout
     assert out.strip() == "[]", out
+
+
+def test_resolve_rejects_sizes_that_are_not_numbers():
+    """Dimensions arrive as int64: a product that overflows (or a rank that would) is refused at planning time
+    instead of wrapping into a small allocation."""
+    big = (1 << 32) + 1
+    with dsl.withGraph():
+        x = dsl.placeholder(tfs.DoubleType, dsl.Unknown, dsl.Unknown).named("x")
+        g = dsl.build_graph((x + 1.0).named("z"), dsl.reduce_sum(x, [0]).named("s"))
+    fake = _native.DeviceArray(256, tfs.DoubleType, (big, big))     # resolve never touches the data
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        with pytest.raises(_native.NativeError, match="too many elements"):
+            s.resolve({"x": fake}, ["z"])
+        assert s.resolve({"x": _native.DeviceArray(256, tfs.DoubleType, (big, 0))}, ["s"]) == [(tfs.DoubleType, (0,))]
+    with dsl.withGraph():
+        x = dsl.placeholder(tfs.DoubleType, 1, 1, 1, 1, 1, 1, 2).named("x")
+        g = dsl.build_graph((x + dsl.constant(np.ones((1,) * 8))).named("z"))
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        assert s.resolve({"x": np.zeros((1,) * 6 + (2,))}, ["z"]) == [(tfs.DoubleType, (1,) * 7 + (2,))]
+        with pytest.raises(_native.NativeError, match="rank above the supported maximum"):
+            s.resolve({"x": np.zeros((5,) + (1,) * 6 + (2,))}, ["z"], rows=True)
