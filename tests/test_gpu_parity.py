@@ -1677,3 +1677,91 @@ def test_damaged_graphs_plan_and_run_without_faults(seed):
     with _native.Graph(graphs[2]) as gr, _native.Session(gr, 0) as s:
         (got,) = s.run({"x": x}, ["s"])
     assert np.array_equal(got, x.sum(0))
+
+
+def _carve(arr, off):
+    """Device copy of arr that starts `off` elements past an aligned address: (DeviceArray, whole buffer, view)."""
+    import torch
+    t = torch.from_numpy(np.ascontiguousarray(arr).reshape(-1))
+    buf = torch.zeros(t.numel() + off + 64, dtype=t.dtype, device="cuda")
+    v = buf[off:off + t.numel()]
+    v.copy_(t)
+    return _native.DeviceArray(v.data_ptr(), _native.scalar_type_from_numpy(arr.dtype), arr.shape, owner=buf), buf, v
+
+
+@pytest.mark.parametrize("seed", range(40))
+def test_device_buffers_that_are_only_element_aligned(seed):
+    """Feeds and outputs 0-3 elements past an aligned address (a slice of a caller's larger buffer): the vector and
+    TMA paths must step aside, results stay exact and nothing is written outside the output range."""
+    import torch
+    rng = np.random.default_rng(33000 + seed)
+    dt = list(T)[seed % 4]
+    st = T[dt]
+    n = int(rng.choice([1, 5, 1000, 65537, 300001]))
+    inner = int(rng.choice([1, 2, 3, 8, 64, 100]))
+    off_out = int(rng.integers(0, 4))
+    x = rng.integers(-3, 4, (n, inner)).astype(st.np_dtype)
+    y = rng.integers(-3, 4, (n, inner)).astype(st.np_dtype)
+    with dsl.withGraph():
+        px = dsl.placeholder(st, dsl.Unknown, inner).named("x")
+        py = dsl.placeholder(st, dsl.Unknown, inner).named("y")
+        g = dsl.build_graph(((px + py) * px - 2).named("z"), dsl.reduce_sum(px, [0]).named("c"),
+                            dsl.reduce_max(px, [1]).named("r"), dsl.reduce_min(py, None).named("a"))
+    dx = _carve(x, int(rng.integers(0, 4)))[0]
+    dy = _carve(y, int(rng.integers(0, 4)))[0]
+    want = {"z": (x + y) * x - st.np_dtype.type(2), "c": x.sum(0, dtype=st.np_dtype), "r": x.max(1), "a": np.asarray(y.min())}
+    outs, keep = {}, []
+    for name, w in want.items():
+        d, buf, v = _carve(np.zeros_like(w), off_out)
+        outs[name] = d
+        keep.append((name, buf, v, w))
+    torch.cuda.synchronize()
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        s.run_into({"x": dx, "y": dy}, outs)
+        s.sync()
+    for name, buf, v, w in keep:
+        assert np.array_equal(v.cpu().numpy().reshape(w.shape), w), (name, dt, n, inner, off_out)
+        b = buf.cpu().numpy()
+        assert not b[:off_out].any() and not b[off_out + w.size:].any(), ("wrote outside", name, dt, n, inner, off_out)
+
+
+@pytest.mark.parametrize("trial", range(8))
+def test_matmul_and_aggregate_on_element_aligned_buffers(trial):
+    import torch
+    rng = np.random.default_rng(34000 + trial)
+    off = trial % 4
+    n = [128, 1000, 70000][trial % 3]
+    x = rng.integers(-2, 3, (n, 256)).astype(np.float32)
+    w = rng.integers(-2, 3, (256, 256)).astype(np.float32)
+    b = rng.integers(-2, 3, 256).astype(np.float32)
+    with dsl.withGraph():
+        px = dsl.placeholder(tfs.FloatType, dsl.Unknown, 256).named("x")
+        g = dsl.build_graph((dsl.matmul(px, dsl.constant(w)) + dsl.constant(b)).named("y"))
+    dx = _carve(x, off)[0]
+    dout, _, v = _carve(np.zeros((n, 256), np.float32), (off + 1) % 4)
+    torch.cuda.synchronize()
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        s.run_into({"x": dx}, {"y": dout})
+        s.sync()
+    assert np.array_equal(v.cpu().numpy().reshape(n, 256), x @ w + b)
+
+    dt = list(T)[trial % 4]
+    st = T[dt]
+    n, cell = [1000, 300001][trial % 2], [1, 2, 3, 64][(trial // 2) % 4]
+    keys = rng.integers(0, 50, n).astype(np.int64)
+    x = rng.integers(-3, 4, (n, cell)).astype(st.np_dtype)
+    with dsl.withGraph():
+        p = dsl.placeholder(st, dsl.Unknown, cell).named("x_input")
+        g = dsl.build_graph(dsl.reduce_sum(p, [0]).named("x"))
+    dk = _carve(keys, trial % 2)[0]
+    dx = _carve(x, trial % 4)[0]
+    dok, _, vk = _carve(np.zeros(64, np.int64), 1)
+    dout, _, vo = _carve(np.zeros((64, cell), st.np_dtype), (trial + 1) % 4)
+    torch.cuda.synchronize()
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        ng = s.aggregate_into(dk, {"x_input": dx}, {"x": dout}, dok)
+        s.sync()
+    uk = np.unique(keys)
+    assert ng == len(uk) and np.array_equal(vk.cpu().numpy()[:ng], uk)
+    want = np.stack([x[keys == k].sum(0, dtype=st.np_dtype) for k in uk])
+    assert np.array_equal(vo.cpu().numpy().reshape(64, cell)[:ng], want)
