@@ -844,8 +844,10 @@ bool make_chain(const EltProgram& prog, ChainProgram& ch) {
   }
   ch.dt = uint8_t(dt);
   ch.out_dt = ch.dt;
-  const int64_t lanes = 16 / ((dt & 1) ? 8 : 4);
-  const int64_t span = int64_t(kChainThreads) * kChainVecsPerThread * lanes;
+  // elements per register tile: 16 bytes of the narrower of the input and the chain dtype (ChainGeom in kernels_chain.inc);
+  // the tile span is the same either way
+  const int64_t lanes = 16 / (((dt & 1) && (in.dt & 1)) ? 8 : 4);
+  const int64_t span = int64_t(kChainThreads) * kChainVecsPerThread * (16 / ((dt & 1) ? 8 : 4));
   static const uint8_t kFwd[B_COUNT] = {CH_ADD, CH_SUB, CH_MUL, CH_DIV, CH_MIN, CH_MAX};
   static const uint8_t kRev[B_COUNT] = {CH_ADD, CH_RSUB, CH_MUL, CH_RDIV, CH_RMIN, CH_RMAX};
   static const uint8_t kUn[U_COUNT] = {CH_NEG, CH_RELU, CH_SQUARE, CH_ABS, CH_SQRT, CH_RECIP};

@@ -1191,6 +1191,18 @@ def test_chains_that_start_with_a_cast_bit_exact(src, dst):
         want_a = (one / ((xc * d_np.type(0.5)).astype(d_np) + one).astype(d_np)).astype(d_np)
         assert a.dtype == d_np and a.tobytes() == want_a.tobytes(), n
         assert b.tobytes() == (xc - y).astype(d_np).tobytes(), n
+    # the same with a row vector as the other operand (a [4] vector is two tiles of an 8-byte chain fed by 8-byte
+    # data, one widened tile when the data is 4 bytes wide)
+    for n, width in ((5, 4), (3001, 8), (20_011, 64)):
+        x = (rng.integers(1, 1000, (n, width)) if s_np.kind == "i" else rng.uniform(1, 2, (n, width))).astype(s_np)
+        w = rng.uniform(1, 2, width).astype(d_np)
+        with dsl.withGraph():
+            px = dsl.placeholder(names[src], dsl.Unknown, width).named("x")
+            g = dsl.build_graph((dsl.cast(px, names[dst]) * dsl.constant(w) + 1.0).named("a"))
+        with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+            (a,) = s.run({"x": x}, ["a"])
+        want = ((x.astype(d_np) * w).astype(d_np) + d_np.type(1)).astype(d_np)
+        assert a.tobytes() == want.tobytes(), (n, width)
 
 
 @pytest.mark.parametrize("dt", list(T))
