@@ -15,7 +15,8 @@ Build the instrumented host side next to the regular device objects and run:
 
 Every mutated graph that still imports is planned for every node as a fetch, in block and in row mode, with
 placeholder dimensions drawn from {0, 1, 16, 2^40}.  Any outcome but a sanitizer report is fine.
-Round 1: 36000 mutations and the whole CPU suite ran clean against the instrumented build.
+Round 1: 36000 mutations and the whole CPU suite ran clean against the instrumented build; 20000 more under
+-fsanitize=undefined (same recipe, libubsan preloaded) reported nothing either.
 """
 import os
 import sys
