@@ -22,7 +22,7 @@ the row-major blocks TFDataOps.convert has to assemble from Row objects
 from __future__ import annotations
 
 from dataclasses import dataclass, field as dc_field, replace
-from typing import Any, Dict, Iterable, List, Optional, Sequence, Tuple, Union
+from typing import Any, Dict, List, Optional, Sequence, Tuple, Union
 
 import numpy as np
 

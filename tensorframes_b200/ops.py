@@ -16,7 +16,7 @@ tfs_session_aggregate on the device; nothing in this module computes on data.
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import Dict, List, Optional, Sequence, Tuple
+from typing import Dict, List, Optional, Tuple
 
 import numpy as np
 

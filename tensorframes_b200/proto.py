@@ -8,8 +8,7 @@ Field numbers are those of the .proto files cited in each function.
 """
 from __future__ import annotations
 
-import struct
-from typing import Dict, Iterable, List, Sequence
+from typing import Dict, Iterable, Sequence
 
 import numpy as np
 

@@ -7,7 +7,7 @@ scalar types and their SQL / TF counterparts).
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import Iterable, Optional, Sequence, Tuple
+from typing import Optional, Tuple
 
 import numpy as np
 
