@@ -132,7 +132,10 @@ void tfs_session_free(tfs_session* s);
  * selected; pass a created stream, cudaStreamLegacy or cudaStreamPerThread.  Lets a
  * caller time with events on the stream the kernels run on.
  * The session's own stream is non-blocking: it does not wait for the legacy default stream.  Device-resident feeds
- * must therefore be complete before a call, or be produced on the stream handed over here. */
+ * must therefore be complete before a call, or be produced on the stream handed over here.
+ * Switching streams is ordered: the new stream first waits for the work earlier calls left pending on the old one
+ * (runs share the session's workspace).  A caller-provided stream may be destroyed before the session is freed;
+ * tfs_session_free waits for the session's own pending work through an event, not through that stream handle. */
 int tfs_session_set_stream(tfs_session* s, void* cuda_stream);
 /* Wait for everything enqueued by this session; reports deferred device-side
  * errors (TFS_ERR_RUNTIME) of asynchronous runs. */

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include <atomic>
+#include <mutex>
 
 #include "common.h"
 #include "graph.h"
@@ -18,12 +19,18 @@ inline void cuda_check(cudaError_t e, const char* what) {
 #define TFS_CUDA(call) ::tfs::cuda_check((call), #call)
 
 // Function attributes (the opt-in to more than 48 KB of dynamic shared memory) belong to a device: a launcher sets them
-// the first time it runs on each device.  One flag word per call site; setting twice is harmless, so a lost race is too.
+// the first time it runs on each device.  One instance per call site.  A thread that finds the set-up under way waits
+// for it: returning early would let its launch go out before the attribute is in place and be rejected.
 struct PerDeviceOnce {
-  std::atomic<uint64_t> done{0};
-  bool first(int device) {
+  std::mutex mu;
+  uint64_t done = 0;
+  template <class F>
+  void run(int device, F&& setup) {
     const uint64_t bit = uint64_t(1) << (device & 63);
-    return (done.fetch_or(bit) & bit) == 0;
+    std::lock_guard<std::mutex> lock(mu);
+    if (done & bit) return;
+    setup();
+    done |= bit;        // only after a set-up that did not throw
   }
 };
 

@@ -101,9 +101,13 @@ agg_insert_kernel(const long long* __restrict__ keys, const int64_t n, unsigned 
           if (prev == k[u]) break;
         }
         h[u] = (h[u] + 1) & mask;
-        // a table this crowded means more distinct keys than max_groups: look at the overflow flag now and
-        // then (not on every probe: the whole grid would hammer one address) and give up when it is set
-        if ((++probes & 255u) == 0u && *reinterpret_cast<volatile unsigned int*>(header + 1)) break;
+        // The table has at least 2 * max_groups slots, so a run of more than max_groups occupied slots holding other
+        // keys proves the block has more distinct keys than max_groups: raise the overflow flag from this lane and
+        // stop.  (Waiting for another warp to publish its claims is not enough: with the table full every warp has a
+        // lane stuck in this loop, so nobody would ever get to publish.)  Other lanes look at the flag now and then --
+        // not on every probe: the whole grid would hammer one address -- and give up when it is set.
+        if (++probes > max_groups) { *reinterpret_cast<volatile unsigned int*>(header + 1) = 1u; break; }
+        if ((probes & 255u) == 0u && *reinterpret_cast<volatile unsigned int*>(header + 1)) break;
         c = *reinterpret_cast<volatile unsigned long long*>(slot_key + h[u]);
       }
     }

@@ -143,6 +143,33 @@ __device__ __forceinline__ void load_periodic(const BufRef& b, int64_t elem, int
   }
 }
 
+// Row mode: an operand with one (smaller) cell per row, broadcast inside the row: element i of the block reads
+// b[(i / rowspan) * period + i % period].  Off the roofline path (per-row normalisations under mapRows); plain
+// per-element index arithmetic, 32-bit when the index allows.
+template <int ES, int P>
+__device__ __forceinline__ void load_rowbcast(const BufRef& b, int64_t elem, int nvalid,
+                                              typename Slot<ES>::type (&x)[P]) {
+  using S = typename Slot<ES>::type;
+  const bool wide_elems = ES == 8 && (b.dt & 1);
+#pragma unroll
+  for (int e = 0; e < P; ++e) {
+    S v = 0;
+    if (e < nvalid) {
+      const int64_t i = elem + e;
+      int64_t src;
+      if (((i | b.rowspan) >> 32) == 0) {
+        const unsigned int r = (unsigned int)i / (unsigned int)b.rowspan;
+        src = int64_t(r) * b.period + (b.period == 1 ? 0 : int64_t(((unsigned int)i - r * (unsigned int)b.rowspan) % (unsigned int)b.period));
+      } else {
+        src = (i / b.rowspan) * b.period + (b.period == 1 ? 0 : (i % b.rowspan) % b.period);
+      }
+      if (wide_elems) v = S(__ldg(static_cast<const unsigned long long*>(b.ptr) + src));
+      else v = S(__ldg(static_cast<const unsigned int*>(b.ptr) + src));
+    }
+    x[e] = v;
+  }
+}
+
 template <int ES, int P>
 __device__ __forceinline__ void store_vec(const BufRef& b, int64_t elem, int nvalid,
                                           const typename Slot<ES>::type (&x)[P]) {
@@ -328,6 +355,18 @@ eltwise_kernel(const __grid_constant__ EltProgram prog, const int64_t n) {
           const BufRef b = prog.bufs[in.arg];
 #pragma unroll
           for (int j = 0; j < kJ; ++j) load_periodic<ES, P>(b, elem[j], nvalid[j], x[j]);
+          break;
+        }
+        case C_LOAD_ROW: {
+          const BufRef b = prog.bufs[in.arg];
+#pragma unroll
+          for (int j = 0; j < kJ; ++j) load_rowbcast<ES, P>(b, elem[j], nvalid[j], acc[j]);
+          break;
+        }
+        case C_FETCH_ROW: {
+          const BufRef b = prog.bufs[in.arg];
+#pragma unroll
+          for (int j = 0; j < kJ; ++j) load_rowbcast<ES, P>(b, elem[j], nvalid[j], x[j]);
           break;
         }
         case C_LOAD_IMM:

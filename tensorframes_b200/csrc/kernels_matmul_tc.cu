@@ -639,10 +639,10 @@ int launch_split_weights(const float* w, bool transposed, int64_t K, int64_t N, 
 int launch_matmul_tc(const float* x, const float* w_hi, const float* w_lo, const float* bias, float* out, int64_t M,
                      int64_t N, int64_t K, const DeviceInfo& dev, cudaStream_t stream) {
   static PerDeviceOnce attr;
-  if (attr.first(dev.device)) {
+  attr.run(dev.device, [] {
     TFS_CUDA(cudaFuncSetAttribute(matmul_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kSmemBytes)));
     TFS_CUDA(cudaFuncSetAttribute(matmul_tc_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kSmemBytes2)));
-  }
+  });
   static const bool single_cta = [] {
     const char* impl = std::getenv("TFS_MATMUL_IMPL");   // "tc1": the single-CTA kernel, kept for A/B measurements
     return impl != nullptr && std::string(impl) == "tc1";

@@ -429,9 +429,10 @@ int launch_axis0_t(const T* in, int64_t outer, int64_t inner, T* out, void* scra
       // TMA-staged: one persistent CTA per SM
       const size_t dyn = size_t(kStages) * size_t(chunk_vecs) * 16;
       static PerDeviceOnce attr;
-      if (attr.first(dev.device))
+      attr.run(dev.device, [] {
         TFS_CUDA(cudaFuncSetAttribute(reduce_axis0_tma_kernel<T, OP, PV>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       int(size_t(kStages) * kMaxThreads * kVecPerThread * 16)));
+      });
       const int64_t n_chunks = (n_vec + chunk_vecs - 1) / chunk_vecs;
       int grid = int(std::max<int64_t>(1, std::min<int64_t>(dev.sm_count, n_chunks)));
       reduce_axis0_tma_kernel<T, OP, PV><<<grid, g.threads, dyn, stream>>>(in, n, int(inner), g.L, g.q, partials, counter, out);

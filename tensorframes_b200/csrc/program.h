@@ -48,6 +48,11 @@ enum : uint8_t {
   C_UNARY = 107,
   // acc <- cast<to>(acc as from);              code = C_CAST + from * 4 + to
   C_CAST = 131,
+  // row mode: a per-row operand smaller than the cell (x / reduce_sum(x) under mapRows).  Element `flat` of the
+  // [n, cell...] block reads bufs[arg][(flat / rowspan) * period + flat % period]: rowspan = elements per row of the
+  // block, period = elements per row of the operand (1 for a per-row scalar).
+  C_LOAD_ROW = 147,
+  C_FETCH_ROW = 148,
 };
 
 struct Instr {
@@ -59,9 +64,10 @@ struct Instr {
 
 struct BufRef {
   void* ptr;
-  int64_t period;  // C_*_PER: number of elements in the small tensor
+  int64_t period;  // C_*_PER: number of elements in the small tensor; C_*_ROW: elements per row of the operand
   int32_t dt;      // dtype index of the buffer's elements
   int32_t pad;
+  int64_t rowspan; // C_*_ROW: elements per row of the block being iterated
 };
 
 struct EltProgram {

@@ -46,6 +46,11 @@ bool is_device_pointer(const void* p) {
   return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
 }
 
+bool matmul_force_simt() {
+  static const bool v = [] { const char* e = std::getenv("TFS_MATMUL_IMPL"); return e && std::string(e) == "simt"; }();
+  return v;
+}
+
 bool is_pinned_host_pointer(const void* p) {
   if (p == nullptr) return false;
   cudaPointerAttributes a{};
@@ -131,8 +136,10 @@ Session::Session(const Graph& g, int device) : g_(g) { dev_.device = device; }
 Session::~Session() {
   if (!device_ready_) return;
   cudaSetDevice(dev_.device);
-  cudaStreamSynchronize(stream_);
-  if (stream_ != own_stream_) cudaStreamSynchronize(own_stream_);
+  // everything this session enqueued, on whichever stream: the event outlives a caller-provided stream that has
+  // been destroyed in the meantime, the stream handle itself would not
+  if (work_event_) cudaEventSynchronize(work_event_);
+  cudaStreamSynchronize(own_stream_);
   for (auto& kv : const_dev_) cudaFree(kv.second);
   for (auto& kv : tc_weights_) { cudaFree(kv.second.first); cudaFree(kv.second.second); }
   DevicePool& pool = g_pools[dev_.device];
@@ -155,6 +162,7 @@ Session::~Session() {
   for (int k = 0; k < 2; ++k)
     if (pipe_stream_[k]) cudaStreamDestroy(pipe_stream_[k]);
   if (pipe_event_) cudaEventDestroy(pipe_event_);
+  if (work_event_) cudaEventDestroy(work_event_);
   if (own_stream_) cudaStreamDestroy(own_stream_);
 }
 
@@ -184,11 +192,24 @@ void Session::ensure_device() {
                 ".x; this library is built for sm_100a (B200) only");
   dev_.sm_count = pool.sm_count;
   TFS_CUDA(cudaStreamCreateWithFlags(&own_stream_, cudaStreamNonBlocking));
+  TFS_CUDA(cudaEventCreateWithFlags(&work_event_, cudaEventDisableTiming));
   if (!stream_) stream_ = own_stream_;
   const ErrSlot slot = borrow_err_slot(pool);
   err_flag_ = slot.dev;
   err_host_ = slot.host;
   device_ready_ = true;
+}
+
+// Runs that only enqueue (device-resident feeds and fetches) return with work pending, and every run shares the
+// workspace, the reduction scratch and the error flag: a new stream first waits for what the old one was given.
+void Session::set_stream(cudaStream_t s) {
+  cudaStream_t next = s ? s : own_stream_;
+  if (device_ready_ && next != nullptr && next != stream_ && work_event_) TFS_CUDA(cudaStreamWaitEvent(next, work_event_, 0));
+  stream_ = next;
+}
+
+void Session::mark_work() {
+  if (work_event_) TFS_CUDA(cudaEventRecord(work_event_, stream_));
 }
 
 void Session::sync() {
@@ -591,6 +612,9 @@ struct GroupCompiler {
   const std::vector<void*>& dev_ptr;
   const std::vector<char>& materialize;
   const Step& step;
+  // row mode (mapRows): which nodes carry the row dimension in front, and how many rows there are
+  const std::vector<char>* batched = nullptr;
+  int64_t n_batch = 0;
   EltProgram prog{};
   bool wide = false;
   std::set<int> members;
@@ -600,7 +624,7 @@ struct GroupCompiler {
   bool tmp_busy[kMaxTmp] = {false, false, false, false};
 
   // where an operand comes from
-  struct Source { enum Kind { BUF, PERIODIC, IMM, TMP } kind; int arg = 0; uint64_t imm = 0; };
+  struct Source { enum Kind { BUF, PERIODIC, ROWBCAST, IMM, TMP } kind; int arg = 0; uint64_t imm = 0; };
 
   GroupCompiler(const Graph& g_, const std::vector<Shape>& sh, const std::vector<void*>& dp,
                 const std::vector<char>& mat, const Step& st)
@@ -635,20 +659,21 @@ struct GroupCompiler {
       if (!tmp_busy[t]) { tmp_busy[t] = true; return t; }
     fail(TFS_ERR_UNSUPPORTED, "element-wise expression needs more than " + std::to_string(kMaxTmp) + " live temporaries");
   }
-  int buffer(int n, int64_t period) {
+  int buffer(int n, int64_t period, int64_t rowspan = 0) {
     void* p = dev_ptr[size_t(n)];
     TFS_CHECK(p != nullptr, TFS_ERR_INVALID, "internal: no device buffer for node '" + node(n).name + "'");
     for (int i = 0; i < prog.n_bufs; ++i)
-      if (prog.bufs[i].ptr == p && prog.bufs[i].period == period) return i;
+      if (prog.bufs[i].ptr == p && prog.bufs[i].period == period && prog.bufs[i].rowspan == rowspan) return i;
     TFS_CHECK(prog.n_bufs < kMaxBufs, TFS_ERR_UNSUPPORTED,
               "element-wise group touches more than " + std::to_string(kMaxBufs) + " tensors");
     BufRef& b = prog.bufs[prog.n_bufs];
     b.ptr = p;
     b.period = period;
+    b.rowspan = rowspan;
     b.dt = di(n);
     // periodic operands: 1 = a vector of the kernel's width never wraps and is aligned (see load_periodic)
     const int64_t lanes = wide ? 2 : 4;
-    b.pad = (period > 0 && period % lanes == 0 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) ? 1 : 0;
+    b.pad = (rowspan == 0 && period > 0 && period % lanes == 0 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) ? 1 : 0;
     return prog.n_bufs++;
   }
 
@@ -677,6 +702,24 @@ struct GroupCompiler {
       src.arg = buffer(o, 0);
       return src;
     }
+    // Row mode: an operand that has its own value per row (a reduction of the cell, a smaller fed cell) broadcasts
+    // INSIDE each row.  Its shape already carries the row dimension, so matching it against the trailing dimensions
+    // of the block below would be wrong -- and would silently pass whenever the row count equals a cell dimension.
+    if (batched != nullptr && (*batched)[size_t(o)]) {
+      TFS_CHECK(n_batch > 0 && os.rank >= 1 && it.rank >= 1 && os.d[0] == n_batch && it.d[0] == n_batch, TFS_ERR_UNSUPPORTED,
+                "row mode: operand '" + no.name + "' " + os.str() + " does not line up with the rows of " + it.str());
+      int lead = 1;
+      while (lead < os.rank && os.d[lead] == 1) ++lead;
+      const int k = os.rank - lead;
+      bool ok = k <= it.rank - 1;
+      for (int i = 0; ok && i < k; ++i) ok = os.d[lead + i] == it.d[it.rank - k + i];
+      TFS_CHECK(ok, TFS_ERR_UNSUPPORTED,
+                "broadcasting the per-row value " + os.str() + " against " + it.str() + " (operand '" + no.name +
+                    "') is not supported: only scalars and trailing-dimension broadcasts within a row are");
+      src.kind = Source::ROWBCAST;
+      src.arg = buffer(o, on / n_batch, n / n_batch);
+      return src;
+    }
     // row broadcast: operand dims (leading 1s dropped) must equal the trailing dims of the block
     int lead = 0;
     while (lead < os.rank && os.d[lead] == 1) ++lead;
@@ -702,6 +745,7 @@ struct GroupCompiler {
     switch (s.kind) {
       case Source::BUF: emit(C_LOAD_BUF, s.arg); break;
       case Source::PERIODIC: emit(C_LOAD_PER, s.arg); break;
+      case Source::ROWBCAST: emit(C_LOAD_ROW, s.arg); break;
       case Source::IMM: emit(C_LOAD_IMM, 0, s.imm); break;
       case Source::TMP: emit(C_LOAD_TMP, s.arg); break;
     }
@@ -739,6 +783,7 @@ struct GroupCompiler {
     switch (s.kind) {
       case Source::BUF: emit(C_FETCH_BUF, s.arg); break;
       case Source::PERIODIC: emit(C_FETCH_PER, s.arg); break;
+      case Source::ROWBCAST: emit(C_FETCH_ROW, s.arg); break;
       default: emit(C_FETCH_TMP, s.arg); break;
     }
     emit(C_BIN_X + sub * 8 + dt * 2 + sw);
@@ -1020,6 +1065,7 @@ void Session::exec_step(const Plan& plan, size_t step_index, std::vector<void*>&
     case Step::ELT: {
       if (s.shape.numel() == 0) break;
       GroupCompiler gc(g_, plan.shape, dev_ptr, plan.materialize, s);
+      if (plan.rows) { gc.batched = &plan.batched; gc.n_batch = plan.n_batch; }
       gc.build(err_flag_);
       if (gc.prog.n_instr == 0) break;          // every member is needed for its shape only
       ChainProgram chain;
@@ -1154,8 +1200,7 @@ void Session::exec_step(const Plan& plan, size_t step_index, std::vector<void*>&
       void* out = dev_ptr[size_t(s.out_node >= 0 ? s.out_node : mm)];
       if (M * Nc == 0) break;
       const bool const_b = g_.nodes[size_t(n.in[1])].cls == OpClass::Const;
-      static const bool force_simt = [] { const char* e = std::getenv("TFS_MATMUL_IMPL"); return e && std::string(e) == "simt"; }();
-      if (n.dtype == TFS_FLOAT && !force_simt && const_b && matmul_tc_supported(a, out, M, Nc, K, n.transpose_a)) {
+      if (n.dtype == TFS_FLOAT && !matmul_force_simt() && const_b && matmul_tc_supported(a, out, M, Nc, K, n.transpose_a)) {
         auto it = ensure_tc_weights(n, static_cast<const float*>(b), Nc, K, stream);
         launches_ += launch_matmul_tc(static_cast<const float*>(a), it->second.first, it->second.second, static_cast<const float*>(bias),
                                       static_cast<float*>(out), M, Nc, K, dev_, stream);
@@ -1222,16 +1267,25 @@ bool Session::run_pipelined(const std::vector<TensorArg>& feeds, const std::vect
     max_row_bytes = std::max(max_row_bytes, row_bytes(f));
   }
   if (total_bytes < 4 * kChunkBytes || max_row_bytes == 0) return false;   // small blocks: one shot is as good
+  // every other operand of the group must be independent of the row count: a constant (or a value computed from
+  // constants) as large as the whole block lines up with the block's rows and cannot be cut along with them
+  if (!is_mm) {
+    std::set<int> members(st.nodes.begin(), st.nodes.end());
+    for (int m : st.nodes)
+      for (int o : elt_operands(g_.nodes[size_t(m)])) {
+        if (members.count(o) || g_.nodes[size_t(o)].cls == OpClass::Placeholder) continue;
+        const int64_t on = plan.shape[size_t(o)].numel();
+        if (on > 1 && on == st.shape.numel()) return false;
+      }
+  }
 
   int64_t chunk_rows = int64_t(kChunkBytes / max_row_bytes);
   chunk_rows = std::max<int64_t>(16, chunk_rows / 16 * 16);    // keeps every chunk start 16-byte aligned
   const int64_t n_chunks = (n + chunk_rows - 1) / chunk_rows;
 
-  if (!pipe_stream_[0]) {
-    for (int k = 0; k < 2; ++k) TFS_CUDA(cudaStreamCreateWithFlags(&pipe_stream_[k], cudaStreamNonBlocking));
-    TFS_CUDA(cudaEventCreateWithFlags(&pipe_event_, cudaEventDisableTiming));
-  }
-  // chunk plans: one for a full chunk, one for the last (shorter) chunk
+  // chunk plans: one for a full chunk, one for the last (shorter) chunk.  Planned before anything is allocated or
+  // enqueued: a graph that does not plan for a chunk of rows (an operand tied to the row count in a way the test
+  // above does not see) goes through the one-shot path instead of failing here.
   std::vector<std::string> names;
   for (auto& f : fetches) names.push_back(f.name);
   auto chunk_feeds = [&](int64_t rows_in_chunk) {
@@ -1240,10 +1294,20 @@ bool Session::run_pipelined(const std::vector<TensorArg>& feeds, const std::vect
     return cf;
   };
   Plan full_plan, tail_plan;
-  build_plan(chunk_feeds(std::min(chunk_rows, n)), names, full_plan, false);
   const int64_t tail_rows = n - (n_chunks - 1) * chunk_rows;
   const bool has_tail = tail_rows != std::min(chunk_rows, n);
-  if (has_tail) build_plan(chunk_feeds(tail_rows), names, tail_plan, false);
+  try {
+    build_plan(chunk_feeds(std::min(chunk_rows, n)), names, full_plan, false);
+    if (has_tail) build_plan(chunk_feeds(tail_rows), names, tail_plan, false);
+  } catch (const Error&) {
+    return false;
+  }
+  if (full_plan.steps.size() != 1 || (has_tail && tail_plan.steps.size() != 1)) return false;
+
+  if (!pipe_stream_[0]) {
+    for (int k = 0; k < 2; ++k) TFS_CUDA(cudaStreamCreateWithFlags(&pipe_stream_[k], cudaStreamNonBlocking));
+    TFS_CUDA(cudaEventCreateWithFlags(&pipe_event_, cudaEventDisableTiming));
+  }
 
   // workspace: two slots, each holding one chunk of every fed column and every fetched column
   const size_t N = g_.nodes.size();
@@ -1265,10 +1329,13 @@ bool Session::run_pipelined(const std::vector<TensorArg>& feeds, const std::vect
   if (is_mm) {
     // the tf32 hi/lo split of the constant matrix is cached per session: make sure it exists (on the session
     // stream) before two pipeline streams would both try to create it
+    // -- under the same conditions as exec_step takes the tensor-core path (workspace chunks are 256-byte aligned)
     const Node& mm = g_.nodes[size_t(st.nodes[0])];
     const Shape& os = plan.shape[size_t(st.nodes[0])];
     const Shape& as = plan.shape[size_t(mm.in[0])];
-    ensure_tc_weights(mm, static_cast<const float*>(const_ptr[size_t(mm.in[1])]), os.d[1], as.d[1], stream_);
+    if (mm.dtype == TFS_FLOAT && !matmul_force_simt() &&
+        matmul_tc_supported(ws_, ws_, std::min(chunk_rows, n), os.d[1], as.d[1], mm.transpose_a))
+      ensure_tc_weights(mm, static_cast<const float*>(const_ptr[size_t(mm.in[1])]), os.d[1], as.d[1], stream_);
   }
   // everything enqueued so far on the session stream (constant uploads) precedes the pipeline
   TFS_CUDA(cudaEventRecord(pipe_event_, stream_));
@@ -1335,7 +1402,7 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
                     fetches[i].shape.str());
   }
   ensure_device();
-  if (!rows && run_pipelined(feeds, fetches, plan)) return;
+  if (!rows && run_pipelined(feeds, fetches, plan)) { mark_work(); return; }
   const size_t N = g_.nodes.size();
   std::vector<void*> dev_ptr(N, nullptr);
   auto nbytes = [&](int idx) { return size_t(plan.shape[size_t(idx)].numel()) * size_t(dtype_size(g_.nodes[size_t(idx)].dtype)); };
@@ -1427,8 +1494,8 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
       prog.err = err_flag_;
       const int di = dtype_index(g_.nodes[size_t(idx)].dtype);
       prog.n_bufs = 2;
-      prog.bufs[0] = BufRef{src, plan.shape[size_t(idx)].numel(), di, 0};
-      prog.bufs[1] = BufRef{dst, 0, di, 0};
+      prog.bufs[0] = BufRef{src, plan.shape[size_t(idx)].numel(), di, 0, 0};
+      prog.bufs[1] = BufRef{dst, 0, di, 0, 0};
       prog.n_instr = 2;
       prog.ins[0] = Instr{};
       prog.ins[0].code = C_LOAD_PER;
@@ -1450,6 +1517,7 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
   }
   // results on the host: the caller may read them as soon as this returns, so a raised flag must fail the call now
   // (device-resident results are checked by tfs_session_sync); graphs that cannot raise skip the round trip
+  mark_work();
   if (any_host) {
     if (plan.may_raise) check_device_error();
     else TFS_CUDA(cudaStreamSynchronize(stream_));     // pinned destinations are written asynchronously

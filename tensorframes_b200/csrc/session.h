@@ -28,7 +28,7 @@ class Session {
   Session(const Session&) = delete;
   Session& operator=(const Session&) = delete;
 
-  void set_stream(cudaStream_t s) { stream_ = s ? s : own_stream_; }
+  void set_stream(cudaStream_t s);
   void sync();
   int64_t launches() const { return launches_; }
 
@@ -55,6 +55,7 @@ class Session {
   void copy_out(void* dst_host, const void* src_dev, size_t bytes);    // device -> host on stream_
   void reserve_workspace(size_t bytes);
   void check_device_error();
+  void mark_work();
 
   Graph g_;
   DeviceInfo dev_;
@@ -63,6 +64,7 @@ class Session {
   cudaStream_t stream_ = nullptr;
   cudaStream_t pipe_stream_[2] = {nullptr, nullptr};   // host ingest pipeline (chunked H2D / kernel / D2H)
   cudaEvent_t pipe_event_ = nullptr;
+  cudaEvent_t work_event_ = nullptr;   // recorded after everything a call enqueues: orders a stream switch and the destructor
   char* ws_ = nullptr;
   size_t ws_cap_ = 0;
   void* red_scratch_ = nullptr;

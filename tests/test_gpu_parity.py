@@ -558,6 +558,22 @@ def test_aggregate_config4_shape_and_group_overflow():
         assert np.all(np.abs(o_[order].astype(np.float64) - want.astype(np.float64)) <= 1e-5 * absum)
 
 
+@pytest.mark.timeout(120)
+def test_aggregate_far_more_keys_than_the_table_holds():
+    """A block with far more distinct keys than max_groups fills the whole hash table (1024 slots for max_groups = 100):
+    every warp then has a lane probing a full table.  The call must come back with the overflow error, not spin."""
+    n = 1_000_000
+    keys = (np.arange(n, dtype=np.int64) * 0x9E3779B97F4A7C15 + 7).astype(np.int64)      # all distinct
+    v = np.ones((n, 4), dtype=np.float32)
+    g = aggregate_graph(tfs.FloatType, (4,), "sum")
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        for mg in (100, 1000, 5000):
+            with pytest.raises(_native.NativeError, match="more than max_groups"):
+                s.aggregate(keys, {"v_input": v}, ["v"], max_groups=mg)
+        got_keys, (got,) = s.aggregate(keys[:5000], {"v_input": v[:5000]}, ["v"], max_groups=5000)    # session still usable
+    assert np.array_equal(np.sort(got_keys), np.sort(keys[:5000])) and np.all(got == 1.0)
+
+
 def test_aggregate_rejects_non_reducer_graphs():
     with dsl.withGraph():
         p = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x_input")
@@ -811,14 +827,50 @@ def test_reduce_rows_tree_matches_fold(n):
     assert b == xf.max()
 
 
-def test_row_mode_rejects_what_it_cannot_batch():
+def test_row_mode_per_row_operands_broadcast_inside_the_row():
+    """A per-row value smaller than the cell (a scalar cell next to a vector cell, a reduction of the cell) broadcasts
+    inside its own row -- also when the number of rows equals a cell dimension, where matching the batched operand
+    against the trailing dimensions of the block would silently pick s[j] instead of s[i]."""
+    rng = np.random.default_rng(63)
     with dsl.withGraph():
         p = dsl.placeholder(tfs.DoubleType).named("x")
         q = dsl.placeholder(tfs.DoubleType, 3).named("y")
         g = dsl.build_graph((p + q).named("z"))          # scalar cell combined with a vector cell
     with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        for n in (3, 4, 1000):                            # n == 3: the row count equals the cell size
+            x, y = rng.uniform(-1, 1, n), rng.uniform(-1, 1, (n, 3))
+            (z,) = s.run({"x": x, "y": y}, ["z"], rows=True)
+            assert_same(z, x[:, None] + y)
+    with dsl.withGraph():
+        p = dsl.placeholder(tfs.FloatType, 128).named("x")
+        m = dsl.placeholder(tfs.FloatType, 2, 128).named("m")
+        outs = [dsl.div(p, dsl.reduce_sum(p, [0])).named("norm"),                 # per-row scalar against the cell
+                (m - p).named("centered"),                                          # per-row vector against a matrix cell
+                (m * dsl.reduce_max(m, None)).named("scaled")]
+        g = dsl.build_graph(*outs)
+    names = ["norm", "centered", "scaled"]
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        for n in (128, 2, 77):                            # 128 rows of 128-wide cells; 2 rows of [2, 128] cells
+            x = rng.uniform(1, 2, (n, 128)).astype(np.float32)
+            mm = rng.uniform(-1, 1, (n, 2, 128)).astype(np.float32)
+            got = s.run({"x": x, "m": mm}, names, rows=True)
+            for i in (0, n // 2, n - 1):
+                want = tf_ops.evaluate(g, {"x": x[i], "m": mm[i]}, names)
+                assert_same(got[1][i], want[1])
+                assert_same(got[2][i], want[2])
+                # the row sum differs from the oracle's by summation order only
+                assert np.allclose(got[0][i], want[0], rtol=1e-5, atol=0)
+            assert np.allclose(got[0].sum(axis=1), 1.0, rtol=1e-5)
+
+
+def test_row_mode_rejects_what_it_cannot_batch():
+    with dsl.withGraph():
+        p = dsl.placeholder(tfs.DoubleType, 2, 1).named("x")
+        q = dsl.placeholder(tfs.DoubleType, 2, 3).named("y")
+        g = dsl.build_graph((p + q).named("z"))          # a [2, 1] cell against a [2, 3] cell: a middle-dimension broadcast
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
         with pytest.raises(_native.UnsupportedError, match="broadcasting"):
-            s.run({"x": np.zeros(4), "y": np.zeros((4, 3))}, ["z"], rows=True)
+            s.run({"x": np.zeros((4, 2, 1)), "y": np.zeros((4, 2, 3))}, ["z"], rows=True)
 
 
 # ---- host ingest pipeline (K0): pinned host blocks, chunked H2D / kernel / D2H ------------------------------

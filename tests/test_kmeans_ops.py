@@ -283,6 +283,24 @@ def test_segment_ids_out_of_range_raise():
 
 
 @pytest.mark.gpu
+@pytest.mark.timeout(120)
+def test_many_distinct_bad_segment_ids_raise():
+    """200000 distinct ids against 3 segments: far more keys than the (1024-slot) table of the keyed pass holds.
+    The run must fail with the out-of-range error instead of probing a full table for ever."""
+    with dsl.withGraph():
+        p = dsl.placeholder(tfs.FloatType, Unknown, 2).named("a")
+        s = dsl.placeholder(tfs.LongType, Unknown).named("ids")
+        g = dsl.build_graph(dsl.unsorted_segment_sum(p, s, 3).named("seg"))
+    n = 200_000
+    a = np.ones((n, 2), dtype=np.float32)
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as sess:
+        with pytest.raises(_native.NativeError, match="out of range"):
+            sess.run({"a": a, "ids": np.arange(n, dtype=np.int64) + 5}, ["seg"])
+        (ok,) = sess.run({"a": a, "ids": (np.arange(n) % 3).astype(np.int64)}, ["seg"])
+        assert ok[:, 0].tolist() == [float(len(range(k, n, 3))) for k in range(3)]
+
+
+@pytest.mark.gpu
 def test_float64_matmul_with_transposes():
     rng = np.random.default_rng(15)
     a = rng.uniform(-1, 1, (300, 17))
