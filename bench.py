@@ -4,22 +4,35 @@
     python bench.py --gpus N --steps K --warmup W            (N > 1: launched under torchrun)
     python bench.py --impl reference --gpus N --steps K --warmup W
 
-Headline workload (BASELINE.json configs[1], name in config.workload): reduce_blocks with
-y = reduce_sum(y_input, [0]) and z = reduce_min(z_input, [0]) over two analysed
-DoubleType[?,2] columns of 100M synthetic rows per GPU.  A "step" is one pass of that block
-through the reducer graph (N > 1: one partition per GPU, weak scaling, plus the exchange of the
-cell-sized partial rows and the merge run).
+The default run measures every BASELINE.json performance config at its stated size, one after the other, and
+prints ONE JSON line.  The top-level keys are the headline workload, BASELINE configs[1]:
 
-  value      rows/s, whole job, inputs resident in HBM, timed with CUDA events on the launch stream
-  e2e        the same metric through the C ABI with HOST (pinned) column buffers: H2D of the block
-             and D2H of the result row are inside the timed region
-  roofline   the dominant kernel (reduce_axis0_tma_kernel) against the measured HBM peak
-  cpu_baseline / --impl reference   oracle/cpu_ref.c, the restatement of the reference's
-             per-block algorithm, on the host cores (the real Spark + TF-CPU stack is not installable here)
+  c2         reduce_blocks, y = reduce_sum(y_input, [0]) and z = reduce_min(z_input, [0]) over two analysed
+             DoubleType[?,2] columns of 1e8 rows per GPU                                  (K2, reduce_axis0_tma_kernel)
 
---workload c3 | c4 | c5 measure the other BASELINE configs the same way: map_blocks on the fused chain (chain_kernel),
-the keyed aggregate (insert / sort / gather passes) and the tcgen05 MatMul (matmul_tc_pair_kernel; roofline.bound =
-"tensor").  With N > 1 the reduce exchange of a block runs on a second stream and overlaps the next block's kernels.
+and `configs` holds one sub-record each, with the same keys (value, ms_per_step, roofline, e2e, cpu_baseline, parity):
+
+  c3         map_blocks, cast_f32(max(x*1.5 + 0.25, 0)) on a 1e9-row float64 column       (K1, chain_kernel)
+  reduce_1b  reduce_blocks, reduce_sum + reduce_min on the same 1e9-row float64 column   (K2)
+  c4         aggregate, groupBy int64 key (1e6 distinct), reduce_sum FloatType[?,64], 5e8 rows   (K3)
+  c5         map_blocks, MatMul FloatType[?,256] x 256x256 + bias, 2^24 rows              (K4, tcgen05)
+
+A "step" is one pass of the block through the graph (N > 1: one partition per GPU, weak scaling, plus the path's
+exchange: the combine of the partial rows for reduce_blocks, the key-owner exchange + merge for aggregate).
+
+  value      rows/s, whole job, inputs resident in HBM, timed with CUDA events on the launch stream, max over ranks
+  e2e        the same metric through the C ABI with HOST (pinned) column buffers: H2D of the block and D2H of the
+             result are inside the timed region
+  roofline   the dominant kernel against the measured HBM peak (tensor peak for c5)
+  cpu_baseline / --impl reference   oracle/cpu_ref.c, the restatement of the reference's per-block algorithm, on the
+             host cores (the real Spark + TF-CPU stack is not installable here); the cpu_baseline leg also checks the
+             GPU result of a prefix block against the oracle on the same generated values
+
+Inputs come from one counter-based generator: value(seed, index) = f(splitmix64(seed ^ index)), written
+twice below -- numpy for the host legs, torch integer ops for the device -- so that the CPU arm and the GPU arm see the
+same numbers (tests/test_bench_generator.py pins the two against each other).
+
+--workload c2|c3|reduce_1b|c4|c5 runs one workload alone (profiling; its record is the line).
 """
 import argparse
 import json
@@ -34,13 +47,27 @@ if ROOT not in sys.path:
 
 import numpy as np  # noqa: E402
 
-ROWS_C2 = 100_000_000
-ROWS_C3 = 1_000_000_000
-ROWS_C4 = 250_000_000          # BASELINE config 4 names 5e8 rows (132 GB); see config.workload
+ROWS = {"c2": 100_000_000, "c3": 1_000_000_000, "reduce_1b": 1_000_000_000, "c4": 500_000_000, "c5": 1 << 24}
 KEYS_C4 = 1_000_000
-ROWS_C5 = 1 << 24               # BASELINE config 5: FloatType[?,256] x 256x256 + bias, 2^24 rows per GPU
-ALG_BYTES_PER_ROW = {"c2": 32, "c3": 12, "c4": 264, "c5": 2048}
+ALG_BYTES_PER_ROW = {"c2": 32, "c3": 12, "reduce_1b": 16, "c4": 264, "c5": 2048}
+FLOP_PER_ROW_C5 = 131072.0
 FALLBACK_HBM_GBS = 6650.0                   # /opt/skills/guides/B200_PROFILING.md
+ALL = ["c2", "c3", "reduce_1b", "c5", "c4"]     # run order: the largest block last
+METRIC = {
+    "c2": "rows/s for reduceBlocks (reduce_sum + reduce_min over DoubleType[?,2])",
+    "c3": "rows/s for mapBlocks (fused x*a+b, max(.,0), cast f32 on a float64 column)",
+    "reduce_1b": "rows/s for reduceBlocks (reduce_sum + reduce_min over a float64 column)",
+    "c4": "rows/s for aggregate (groupBy int64 key, reduce_sum over FloatType[?,64])",
+    "c5": "rows/s for mapBlocks (MatMul FloatType[?,256] x 256x256 + bias)",
+}
+WORKLOAD = {
+    "c2": "BASELINE configs[1]: reduce_blocks reduce_sum+reduce_min, DoubleType[?,2], ",
+    "c3": "BASELINE configs[2]: map_blocks fused chain cast_f32(max(x*1.5+0.25,0)), float64 column, ",
+    "reduce_1b": "north_star target: reduce_blocks reduce_sum+reduce_min on a float64 column, ",
+    "c4": "BASELINE configs[3]: aggregate groupBy int64 key (1e6 distinct), reduce_sum FloatType[?,64], ",
+    "c5": "BASELINE configs[4]: map_blocks matmul FloatType[?,256] x 256x256 + bias, ",
+}
+DTYPE = {"c2": "f64", "c3": "f64", "reduce_1b": "f64", "c4": "f32", "c5": "f32 (3xTF32 on tcgen05, fp32 accumulate)"}
 
 
 def env_int(name, default):
@@ -50,37 +77,205 @@ def env_int(name, default):
         return default
 
 
-def hbm_peak():
-    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+def peaks():
     try:
-        with open(path) as f:
-            return float(json.load(f)["hbm_gbs"]), "measured"
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)
     except Exception:
-        return FALLBACK_HBM_GBS, "fallback"
+        return {}
 
 
-def ncu_traffic(workload, rows=None):
-    """Per-launch DRAM bytes of the dominant kernel from the committed ncu capture (profiles/traffic.json),
-    scaled by rows when this run's block differs from the captured one; None when there is no capture."""
+def hbm_peak():
+    p = peaks()
+    if "hbm_gbs" in p:
+        return float(p["hbm_gbs"]), "measured"
+    return FALLBACK_HBM_GBS, "fallback"
+
+
+def ncu_traffic(workload, rows):
+    """Per-launch DRAM bytes of the dominant kernel from the committed ncu capture (profiles/traffic.json), scaled by
+    rows when this run's block differs from the captured one.  Returns (bytes or None, source): a capture whose
+    summary file is no longer in profiles/ is refused rather than quoted."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             e = json.load(f).get(workload)
         if not e:
-            return None
-        if rows is None or rows == e["rows"]:
-            return e["bytes"]
-        return e["bytes"] * rows / e["rows"]
+            return None, None
+        if not os.path.exists(os.path.join(ROOT, "profiles", e["source"])):
+            return None, f"{e['source']} (missing: not quoted)"
+        return e["bytes"] * rows / e["rows"], f"profiles/{e['source']} ({e['kernel']}, captured at {e['rows']} rows)"
     except Exception:
-        return None
+        return None, None
 
 
 def ncu_extra(workload, key):
-    """Another figure of the committed ncu capture of the workload's dominant kernel (profiles/traffic.json), or None."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             return json.load(f).get(workload, {}).get(key)
     except Exception:
         return None
+
+
+# ---------------------------------------------------------------------------------------------
+# The synthetic-column generator (SURVEY.md §8(d)), host and device versions of the same arithmetic.
+# ---------------------------------------------------------------------------------------------
+GAMMA, M1, M2 = 0x9E3779B97F4A7C15, 0xBF58476D1CE4E5B9, 0x94D049BB133111EB
+MASK64 = (1 << 64) - 1
+
+
+def _mix_py(x):
+    x = (x + GAMMA) & MASK64
+    x = ((x ^ (x >> 30)) * M1) & MASK64
+    x = ((x ^ (x >> 27)) * M2) & MASK64
+    return x ^ (x >> 31)
+
+
+def seed_const(seed):
+    return _mix_py(seed * 0x632BE59BD9B4E019 & MASK64)
+
+
+def mix_np(x):
+    """splitmix64 of a uint64 array."""
+    with np.errstate(over="ignore"):
+        x = x + np.uint64(GAMMA)
+        x = (x ^ (x >> np.uint64(30))) * np.uint64(M1)
+        x = (x ^ (x >> np.uint64(27))) * np.uint64(M2)
+        return x ^ (x >> np.uint64(31))
+
+
+def _i64(c):
+    return c - (1 << 64) if c >= (1 << 63) else c
+
+
+def mix_torch(x):
+    """splitmix64 of an int64 tensor holding the bits of a uint64: wrapping multiplies, logical shifts by masking."""
+    def lsr(v, k):
+        return (v >> k) & ((1 << (64 - k)) - 1)
+    x = x + _i64(GAMMA)
+    x = (x ^ lsr(x, 30)) * _i64(M1)
+    x = (x ^ lsr(x, 27)) * _i64(M2)
+    return x ^ lsr(x, 31)
+
+
+class HostGen:
+    """numpy side.  idx: uint64 array of element indices."""
+
+    @staticmethod
+    def bits(seed, idx):
+        return mix_np(np.uint64(seed_const(seed)) ^ idx)
+
+    @staticmethod
+    def u01_f64(seed, idx):
+        return (HostGen.bits(seed, idx) >> np.uint64(11)).astype(np.float64) * 2.0 ** -53
+
+    @staticmethod
+    def u01_f32(seed, idx):
+        return (HostGen.bits(seed, idx) >> np.uint64(40)).astype(np.float32) * np.float32(2.0 ** -24)
+
+
+class DevGen:
+    """torch side.  idx: int64 tensor (non-negative)."""
+
+    @staticmethod
+    def bits(seed, idx):
+        return mix_torch(idx ^ _i64(seed_const(seed)))
+
+    @staticmethod
+    def u01_f64(torch, seed, idx):
+        h = DevGen.bits(seed, idx)
+        return ((h >> 11) & ((1 << 53) - 1)).to(torch.float64) * 2.0 ** -53
+
+    @staticmethod
+    def u01_f32(torch, seed, idx):
+        h = DevGen.bits(seed, idx)
+        return ((h >> 40) & ((1 << 24) - 1)).to(torch.float32) * 2.0 ** -24
+
+
+def host_columns(wl, row0, rows):
+    """The block [row0, row0 + rows) of a workload's columns as numpy arrays."""
+    g = np.arange(row0, row0 + rows, dtype=np.uint64)
+    if wl == "c2":
+        u = HostGen.u01_f64(2, g * np.uint64(2))
+        y = np.stack([u, -u], axis=1)
+        u = HostGen.u01_f64(2, g * np.uint64(2) + np.uint64(1))
+        return {"y_input": y, "z_input": np.stack([u, -u], axis=1)}
+    if wl in ("c3", "reduce_1b"):
+        return {"x": HostGen.u01_f64(3, g) * 2.0 - 1.0}
+    if wl == "c4":
+        r = (HostGen.bits(4, g) >> np.uint64(11)) % np.uint64(KEYS_C4)
+        keys = mix_np(np.uint64(0x4B455953) ^ r).view(np.int64)
+        e = (g[:, None] * np.uint64(64) + np.arange(64, dtype=np.uint64)[None, :])
+        return {"keys": keys, "v_input": HostGen.u01_f32(44, e)}
+    e = (g[:, None] * np.uint64(256) + np.arange(256, dtype=np.uint64)[None, :])
+    return {"x": HostGen.u01_f32(5, e)}
+
+
+def device_columns(torch, wl, row0, rows, device, chunk=1 << 22):
+    """The same block generated on the device, chunk by chunk into preallocated tensors."""
+    def rows_of(a, b):
+        return torch.arange(row0 + a, row0 + b, dtype=torch.int64, device=device)
+    out = {}
+    if wl == "c2":
+        out = {"y_input": torch.empty((rows, 2), dtype=torch.float64, device=device),
+               "z_input": torch.empty((rows, 2), dtype=torch.float64, device=device)}
+    elif wl in ("c3", "reduce_1b"):
+        out = {"x": torch.empty(rows, dtype=torch.float64, device=device)}
+    elif wl == "c4":
+        out = {"keys": torch.empty(rows, dtype=torch.int64, device=device),
+               "v_input": torch.empty((rows, 64), dtype=torch.float32, device=device)}
+    else:
+        out = {"x": torch.empty((rows, 256), dtype=torch.float32, device=device)}
+    if wl in ("c4", "c5"):
+        chunk = 1 << 20
+    for a in range(0, rows, chunk):
+        b = min(rows, a + chunk)
+        g = rows_of(a, b)
+        if wl == "c2":
+            u = DevGen.u01_f64(torch, 2, g * 2)
+            out["y_input"][a:b, 0] = u
+            out["y_input"][a:b, 1] = -u
+            u = DevGen.u01_f64(torch, 2, g * 2 + 1)
+            out["z_input"][a:b, 0] = u
+            out["z_input"][a:b, 1] = -u
+        elif wl in ("c3", "reduce_1b"):
+            out["x"][a:b] = DevGen.u01_f64(torch, 3, g) * 2.0 - 1.0
+        elif wl == "c4":
+            r = ((DevGen.bits(4, g) >> 11) & ((1 << 53) - 1)) % KEYS_C4
+            out["keys"][a:b] = mix_torch(r ^ 0x4B455953)
+            e = g[:, None] * 64 + torch.arange(64, dtype=torch.int64, device=device)[None, :]
+            out["v_input"][a:b] = DevGen.u01_f32(torch, 44, e)
+        else:
+            e = g[:, None] * 256 + torch.arange(256, dtype=torch.int64, device=device)[None, :]
+            out["x"][a:b] = DevGen.u01_f32(torch, 5, e)
+    return out
+
+
+def c5_constants():
+    rng = np.random.default_rng(5)
+    return (rng.uniform(-1 / 16, 1 / 16, (256, 256)).astype(np.float32), rng.uniform(-1, 1, 256).astype(np.float32))
+
+
+def build_graph(wl):
+    import tensorframes_b200 as tfs
+    from tensorframes_b200 import dsl
+    with dsl.withGraph():
+        if wl == "c2":
+            y = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("y_input")
+            z = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("z_input")
+            return dsl.build_graph(dsl.reduce_sum(y, [0]).named("y"), dsl.reduce_min(z, [0]).named("z"))
+        if wl == "reduce_1b":
+            s = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("s_input")
+            m = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("m_input")
+            return dsl.build_graph(dsl.reduce_sum(s, [0]).named("s"), dsl.reduce_min(m, [0]).named("m"))
+        if wl == "c5":
+            w, b = c5_constants()
+            x = dsl.placeholder(tfs.FloatType, dsl.Unknown, 256).named("x")
+            return dsl.build_graph((dsl.matmul(x, dsl.constant(w)) + dsl.constant(b)).named("y"))
+        if wl == "c4":
+            v = dsl.placeholder(tfs.FloatType, dsl.Unknown, 64).named("v_input")
+            return dsl.build_graph(dsl.reduce_sum(v, [0]).named("v"))
+        x = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x")
+        return dsl.build_graph(dsl.cast(dsl.maximum(x * 1.5 + 0.25, 0.0), tfs.FloatType).named("z"))
 
 
 class ClockSampler:
@@ -136,633 +331,678 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------------------------------------
-def build_graph(workload):
-    import tensorframes_b200 as tfs
-    from tensorframes_b200 import dsl
-    with dsl.withGraph():
-        if workload == "c2":
-            y = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("y_input")
-            z = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("z_input")
-            return dsl.build_graph(dsl.reduce_sum(y, [0]).named("y"), dsl.reduce_min(z, [0]).named("z"))
-        if workload == "c5":
-            rng = np.random.default_rng(5)
-            w = rng.uniform(-1 / 16, 1 / 16, (256, 256)).astype(np.float32)
-            b = rng.uniform(-1, 1, 256).astype(np.float32)
-            x = dsl.placeholder(tfs.FloatType, dsl.Unknown, 256).named("x")
-            return dsl.build_graph((dsl.matmul(x, dsl.constant(w)) + dsl.constant(b)).named("y"))
-        if workload == "c4":
-            v = dsl.placeholder(tfs.FloatType, dsl.Unknown, 64).named("v_input")
-            return dsl.build_graph(dsl.reduce_sum(v, [0]).named("v"))
-        x = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x")
-        return dsl.build_graph(dsl.cast(dsl.maximum(x * 1.5 + 0.25, 0.0), tfs.FloatType).named("z"))
+class Ctx:
+    """What every workload needs: torch, the rank layout, the launch stream, the communicator."""
 
-
-def make_inputs(torch, workload, rows, seed, device):
-    g = torch.Generator(device=device)
-    g.manual_seed(seed)
-    if workload == "c2":
-        u = torch.rand(rows, generator=g, device=device, dtype=torch.float64)
-        y = torch.stack([u, -u], dim=1).contiguous()
-        u = torch.rand(rows, generator=g, device=device, dtype=torch.float64)
-        z = torch.stack([u, -u], dim=1).contiguous()
-        return {"y_input": y, "z_input": z}
-    if workload == "c4":
-        # keys: a table of 1e6 distinct random 64-bit values (not dense ids, so the hash is really exercised)
-        # (the key universe is shared by all ranks, as the partitions of one DataFrame would share it)
-        gk = torch.Generator(device=device)
-        gk.manual_seed(4)
-        table = torch.randint(-2**62, 2**62, (KEYS_C4,), generator=gk, device=device, dtype=torch.int64)
-        table = torch.unique(table)
-        idx = torch.randint(0, table.numel(), (rows,), generator=g, device=device, dtype=torch.int64)
-        keys = table[idx]
-        del idx
-        v = torch.rand((rows, 64), generator=g, device=device, dtype=torch.float32)
-        return {"keys": keys, "v_input": v}
-    x = torch.rand(rows, generator=g, device=device, dtype=torch.float64) * 2.0 - 1.0
-    return {"x": x}
-
-
-def run_ours(args):
-    import torch
-    import torch.distributed as dist
-    from tensorframes_b200 import _native
-    from tensorframes_b200.distributed import combine_reduce_blocks
-
-    world = env_int("WORLD_SIZE", 1)
-    rank = env_int("RANK", 0)
-    local = env_int("LOCAL_RANK", 0)
-    if world != args.gpus:
-        if world == 1 and args.gpus > 1:
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+        from tensorframes_b200 import _native
+        self.torch, self.dist, self.native, self.args = torch, dist, _native, args
+        self.world = env_int("WORLD_SIZE", 1)
+        self.rank = env_int("RANK", 0)
+        self.local = env_int("LOCAL_RANK", 0)
+        if self.world != args.gpus and self.world == 1 and args.gpus > 1:
             raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run --nproc-per-node N")
-    torch.cuda.set_device(local)
-    device = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=device)
-    wl = args.workload
-    rows = args.rows or {"c2": ROWS_C2, "c3": ROWS_C3, "c4": ROWS_C4, "c5": ROWS_C5}[wl]
-    DA = _native.DeviceArray.from_torch
-    if wl == "c4":
-        return run_c4(args, torch, dist, _native, world, rank, local, device, rows)
-    if wl == "c5":
-        return run_c5(args, torch, dist, _native, world, rank, local, device, rows)
+        torch.cuda.set_device(self.local)
+        self.device = torch.device("cuda", self.local)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.device)
+        # a real (non-default) stream: the C ABI treats a NULL stream handle as "use the session's own"
+        self.stream = torch.cuda.Stream(device=self.device)
+        torch.cuda.set_stream(self.stream)
+        self.DA = _native.DeviceArray.from_torch
+        self.comm = None
+        if self.world > 1:
+            # the library's own communicator (NCCL behind the C ABI): rank 0 draws the id, torch.distributed carries it
+            ident = torch.zeros(128, dtype=torch.uint8, device=self.device)
+            if self.rank == 0:
+                ident.copy_(torch.frombuffer(bytearray(_native.comm_unique_id()), dtype=torch.uint8))
+            dist.broadcast(ident, 0)
+            self.comm = _native.Comm(self.local, self.world, self.rank, bytes(ident.cpu().numpy().tobytes()))
 
-    graph_bytes = build_graph(wl)
-    graph = _native.Graph(graph_bytes)
-    sess = _native.Session(graph, local)
-    # a real (non-default) stream: the C ABI treats a NULL stream handle as "use the session's own"
-    stream = torch.cuda.Stream(device=device)
-    torch.cuda.set_stream(stream)
-    sess.set_stream(stream.cuda_stream)
-    feeds_t = make_inputs(torch, wl, rows, seed=(2 if wl == "c2" else 3) + 1000 * rank, device=device)
-    feeds = {k: DA(v) for k, v in feeds_t.items()}
+    def session(self, wl):
+        g = self.native.Graph(build_graph(wl))
+        s = self.native.Session(g, self.local)
+        s.set_stream(self.stream.cuda_stream)
+        return g, s
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, x):
+        t = self.torch.tensor([x], dtype=self.torch.float64, device=self.device)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def timed(self, step, after_last=None):
+        """W warm-up steps, then exactly K steps between barrier + synchronize on both sides; device time of the
+        K steps (events on the launch stream), max over ranks; host time spent enqueueing one step."""
+        torch, args = self.torch, self.args
+        for _ in range(args.warmup):
+            step(False)
+        if after_last:
+            after_last()
+        self.barrier()
+        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with ClockSampler(self.local) as clocks:
+            self.barrier()
+            start.record(self.stream)
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                step(True)
+            host_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+            if after_last:
+                after_last()            # the last block's exchange belongs to the timed region
+            end.record(self.stream)
+            self.barrier()
+        return self.max_over_ranks(start.elapsed_time(end)), clocks.summary(), host_ms
+
+    def e2e_timed(self, step, k):
+        """k end-to-end steps (host buffers in, host results out, synchronous), wall clock, max over ranks."""
+        step()
+        self.barrier()
+        t0 = time.perf_counter()
+        for _ in range(k):
+            step()
+        self.barrier()
+        return self.max_over_ranks(time.perf_counter() - t0)
+
+    def pinned(self, shape, dtype, like=None):
+        pb = self.native.PinnedBuffer(tuple(shape), dtype)
+        if like is not None:
+            self.torch.from_numpy(pb.array).copy_(like)      # fill the pinned block once, outside the timing
+        return pb
+
+
+def record(ctx, wl, rows, elapsed_ms, clocks, launches, roofline, e2e, cpu, parity, extra_config=None, **more):
+    args = ctx.args
+    step_s = elapsed_ms / 1e3 / args.steps
+    cfg = {"workload": WORKLOAD[wl] + f"{rows} rows per GPU", "rows_per_gpu": rows, "partitions": ctx.world,
+           "l2": "inputs larger than L2 (no flush needed)"}
+    cfg.update(extra_config or {})
+    rec = {"metric": METRIC[wl], "value": ctx.world * rows / step_s, "unit": "rows/s", "n_gpus": ctx.world,
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": DTYPE[wl], "data": "synthetic (counter-based generator, SURVEY 8(d))",
+           "config": cfg, "roofline": roofline, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+           "cpu_baseline": cpu, "parity": parity}
+    rec.update(more)
+    return rec
+
+
+def hbm_roofline(wl, rows, bytes_per_launch, avg_launch_s, kernel):
+    peak, src = hbm_peak()
+    achieved = bytes_per_launch / avg_launch_s / 1e9
+    traffic, tsrc = ncu_traffic("c2" if wl == "reduce_1b" else wl, rows if wl != "reduce_1b" else rows // 2)
+    return {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": traffic, "traffic_source": tsrc, "peak_source": src, "kernel": kernel,
+            "algorithmic_bytes_per_launch": bytes_per_launch, "avg_launch_ms": avg_launch_s * 1e3,
+            "frac_of_nominal_8000": achieved / 8000.0}
+
+
+def cpu_sample(fn, rows_avail, probe_rows, budget_s=10.0):
+    """Times fn(rows) on a bounded prefix: a probe sizes the sample so that 3 repeats take about budget_s."""
+    from oracle import cpu_baseline as cb
+    probe = min(rows_avail, probe_rows)
+    t, _ = cb.timed(fn, probe)
+    sample = int(min(rows_avail, max(probe, budget_s / max(t, 1e-6) * probe / 3)))
+    t, res = cb.timed(fn, sample, repeat=3)
+    return sample, t, res
+
+
+# ---------------------------------------------------------------------------------------------
+# reduce_blocks: c2 (two f64[?,2] columns) and reduce_1b (sum + min over one 1e9-row f64 column)
+# ---------------------------------------------------------------------------------------------
+def run_reduce(ctx, wl, rows, cols=None):
+    torch, dist, DA, args = ctx.torch, ctx.dist, ctx.DA, ctx.args
+    world, device, stream = ctx.world, ctx.device, ctx.stream
+    graph, sess = ctx.session(wl)
     if wl == "c2":
-        outs_t = {"y": torch.empty(2, dtype=torch.float64, device=device),
-                  "z": torch.empty(2, dtype=torch.float64, device=device)}
-        merged_t = {k: torch.empty_like(v) for k, v in outs_t.items()}
+        feeds_t = cols or device_columns(torch, "c2", ctx.rank * rows, rows, device)
+        names, cell = ["y", "z"], (2,)
+        sum_name, min_name = "y", "z"
     else:
-        outs_t = {"z": torch.empty(rows, dtype=torch.float32, device=device)}
-        merged_t = {}
+        x = (cols or device_columns(torch, "c3", ctx.rank * rows, rows, device))["x"]
+        feeds_t = {"s_input": x, "m_input": x}
+        names, cell = ["s", "m"], ()
+        sum_name, min_name = "s", "m"
+    torch.cuda.synchronize()
+    feeds = {k: DA(v) for k, v in feeds_t.items()}
+    outs_t = {n: torch.empty(cell, dtype=torch.float64, device=device) for n in names}
+    merged_t = {n: torch.empty(cell, dtype=torch.float64, device=device) for n in names}
     outs = {k: DA(v) for k, v in outs_t.items()}
-    names = list(outs_t)
-    # N > 1: the exchange of a block (all_gather of the partial rows + merge run) goes on a second stream with its own
-    # session, so it overlaps the next block's reduction kernels; the partial rows are kept in a small ring of buffers for that
-    overlap = wl == "c2" and world > 1
-    if overlap:
-        side = torch.cuda.Stream(device=device)
-        merge_sess = _native.Session(graph, local)
-        merge_sess.set_stream(side.cuda_stream)
-        depth = max(2, env_int("TFS_BENCH_EXCHANGE_DEPTH", 4))      # partial-row buffers in flight
-        part_t = [outs_t] + [{k: torch.empty_like(v) for k, v in outs_t.items()} for _ in range(depth - 1)]
-        part = [{k: DA(v) for k, v in p.items()} for p in part_t]
-        reduced_ev = [torch.cuda.Event() for _ in range(depth)]
-        exchanged_ev = [torch.cuda.Event() for _ in range(depth)]
-        step_no = [0]
-
-    def merge(feeds_stacked):
-        (merge_sess if overlap else sess).run_into({k: DA(v) for k, v in feeds_stacked.items()}, {k: DA(v) for k, v in merged_t.items()})
-        return [merged_t[n] for n in names]
-
+    merged = {k: DA(v) for k, v in merged_t.items()}
     kernel_events = []
 
     def step(timed):
         if timed:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(stream)
-        if overlap:
-            b = step_no[0] % depth
-            step_no[0] += 1
-            stream.wait_event(exchanged_ev[b])          # the exchange that last read this buffer set (`depth` blocks ago)
-            sess.run_into(feeds, part[b])
-        else:
-            sess.run_into(feeds, outs)
+        sess.run_into(feeds, outs)
         if timed:
             e1.record(stream)
             kernel_events.append((e0, e1))
-        if overlap:
-            reduced_ev[b].record(stream)
-            with torch.cuda.stream(side):
-                side.wait_event(reduced_ev[b])
-                combine_reduce_blocks([part_t[b][n] for n in names], names, merge)
-                exchanged_ev[b].record(side)
-
-    def barrier():
-        if overlap:
-            stream.wait_stream(side)
         if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+            # the path's exchange step, behind the C ABI: the partial rows are combined across ranks on the
+            # communicator's side stream, so it overlaps the next block's reduction kernels
+            sess.reduce_combine(ctx.comm, outs, merged, overlap=True)
 
-    for _ in range(args.warmup):
-        step(False)
-    barrier()
+    def drain():
+        if world > 1:
+            sess.combine_wait()          # launch stream waits for the side stream's last exchange
+
     launches0 = sess.launch_count
-    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clocks:
-        barrier()
-        start.record(stream)
-        t_host0 = time.perf_counter()
-        for _ in range(args.steps):
-            step(True)
-        host_enqueue_ms = (time.perf_counter() - t_host0) * 1e3 / args.steps   # CPU time to enqueue one step
-        if overlap:
-            stream.wait_stream(side)       # the last block's exchange belongs to the timed region
-        end.record(stream)
-        barrier()
-    elapsed_ms = start.elapsed_time(end)
-    launches = sess.launch_count - launches0
-    big_launches = args.steps * (2 if wl == "c2" else 1)
+    elapsed_ms, clocks, host_ms = ctx.timed(step, drain)
+    launches = (sess.launch_count - launches0) * args.steps // (args.steps + args.warmup)
     kernel_ms = sum(a.elapsed_time(b) for a, b in kernel_events)
-    t = torch.tensor([elapsed_ms], dtype=torch.float64, device=device)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    elapsed_ms = float(t.item())
 
-    # parity spot check on the device (the tests hold the real parity checks)
-    if wl == "c2":
-        res = merged_t if world > 1 else outs_t
-        y = feeds_t["y_input"]
-        ref_sum, ref_abs, ref_min = y.sum(dim=0), y.abs().sum(dim=0), feeds_t["z_input"].min(dim=0).values
-        if world > 1:       # the merged row must be the reduction over every rank's partition
-            dist.all_reduce(ref_sum)
-            dist.all_reduce(ref_abs)
-            dist.all_reduce(ref_min, op=dist.ReduceOp.MIN)
-        assert torch.all((res["y"] - ref_sum).abs() <= 1e-12 * ref_abs), (res["y"], ref_sum)
-        assert torch.equal(res["z"], ref_min)
-    else:
-        n_chk = min(rows, 1 << 24)
-        x = feeds_t["x"][:n_chk]
-        assert torch.equal(outs_t["z"][:n_chk], torch.clamp_min(x * 1.5 + 0.25, 0.0).to(torch.float32))
+    # parity on the device against torch's own reductions over the whole block (and over every rank's block)
+    res = merged_t if world > 1 else outs_t
+    ys = feeds_t["y_input" if wl == "c2" else "s_input"]
+    zs = feeds_t["z_input" if wl == "c2" else "m_input"]
+    ref_sum = torch.zeros(cell, dtype=torch.float64, device=device)
+    ref_abs = torch.zeros(cell, dtype=torch.float64, device=device)
+    for a in range(0, rows, 1 << 26):
+        ref_sum += ys[a:a + (1 << 26)].sum(dim=0)
+        ref_abs += ys[a:a + (1 << 26)].abs().sum(dim=0)
+    ref_min = zs.min(dim=0).values
+    if world > 1:
+        dist.all_reduce(ref_sum)
+        dist.all_reduce(ref_abs)
+        dist.all_reduce(ref_min, op=dist.ReduceOp.MIN)
+    assert torch.all((res[sum_name] - ref_sum).abs() <= 1e-12 * ref_abs), (res[sum_name], ref_sum)
+    assert torch.equal(res[min_name], ref_min)
+    parity = {"full_block_vs_torch": "sum within 1e-12 of sum|x|, min bit-exact" + (", merged over all ranks" if world > 1 else "")}
 
     # ---- end to end: host (pinned) column buffers through the same C-ABI call -----------------
-    e2e = None
-    host_in = {}
-    pinned = []
-    h2d = sum(v.numel() * v.element_size() for v in feeds_t.values())
+    h2d = sum(v.numel() * v.element_size() for v in feeds_t.values())     # every fed placeholder is staged (reduce_1b feeds its column twice)
     d2h = sum(v.numel() * v.element_size() for v in outs_t.values())
+    e2e, pinned, host_in = None, [], {}
     if not args.no_e2e:
         try:
+            seen = {}
             for k, v in feeds_t.items():
-                pb = _native.PinnedBuffer(tuple(v.shape), np.float64)
-                pinned.append(pb)
-                torch.from_numpy(pb.array).copy_(v)       # fill the pinned block once, outside the timing
-                host_in[k] = pb.array
+                if id(v) not in seen:
+                    pb = ctx.pinned(v.shape, np.float64, v)
+                    pinned.append(pb)
+                    seen[id(v)] = pb.array
+                host_in[k] = seen[id(v)]
             host_out = {}
             for k, v in outs_t.items():
-                pb = _native.PinnedBuffer(tuple(v.shape), np.float64 if v.dtype == torch.float64 else np.float32)
+                pb = ctx.pinned(v.shape, np.float64)
                 pinned.append(pb)
                 host_out[k] = pb.array
             torch.cuda.synchronize()
-            k_e2e = max(1, min(args.steps, 5))
+            k_e2e = max(1, min(args.steps, 5 if wl == "c2" else 3))
 
             def e2e_step():
                 sess.run_into(host_in, host_out)      # H2D + kernels + D2H + sync inside
-                if wl == "c2" and world > 1:
-                    parts = [torch.from_numpy(host_out[n]).to(device) for n in names]
-                    if overlap:      # the merge session lives on the side stream: order it after the copies above
-                        side.wait_stream(torch.cuda.current_stream())
-                        with torch.cuda.stream(side):
-                            combine_reduce_blocks(parts, names, merge)
-                    else:
-                        combine_reduce_blocks(parts, names, merge)
+                if world > 1:
+                    for n in names:
+                        outs_t[n].copy_(torch.from_numpy(host_out[n]))
+                    sess.reduce_combine(ctx.comm, outs, merged, overlap=False)
+                    for n in names:
+                        torch.from_numpy(host_out[n]).copy_(merged_t[n])
                     torch.cuda.synchronize()
 
-            e2e_step()
-            barrier()
-            t0 = time.perf_counter()
-            for _ in range(k_e2e):
-                e2e_step()
-            barrier()
-            dt = time.perf_counter() - t0
-            tt = torch.tensor([dt], dtype=torch.float64, device=device)
-            if world > 1:
-                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            e2e = {"value": world * rows * k_e2e / float(tt.item()), "unit": "rows/s", "steps": k_e2e,
-                   "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)}
-            if wl == "c2" and world == 1:
-                assert np.array_equal(host_out["z"], outs_t["z"].cpu().numpy())
+            dt = ctx.e2e_timed(e2e_step, k_e2e)
+            e2e = {"value": world * rows * k_e2e / dt, "unit": "rows/s", "steps": k_e2e,
+                   "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                   "h2d_gbs_per_gpu": h2d * k_e2e / dt / 1e9}
+            if world == 1:
+                assert np.array_equal(host_out[min_name], res[min_name].cpu().numpy())
         except Exception as exc:   # e.g. not enough pinnable host memory on this box
             e2e = {"value": None, "unit": "rows/s", "error": str(exc)[:200],
                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)}
 
-    # ---- CPU baseline beside it (rank 0, N = 1 only): the oracle's restatement of the reference ----
+    # ---- CPU baseline beside it (rank 0, N = 1 only) + oracle check of a prefix block ----------------------
     cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu:
+    if ctx.rank == 0 and world == 1 and not args.no_cpu:
+        from oracle import cpu_baseline as cb, tf_ops
+        cores = cb.cores()
         have_host = len(host_in) == len(feeds_t)
-        cpu = cpu_baseline_leg(wl, host_in if have_host else {k: v.cpu().numpy() for k, v in feeds_t.items()}, rows)
+        hy = host_in[list(feeds_t)[0]] if have_host else None
+        hz = host_in[list(feeds_t)[1]] if have_host else None
+        avail = rows if have_host else min(rows, 20_000_000)
+        if not have_host:
+            hc = host_columns("c2" if wl == "c2" else "c3", 0, avail)
+            hy, hz = (hc["y_input"], hc["z_input"]) if wl == "c2" else (hc["x"], hc["x"])
+        y2 = hy if wl == "c2" else hy.reshape(-1, 1)
+        z2 = hz if wl == "c2" else hz.reshape(-1, 1)
+        sample, t, _ = cpu_sample(lambda r: cb.reduce_blocks_sum_min(y2[:r], z2[:r], cores, cores), avail, 2_000_000)
+        cpu = {"value": sample / t, "unit": "rows/s", "cores": cores, "kind": "port",
+               "sample": f"first {sample} rows of the same block, {cores} partitions on {cores} threads, best of 3; "
+                         "columnar unboxed input, so an upper bound on the JVM reference"}
+        # oracle on a prefix block regenerated on the host: same generator, GPU result through the same session
+        n_chk = min(rows, 1 << 20)
+        hc = host_columns("c2" if wl == "c2" else "c3", 0, n_chk)
+        o_feeds = hc if wl == "c2" else {"s_input": hc["x"], "m_input": hc["x"]}
+        want = tf_ops.evaluate(build_graph(wl), o_feeds, names)
+        pre_feeds = {k: DA(v[:n_chk]) for k, v in feeds_t.items()}
+        sess.run_into(pre_feeds, outs)
+        sess.sync()
+        got = [outs_t[n].cpu().numpy() for n in names]
+        scale = np.abs(o_feeds[list(o_feeds)[0]]).sum(axis=0)
+        assert np.all(np.abs(got[0] - want[0]) <= 1e-12 * scale), (got[0], want[0])
+        assert np.array_equal(got[1], want[1])
+        parity["oracle_prefix_rows"] = n_chk
+        parity["oracle"] = "sum within 1e-12 of sum|x| of oracle.tf_ops, min bit-exact, on host-regenerated values"
     host_in = {}
     for pb in pinned:
         pb.free()
-
-    if rank == 0:
-        peak, peak_src = hbm_peak()
-        alg = ALG_BYTES_PER_ROW[wl]
-        bytes_per_launch = rows * alg / (2 if wl == "c2" else 1)
-        avg_launch_s = kernel_ms / 1e3 / big_launches
-        achieved = bytes_per_launch / avg_launch_s / 1e9
-        line = {
-            "metric": "rows/s for reduceBlocks (reduce_sum + reduce_min over DoubleType[?,2])" if wl == "c2"
-                      else "rows/s for mapBlocks (fused x*a+b, max(.,0), cast f32 on a float64 column)",
-            "value": world * rows * args.steps / (elapsed_ms / 1e3),
-            "unit": "rows/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": elapsed_ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f64", "data": "synthetic",
-            "config": {"workload": ("BASELINE configs[1]: reduce_blocks reduce_sum+reduce_min, DoubleType[?,2], "
-                                    if wl == "c2" else
-                                    "BASELINE configs[2]: map_blocks fused chain cast_f32(max(x*1.5+0.25,0)), float64 column, ")
-                                   + f"{rows} rows per GPU", "rows_per_gpu": rows, "partitions": world,
-                       "l2": "inputs larger than L2 (no flush needed)",
-                       "exchange": ("all_gather of partial rows + merge run, on a second stream: overlaps the next block's kernels"
-                                    if (wl == "c2" and world > 1) else "none")},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": ncu_traffic(wl, rows), "peak_source": peak_src,
-                         "kernel": "reduce_axis0_tma_kernel" if wl == "c2" else "chain_kernel",
-                         "algorithmic_bytes_per_launch": bytes_per_launch,
-                         "avg_launch_ms": avg_launch_s * 1e3, "frac_of_nominal_8000": achieved / 8000.0},
-            "e2e": e2e,
-            "gpu_launches": int(launches),
-            "clocks": clocks.summary(),
-            "cpu_baseline": cpu,
-            "host_enqueue_ms_per_step": host_enqueue_ms,
-        }
-        print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
+    bytes_per_launch = rows * ALG_BYTES_PER_ROW[wl] / 2
+    roof = hbm_roofline(wl, rows, bytes_per_launch, kernel_ms / 1e3 / (2 * args.steps), "reduce_axis0_tma_kernel")
+    ex = ("grouped ncclAllReduce of the cell-sized partial rows behind the C ABI (tfs_session_reduce_combine), on the "
+          "communicator's side stream: overlaps the next block's kernels") if world > 1 else "none"
+    rec = record(ctx, wl, rows, elapsed_ms, clocks, launches, roof, e2e, cpu, parity, {"exchange": ex},
+                 host_enqueue_ms_per_step=host_ms)
+    sess.close()
+    graph.close()
+    return rec
 
 
-def run_c4(args, torch, dist, _native, world, rank, local, device, rows):
-    """BASELINE config 4: groupBy(int64 key).aggregate(reduce_sum(v_input, [0])), FloatType[?,64].
-    One block per GPU; with N > 1 the step also moves every partial group to the rank owning its key
-    (all_to_all) and merges there, so the result is one row per distinct key, sharded by owner."""
-    DA = _native.DeviceArray.from_torch
-    graph = _native.Graph(build_graph("c4"))
-    sess = _native.Session(graph, local)
-    stream = torch.cuda.Stream(device=device)
-    torch.cuda.set_stream(stream)
-    sess.set_stream(stream.cuda_stream)
-    t = make_inputs(torch, "c4", rows, seed=4 + 1000 * rank, device=device)
-    keys, v = t["keys"], t["v_input"]
-    out_keys = torch.empty(KEYS_C4, dtype=torch.int64, device=device)
-    out = torch.empty((KEYS_C4, 64), dtype=torch.float32, device=device)
+# ---------------------------------------------------------------------------------------------
+def run_c3(ctx, rows, cols=None):
+    torch, DA, args = ctx.torch, ctx.DA, ctx.args
+    world, device, stream = ctx.world, ctx.device, ctx.stream
+    graph, sess = ctx.session("c3")
+    x = (cols or device_columns(torch, "c3", ctx.rank * rows, rows, device))["x"]
+    z = torch.empty(rows, dtype=torch.float32, device=device)
+    torch.cuda.synchronize()
+    feeds, outs = {"x": DA(x)}, {"z": DA(z)}
 
-    out_keys2 = torch.empty(KEYS_C4, dtype=torch.int64, device=device)
-    out2 = torch.empty((KEYS_C4, 64), dtype=torch.float32, device=device)
+    def step(timed):
+        sess.run_into(feeds, outs)
+
+    launches0 = sess.launch_count
+    elapsed_ms, clocks, host_ms = ctx.timed(step)
+    launches = (sess.launch_count - launches0) * args.steps // (args.steps + args.warmup)
+    # parity over the WHOLE block against torch on the device (bit-exact), chunked to bound the temporaries
+    for a in range(0, rows, 1 << 26):
+        xa = x[a:a + (1 << 26)]
+        assert torch.equal(z[a:a + (1 << 26)], torch.clamp_min(xa * 1.5 + 0.25, 0.0).to(torch.float32))
+    parity = {"full_block_vs_torch": "bit-exact over all rows"}
+    h2d, d2h = rows * 8, rows * 4
+    e2e, pinned, hx = None, [], None
+    if not args.no_e2e:
+        try:
+            px = ctx.pinned((rows,), np.float64, x)
+            pinned.append(px)
+            pz = ctx.pinned((rows,), np.float32)
+            pinned.append(pz)
+            hx = px.array
+            k_e2e = max(1, min(args.steps, 3))
+            dt = ctx.e2e_timed(lambda: sess.run_into({"x": px.array}, {"z": pz.array}), k_e2e)
+            e2e = {"value": world * rows * k_e2e / dt, "unit": "rows/s", "steps": k_e2e, "h2d_bytes_per_step": int(h2d),
+                   "d2h_bytes_per_step": int(d2h), "h2d_gbs_per_gpu": h2d * k_e2e / dt / 1e9}
+            assert np.array_equal(pz.array[:1 << 20], z[:1 << 20].cpu().numpy())
+        except Exception as exc:
+            e2e = {"value": None, "unit": "rows/s", "error": str(exc)[:200], "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)}
+    cpu = None
+    if ctx.rank == 0 and world == 1 and not args.no_cpu:
+        from oracle import cpu_baseline as cb, tf_ops
+        cores = cb.cores()
+        avail = rows if hx is not None else min(rows, 50_000_000)
+        hxx = hx if hx is not None else host_columns("c3", 0, avail)["x"]
+        sample, t, _ = cpu_sample(lambda r: cb.map_blocks_chain(hxx[:r], 1.5, 0.25, cores, cores), avail, 4_000_000)
+        cpu = {"value": sample / t, "unit": "rows/s", "cores": cores, "kind": "port",
+               "sample": f"first {sample} rows of the same block, {cores} partitions on {cores} threads, best of 3; "
+                         "columnar unboxed input, so an upper bound on the JVM reference"}
+        n_chk = min(rows, 1 << 20)
+        hc = host_columns("c3", 0, n_chk)
+        (want,) = tf_ops.evaluate(build_graph("c3"), hc, ["z"])
+        assert np.array_equal(z[:n_chk].cpu().numpy(), want)
+        parity["oracle_prefix_rows"] = n_chk
+        parity["oracle"] = "bit-exact against oracle.tf_ops on host-regenerated values"
+    hx = None
+    for pb in pinned:
+        pb.free()
+    roof = hbm_roofline("c3", rows, rows * 12.0, elapsed_ms / 1e3 / args.steps, "chain_kernel")
+    rec = record(ctx, "c3", rows, elapsed_ms, clocks, launches, roof, e2e, cpu, parity, {"exchange": "none"},
+                 host_enqueue_ms_per_step=host_ms)
+    sess.close()
+    graph.close()
+    return rec
+
+
+# ---------------------------------------------------------------------------------------------
+def run_c4(ctx, rows):
+    """BASELINE config 4.  One block per GPU; with N > 1 the step also moves every partial group to the rank owning its
+    key and merges there (tfs_session_aggregate_combine), so the result is one row per distinct key, sharded by owner."""
+    torch, dist, DA, args = ctx.torch, ctx.dist, ctx.DA, ctx.args
+    world, device = ctx.world, ctx.device
+    graph, sess = ctx.session("c4")
+    tried = []
+    while True:       # 5e8 rows need 132 GB + ~8 GB of scratch: halve on an allocation failure and say so
+        try:
+            t = device_columns(torch, "c4", ctx.rank * rows, rows, device)
+            keys, v = t["keys"], t["v_input"]
+            out_keys = torch.empty(KEYS_C4, dtype=torch.int64, device=device)
+            out = torch.empty((KEYS_C4, 64), dtype=torch.float32, device=device)
+            torch.cuda.synchronize()
+            torch.cuda.empty_cache()      # the generator's temporaries must not sit in torch's cache next to the library's scratch
+            n_groups = sess.aggregate_into(DA(keys), {"v_input": DA(v)}, {"v": DA(out)}, DA(out_keys))
+            break
+        except (RuntimeError, ctx.native.NativeError) as exc:
+            if "memory" not in str(exc).lower() or rows <= 50_000_000:
+                raise
+            tried.append({"rows": rows, "error": str(exc)[:160]})
+            t = keys = v = out = out_keys = None
+            torch.cuda.empty_cache()
+            rows //= 2
+    if world > 1:      # every rank must run the same block size
+        r = torch.tensor([rows], dtype=torch.int64, device=device)
+        dist.all_reduce(r, op=dist.ReduceOp.MIN)
+        if int(r.item()) != rows:
+            rows = int(r.item())
+            keys, v = keys[:rows], v[:rows]
+    out_keys2 = torch.empty(KEYS_C4, dtype=torch.int64, device=device) if world > 1 else None
+    out2 = torch.empty((KEYS_C4, 64), dtype=torch.float32, device=device) if world > 1 else None
     owned = [0]
 
-    def step():
+    def step(timed):
         g = sess.aggregate_into(DA(keys), {"v_input": DA(v)}, {"v": DA(out)}, DA(out_keys))
         if world > 1:
-            # exchange: partial groups travel to the rank that owns their key, which merges them
-            from tensorframes_b200.distributed import exchange_groups
-            rk, (rv,) = exchange_groups(out_keys[:g], [out[:g]])
-            owned[0] = sess.aggregate_into(DA(rk), {"v_input": DA(rv)}, {"v": DA(out2)}, DA(out_keys2))
+            owned[0] = sess.aggregate_combine(ctx.comm, g, DA(out_keys), {"v": DA(out)}, {"v": DA(out2)}, DA(out_keys2))
         return g
 
-    for _ in range(args.warmup):
-        n_groups = step()
-    torch.cuda.synchronize()
     launches0 = sess.launch_count
-    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clocks:
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        start.record(stream)
-        for _ in range(args.steps):
-            n_groups = step()
-        end.record(stream)
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-    elapsed_ms = start.elapsed_time(end)
-    tt = torch.tensor([elapsed_ms], dtype=torch.float64, device=device)
+    elapsed_ms, clocks, host_ms = ctx.timed(step)
+    launches = (sess.launch_count - launches0) * args.steps // (args.steps + args.warmup)
+    # ---- parity at the full block size: keys exactly once each; sampled groups and the checksum of checksums in f64
+    ok = out_keys[:n_groups]
+    assert n_groups <= KEYS_C4 and bool(torch.all(ok[1:] > ok[:-1]))               # each key once, ascending
+    universe = torch.sort(mix_torch(torch.arange(KEYS_C4, dtype=torch.int64, device=device) ^ 0x4B455953)).values
+    assert torch.equal(universe[torch.searchsorted(universe, ok).clamp_max(KEYS_C4 - 1)], ok)     # no key that is not in the data's key table
+    sample_keys = ok[torch.linspace(0, n_groups - 1, 64, device=device).long()]
+    ref = torch.zeros((64, 64), dtype=torch.float64, device=device)
+    col = torch.zeros(64, dtype=torch.float64, device=device)
+    for a in range(0, rows, 1 << 24):
+        kc, vc = keys[a:a + (1 << 24)], v[a:a + (1 << 24)]
+        col += vc.sum(0, dtype=torch.float64)
+        assert torch.equal(ok[torch.searchsorted(ok, kc).clamp_max(n_groups - 1)], kc)             # every row's key has its group, bit-exact
+        pos = torch.searchsorted(sample_keys, kc).clamp_max(63)
+        hit = sample_keys[pos] == kc
+        ref.index_add_(0, pos[hit], vc[hit].double())
+    got = out[:n_groups][torch.searchsorted(ok, sample_keys)].double()
+    assert torch.all((got - ref).abs() <= 1e-5 * ref.abs().clamp_min(1e-30)), "sampled group sums"
+    tot = out[:n_groups].sum(0, dtype=torch.float64)
+    assert torch.all((tot - col).abs() <= 1e-5 * col), "group sums must add up to the column sums"
+    parity = {"full_block_vs_torch": f"{n_groups} keys bit-exact and ascending; 64 sampled groups and the column totals within 1e-5 (f64 reference)"}
     if world > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    elapsed_ms = float(tt.item())
-    launches = sess.launch_count - launches0
-    # parity spot check on the device: keys exactly once each, sums within the f32 tolerance
-    ref_keys, inv = torch.unique(keys, return_inverse=True)
-    assert n_groups == ref_keys.numel()
-    order = torch.argsort(out_keys[:n_groups])
-    assert torch.equal(out_keys[:n_groups][order], ref_keys)
-    ref = torch.zeros((n_groups, 64), dtype=torch.float64, device=device)
-    chk = min(rows, 20_000_000)
-    ref.index_add_(0, inv[:chk], v[:chk].double())
-    if chk == rows:
-        assert torch.all((out[:n_groups][order].double() - ref).abs() <= 1e-5 * ref.abs().clamp_min(1e-30))
-    # ---- end to end: host (pinned) key and payload columns through the same C-ABI call ----------------
-    # bounded block (the full 66 GB block would have to be pinned and staged next to the resident one)
-    e2e = None
+        tot_owned = torch.tensor([owned[0]], dtype=torch.int64, device=device)
+        dist.all_reduce(tot_owned)
+        all_keys = torch.tensor([n_groups], dtype=torch.int64, device=device)
+        dist.all_reduce(all_keys, op=dist.ReduceOp.MAX)
+        assert int(tot_owned.item()) >= int(all_keys.item()) and int(tot_owned.item()) <= KEYS_C4
+        tot2 = out2[:owned[0]].sum(0, dtype=torch.float64)
+        dist.all_reduce(tot2)
+        col_all = col.clone()
+        dist.all_reduce(col_all)
+        assert torch.all((tot2 - col_all).abs() <= 1e-5 * col_all), "merged group sums must add up to all ranks' column sums"
+        parity["merged"] = f"{int(tot_owned.item())} owned groups over all ranks; merged totals within 1e-5 of all ranks' column sums"
+    # ---- end to end: host (pinned) key and payload columns through the same C-ABI call; bounded block
     rows_e2e = min(rows, 50_000_000)
-    pinned = []
-    host = {}
+    e2e, pinned, host = None, [], {}
     if not args.no_e2e:
         try:
             from tensorframes_b200.shape import LongType
-            pk = _native.PinnedBuffer((rows_e2e,), np.int64); pinned.append(pk)
-            pv = _native.PinnedBuffer((rows_e2e, 64), np.float32); pinned.append(pv)
-            po = _native.PinnedBuffer((KEYS_C4, 64), np.float32); pinned.append(po)
-            pok = _native.PinnedBuffer((KEYS_C4,), np.int64); pinned.append(pok)
-            torch.from_numpy(pk.array).copy_(keys[:rows_e2e])
-            torch.from_numpy(pv.array).copy_(v[:rows_e2e])
+            pk = ctx.pinned((rows_e2e,), np.int64, keys[:rows_e2e]); pinned.append(pk)
+            pv = ctx.pinned((rows_e2e, 64), np.float32, v[:rows_e2e]); pinned.append(pv)
+            po = ctx.pinned((KEYS_C4, 64), np.float32); pinned.append(po)
+            pok = ctx.pinned((KEYS_C4,), np.int64); pinned.append(pok)
             host = {"keys": pk.array, "v_input": pv.array}
-            hk = _native.DeviceArray(pk.array.ctypes.data, LongType, pk.array.shape, owner=pk.array)
-            hok = _native.DeviceArray(pok.array.ctypes.data, LongType, pok.array.shape, owner=pok.array)
+            NDA = ctx.native.DeviceArray
+            hk = NDA(pk.array.ctypes.data, LongType, pk.array.shape, owner=pk.array)
+            hok = NDA(pok.array.ctypes.data, LongType, pok.array.shape, owner=pok.array)
+            g_last = [0]
 
             def e2e_step():
                 if world == 1:
-                    return sess.aggregate_into(hk, {"v_input": pv.array}, {"v": po.array}, hok)   # H2D, passes, D2H, sync
-                from tensorframes_b200.distributed import exchange_groups
+                    g_last[0] = sess.aggregate_into(hk, {"v_input": pv.array}, {"v": po.array}, hok)   # H2D, passes, D2H, sync
+                    return
                 g = sess.aggregate_into(hk, {"v_input": pv.array}, {"v": DA(out)}, DA(out_keys))
-                rk, (rv,) = exchange_groups(out_keys[:g], [out[:g]])
-                g2 = sess.aggregate_into(DA(rk), {"v_input": DA(rv)}, {"v": DA(out2)}, DA(out_keys2))
+                g2 = sess.aggregate_combine(ctx.comm, g, DA(out_keys), {"v": DA(out)}, {"v": DA(out2)}, DA(out_keys2))
                 torch.from_numpy(po.array)[:g2].copy_(out2[:g2])
                 torch.from_numpy(pok.array)[:g2].copy_(out_keys2[:g2])
                 torch.cuda.synchronize()
-                return g2
+                g_last[0] = g2
 
             k_e2e = max(1, min(args.steps, 3))
-            g_e2e = e2e_step()
-            if world > 1:
-                dist.barrier()
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            for _ in range(k_e2e):
-                g_e2e = e2e_step()
-            torch.cuda.synchronize()
-            if world > 1:
-                dist.barrier()
-            dt = time.perf_counter() - t0
-            td = torch.tensor([dt], dtype=torch.float64, device=device)
-            if world > 1:
-                dist.all_reduce(td, op=dist.ReduceOp.MAX)
-            e2e = {"value": world * rows_e2e * k_e2e / float(td.item()), "unit": "rows/s", "steps": k_e2e,
-                   "rows_per_gpu": rows_e2e, "h2d_bytes_per_step": int(rows_e2e * 264),
-                   "d2h_bytes_per_step": int(g_e2e * 264)}
+            dt = ctx.e2e_timed(e2e_step, k_e2e)
+            e2e = {"value": world * rows_e2e * k_e2e / dt, "unit": "rows/s", "steps": k_e2e, "rows_per_gpu": rows_e2e,
+                   "h2d_bytes_per_step": int(rows_e2e * 264), "d2h_bytes_per_step": int(g_last[0] * 264),
+                   "h2d_gbs_per_gpu": rows_e2e * 264 * k_e2e / dt / 1e9}
         except Exception as exc:
-            e2e = {"value": None, "unit": "rows/s", "error": str(exc)[:200],
-                   "h2d_bytes_per_step": int(rows_e2e * 264), "d2h_bytes_per_step": 0}
+            e2e = {"value": None, "unit": "rows/s", "error": str(exc)[:200], "h2d_bytes_per_step": int(rows_e2e * 264), "d2h_bytes_per_step": 0}
     cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu:
+    if ctx.rank == 0 and world == 1 and not args.no_cpu:
         from oracle import cpu_baseline as cb
         cores = cb.cores()
-        hk_np = host["keys"] if host else keys[:rows_e2e].cpu().numpy()
-        hv_np = host["v_input"] if host else v[:rows_e2e].cpu().numpy()
-        probe = min(rows_e2e, 2_000_000)
-        t, _ = cb.timed(cb.aggregate_sum, hk_np[:probe], hv_np[:probe], cores, cores, KEYS_C4)
-        sample = int(min(rows_e2e, max(probe, 12.0 / max(t, 1e-6) * probe / 3)))
-        t, _ = cb.timed(cb.aggregate_sum, hk_np[:sample], hv_np[:sample], cores, cores, KEYS_C4, repeat=3)
+        avail = rows_e2e if host else min(rows, 4_000_000)
+        hc = host if host else host_columns("c4", 0, avail)
+        hk_np, hv_np = hc["keys"], hc["v_input"]
+        sample, t, _ = cpu_sample(lambda r: cb.aggregate_sum(hk_np[:r], hv_np[:r], cores, cores, KEYS_C4), avail, 2_000_000)
         cpu = {"value": sample / t, "unit": "rows/s", "cores": cores, "kind": "port",
                "sample": f"first {sample} rows of the same block, {cores} partitions on {cores} threads (per-partition hash "
                          "aggregation + merge), best of 3; columnar unboxed input, so an upper bound on the JVM reference"}
+        # oracle on a prefix block regenerated on the host: keys bit-exact, sums within 1e-5 of an f64 group-by
+        n_chk = min(rows, 1 << 19)
+        hcc = host_columns("c4", 0, n_chk)
+        assert np.array_equal(hcc["keys"], keys[:n_chk].cpu().numpy()) and np.array_equal(hcc["v_input"][:4096], v[:4096].cpu().numpy())
+        uk, inv = np.unique(hcc["keys"], return_inverse=True)
+        want = np.zeros((len(uk), 64))
+        np.add.at(want, inv, hcc["v_input"].astype(np.float64))
+        ok_t = torch.empty(len(uk), dtype=torch.int64, device=device)
+        o_t = torch.empty((len(uk), 64), dtype=torch.float32, device=device)
+        g = sess.aggregate_into(DA(keys[:n_chk]), {"v_input": DA(v[:n_chk])}, {"v": DA(o_t)}, DA(ok_t))
+        assert g == len(uk) and np.array_equal(ok_t.cpu().numpy(), uk)
+        assert np.all(np.abs(o_t.cpu().numpy().astype(np.float64) - want) <= 1e-5 * np.maximum(want, 1e-30))
+        parity["oracle_prefix_rows"] = n_chk
+        parity["oracle"] = "keys bit-exact, sums within 1e-5 of an f64 group-by on host-regenerated values"
     host = {}
     for pb in pinned:
         pb.free()
-    if rank == 0:
-        peak, peak_src = hbm_peak()
-        step_s = elapsed_ms / 1e3 / args.steps
-        achieved = rows * 264 / step_s / 1e9
-        print(json.dumps({
-            "metric": "rows/s for aggregate (groupBy int64 key, reduce_sum over FloatType[?,64])",
-            "value": world * rows / step_s, "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"BASELINE configs[3]: aggregate groupBy int64 key ({n_groups} distinct), reduce_sum "
-                                   f"FloatType[?,64], {rows} rows per GPU (config names 5e8; reduced to bound memory)",
-                       "rows_per_gpu": rows, "l2": "inputs larger than L2 (no flush needed)", "exchange": "none" if world == 1 else "key-owner all_to_all of partial groups + merge aggregate"},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": ncu_traffic("c4", rows), "peak_source": peak_src, "kernel": "whole step (insert, table scan, pair sort, gather-reduce; agg_gather_reduce_kernel dominant)",
-                         "algorithmic_bytes_per_launch": rows * 264.0, "frac_of_nominal_8000": achieved / 8000.0},
-            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks.summary(), "cpu_baseline": cpu}))
-    if world > 1:
-        dist.destroy_process_group()
+    peak, peak_src = hbm_peak()
+    step_s = elapsed_ms / 1e3 / args.steps
+    achieved = rows * 264 / step_s / 1e9
+    traffic, tsrc = ncu_traffic("c4", rows)
+    roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+            "traffic_source": tsrc, "peak_source": peak_src,
+            "kernel": "whole step (insert, table scan, row partition, gather-reduce; agg_gather_reduce_kernel dominant)",
+            "algorithmic_bytes_per_launch": rows * 264.0, "avg_launch_ms": step_s * 1e3, "frac_of_nominal_8000": achieved / 8000.0}
+    ex = "none" if world == 1 else "key-owner exchange of partial groups + merge behind the C ABI (tfs_session_aggregate_combine)"
+    cfg = {"exchange": ex, "distinct_keys": int(n_groups)}
+    if tried:
+        cfg["sizes_that_failed"] = tried
+    rec = record(ctx, "c4", rows, elapsed_ms, clocks, launches, roof, e2e, cpu, parity, cfg, host_enqueue_ms_per_step=host_ms)
+    sess.close()
+    graph.close()
+    return rec
 
 
-def run_c5(args, torch, dist, _native, world, rank, local, device, rows):
-    """BASELINE config 5: map_blocks with MatMul(x[rows,256], W[256,256]) + bias on the tcgen05 path."""
-    DA = _native.DeviceArray.from_torch
-    graph = _native.Graph(build_graph("c5"))
-    sess = _native.Session(graph, local)
-    stream = torch.cuda.Stream(device=device)
-    torch.cuda.set_stream(stream)
-    sess.set_stream(stream.cuda_stream)
-    g = torch.Generator(device=device)
-    g.manual_seed(5 + 1000 * rank)
-    x = torch.rand((rows, 256), generator=g, device=device, dtype=torch.float32)
+# ---------------------------------------------------------------------------------------------
+def run_c5(ctx, rows):
+    torch, DA, args = ctx.torch, ctx.DA, ctx.args
+    world, device = ctx.world, ctx.device
+    graph, sess = ctx.session("c5")
+    x = device_columns(torch, "c5", ctx.rank * rows, rows, device)["x"]
     y = torch.empty((rows, 256), dtype=torch.float32, device=device)
+    torch.cuda.synchronize()
 
-    def step():
+    def step(timed):
         sess.run_into({"x": DA(x)}, {"y": DA(y)})
 
-    for _ in range(args.warmup):
-        step()
-    torch.cuda.synchronize()
     launches0 = sess.launch_count
-    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clocks:
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-        start.record(stream)
-        for _ in range(args.steps):
-            step()
-        end.record(stream)
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-    elapsed_ms = start.elapsed_time(end)
-    tt = torch.tensor([elapsed_ms], dtype=torch.float64, device=device)
-    if world > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    elapsed_ms = float(tt.item())
-    launches = sess.launch_count - launches0
-    # parity spot check against float64 on a slice (normwise 1e-5)
-    rng = np.random.default_rng(5)
-    w = torch.from_numpy(rng.uniform(-1 / 16, 1 / 16, (256, 256)).astype(np.float32)).to(device)
-    b = torch.from_numpy(rng.uniform(-1, 1, 256).astype(np.float32)).to(device)
-    xs = x[:65536].double()
-    exact = xs @ w.double() + b.double()
-    scale = xs.abs() @ w.double().abs() + b.double().abs()
-    assert torch.all((y[:65536].double() - exact).abs() <= 1e-5 * scale)
-    # ---- end to end: pinned host block in, pinned host block out (bounded block; PCIe-bound) ---------
-    e2e = None
+    elapsed_ms, clocks, host_ms = ctx.timed(step)
+    launches = (sess.launch_count - launches0) * args.steps // (args.steps + args.warmup)
+    # parity against float64 on slices at both ends and the middle (normwise 1e-5)
+    w_np, b_np = c5_constants()
+    w, b = torch.from_numpy(w_np).to(device), torch.from_numpy(b_np).to(device)
+    for lo in (0, rows // 2, max(0, rows - 65536)):
+        xs = x[lo:lo + 65536].double()
+        exact = xs @ w.double() + b.double()
+        scale = xs.abs() @ w.double().abs() + b.double().abs()
+        assert torch.all((y[lo:lo + 65536].double() - exact).abs() <= 1e-5 * scale)
+    parity = {"full_block_vs_torch": "three 65536-row slices within 1e-5 (normwise) of an f64 product"}
     rows_e2e = min(rows, 1 << 22)
-    pinned = []
-    hx = None
+    e2e, pinned, hx = None, [], None
     if not args.no_e2e:
         try:
-            px = _native.PinnedBuffer((rows_e2e, 256), np.float32); pinned.append(px)
-            py = _native.PinnedBuffer((rows_e2e, 256), np.float32); pinned.append(py)
-            torch.from_numpy(px.array).copy_(x[:rows_e2e])
+            px = ctx.pinned((rows_e2e, 256), np.float32, x[:rows_e2e]); pinned.append(px)
+            py = ctx.pinned((rows_e2e, 256), np.float32); pinned.append(py)
             hx = px.array
             k_e2e = max(1, min(args.steps, 3))
-            sess.run_into({"x": px.array}, {"y": py.array})
-            if world > 1:
-                dist.barrier()
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            for _ in range(k_e2e):
-                sess.run_into({"x": px.array}, {"y": py.array})      # H2D + kernel + D2H + sync inside
-            if world > 1:
-                dist.barrier()
-            dt = time.perf_counter() - t0
-            td = torch.tensor([dt], dtype=torch.float64, device=device)
-            if world > 1:
-                dist.all_reduce(td, op=dist.ReduceOp.MAX)
+            dt = ctx.e2e_timed(lambda: sess.run_into({"x": px.array}, {"y": py.array}), k_e2e)
             assert np.array_equal(py.array[:4096], y[:4096].cpu().numpy())
-            e2e = {"value": world * rows_e2e * k_e2e / float(td.item()), "unit": "rows/s", "steps": k_e2e,
-                   "rows_per_gpu": rows_e2e, "h2d_bytes_per_step": int(rows_e2e * 1024), "d2h_bytes_per_step": int(rows_e2e * 1024)}
+            e2e = {"value": world * rows_e2e * k_e2e / dt, "unit": "rows/s", "steps": k_e2e, "rows_per_gpu": rows_e2e,
+                   "h2d_bytes_per_step": int(rows_e2e * 1024), "d2h_bytes_per_step": int(rows_e2e * 1024),
+                   "h2d_gbs_per_gpu": rows_e2e * 1024 * k_e2e / dt / 1e9}
         except Exception as exc:
             e2e = {"value": None, "unit": "rows/s", "error": str(exc)[:200],
                    "h2d_bytes_per_step": int(rows_e2e * 1024), "d2h_bytes_per_step": int(rows_e2e * 1024)}
     cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu:
-        from oracle import cpu_baseline as cb
+    if ctx.rank == 0 and world == 1 and not args.no_cpu:
+        from oracle import cpu_baseline as cb, tf_ops
         cores = cb.cores()
-        xs_np = hx if hx is not None else x[:rows_e2e].cpu().numpy()
-        w_np, b_np = w.cpu().numpy(), b.cpu().numpy()
-        probe = min(rows_e2e, 65536)
-        t, _ = cb.timed(cb.matmul_bias, xs_np[:probe], w_np, b_np, cores, cores)
-        sample = int(min(rows_e2e, max(probe, 12.0 / max(t, 1e-6) * probe / 3)))
-        t, _ = cb.timed(cb.matmul_bias, xs_np[:sample], w_np, b_np, cores, cores, repeat=3)
+        avail = rows_e2e if hx is not None else min(rows, 262_144)
+        xs_np = hx if hx is not None else host_columns("c5", 0, avail)["x"]
+        sample, t, _ = cpu_sample(lambda r: cb.matmul_bias(xs_np[:r], w_np, b_np, cores, cores), avail, 65536)
         cpu = {"value": sample / t, "unit": "rows/s", "cores": cores, "kind": "port",
                "sample": f"first {sample} rows of the same block, {cores} partitions on {cores} threads, best of 3; "
                          "plain C loops (the reference's TF-CPU build calls Eigen's GEMM, which would be faster than this port)"}
+        n_chk = 4096
+        hc = host_columns("c5", 0, n_chk)
+        (want,) = tf_ops.evaluate(build_graph("c5"), hc, ["y"])
+        scale = np.abs(hc["x"].astype(np.float64)) @ np.abs(w_np.astype(np.float64)) + np.abs(b_np)
+        assert np.all(np.abs(y[:n_chk].cpu().numpy().astype(np.float64) - want.astype(np.float64)) <= 2e-5 * scale)
+        parity["oracle_prefix_rows"] = n_chk
+        parity["oracle"] = "within 1e-5 (normwise, each side) of oracle.tf_ops' MatMul on host-regenerated values"
     hx = None
     for pb in pinned:
         pb.free()
-    if rank == 0:
-        peaks = {}
+    pk = peaks()
+    bf16 = float(pk.get("bf16_tflops_sustained", 1400.0))
+    step_s = elapsed_ms / 1e3 / args.steps
+    tflops = rows * FLOP_PER_ROW_C5 / step_s / 1e12
+    hbm, _ = hbm_peak()
+    traffic, tsrc = ncu_traffic("c5", rows)
+    roof = {"bound": "tensor", "achieved": tflops, "peak": bf16, "unit": "TFLOP/s", "frac": tflops / bf16,
+            "traffic": traffic, "traffic_source": tsrc,
+            "peak_source": "measured bf16 sustained; tf32 runs at half of it and each fp32 product costs 3 tf32 MMAs, "
+                           "so the attainable ceiling is ~peak/6",
+            "kernel": "matmul_tc_pair_kernel", "mma_tflops_issued": 3 * tflops, "frac_of_attainable_peak_over_6": tflops / (bf16 / 6),
+            "avg_launch_ms": step_s * 1e3, "hbm_gbs": rows * 2048.0 / step_s / 1e9, "hbm_frac": rows * 2048.0 / step_s / 1e9 / hbm,
+            "ncu_tensor_pipe_active_pct_of_elapsed": ncu_extra("c5", "tensor_pipe_active_pct_of_elapsed")}
+    rec = record(ctx, "c5", rows, elapsed_ms, clocks, launches, roof, e2e, cpu, parity, {"exchange": "none"},
+                 host_enqueue_ms_per_step=host_ms)
+    sess.close()
+    graph.close()
+    return rec
+
+
+def run_ours(args):
+    ctx = Ctx(args)
+    torch = ctx.torch
+    todo = ALL if args.workload == "all" else [args.workload]
+    recs = {}
+    shared_x = None
+    for wl in todo:
+        rows = args.rows or ROWS[wl]
         try:
-            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-                peaks = json.load(f)
-        except Exception:
-            pass
-        bf16 = float(peaks.get("bf16_tflops_sustained", 1400.0))
-        step_s = elapsed_ms / 1e3 / args.steps
-        tflops = rows * 131072.0 / step_s / 1e12
-        hbm, _ = hbm_peak()
-        print(json.dumps({
-            "metric": "rows/s for mapBlocks (MatMul FloatType[?,256] x 256x256 + bias)",
-            "value": world * rows / step_s, "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32 (3xTF32 on tcgen05, fp32 accumulate)", "data": "synthetic",
-            "config": {"workload": f"BASELINE configs[4]: map_blocks matmul FloatType[?,256] x 256x256 + bias, {rows} rows per GPU",
-                       "rows_per_gpu": rows, "l2": "inputs larger than L2 (no flush needed)", "exchange": "none"},
-            "roofline": {"bound": "tensor", "achieved": tflops, "peak": bf16, "unit": "TFLOP/s", "frac": tflops / bf16,
-                         "traffic": ncu_traffic("c5", rows), "peak_source": "measured bf16 sustained; tf32 runs at half of it and "
-                         "each fp32 product costs 3 tf32 MMAs, so the attainable ceiling is ~peak/6",
-                         "kernel": "matmul_tc_pair_kernel", "mma_tflops_issued": 3 * tflops,
-                         "hbm_gbs": rows * 2048.0 / step_s / 1e9, "hbm_frac": rows * 2048.0 / step_s / 1e9 / hbm,
-                         "ncu_tensor_pipe_active_pct_of_elapsed": ncu_extra("c5", "tensor_pipe_active_pct_of_elapsed")},
-            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks.summary(), "cpu_baseline": cpu}))
-    if world > 1:
-        dist.destroy_process_group()
+            if wl == "c2":
+                recs[wl] = run_reduce(ctx, "c2", rows)
+            elif wl == "c3":
+                # the 1e9-row column is generated once and shared with reduce_1b
+                if "reduce_1b" in todo and (args.rows or ROWS["reduce_1b"]) == rows:
+                    shared_x = device_columns(torch, "c3", ctx.rank * rows, rows, ctx.device)
+                recs[wl] = run_c3(ctx, rows, shared_x)
+            elif wl == "reduce_1b":
+                recs[wl] = run_reduce(ctx, "reduce_1b", rows, shared_x)
+                shared_x = None
+            elif wl == "c4":
+                recs[wl] = run_c4(ctx, rows)
+            else:
+                recs[wl] = run_c5(ctx, rows)
+        except Exception as exc:      # one workload failing must not take the headline line with it
+            if wl == todo[0]:
+                raise
+            import traceback
+            recs[wl] = {"metric": METRIC[wl], "value": None, "error": (str(exc) or repr(exc))[:300],
+                        "where": traceback.format_exc().strip().splitlines()[-3:]}
+        if wl != "c3":
+            shared_x = None
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
+    if ctx.rank == 0:
+        line = dict(recs[todo[0]])
+        if len(todo) > 1:
+            line["configs"] = {wl: recs[wl] for wl in todo[1:]}
+        print(json.dumps(line))
+    if ctx.comm is not None:
+        ctx.comm.close()
+    if ctx.world > 1:
+        ctx.dist.destroy_process_group()
 
 
-def cpu_baseline_leg(wl, host_feeds, rows, budget_s=12.0):
-    """oracle/cpu_ref.c on a bounded sample: the whole block if it finishes within the budget,
-    else a prefix sized from a calibration run."""
+# ---------------------------------------------------------------------------------------------
+REF_ROWS = {"c2": 100_000_000, "c3": 100_000_000, "reduce_1b": 100_000_000, "c4": 4_000_000, "c5": 262_144}
+
+
+def reference_record(args, wl, steps, warmup):
+    """oracle/cpu_ref.c on all host threads, one bounded block per step (same generator as the GPU arm)."""
     from oracle import cpu_baseline as cb
     cores = cb.cores()
+    rows_full = args.rows or ROWS[wl]
+    sample = min(rows_full, REF_ROWS[wl])
+    cols = host_columns("c3" if wl == "reduce_1b" else wl, 0, sample)
     if wl == "c2":
-        y, z = host_feeds["y_input"], host_feeds["z_input"]
-        probe = min(rows, 2_000_000)
-        t, _ = cb.timed(cb.reduce_blocks_sum_min, y[:probe], z[:probe], cores, cores)
-        sample = int(min(rows, max(probe, budget_s / max(t, 1e-6) * probe / 3)))
-        t, (s, m) = cb.timed(cb.reduce_blocks_sum_min, y[:sample], z[:sample], cores, cores, repeat=3)
-    else:
-        x = host_feeds["x"]
-        probe = min(rows, 4_000_000)
-        t, _ = cb.timed(cb.map_blocks_chain, x[:probe], 1.5, 0.25, cores, cores)
-        sample = int(min(rows, max(probe, budget_s / max(t, 1e-6) * probe / 3)))
-        t, _ = cb.timed(cb.map_blocks_chain, x[:sample], 1.5, 0.25, cores, cores, repeat=3)
-    return {"value": sample / t, "unit": "rows/s", "cores": cores, "kind": "port",
-            "sample": f"first {sample} rows of the same block, {cores} partitions on {cores} threads, best of 3; "
-                      "columnar unboxed input, so an upper bound on the JVM reference"}
-
-
-def run_reference(args):
-    """The reference arm: the restatement of the reference's own CPU algorithm (oracle/cpu_ref.c),
-    all host threads, same workload / metric / unit. Rank 0 only."""
-    rank = env_int("RANK", 0)
-    if rank != 0:
-        return
-    from oracle import cpu_baseline as cb
-    wl = args.workload
-    cores = cb.cores()
-    rows_full = args.rows or {"c2": ROWS_C2, "c3": ROWS_C3, "c4": ROWS_C4, "c5": ROWS_C5}[wl]
-    rng = np.random.default_rng({"c2": 2, "c3": 3, "c4": 4, "c5": 5}[wl])
-    # bounded sample: sized so that warmup + steps stay within a few minutes
-    sample = min(rows_full, {"c2": 20_000_000, "c3": 50_000_000, "c4": 4_000_000, "c5": 262_144}[wl])
-    if wl == "c2":
-        u = rng.random(sample)
-        y = np.stack([u, -u], axis=1)
-        u = rng.random(sample)
-        z = np.stack([u, -u], axis=1)
-        fn = lambda: cb.reduce_blocks_sum_min(y, z, cores, cores)
+        fn = lambda: cb.reduce_blocks_sum_min(cols["y_input"], cols["z_input"], cores, cores)
+    elif wl == "reduce_1b":
+        x2 = cols["x"].reshape(-1, 1)
+        fn = lambda: cb.reduce_blocks_sum_min(x2, x2, cores, cores)
     elif wl == "c3":
-        x = rng.random(sample) * 2.0 - 1.0
-        fn = lambda: cb.map_blocks_chain(x, 1.5, 0.25, cores, cores)
+        fn = lambda: cb.map_blocks_chain(cols["x"], 1.5, 0.25, cores, cores)
     elif wl == "c4":
-        table = np.unique(rng.integers(-2**62, 2**62, KEYS_C4, dtype=np.int64))
-        keys = table[rng.integers(0, table.size, sample)]
-        v = rng.random((sample, 64), dtype=np.float32)
-        fn = lambda: cb.aggregate_sum(keys, v, cores, cores, KEYS_C4)
+        fn = lambda: cb.aggregate_sum(cols["keys"], cols["v_input"], cores, cores, KEYS_C4)
     else:
-        w = rng.uniform(-1 / 16, 1 / 16, (256, 256)).astype(np.float32)
-        b = rng.uniform(-1, 1, 256).astype(np.float32)
-        x = rng.random((sample, 256), dtype=np.float32)
-        fn = lambda: cb.matmul_bias(x, w, b, cores, cores)
-    for _ in range(args.warmup):
+        w, b = c5_constants()
+        fn = lambda: cb.matmul_bias(cols["x"], w, b, cores, cores)
+    for _ in range(warmup):
         fn()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
+    for _ in range(steps):
         fn()
     dt = time.perf_counter() - t0
-    value = sample * args.steps / dt
-    desc = (f"{sample} rows per step (bounded sample of the {rows_full}-row block), {cores} partitions on "
-            f"{cores} threads; oracle/cpu_ref.c restates the reference's per-block algorithm on columnar input "
-            "(Spark + TF-Java are not installable here)")
-    line = {
-        "impl": "reference",
-        "metric": {"c2": "rows/s for reduceBlocks (reduce_sum + reduce_min over DoubleType[?,2])",
-                   "c3": "rows/s for mapBlocks (fused x*a+b, max(.,0), cast f32 on a float64 column)",
-                   "c4": "rows/s for aggregate (groupBy int64 key, reduce_sum over FloatType[?,64])",
-                   "c5": "rows/s for mapBlocks (MatMul FloatType[?,256] x 256x256 + bias)"}[wl],
-        "value": value, "unit": "rows/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f64" if wl in ("c2", "c3") else "f32", "data": "synthetic",
-        "config": {"workload": {"c2": "BASELINE configs[1]: reduce_blocks reduce_sum+reduce_min, DoubleType[?,2], ",
-                                "c3": "BASELINE configs[2]: map_blocks fused chain, float64 column, ",
-                                "c4": "BASELINE configs[3]: aggregate groupBy int64 key, reduce_sum FloatType[?,64], ",
-                                "c5": "BASELINE configs[4]: map_blocks matmul FloatType[?,256] x 256x256 + bias, "}[wl]
-                               + f"{rows_full} rows per GPU", "rows_per_gpu": rows_full},
+    value = sample * steps / dt
+    same = sample == rows_full
+    desc = (f"{sample} rows per step ({'the whole block' if same else 'bounded sample of the ' + str(rows_full) + '-row block'}), "
+            f"{cores} partitions on {cores} threads; oracle/cpu_ref.c restates the reference's per-block algorithm on "
+            "columnar input (Spark + TF-Java are not installable here)")
+    return {
+        "impl": "reference", "metric": METRIC[wl], "value": value, "unit": "rows/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": warmup, "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": DTYPE[wl], "data": "synthetic (counter-based generator, SURVEY 8(d))",
+        "config": {"workload": WORKLOAD[wl] + f"{rows_full} rows per GPU", "rows_per_gpu": rows_full, "partitions": args.gpus,
+                   "l2": "inputs larger than L2 (no flush needed)", "exchange": "none"},
         "cpu_baseline": {"value": value, "unit": "rows/s", "cores": cores, "kind": "port", "sample": desc},
         "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+
+
+def run_reference(args):
+    """The reference arm: the restatement of the reference's own CPU algorithm (oracle/cpu_ref.c), all host threads,
+    same workloads / metric / unit.  Rank 0 only."""
+    if env_int("RANK", 0) != 0:
+        return
+    todo = ALL if args.workload == "all" else [args.workload]
+    line = reference_record(args, todo[0], args.steps, args.warmup)
+    if len(todo) > 1:
+        line["configs"] = {wl: reference_record(args, wl, max(1, min(args.steps, 5)), min(args.warmup, 1)) for wl in todo[1:]}
     print(json.dumps(line))
 
 
@@ -772,7 +1012,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4", "c5"])
+    ap.add_argument("--workload", default="all", choices=["all"] + ALL)
     ap.add_argument("--rows", type=int, default=0, help="rows per GPU (default: the BASELINE config's)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

@@ -24,6 +24,14 @@
  *     (impl/datatypes.scala:365-370,438-443,488-493,546-551) fetch buffers of _run
  *   TensorFlowUDAF update/merge/evaluate                  tfs_session_aggregate
  *     (impl/DebugRowOps.scala:601-695)
+ *   analyzeGraphTF: inputs, fetches, hinted shapes        tfs_graph_analyze
+ *     (impl/TensorFlowOps.scala:101-141)
+ *   transformRdd.reduce(reducePairBlock(...))             tfs_session_reduce_combine
+ *     (impl/DebugRowOps.scala:524-525, 741-750)
+ *   data.agg(udaf(...)): partial -> shuffle -> final      tfs_session_aggregate_combine
+ *     (impl/DebugRowOps.scala:573-576)
+ *   TensorConverter.append / convertBuffer1-3 loops       tfs_pack_rows / tfs_unpack_rows
+ *     (impl/DataOps.scala:63-81, impl/datatypes.scala:114-127, 204-256)
  *
  * Conventions
  *  - plain C, no callbacks, no C++/torch types; all sizes are int64.
@@ -42,12 +50,13 @@
  *    session must not run two calls at the same time (the reference uses one
  *    Session per task thread, impl/DebugRowOps.scala:783).
  *  - there is no CPU execution path: every run needs a CUDA device.
- *  - several GPUs: one session per device (any mix of processes and threads).  The library moves no data between
- *    devices; the exchange steps of the reference stay where they are -- RDD.reduce / the UDAF's shuffle on the JVM
- *    side (impl/DebugRowOps.scala:524-525, 573-576), torch.distributed in this repository's harness -- and their
- *    merge halves are the same two entry points on the gathered data: tfs_session_run on the stacked
- *    [n_partitions, cell...] partial rows (reducePairBlock, :741-750) and tfs_session_aggregate on the
- *    concatenated (key, partial row) pairs (TensorFlowUDAF.merge, :659-672).
+ *  - several GPUs: one session per device (any mix of processes and threads) and, for the operators that have an
+ *    exchange step, one communicator per session (tfs_comm_*, below).  mapBlocks needs none: partitions are
+ *    independent (impl/DebugRowOps.scala:377-391).  The exchange steps the reference hands to Spark -- RDD.reduce with
+ *    reducePairBlock (impl/DebugRowOps.scala:524-525, 741-750) and the UDAF's shuffle (:573-576) -- are
+ *    tfs_session_reduce_combine and tfs_session_aggregate_combine: NCCL over NVLink, driven from inside the library.
+ *    Feeds, fetch buffers and keys must be host memory or memory of the session's own device; memory of another
+ *    device is TFS_ERR_INVALID.
  */
 #ifndef TFS_B200_H
 #define TFS_B200_H
@@ -120,6 +129,31 @@ const char* tfs_graph_node_op(const tfs_graph* g, int i);
  * other output index is TFS_ERR_INVALID: only output 0 is addressable,
  * impl/TensorFlowOps.scala:127-129). */
 int tfs_graph_node_info(const tfs_graph* g, const char* name, tfs_node_info* out);
+
+/* analyzeGraphTF (impl/TensorFlowOps.scala:101-141) in one call: the summary of every input -- a Placeholder without
+ * inputs (:106-108) -- and of every requested fetch (names with or without a trailing ":0", :110), in GraphDef order.
+ * A shape hint for a node (looked up under `name`, then `name:0`) overrides the statically inferred shape (:124-133).
+ * A node whose rank is unknown and that has no hint is reported as a scalar (rank 0), which is what Shape.from does
+ * with TF's "unknown shape" (Shape.scala:107-109).  A requested fetch that is not in the graph is TFS_ERR_INVALID.
+ * `out` has room for `capacity` entries; *n_out is the number of summaries (also when it exceeds capacity, in which
+ * case only `capacity` are written).  `name` points into the graph and lives as long as it. */
+typedef struct tfs_shape_hint {
+  const char* name;
+  int32_t rank;
+  int64_t dims[TFS_MAX_RANK];
+} tfs_shape_hint;
+typedef struct tfs_node_summary {
+  const char* name;
+  int32_t dtype;
+  int32_t rank;
+  int64_t dims[TFS_MAX_RANK];
+  int32_t is_placeholder;
+  int32_t is_input;
+  int32_t is_output;
+  int32_t pad_;
+} tfs_node_summary;
+int tfs_graph_analyze(const tfs_graph* g, int n_hints, const tfs_shape_hint* hints, int n_fetches,
+                      const char* const* requested_fetches, int capacity, tfs_node_summary* out, int* n_out);
 
 /* ---- session: one graph bound to one device --------------------------------
  * Replaces new Session(graph) (impl/TensorFlowOps.scala:78).  The session owns
@@ -195,6 +229,49 @@ int tfs_session_aggregate(tfs_session* s, int64_t n_rows, const int64_t* keys,
                           int n_fetches, const tfs_tensor* fetches,
                           int64_t max_groups, int64_t* out_keys, int64_t* n_groups);
 
+/* ---- several GPUs: communicators and the exchange steps ---------------------------
+ * One partition per GPU.  A communicator is this rank's end of an NCCL clique (NCCL is loaded at run time --
+ * libnccl.so.2, or the name in TFS_NCCL_LIB; a process that never creates a communicator never loads it).
+ *   - one rank per process or thread: rank 0 calls tfs_comm_unique_id, the caller carries the 128 bytes to the other
+ *     ranks (Spark broadcast, a file, MPI...), then every rank calls tfs_comm_create -- collectively, like
+ *     ncclCommInitRank;
+ *   - one thread creating the communicators of n devices of one process: tfs_comm_create_all.  The exchange calls of
+ *     different ranks must still be made concurrently, one thread per device. */
+typedef struct tfs_comm tfs_comm;
+#define TFS_COMM_ID_BYTES 128
+int tfs_comm_unique_id(void* id_out);
+int tfs_comm_create(int device, int world, int rank, const void* id, tfs_comm** out);
+int tfs_comm_create_all(int n, const int* devices, tfs_comm** out);
+void tfs_comm_free(tfs_comm* c);
+int tfs_comm_world(const tfs_comm* c);
+int tfs_comm_rank(const tfs_comm* c);
+
+/* The exchange step of reduceBlocks = transformRdd.reduce(reducePairBlock(...)) (impl/DebugRowOps.scala:524-525,
+ * 741-750): `partials` are the fetches of this rank's tfs_session_run on its partition (device memory, named by fetch),
+ * `merged` receives the row reduced over every rank's partition -- on every rank (same shapes; may alias partials).
+ *   - fetches that are a Sum / Min / Max taken directly from their placeholder are combined by one grouped
+ *     ncclAllReduce; any other reducer graph by an all-gather of the rows and one more run of the graph on the stacked
+ *     [world, cell...] block (fetch X <- placeholder X_input, the reduce contract).
+ *   - overlap = 0: enqueued on the session's stream, in order.  overlap = 1 (all-reduce path only, rows of at most
+ *     64 KiB in total): the rows are copied to a ring slot and exchanged on the communicator's own stream, so the
+ *     exchange overlaps whatever the session runs next -- the next partition's kernels -- and `partials` may be
+ *     overwritten at once; `merged` is complete after tfs_session_combine_wait + tfs_session_sync.
+ * Collective: every rank calls it with the same fetches.  Returns without synchronising. */
+int tfs_session_reduce_combine(tfs_session* s, tfs_comm* c, int n_fetches, const tfs_tensor* partials,
+                               const tfs_tensor* merged, int overlap);
+/* the session's stream waits for the overlapped exchanges enqueued so far */
+int tfs_session_combine_wait(tfs_session* s, tfs_comm* c);
+
+/* The exchange step of aggregate = the shuffle between the UDAF's partial and final aggregation
+ * (impl/DebugRowOps.scala:573-576): `keys[n_groups]` and `partials` (dims[0] == n_groups, device memory) are this
+ * rank's tfs_session_aggregate result; every group is sent to the rank that owns its key (a fixed 64-bit mix of the
+ * key, modulo the number of ranks) and merged there by one more keyed reduction.  `merged` (dims[0] == max_groups,
+ * device or host), out_keys and *n_owned receive the groups this rank owns, in ascending key order; the result stays
+ * sharded by owner (the reference leaves row order unspecified).  Collective and synchronous. */
+int tfs_session_aggregate_combine(tfs_session* s, tfs_comm* c, int64_t n_groups, const int64_t* keys,
+                                  int n_fetches, const tfs_tensor* partials, const tfs_tensor* merged,
+                                  int64_t max_groups, int64_t* out_keys, int64_t* n_owned);
+
 /* ---- block reduction without any allocation ------------------------------------
  * (No counterpart in the reference: TF-Java gives its callers no say over allocation.)
  *
@@ -224,6 +301,14 @@ int tfs_reduce_axis0_noalloc(int device, void* cuda_stream, int32_t dtype, int32
  * the counterpart of TensorConverter.reserve (impl/datatypes.scala:334-338). */
 int tfs_host_alloc(size_t bytes, void** out);
 int tfs_host_free(void* p);
+
+/* Row <-> block packing = the loops of DataOps.convertFast0 / TensorConverter.append (impl/DataOps.scala:63-81,
+ * impl/datatypes.scala:85-127) and of convertBuffer1-3 (impl/datatypes.scala:204-256), for a caller that holds one
+ * array per row (a JVM binding pins each row's primitive array): rows[i] points at the `cell_elems` scalars of row i,
+ * `block` is the dense row-major [n_rows, cell_elems] buffer (ideally from tfs_host_alloc).  Plain copies on a few
+ * host threads; rows of a block share one cell shape, as the reference requires (impl/datatypes.scala:80-83). */
+int tfs_pack_rows(int32_t dtype, int64_t n_rows, int64_t cell_elems, const void* const* rows, void* block);
+int tfs_unpack_rows(int32_t dtype, int64_t n_rows, int64_t cell_elems, const void* block, void* const* rows);
 
 #ifdef __cplusplus
 }

@@ -43,6 +43,15 @@ class Tensor(C.Structure):
                 ("dims", C.c_int64 * TFS_MAX_RANK), ("data", C.c_void_p)]
 
 
+class ShapeHint(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("rank", C.c_int32), ("dims", C.c_int64 * TFS_MAX_RANK)]
+
+
+class NodeSummary(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("dtype", C.c_int32), ("rank", C.c_int32), ("dims", C.c_int64 * TFS_MAX_RANK),
+                ("is_placeholder", C.c_int32), ("is_input", C.c_int32), ("is_output", C.c_int32), ("pad_", C.c_int32)]
+
+
 # every symbol include/tfs_b200.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "tfs_last_error": (C.c_char_p, []),
@@ -54,6 +63,8 @@ SYMBOLS = {
     "tfs_graph_node_name": (C.c_char_p, [C.c_void_p, C.c_int]),
     "tfs_graph_node_op": (C.c_char_p, [C.c_void_p, C.c_int]),
     "tfs_graph_node_info": (C.c_int, [C.c_void_p, C.c_char_p, C.POINTER(NodeInfo)]),
+    "tfs_graph_analyze": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(ShapeHint), C.c_int, C.POINTER(C.c_char_p), C.c_int,
+                                    C.POINTER(NodeSummary), C.POINTER(C.c_int)]),
     "tfs_session_create": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]),
     "tfs_session_free": (None, [C.c_void_p]),
     "tfs_session_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
@@ -67,6 +78,18 @@ SYMBOLS = {
                                         C.POINTER(Tensor), C.c_int64, C.c_void_p, C.POINTER(C.c_int64)]),
     "tfs_reduce_axis0_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_int64,
                                            C.c_void_p]),
+    "tfs_comm_unique_id": (C.c_int, [C.c_void_p]),
+    "tfs_comm_create": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]),
+    "tfs_comm_create_all": (C.c_int, [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_void_p)]),
+    "tfs_comm_free": (None, [C.c_void_p]),
+    "tfs_comm_world": (C.c_int, [C.c_void_p]),
+    "tfs_comm_rank": (C.c_int, [C.c_void_p]),
+    "tfs_session_reduce_combine": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(Tensor), C.POINTER(Tensor), C.c_int]),
+    "tfs_session_combine_wait": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "tfs_session_aggregate_combine": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.POINTER(Tensor),
+                                                C.POINTER(Tensor), C.c_int64, C.c_void_p, C.POINTER(C.c_int64)]),
+    "tfs_pack_rows": (C.c_int, [C.c_int32, C.c_int64, C.c_int64, C.POINTER(C.c_void_p), C.c_void_p]),
+    "tfs_unpack_rows": (C.c_int, [C.c_int32, C.c_int64, C.c_int64, C.c_void_p, C.POINTER(C.c_void_p)]),
     "tfs_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
     "tfs_host_free": (C.c_int, [C.c_void_p]),
 }
@@ -99,6 +122,79 @@ def _check(status: int) -> None:
 
 def device_count() -> int:
     return int(lib().tfs_device_count())
+
+
+COMM_ID_BYTES = 128
+
+
+def comm_unique_id() -> bytes:
+    """The 128-byte rendezvous token rank 0 draws and the caller carries to the other ranks (tfs_comm_unique_id)."""
+    buf = (C.c_char * COMM_ID_BYTES)()
+    _check(lib().tfs_comm_unique_id(buf))
+    return bytes(buf.raw)
+
+
+class Comm:
+    """This rank's end of the exchange steps (tfs_comm_create): one partition per GPU, NCCL behind the C ABI."""
+
+    def __init__(self, device: int, world: int, rank: int, ident: bytes, _handle=None):
+        self._h = C.c_void_p()
+        if _handle is not None:
+            self._h = _handle
+            return
+        if len(ident) != COMM_ID_BYTES:
+            raise ValueError(f"communicator id must be {COMM_ID_BYTES} bytes")
+        _check(lib().tfs_comm_create(device, world, rank, ident, C.byref(self._h)))
+
+    @staticmethod
+    def create_all(devices: Sequence[int]) -> List["Comm"]:
+        """The communicators of several devices of this process, created by one thread (tfs_comm_create_all)."""
+        n = len(devices)
+        out = (C.c_void_p * n)()
+        _check(lib().tfs_comm_create_all(n, (C.c_int * n)(*devices), out))
+        return [Comm(0, 0, 0, b"", _handle=C.c_void_p(out[i])) for i in range(n)]
+
+    @property
+    def handle(self):
+        return self._h
+
+    @property
+    def world(self) -> int:
+        return int(lib().tfs_comm_world(self._h))
+
+    @property
+    def rank(self) -> int:
+        return int(lib().tfs_comm_rank(self._h))
+
+    def close(self) -> None:
+        if self._h:
+            lib().tfs_comm_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def pack_rows(rows: Sequence[np.ndarray], out: np.ndarray) -> None:
+    """Dense [n_rows, cell] block from one array per row (tfs_pack_rows)."""
+    st = scalar_type_from_numpy(out.dtype)
+    n = len(rows)
+    cell = int(out.size // n) if n else 0
+    keep = [np.ascontiguousarray(r, dtype=out.dtype) for r in rows]
+    ptrs = (C.c_void_p * max(n, 1))(*[k.ctypes.data for k in keep])
+    _check(lib().tfs_pack_rows(st.tf_code, n, cell, ptrs, C.c_void_p(out.ctypes.data)))
+
+
+def unpack_rows(block: np.ndarray, rows: Sequence[np.ndarray]) -> None:
+    """The inverse of pack_rows: row i of the block is copied into rows[i] (tfs_unpack_rows)."""
+    st = scalar_type_from_numpy(block.dtype)
+    n = len(rows)
+    cell = int(block.size // n) if n else 0
+    ptrs = (C.c_void_p * max(n, 1))(*[r.ctypes.data for r in rows])
+    _check(lib().tfs_unpack_rows(st.tf_code, n, cell, C.c_void_p(block.ctypes.data), ptrs))
 
 
 class DeviceArray:
@@ -168,6 +264,23 @@ class Graph:
         _check(lib().tfs_graph_node_info(self._h, name.encode(), C.byref(info)))
         shape = None if info.rank < 0 else Shape([info.dims[i] for i in range(info.rank)])
         return scalar_type_from_tf(info.dtype), shape, bool(info.is_placeholder), int(info.n_inputs)
+
+    def analyze(self, hints: Dict[str, Sequence[int]], requested_fetches: Sequence[str]):
+        """analyzeGraphTF in the library (tfs_graph_analyze): [(name, ScalarType, Shape, is_placeholder, is_input,
+        is_output)] for every input and requested fetch, hinted shapes winning over inferred ones."""
+        harr = (ShapeHint * max(1, len(hints)))()
+        for i, (name, dims) in enumerate(hints.items()):
+            harr[i].name = name.encode()
+            harr[i].rank = len(dims)
+            for d, v in enumerate(dims):
+                harr[i].dims[d] = int(v)
+        farr = (C.c_char_p * max(1, len(requested_fetches)))(*[f.encode() for f in requested_fetches])
+        cap = lib().tfs_graph_num_nodes(self._h)
+        out = (NodeSummary * max(1, cap))()
+        n = C.c_int(0)
+        _check(lib().tfs_graph_analyze(self._h, len(hints), harr, len(requested_fetches), farr, cap, out, C.byref(n)))
+        return [(out[i].name.decode(), scalar_type_from_tf(out[i].dtype), Shape([out[i].dims[d] for d in range(out[i].rank)]),
+                 bool(out[i].is_placeholder), bool(out[i].is_input), bool(out[i].is_output)) for i in range(n.value)]
 
 
 class Session:
@@ -301,6 +414,31 @@ class Session:
         _check(lib().tfs_session_aggregate(self._h, keys.shape[0], C.c_void_p(keys.ptr), len(feeds), farr, len(fetches),
                                            oarr, out_keys.shape[0], C.c_void_p(out_keys.ptr), C.byref(n_groups)))
         return int(n_groups.value)
+
+
+    # ---- exchange steps over a communicator (one partition per GPU) ----------------------------------------
+    def reduce_combine(self, comm: "Comm", partials: Dict[str, DeviceArray], merged: Dict[str, DeviceArray],
+                       overlap: bool = False) -> None:
+        """The exchange step of reduce_blocks (tfs_session_reduce_combine): `merged` receives the rows reduced over
+        every rank's partition.  overlap=True leaves the exchange running on the communicator's stream."""
+        parr, keep = self._feed_array(partials)
+        marr, keep2 = self._feed_array({k: merged[k] for k in partials})
+        _check(lib().tfs_session_reduce_combine(self._h, comm.handle, len(partials), parr, marr, 1 if overlap else 0))
+
+    def combine_wait(self, comm: "Comm") -> None:
+        _check(lib().tfs_session_combine_wait(self._h, comm.handle))
+
+    def aggregate_combine(self, comm: "Comm", n_groups: int, keys: DeviceArray, partials: Dict[str, DeviceArray],
+                          merged: Dict[str, object], out_keys: DeviceArray) -> int:
+        """The exchange step of aggregate (tfs_session_aggregate_combine).  partials[name] holds n_groups rows (a
+        larger buffer is fine: only the first n_groups rows are sent).  Returns the number of groups this rank owns."""
+        trimmed = {k: DeviceArray(v.ptr, v.dtype, (n_groups,) + tuple(v.shape[1:]), owner=v.owner) for k, v in partials.items()}
+        parr, keep = self._feed_array(trimmed)
+        marr, keep2 = self._feed_array({k: merged[k] for k in partials})
+        n_owned = C.c_int64(0)
+        _check(lib().tfs_session_aggregate_combine(self._h, comm.handle, n_groups, C.c_void_p(keys.ptr), len(partials), parr, marr,
+                                                   out_keys.shape[0], C.c_void_p(out_keys.ptr), C.byref(n_owned)))
+        return int(n_owned.value)
 
 
 class PinnedBuffer:

@@ -34,6 +34,31 @@ struct PerDeviceOnce {
   }
 };
 
+// Where a caller's pointer lives: kHostMemory (pageable or pinned host memory, or unknown to CUDA), kManagedMemory,
+// or the ordinal of the device that owns the allocation.
+constexpr int kHostMemory = -1, kManagedMemory = -2;
+inline int pointer_location(const void* p) {
+  if (p == nullptr) return kHostMemory;
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return kHostMemory;
+  }
+  if (a.type == cudaMemoryTypeManaged) return kManagedMemory;
+  return a.type == cudaMemoryTypeDevice ? a.device : kHostMemory;
+}
+// true: device memory of `device` (or managed memory); false: host memory.  Memory of ANOTHER device is refused: the
+// kernels (and the tensor maps of the MatMul path) address this GPU's memory only, the library moves nothing between
+// devices behind the caller's back.
+inline bool on_device_or_refuse(const void* p, int device, const std::string& what) {
+  const int loc = pointer_location(p);
+  if (loc == kHostMemory) return false;
+  TFS_CHECK(loc == kManagedMemory || loc == device, TFS_ERR_INVALID,
+            what + " lives on device " + std::to_string(loc) + " but the call runs on device " + std::to_string(device) +
+                ": pass memory of that device, or host memory");
+  return true;
+}
+
 struct DeviceInfo {
   int device = 0;
   int sm_count = 148;
@@ -84,16 +109,31 @@ int launch_split_weights(const float* w, bool transposed, int64_t K, int64_t N, 
 int launch_matmul_tc(const float* x, const float* w_hi, const float* w_lo, const float* bias, float* out, int64_t M,
                      int64_t N, int64_t K, const DeviceInfo& dev, cudaStream_t stream);
 
+// Stable radix partition passes (kernels_radix.cu): n (key, value) pairs ordered by `bits` (<= 11) key bits from `shift`
+// up; keys are 4 or 8 bytes (xor_mask is applied before the digit is taken: the sign bit for signed order), values 4 or
+// 8 bytes, or -- vals_in null, 4-byte values -- the element's own index.  keys_out may be null.  `scratch` holds
+// radix_scratch_bytes().  launch_radix_sort chains ceil(bits / 11) passes from `keys_in / vals_in` through the two
+// buffer pairs and returns the index of the pair that holds the result (the last pass writes keys only if want_keys).
+size_t radix_scratch_bytes(const DeviceInfo& dev);
+int radix_passes(int bits);
+int launch_radix_pass(int key_bytes, int val_bytes, const void* keys_in, const void* vals_in, void* keys_out, void* vals_out,
+                      int64_t n, uint64_t xor_mask, int shift, int bits, void* scratch, const DeviceInfo& dev, cudaStream_t stream);
+int launch_radix_sort(int key_bytes, int val_bytes, const void* keys_in, const void* vals_in, void* keys_buf[2], void* vals_buf[2],
+                      int64_t n, uint64_t xor_mask, int bits, bool want_keys, void* scratch, const DeviceInfo& dev, cudaStream_t stream,
+                      int* launches);
+
 // K3: keyed block reduction. Scratch layout for n_rows rows and at most max_groups groups.
 struct AggLayout {
   uint64_t table_slots;
   size_t off_header, off_slot_key, off_counts, off_offsets, off_group_slot, off_tile_sums, off_perm, off_sort_temp;
   size_t off_group_slot_tab, off_keys_tab;   // groups in table order, before they are sorted by key
-  size_t off_row_slot[2], off_row_id[2];   // (slot, row) u32 pairs, ping-pong buffers of the sort
+  size_t off_row_slot[3];   // [0] the slot column written by the insert pass, [1] / [2] the slot column between passes
+  size_t off_row_id[2];     // row-index columns of the partition (ping-pong)
+  size_t off_group_tmp_keys, off_group_tmp_slot;   // second (key, slot) column pair of the group sort
   size_t sort_temp_bytes;
   size_t bytes;
 };
-AggLayout agg_layout(int64_t n_rows, int64_t max_groups);
+AggLayout agg_layout(int64_t n_rows, int64_t max_groups, const DeviceInfo& dev);
 // passes 1-2: hash-insert the keys (each row records its slot, each slot counts its rows), then scan the
 // table: segment offsets, dense group ids and keys in table order. header (first 16 bytes of scratch):
 // [0] = occupied slots, [1] = overflow flag (more than max_groups distinct keys), [2] = number of groups.
@@ -115,6 +155,13 @@ size_t agg_split_scratch_bytes(int64_t cell, const DeviceInfo& dev);
 int launch_agg_reduce(int dtype, int red_op, const void* payload, int64_t cell, int64_t n_groups, int64_t n_rows, char* scratch,
                       const AggLayout& L, void* out, void* split_scratch, size_t split_bytes, const DeviceInfo& dev,
                       cudaStream_t stream);
+
+// Exchange step of aggregate: owner[i] = mix64(key[i]) mod world and the number of groups per owner (counts[world],
+// zeroed by the call); rows gathered through a permutation (row_bytes a multiple of 4).
+int launch_agg_owner(const int64_t* keys, int64_t n, int world, unsigned int* owner, unsigned long long* counts, const DeviceInfo& dev,
+                     cudaStream_t stream);
+int launch_gather_rows(const void* src, const unsigned int* perm, int64_t n, int64_t row_bytes, void* dst, const DeviceInfo& dev,
+                       cudaStream_t stream);
 
 // K0 (host_staging.cpp): copies of at least 64 MiB between PAGEABLE host memory and the device go through a pinned
 // ring filled / drained by a few host threads; `stream` is ordered after the copy.

@@ -10,8 +10,9 @@
 //                                                                         8 B read + 8 B written / row
 //   2. scan     one pass over the table: segment offset of every slot, dense group id of every
 //               occupied slot, out_keys                                   (table only)
-//   3. sort     rows by slot (stable LSD radix sort of the (slot, row) u32 pairs on the slot bits --
-//               cub::DeviceRadixSort, the one library call on this path, used as plain plumbing)
+//   3. sort     rows by slot: a stable radix partition of the (slot, row) pairs on the slot bits, two 11-bit passes
+//               for tables of up to 2^22 slots (kernels_radix.cu); the first pass takes the row index from the
+//               element's position, the last one writes row indices only
 //   4. gather-reduce  one warp per group walks its segment of the sorted row list and gathers
 //               the payload rows -- each a contiguous cell, read with coalesced vector loads --
 //               accumulating in registers; one coalesced store per group.      cell bytes / row
@@ -22,8 +23,6 @@
 // table order of the groups is not reproducible; the (few) groups are therefore sorted by key before
 // the gather, and -- the row sort being stable -- the rows of a group are folded in block order:
 // output order and values are run-to-run deterministic, floats included.
-#include <cub/device/device_radix_sort.cuh>
-
 #include <cstdlib>
 
 #include "kernels.h"
@@ -42,6 +41,7 @@ __device__ __forceinline__ unsigned long long mix64(unsigned long long x) {
 }
 
 // header[0] = occupied slots so far, header[1] = overflow flag, header[2] = number of groups (after the scan)
+// Every row records its slot; its own index needs no column: the first partition pass reads it off the position.
 // Slot `slots` (one past the table) belongs to the one key value that equals the empty marker.
 //
 // Each thread takes kInsU keys of a CTA tile: the first probes of all of them are in flight together, the
@@ -60,7 +60,7 @@ template <bool SMEM_COUNTS>
 __global__ void __launch_bounds__(kThreads)
 agg_insert_kernel(const long long* __restrict__ keys, const int64_t n, unsigned long long* __restrict__ slot_key,
                   unsigned int* __restrict__ counts, const unsigned long long slots, unsigned int* __restrict__ header,
-                  const unsigned int max_groups, unsigned int* __restrict__ row_slot, unsigned int* __restrict__ row_id) {
+                  const unsigned int max_groups, unsigned int* __restrict__ row_slot) {
   __shared__ unsigned int sm_counts[SMEM_COUNTS ? kSmemSlots + 1 : 1];
   if (SMEM_COUNTS) {
     for (unsigned int j = threadIdx.x; j <= (unsigned int)slots; j += kThreads) sm_counts[j] = 0u;
@@ -121,7 +121,6 @@ agg_insert_kernel(const long long* __restrict__ keys, const int64_t n, unsigned 
       const int64_t i = base + int64_t(u) * kThreads;
       if (i < n) {
         __stcs(row_slot + i, (unsigned int)h[u]);
-        __stcs(row_id + i, (unsigned int)i);
         if (SMEM_COUNTS) atomicAdd(sm_counts + h[u], 1u);
         else atomicAdd(counts + h[u], 1u);
       }
@@ -431,16 +430,9 @@ int slot_bits(uint64_t slots) {   // bits needed for slot indices 0..slots (incl
   return b;
 }
 
-size_t sort_temp_bytes(int64_t n_rows, uint64_t slots) {
-  size_t bytes = 0;
-  cub::DoubleBuffer<unsigned int> k(nullptr, nullptr), v(nullptr, nullptr);
-  cub::DeviceRadixSort::SortPairs(nullptr, bytes, k, v, n_rows, 0, slot_bits(slots));
-  return bytes;
-}
-
 }  // namespace
 
-AggLayout agg_layout(int64_t n_rows, int64_t max_groups) {
+AggLayout agg_layout(int64_t n_rows, int64_t max_groups, const DeviceInfo& dev) {
   AggLayout L{};
   uint64_t cap = 1024;
   while (cap < 2 * uint64_t(std::max<int64_t>(max_groups, 1))) cap <<= 1;
@@ -455,19 +447,18 @@ AggLayout agg_layout(int64_t n_rows, int64_t max_groups) {
   L.off_group_slot_tab = off; off += up(size_t(max_groups + 1) * 4);     // table order, before the sort by key
   L.off_keys_tab = off; off += up(size_t(max_groups + 1) * 8);
   L.off_tile_sums = off; off += up(size_t((cap + 1 + kScanTile) / kScanTile + 1) * 8);
-  for (int b = 0; b < 2; ++b) {   // ping-pong buffers of the pair sort
-    L.off_row_slot[b] = off; off += up(size_t(n_rows) * 4);
-    L.off_row_id[b] = off; off += up(size_t(n_rows) * 4);
-  }
-  L.off_perm = L.off_row_id[0];   // set by launch_agg_segments to the buffer the sort finished in
-  L.sort_temp_bytes = n_rows > 0 ? sort_temp_bytes(n_rows, cap) : 0;
-  {
-    size_t b = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, b, static_cast<const long long*>(nullptr), static_cast<long long*>(nullptr),
-                                    static_cast<const unsigned int*>(nullptr), static_cast<unsigned int*>(nullptr),
-                                    std::max<int64_t>(max_groups, 1));
-    L.sort_temp_bytes = std::max(L.sort_temp_bytes, b);
-  }
+  // row partition: the slot column the insert pass wrote (kept: every carried fetch sorts from it again), the slot
+  // column between passes (a second one only when the table needs a third pass) and two row-index columns
+  const int passes = radix_passes(slot_bits(cap));
+  L.off_row_slot[0] = off; off += up(size_t(n_rows) * 4);
+  L.off_row_slot[1] = off; off += up(size_t(n_rows) * 4);
+  L.off_row_slot[2] = off; off += passes >= 3 ? up(size_t(n_rows) * 4) : 0;
+  for (int b = 0; b < 2; ++b) { L.off_row_id[b] = off; off += up(size_t(n_rows) * 4); }
+  L.off_perm = L.off_row_id[0];   // set by launch_agg_segments to the buffer the partition finished in
+  // group sort by key: one more (key, slot) column pair; then the histogram table of a pass
+  L.off_group_tmp_keys = off; off += up(size_t(max_groups + 1) * 8);
+  L.off_group_tmp_slot = off; off += up(size_t(max_groups + 1) * 4);
+  L.sort_temp_bytes = radix_scratch_bytes(dev);
   L.off_sort_temp = off; off += up(L.sort_temp_bytes);
   L.bytes = off;
   return L;
@@ -483,7 +474,6 @@ int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, ch
   long long* keys_tab = reinterpret_cast<long long*>(scratch + L.off_keys_tab);
   unsigned long long* tile_sums = reinterpret_cast<unsigned long long*>(scratch + L.off_tile_sums);
   unsigned int* row_slot = reinterpret_cast<unsigned int*>(scratch + L.off_row_slot[0]);
-  unsigned int* row_id = reinterpret_cast<unsigned int*>(scratch + L.off_row_id[0]);
   const int64_t m = int64_t(L.table_slots) + 1;   // table + the marker-key slot
   TFS_CUDA(cudaMemsetAsync(header, 0, 256, stream));
   TFS_CUDA(cudaMemsetAsync(counts, 0, size_t(m) * 4, stream));
@@ -496,10 +486,10 @@ int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, ch
     const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(tiles, int64_t(dev.sm_count) * 16));
     if (L.table_slots <= uint64_t(kSmemSlots))
       agg_insert_kernel<true><<<grid, kThreads, 0, stream>>>(reinterpret_cast<const long long*>(keys), n_rows, slot_key, counts,
-                                                             L.table_slots, header, (unsigned int)max_groups, row_slot, row_id);
+                                                             L.table_slots, header, (unsigned int)max_groups, row_slot);
     else
       agg_insert_kernel<false><<<grid, kThreads, 0, stream>>>(reinterpret_cast<const long long*>(keys), n_rows, slot_key, counts,
-                                                              L.table_slots, header, (unsigned int)max_groups, row_slot, row_id);
+                                                              L.table_slots, header, (unsigned int)max_groups, row_slot);
     TFS_CUDA(cudaGetLastError());
     ++launches;
   }
@@ -516,77 +506,62 @@ int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, ch
 
 int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, char* scratch, AggLayout& L,
                         int64_t* out_keys_dev, bool sort_groups, bool sort_rows, const DeviceInfo& dev, cudaStream_t stream) {
-  (void)keys; (void)dev;
+  (void)keys;
   if (n_rows <= 0) return 0;
-  // groups by key (signed order): out_keys ascending, group_slot permuted alongside
+  int launches = 0;
+  void* temp = scratch + L.off_sort_temp;
+  // groups by key (signed order: the sign bit is flipped for the digit extraction): out_keys ascending, group_slot
+  // permuted alongside.  64 key bits are six passes over a column that is small next to the rows.
   if (sort_groups && n_groups > 0) {
-    size_t temp = L.sort_temp_bytes;
-    TFS_CUDA(cub::DeviceRadixSort::SortPairs(scratch + L.off_sort_temp, temp, reinterpret_cast<const long long*>(scratch + L.off_keys_tab),
-                                             reinterpret_cast<long long*>(out_keys_dev),
-                                             reinterpret_cast<const unsigned int*>(scratch + L.off_group_slot_tab),
-                                             reinterpret_cast<unsigned int*>(scratch + L.off_group_slot), n_groups, 0, 64, stream));
+    void* kbuf[2] = {scratch + L.off_group_tmp_keys, out_keys_dev};
+    void* vbuf[2] = {scratch + L.off_group_tmp_slot, scratch + L.off_group_slot};
+    const int at = launch_radix_sort(8, 4, scratch + L.off_keys_tab, scratch + L.off_group_slot_tab, kbuf, vbuf, n_groups,
+                                     0x8000000000000000ULL, 64, true, temp, dev, stream, &launches);
+    TFS_CHECK(at == 1, TFS_ERR_INVALID, "internal: group sort ended in the wrong buffer");
   }
-  if (!sort_rows) return 1;       // every fetch carries its values through its own sort (launch_agg_reduce_carried)
-  // rows by slot, stable
-  cub::DoubleBuffer<unsigned int> slot(reinterpret_cast<unsigned int*>(scratch + L.off_row_slot[0]),
-                                       reinterpret_cast<unsigned int*>(scratch + L.off_row_slot[1]));
-  cub::DoubleBuffer<unsigned int> row(reinterpret_cast<unsigned int*>(scratch + L.off_row_id[0]),
-                                      reinterpret_cast<unsigned int*>(scratch + L.off_row_id[1]));
-  size_t temp = L.sort_temp_bytes;
-  TFS_CUDA(cub::DeviceRadixSort::SortPairs(scratch + L.off_sort_temp, temp, slot, row, n_rows, 0,
-                                           slot_bits(L.table_slots), stream));
-  L.off_perm = L.off_row_id[row.selector];
-  return 1;   // counted as one launch of ours: the sorts' internal kernels are library code
+  if (!sort_rows) return launches;       // every fetch carries its values through its own sort (launch_agg_reduce_carried)
+  // rows by slot, stable: values = row indices, read off the position in the first pass
+  void* kbuf[2] = {scratch + L.off_row_slot[1], scratch + L.off_row_slot[2]};
+  void* vbuf[2] = {scratch + L.off_row_id[0], scratch + L.off_row_id[1]};
+  const int at = launch_radix_sort(4, 4, scratch + L.off_row_slot[0], nullptr, kbuf, vbuf, n_rows, 0, slot_bits(L.table_slots), false,
+                                   temp, dev, stream, &launches);
+  L.off_perm = L.off_row_id[at];
+  return launches;
 }
 
 // Scalar payloads (one 4- or 8-byte value per row: groupBy(key).sum(x)): gathering them through the row permutation
 // costs a 128-byte DRAM fill per value (measured 32.9 GB of reads for 2 GB of payload).  Instead the values ride
 // through the stable slot sort themselves and the per-group reduction reads them sequentially.  Same fold order as the
 // gather path, so the same bits.  Must run before the row sort (which reuses the unsorted slot buffer).
-namespace {
-template <class V>
-size_t carried_temp_bytes_t(int64_t n_rows, uint64_t slots) {
-  size_t b = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, b, static_cast<const unsigned int*>(nullptr), static_cast<unsigned int*>(nullptr),
-                                  static_cast<const V*>(nullptr), static_cast<V*>(nullptr), n_rows, 0, slot_bits(slots));
-  return b;
-}
-}  // namespace
-
 size_t agg_carried_bytes(int64_t n_rows, int elem_size, const AggLayout& L) {
+  (void)L;
   if (n_rows <= 0) return 0;
-  const size_t temp = elem_size == 8 ? carried_temp_bytes_t<unsigned long long>(n_rows, L.table_slots)
-                                     : carried_temp_bytes_t<unsigned int>(n_rows, L.table_slots);
-  return ((size_t(n_rows) * size_t(elem_size) + 255) / 256 * 256) + temp;
+  return 2 * ((size_t(n_rows) * size_t(elem_size) + 255) / 256 * 256);      // two value columns, alternating between passes
 }
 
 int launch_agg_reduce_carried(int dtype, int red_op, const void* payload, int64_t cell, int64_t n_groups, int64_t n_rows, char* scratch,
-                              const AggLayout& L, void* out, char* carried, size_t carried_bytes, void* split_scratch,
+                              const AggLayout& L, void* out, char* carried_buf, size_t carried_bytes, void* split_scratch,
                               size_t split_bytes, const DeviceInfo& dev, cudaStream_t stream) {
   const int es = dtype_size(dtype) * int(cell);      // bytes per row: 4 or 8
   TFS_CHECK(es == 4 || es == 8, TFS_ERR_INVALID, "internal: carried rows must be 4 or 8 bytes");
   const size_t values_bytes = (size_t(n_rows) * size_t(es) + 255) / 256 * 256;
-  TFS_CHECK(carried_bytes >= values_bytes, TFS_ERR_INVALID, "internal: carried-sort scratch too small");
-  size_t temp = carried_bytes - values_bytes;
-  const unsigned int* slot_in = reinterpret_cast<const unsigned int*>(scratch + L.off_row_slot[0]);
-  unsigned int* slot_out = reinterpret_cast<unsigned int*>(scratch + L.off_row_slot[1]);
-  const int bits = slot_bits(L.table_slots);
-  if (es == 8)
-    TFS_CUDA(cub::DeviceRadixSort::SortPairs(carried + values_bytes, temp, slot_in, slot_out, static_cast<const unsigned long long*>(payload),
-                                             reinterpret_cast<unsigned long long*>(carried), n_rows, 0, bits, stream));
-  else
-    TFS_CUDA(cub::DeviceRadixSort::SortPairs(carried + values_bytes, temp, slot_in, slot_out, static_cast<const unsigned int*>(payload),
-                                             reinterpret_cast<unsigned int*>(carried), n_rows, 0, bits, stream));
+  TFS_CHECK(carried_bytes >= 2 * values_bytes, TFS_ERR_INVALID, "internal: carried-sort scratch too small");
+  void* kbuf[2] = {scratch + L.off_row_slot[1], scratch + L.off_row_slot[2]};
+  void* vbuf[2] = {carried_buf, carried_buf + values_bytes};
+  int sort_launches = 0;
+  const int at = launch_radix_sort(4, es, scratch + L.off_row_slot[0], payload, kbuf, vbuf, n_rows, 0, slot_bits(L.table_slots), false,
+                                   scratch + L.off_sort_temp, dev, stream, &sort_launches);
+  const char* carried = static_cast<const char*>(vbuf[at]);
   const unsigned int* offsets = reinterpret_cast<const unsigned int*>(scratch + L.off_offsets);
   const unsigned int* counts = reinterpret_cast<const unsigned int*>(scratch + L.off_counts);
   const unsigned int* group_slot = reinterpret_cast<const unsigned int*>(scratch + L.off_group_slot);
   if (split_bytes == 0) split_scratch = nullptr;
   const unsigned int* no_perm = nullptr;      // the values are already in segment order
   switch (dtype) {
-    case TFS_FLOAT: return 1 + launch_gather_op<float>(red_op, carried, cell, no_perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
-    case TFS_DOUBLE: return 1 + launch_gather_op<double>(red_op, carried, cell, no_perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
-    case TFS_INT32: return 1 + launch_gather_op<int>(red_op, carried, cell, no_perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
-    case TFS_INT64: return 1 + launch_gather_op<long long>(red_op, carried, cell, no_perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
+    case TFS_FLOAT: return sort_launches + launch_gather_op<float>(red_op, carried, cell, no_perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
+    case TFS_DOUBLE: return sort_launches + launch_gather_op<double>(red_op, carried, cell, no_perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
+    case TFS_INT32: return sort_launches + launch_gather_op<int>(red_op, carried, cell, no_perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
+    case TFS_INT64: return sort_launches + launch_gather_op<long long>(red_op, carried, cell, no_perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
   }
   fail(TFS_ERR_UNSUPPORTED, "aggregate: unsupported dtype");
 }
@@ -613,6 +588,59 @@ int launch_agg_reduce(int dtype, int red_op, const void* payload, int64_t cell, 
     case TFS_INT64: return launch_gather_op<long long>(red_op, payload, cell, perm, offsets, counts, group_slot, n_groups, n_rows, out, split_scratch, split_bytes, dev, stream);
   }
   fail(TFS_ERR_UNSUPPORTED, "aggregate: unsupported dtype");
+}
+
+// ---- the exchange step of aggregate over several GPUs ---------------------------------------------------------
+// owner[i] = mix64(key[i]) mod world -- the rank that merges group i -- and how many groups go to each rank.
+namespace {
+__global__ void __launch_bounds__(kThreads)
+agg_owner_kernel(const long long* __restrict__ keys, const int64_t n, const unsigned int world, unsigned int* __restrict__ owner,
+                 unsigned long long* __restrict__ counts) {
+  __shared__ unsigned int sm[64];
+  if (threadIdx.x < 64) sm[threadIdx.x] = 0u;
+  __syncthreads();
+  const int64_t stride = int64_t(gridDim.x) * blockDim.x;
+  for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const unsigned int o = (unsigned int)(mix64((unsigned long long)keys[i]) % world);
+    owner[i] = o;
+    atomicAdd(&sm[o], 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x < world && sm[threadIdx.x] != 0u) atomicAdd(counts + threadIdx.x, (unsigned long long)sm[threadIdx.x]);
+}
+
+// dst[i, :] = src[perm[i], :] for rows of `words` 4-byte words
+__global__ void __launch_bounds__(kThreads)
+agg_gather_rows_kernel(const unsigned int* __restrict__ src, const unsigned int* __restrict__ perm, const int64_t n, const int64_t words,
+                       unsigned int* __restrict__ dst) {
+  const int64_t total = n * words;
+  const int64_t stride = int64_t(gridDim.x) * blockDim.x;
+  for (int64_t e = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; e < total; e += stride) {
+    const int64_t row = e / words, w = e - row * words;
+    dst[e] = src[int64_t(perm[row]) * words + w];
+  }
+}
+}  // namespace
+
+int launch_agg_owner(const int64_t* keys, int64_t n, int world, unsigned int* owner, unsigned long long* counts, const DeviceInfo& dev,
+                     cudaStream_t stream) {
+  TFS_CHECK(world >= 1 && world <= 64, TFS_ERR_UNSUPPORTED, "aggregate exchange: at most 64 ranks");
+  TFS_CUDA(cudaMemsetAsync(counts, 0, size_t(world) * 8, stream));
+  if (n <= 0) return 0;
+  agg_owner_kernel<<<(unsigned)grid_for(n, dev), kThreads, 0, stream>>>(reinterpret_cast<const long long*>(keys), n, (unsigned int)world,
+                                                                        owner, counts);
+  TFS_CUDA(cudaGetLastError());
+  return 1;
+}
+
+int launch_gather_rows(const void* src, const unsigned int* perm, int64_t n, int64_t row_bytes, void* dst, const DeviceInfo& dev,
+                       cudaStream_t stream) {
+  if (n <= 0 || row_bytes <= 0) return 0;
+  TFS_CHECK(row_bytes % 4 == 0, TFS_ERR_INVALID, "internal: rows are whole 4-byte words");
+  agg_gather_rows_kernel<<<(unsigned)grid_for(n * (row_bytes / 4), dev), kThreads, 0, stream>>>(
+      static_cast<const unsigned int*>(src), perm, n, row_bytes / 4, static_cast<unsigned int*>(dst));
+  TFS_CUDA(cudaGetLastError());
+  return 1;
 }
 
 }  // namespace tfs

@@ -33,6 +33,7 @@
 
 #include "common.h"
 #include "graph.h"
+#include "kernels.h"
 
 namespace tfs {
 void set_last_error(const std::string& msg);   // capi.cpp
@@ -248,6 +249,10 @@ extern "C" int tfs_reduce_axis0_noalloc(int device, void* cuda_stream, int32_t d
       if (e != cudaSuccess) tfs::fail(TFS_ERR_CUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
     }
     struct Restore { int prev, cur; ~Restore() { if (prev != cur && prev >= 0) cudaSetDevice(prev); } } restore{previous, device};
+    // input and output must already be memory of this device (a lookup, not an allocation)
+    if (outer > 0)
+      TFS_CHECK(tfs::on_device_or_refuse(in, device, "`in`"), TFS_ERR_INVALID, "`in` must be a device pointer");
+    TFS_CHECK(tfs::on_device_or_refuse(out, device, "`out`"), TFS_ERR_INVALID, "`out` must be a device pointer");
     const DeviceSlot& slot = device_slot(device);
     cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
     const int op = red_op == TFS_REDUCE_SUM ? tfs::R_SUM : (red_op == TFS_REDUCE_MIN ? tfs::R_MIN : tfs::R_MAX);

@@ -231,13 +231,55 @@ __device__ __forceinline__ void bulk_load(void* smem_dst, const void* gmem_src, 
                "r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// Work is handed out in UNITS of `unit_chunks` consecutive stages, by ticket (one atomicAdd per unit): an SM that
+// starts late or is shared with another kernel's CTAs -- the exchange of the previous block runs on a second stream
+// while this kernel streams the next block -- simply takes fewer units, instead of holding the whole launch back by
+// its fixed share.  Which CTA folds a unit changes from run to run; what is folded, and in which order, does not:
+// every unit is reduced to its own partial (fixed order inside the CTA), partials are indexed by unit, and the last
+// CTA folds them in index order.  So the result bits do not depend on the hand-out.
+struct StageMeta { long long unit; int first_in_unit, last_in_unit; long long chunk; };
+
+template <class T, int OP, int P>
+__device__ __forceinline__ void cta_fold_to(T (&a)[P], const int L, const int q, T* __restrict__ dst, T* sm) {
+  using R = Red<T, OP>;
+  const int b = blockDim.x;
+  const bool shuffle_ok = (q <= 32) && ((q & (q - 1)) == 0);
+  int contributors;
+  if (shuffle_ok) {
+    for (int m = 16; m >= q; m >>= 1) {
+#pragma unroll
+      for (int e = 0; e < P; ++e) a[e] = R::op(a[e], shfl_xor(a[e], m));
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane < q) {
+#pragma unroll
+      for (int e = 0; e < P; ++e) sm[(warp * q + lane) * P + e] = a[e];
+    }
+    contributors = (b >> 5) * q;
+  } else {
+#pragma unroll
+    for (int e = 0; e < P; ++e) sm[threadIdx.x * P + e] = a[e];
+    contributors = b;
+  }
+  __syncthreads();
+  if (threadIdx.x < L) {
+    const int tc = threadIdx.x / P, e = threadIdx.x % P;
+    T r = R::identity();
+    for (int t = tc; t < contributors; t += q) r = R::op(r, sm[t * P + e]);
+    dst[threadIdx.x] = r;
+  }
+}
+
+// header: header[0] = CTAs finished, header[1] = next unit ticket; both zero on entry and zero again on exit.
 template <class T, int OP, int P>
 __global__ void __launch_bounds__(kMaxThreads, 1)
 reduce_axis0_tma_kernel(const T* __restrict__ in, const int64_t n, const int inner, const int L, const int q,
-                        T* __restrict__ partials, unsigned int* __restrict__ counter, T* __restrict__ out) {
+                        const int64_t n_units, const int unit_chunks, T* __restrict__ partials,
+                        unsigned int* __restrict__ header, T* __restrict__ out) {
   using R = Red<T, OP>;
   extern __shared__ __align__(128) unsigned char dyn_smem[];
   __shared__ __align__(8) uint64_t full_bar[kStages];
+  __shared__ StageMeta meta[kStages];
   __shared__ T sm[kMaxThreads * P];
   __shared__ T sm2[kMaxThreads];
   __shared__ bool is_last;
@@ -247,8 +289,6 @@ reduce_axis0_tma_kernel(const T* __restrict__ in, const int64_t n, const int inn
   const int64_t chunk_vecs = int64_t(b) * kVecPerThread;          // vectors per stage
   const uint32_t stage_bytes = uint32_t(chunk_vecs) * 16u;
   const int64_t n_chunks = (n_vec + chunk_vecs - 1) / chunk_vecs;
-  // chunks are dealt round-robin: CTA c owns chunks c, c + grid, ...
-  const int64_t my_chunks = n_chunks > blockIdx.x ? (n_chunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) mbar_init(&full_bar[s], 1);
@@ -256,30 +296,63 @@ reduce_axis0_tma_kernel(const T* __restrict__ in, const int64_t n, const int inn
   }
   __syncthreads();
 
-  auto issue = [&](int64_t k) {   // thread 0 only
-    const int64_t chunk = blockIdx.x + k * gridDim.x;
+  // producer state (thread 0 only): the unit being issued and the position inside it
+  long long p_unit = -1;
+  int p_pos = 0, p_len = 0;
+  auto issue = [&](int64_t k) {   // thread 0 only: the k-th stage of this CTA's own sequence
+    const int st = int(k % kStages);
+    if (p_pos == p_len) {         // next unit, by ticket
+      const long long t = (long long)atomicAdd(header + 1, 1u);
+      if (t >= n_units) {
+        meta[st].unit = -1;
+        p_unit = -1;
+        p_pos = p_len = 0;
+        return;
+      }
+      p_unit = t;
+      p_pos = 0;
+      const int64_t c0 = t * unit_chunks;
+      p_len = int((n_chunks - c0) < unit_chunks ? (n_chunks - c0) : unit_chunks);
+    }
+    const int64_t chunk = p_unit * unit_chunks + p_pos;
     const int64_t v0 = chunk * chunk_vecs;
     const int64_t vecs = (n_vec - v0) < chunk_vecs ? (n_vec - v0) : chunk_vecs;
     const uint32_t bytes = uint32_t(vecs) * 16u;
-    const int st = int(k % kStages);
+    meta[st].unit = p_unit;
+    meta[st].chunk = chunk;
+    meta[st].first_in_unit = p_pos == 0;
+    meta[st].last_in_unit = p_pos == p_len - 1;
+    ++p_pos;
     mbar_expect_tx(&full_bar[st], bytes);
     bulk_load(dyn_smem + size_t(st) * stage_bytes, in + v0 * P, bytes, &full_bar[st]);
   };
-  if (threadIdx.x == 0)
-    for (int64_t k = 0; k < kStages - 1 && k < my_chunks; ++k) issue(k);
+  if (threadIdx.x == 0) {
+    bool open = true;
+    for (int64_t k = 0; k < kStages - 1; ++k) {
+      if (open) { issue(k); open = meta[k % kStages].unit >= 0; }
+      else meta[k % kStages].unit = -1;
+    }
+  }
 
   T acc[2][P];
 #pragma unroll
   for (int e = 0; e < P; ++e) acc[0][e] = acc[1][e] = R::identity();
 
   using V = typename Vec<T, P>::type;
-  for (int64_t k = 0; k < my_chunks; ++k) {
-    __syncthreads();   // every thread is done with the stage that chunk k + kStages - 1 will overwrite
-    if (threadIdx.x == 0 && k + kStages - 1 < my_chunks) issue(k + kStages - 1);
+  bool producer_open = true;     // thread 0: tickets may be left
+  for (int64_t k = 0;; ++k) {
+    __syncthreads();   // every thread is done with the stage the next load overwrites; thread 0's meta writes are visible
+    if (threadIdx.x == 0) {
+      const int st_new = int((k + kStages - 1) % kStages);
+      if (k == 0) producer_open = meta[(kStages - 2) % kStages].unit >= 0;
+      if (producer_open) { issue(k + kStages - 1); producer_open = meta[st_new].unit >= 0; }
+      else meta[st_new].unit = -1;
+    }
     const int st = int(k % kStages);
+    const StageMeta m = meta[st];
+    if (m.unit < 0) break;       // the same for every thread: the hand-out is over for this CTA
     mbar_wait(&full_bar[st], uint32_t((k / kStages) & 1));
-    const int64_t chunk = blockIdx.x + k * gridDim.x;
-    const int64_t left = n_vec - chunk * chunk_vecs;   // valid vectors in this stage
+    const int64_t left = n_vec - m.chunk * chunk_vecs;   // valid vectors in this stage
     const V* stage = reinterpret_cast<const V*>(dyn_smem + size_t(st) * stage_bytes);
     if (left >= chunk_vecs) {
 #pragma unroll
@@ -299,11 +372,47 @@ reduce_axis0_tma_kernel(const T* __restrict__ in, const int64_t n, const int inn
         }
       }
     }
-  }
-  T a[P];
+    if (m.last_in_unit) {        // this unit's partial, then start afresh
+      T a[P];
 #pragma unroll
-  for (int e = 0; e < P; ++e) a[e] = R::op(acc[0][e], acc[1][e]);
-  combine_and_finish<T, OP, P>(a, in, n, n_vec, inner, L, q, partials, counter, out, sm, sm2, &is_last);
+      for (int e = 0; e < P; ++e) a[e] = R::op(acc[0][e], acc[1][e]);
+      cta_fold_to<T, OP, P>(a, L, q, partials + m.unit * L, sm);
+#pragma unroll
+      for (int e = 0; e < P; ++e) acc[0][e] = acc[1][e] = R::identity();
+    }
+  }
+  // ---- grid combine by the last CTA to finish: partials in unit order
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int done = atomicAdd(header, 1u);
+    is_last = (done == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  const int bl = (b / L) * L;            // threads used, a multiple of L (L <= b by construction)
+  T r = R::identity();
+  if (threadIdx.x < bl) {
+    const int64_t total = n_units * L;
+    for (int64_t i = threadIdx.x; i < total; i += bl) r = R::op(r, __ldcg(partials + i));
+  }
+  sm2[threadIdx.x] = r;
+  __syncthreads();
+  if (threadIdx.x < L) {
+    T s = R::identity();
+    for (int t = threadIdx.x; t < bl; t += L) s = R::op(s, sm2[t]);
+    sm[threadIdx.x] = s;   // per flat-slot totals
+  }
+  __syncthreads();
+  if (threadIdx.x < inner) {
+    T s = R::identity();
+    for (int f = threadIdx.x; f < L; f += inner) s = R::op(s, sm[f]);
+    for (int64_t i = n_vec * P; i < n; ++i)   // elements past the last full vector (n % P of them)
+      if (int(i % inner) == int(threadIdx.x)) s = R::op(s, in[i]);
+    out[threadIdx.x] = s;
+  }
+  if (threadIdx.x == 0) { header[0] = 0; header[1] = 0; }
 }
 
 // Wide cells: one thread per column, a slice of rows per blockIdx.y; partials[split][inner].
@@ -435,7 +544,14 @@ int launch_axis0_t(const T* in, int64_t outer, int64_t inner, T* out, void* scra
       });
       const int64_t n_chunks = (n_vec + chunk_vecs - 1) / chunk_vecs;
       int grid = int(std::max<int64_t>(1, std::min<int64_t>(dev.sm_count, n_chunks)));
-      reduce_axis0_tma_kernel<T, OP, PV><<<grid, g.threads, dyn, stream>>>(in, n, int(inner), g.L, g.q, partials, counter, out);
+      // units per launch: about 32 per CTA so that an SM that falls behind loses ~3 % of its share at most, fewer for
+      // wide cells (every unit costs one L-element partial that the last CTA has to fold)
+      int64_t want_units = std::min<int64_t>(int64_t(grid) * 32, std::max<int64_t>(grid, 65536 / g.L));
+      int64_t unit_chunks = std::max<int64_t>(1, (n_chunks + want_units - 1) / want_units);
+      unit_chunks = std::min<int64_t>(unit_chunks, int64_t(1) << 20);
+      const int64_t n_units = (n_chunks + unit_chunks - 1) / unit_chunks;
+      reduce_axis0_tma_kernel<T, OP, PV><<<grid, g.threads, dyn, stream>>>(in, n, int(inner), g.L, g.q, n_units, int(unit_chunks),
+                                                                            partials, counter, out);
       TFS_CUDA(cudaGetLastError());
       return 1;
     }

@@ -35,17 +35,6 @@ std::vector<int> elt_operands(const Node& n) {
   return n.in;
 }
 
-bool is_device_pointer(const void* p) {
-  if (p == nullptr) return false;
-  cudaPointerAttributes a{};
-  cudaError_t e = cudaPointerGetAttributes(&a, p);
-  if (e != cudaSuccess) {
-    cudaGetLastError();
-    return false;
-  }
-  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
-}
-
 bool matmul_force_simt() {
   static const bool v = [] { const char* e = std::getenv("TFS_MATMUL_IMPL"); return e && std::string(e) == "simt"; }();
   return v;
@@ -159,6 +148,8 @@ Session::~Session() {
   if (ws_) cudaFree(ws_);
   if (red_scratch_) cudaFree(red_scratch_);
   if (seg_scratch_) cudaFree(seg_scratch_);
+  for (int k = 0; k < 2; ++k)
+    if (xchg_[k]) cudaFree(xchg_[k]);
   for (int k = 0; k < 2; ++k)
     if (pipe_stream_[k]) cudaStreamDestroy(pipe_stream_[k]);
   if (pipe_event_) cudaEventDestroy(pipe_event_);
@@ -1150,7 +1141,7 @@ void Session::exec_step(const Plan& plan, size_t step_index, std::vector<void*>&
       }
       TFS_CHECK(n_rows < (int64_t(1) << 32), TFS_ERR_UNSUPPORTED, "UnsortedSegmentSum: blocks of 2^32 rows or more are not supported");
       const int64_t max_groups = std::min(n_rows, segments);
-      const AggLayout L0 = agg_layout(n_rows, max_groups);
+      const AggLayout L0 = agg_layout(n_rows, max_groups, dev_);
       AggLayout L = L0;
       const size_t off_keys64 = align_up(L.bytes);
       const size_t off_out_keys = off_keys64 + align_up(size_t(n_rows) * 8);
@@ -1413,11 +1404,11 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
   for (size_t i = 0; i < feeds.size(); ++i) {
     TFS_CHECK(feeds[i].data != nullptr || feeds[i].shape.numel() == 0, TFS_ERR_INVALID,
               "feed '" + feeds[i].name + "' has a null data pointer");
-    feed_dev[i] = is_device_pointer(feeds[i].data);
+    feed_dev[i] = on_device_or_refuse(feeds[i].data, dev_.device, "feed '" + feeds[i].name + "'");
     if (!feed_dev[i]) any_host = true;
   }
   for (size_t i = 0; i < fetches.size(); ++i) {
-    fetch_dev[i] = is_device_pointer(fetches[i].data);
+    fetch_dev[i] = on_device_or_refuse(fetches[i].data, dev_.device, "fetch buffer '" + fetches[i].name + "'");
     if (!fetch_dev[i]) any_host = true;
   }
 
@@ -1571,9 +1562,10 @@ void Session::aggregate(int64_t n_rows, const int64_t* keys, const std::vector<T
   ensure_device();
   *n_groups_out = 0;
   if (n_rows == 0) return;
+  (void)on_device_or_refuse(out_keys, dev_.device, "out_keys");     // refused before any work, not at the final copy
   TFS_CHECK(max_groups > 0, TFS_ERR_INVALID, "aggregate: max_groups must be positive for a non-empty block");
 
-  AggLayout L = agg_layout(n_rows, max_groups);
+  AggLayout L = agg_layout(n_rows, max_groups, dev_);
   auto up = [](size_t x) { return align_up(x); };
   // workspace: [agg scratch][out_keys][staged keys][staged feeds][staged outputs]
   size_t off = up(L.bytes);
@@ -1598,15 +1590,15 @@ void Session::aggregate(int64_t n_rows, const int64_t* keys, const std::vector<T
         }
   }
   const size_t off_carried = off; off += up(carried_bytes);
-  const bool keys_dev = is_device_pointer(keys);
+  const bool keys_dev = on_device_or_refuse(keys, dev_.device, "the key column");
   size_t off_keys = 0;
   if (!keys_dev) { off_keys = off; off += up(size_t(n_rows) * 8); }
   std::vector<size_t> off_feed(items.size(), SIZE_MAX), off_out(items.size(), SIZE_MAX);
   for (size_t k = 0; k < items.size(); ++k) {
     const Node& n = g_.nodes[size_t(items[k].node)];
     const size_t es = size_t(dtype_size(n.dtype));
-    if (!is_device_pointer(feeds[size_t(items[k].feed)].data)) { off_feed[k] = off; off += up(size_t(n_rows) * items[k].cell * es); }
-    if (!is_device_pointer(fetches[items[k].fetch].data)) { off_out[k] = off; off += up(size_t(max_groups) * items[k].cell * es); }
+    if (!on_device_or_refuse(feeds[size_t(items[k].feed)].data, dev_.device, "feed '" + feeds[size_t(items[k].feed)].name + "'")) { off_feed[k] = off; off += up(size_t(n_rows) * items[k].cell * es); }
+    if (!on_device_or_refuse(fetches[items[k].fetch].data, dev_.device, "fetch buffer '" + fetches[items[k].fetch].name + "'")) { off_out[k] = off; off += up(size_t(max_groups) * items[k].cell * es); }
   }
   reserve_workspace(off);
   char* scratch = ws_;
@@ -1653,12 +1645,244 @@ void Session::aggregate(int64_t n_rows, const int64_t* keys, const std::vector<T
    }
   }
   if (n_groups > 0) {
-    const bool ok_dev = is_device_pointer(out_keys);
+    const bool ok_dev = on_device_or_refuse(out_keys, dev_.device, "out_keys");
     TFS_CUDA(cudaMemcpyAsync(out_keys, d_out_keys, size_t(n_groups) * 8,
                              ok_dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, stream_));
   }
   TFS_CUDA(cudaStreamSynchronize(stream_));
   *n_groups_out = n_groups;
+}
+
+// ---------------------------------------------------------------------------
+// Exchange steps (one rank per partition)
+// ---------------------------------------------------------------------------
+char* Session::reserve_exchange(int which, size_t bytes) {
+  if (bytes > xchg_cap_[which]) {
+    TFS_CUDA(cudaStreamSynchronize(stream_));
+    if (xchg_[which]) TFS_CUDA(cudaFree(xchg_[which]));
+    xchg_[which] = nullptr;
+    xchg_cap_[which] = 0;
+    const size_t cap = align_up(bytes + bytes / 4);
+    TFS_CUDA(cudaMalloc(reinterpret_cast<void**>(&xchg_[which]), cap));
+    xchg_cap_[which] = cap;
+  }
+  return xchg_[which];
+}
+
+void Session::combine_wait(Comm& comm) {
+  ensure_device();
+  comm.wait_side(stream_);
+  mark_work();
+}
+
+void Session::reduce_combine(Comm& comm, const std::vector<TensorArg>& partials, const std::vector<TensorArg>& merged, bool overlap) {
+  TFS_CHECK(!partials.empty() && partials.size() == merged.size(), TFS_ERR_INVALID,
+            "reduce_combine: one merged buffer per partial row is needed");
+  ensure_device();
+  TFS_CHECK(comm.device() == dev_.device, TFS_ERR_INVALID,
+            "reduce_combine: the communicator belongs to device " + std::to_string(comm.device()) + ", the session to device " +
+                std::to_string(dev_.device));
+  struct Item { int node; size_t count, bytes; bool bare; };
+  std::vector<Item> items;
+  bool all_bare = true;
+  size_t ring_bytes = 0;
+  for (size_t i = 0; i < partials.size(); ++i) {
+    const int idx = g_.find(partials[i].name);
+    TFS_CHECK(idx >= 0, TFS_ERR_INVALID, "fetch '" + partials[i].name + "' is not a node of the graph");
+    TFS_CHECK(merged[i].name == partials[i].name, TFS_ERR_INVALID, "reduce_combine: partials and merged must name the same fetches in the same order");
+    const Node& n = g_.nodes[size_t(idx)];
+    TFS_CHECK(partials[i].shape.fully_known() && merged[i].shape.fully_known() && partials[i].shape.numel() == merged[i].shape.numel(),
+              TFS_ERR_INVALID, "reduce_combine: fetch '" + n.name + "': partial " + partials[i].shape.str() + " and merged " +
+                                   merged[i].shape.str() + " rows differ in size");
+    TFS_CHECK((partials[i].dtype == 0 || partials[i].dtype == n.dtype) && (merged[i].dtype == 0 || merged[i].dtype == n.dtype),
+              TFS_ERR_INVALID, "reduce_combine: fetch '" + n.name + "' is " + dtype_name(n.dtype));
+    const size_t count = size_t(partials[i].shape.numel());
+    if (count > 0) {
+      TFS_CHECK(on_device_or_refuse(partials[i].data, dev_.device, "partial row '" + n.name + "'") &&
+                    on_device_or_refuse(merged[i].data, dev_.device, "merged row '" + n.name + "'"),
+                TFS_ERR_INVALID, "reduce_combine: partial and merged rows must be device memory");
+    }
+    // Sum / Min / Max taken directly from the placeholder: merging partial rows is the same operation element by element
+    const bool bare = n.cls == OpClass::Reduce && g_.nodes[size_t(n.in[0])].cls == OpClass::Placeholder;
+    all_bare = all_bare && bare;
+    items.push_back({idx, count, count * size_t(dtype_size(n.dtype)), bare});
+    ring_bytes += align_up(items.back().bytes);
+  }
+  if (comm.world() == 1) {       // a single partition: RDD.reduce returns its row untouched
+    for (size_t i = 0; i < items.size(); ++i)
+      if (items[i].bytes > 0 && partials[i].data != merged[i].data)
+        TFS_CUDA(cudaMemcpyAsync(merged[i].data, partials[i].data, items[i].bytes, cudaMemcpyDeviceToDevice, stream_));
+    mark_work();
+    return;
+  }
+  if (all_bare) {
+    if (overlap && ring_bytes <= Comm::kSlotBytes) {
+      // The exchange runs on the communicator's side stream and overlaps whatever the caller enqueues next.  The rows
+      // are first copied to a ring slot on the launch stream, so the caller may overwrite `partials` right away.
+      int slot = 0;
+      char* buf = comm.ring_acquire(stream_, &slot);
+      size_t off = 0;
+      for (size_t i = 0; i < items.size(); ++i) {
+        if (items[i].bytes > 0)
+          TFS_CUDA(cudaMemcpyAsync(buf + off, partials[i].data, items[i].bytes, cudaMemcpyDeviceToDevice, stream_));
+        off += align_up(items[i].bytes);
+      }
+      comm.ring_produced(slot, stream_);
+      comm.group_start();
+      off = 0;
+      for (size_t i = 0; i < items.size(); ++i) {
+        const Node& n = g_.nodes[size_t(items[i].node)];
+        if (items[i].count > 0) comm.all_reduce(buf + off, merged[i].data, items[i].count, n.dtype, n.red_op, comm.side_stream());
+        off += align_up(items[i].bytes);
+      }
+      comm.group_end();
+      comm.ring_consumed(slot);
+    } else {
+      comm.group_start();
+      for (size_t i = 0; i < items.size(); ++i) {
+        const Node& n = g_.nodes[size_t(items[i].node)];
+        if (items[i].count > 0) comm.all_reduce(partials[i].data, merged[i].data, items[i].count, n.dtype, n.red_op, stream_);
+      }
+      comm.group_end();
+    }
+    mark_work();
+    return;
+  }
+  // Any other reducer graph: gather every rank's partial rows and run the graph once more on the stacked
+  // [world, cell...] block -- the reference's pairwise reducePairBlock merge, done in one run.  In stream order.
+  const size_t world = size_t(comm.world());
+  size_t total = 0;
+  std::vector<size_t> off(items.size());
+  for (size_t i = 0; i < items.size(); ++i) { off[i] = total; total += align_up(items[i].bytes * world); }
+  char* buf = reserve_exchange(0, total);
+  comm.group_start();
+  for (size_t i = 0; i < items.size(); ++i)
+    if (items[i].bytes > 0) comm.all_gather_bytes(partials[i].data, buf + off[i], items[i].bytes, stream_);
+  comm.group_end();
+  std::vector<TensorArg> feeds(items.size());
+  for (size_t i = 0; i < items.size(); ++i) {
+    const Node& n = g_.nodes[size_t(items[i].node)];
+    feeds[i].name = n.name + "_input";       // the reduce contract: fetch X <- placeholder X_input (impl/DebugRowOps.scala:89-113)
+    TFS_CHECK(g_.find(feeds[i].name) >= 0, TFS_ERR_INVALID,
+              "reduce_combine: the graph has no placeholder '" + feeds[i].name + "' for fetch '" + n.name + "'");
+    feeds[i].dtype = n.dtype;
+    feeds[i].shape = with_lead(int64_t(world), partials[i].shape);
+    feeds[i].data = buf + off[i];
+  }
+  run(feeds, merged, false);
+}
+
+// aggregate over several GPUs: after the per-GPU keyed reduction every rank holds partial groups; each group goes to the
+// rank that owns its key (owner = mix64(key) mod world) and is merged there by one more keyed reduction.  The reference
+// does this with Spark's hash shuffle between the UDAF's partial and final aggregation (impl/DebugRowOps.scala:573-576).
+// Partition (stable, by owner), one grouped send / receive per peer, merge: all enqueued from here, no host work per
+// group; one small readback (the per-peer counts) sizes the receives.
+void Session::aggregate_combine(Comm& comm, int64_t n_groups, const int64_t* keys, const std::vector<TensorArg>& partials,
+                                const std::vector<TensorArg>& merged, int64_t max_groups, int64_t* out_keys, int64_t* n_owned) {
+  TFS_CHECK(n_groups >= 0 && max_groups >= 0 && n_owned != nullptr, TFS_ERR_INVALID, "aggregate_combine: bad arguments");
+  TFS_CHECK(!partials.empty() && partials.size() == merged.size(), TFS_ERR_INVALID,
+            "aggregate_combine: one merged buffer per partial column is needed");
+  TFS_CHECK(n_groups < (int64_t(1) << 32), TFS_ERR_UNSUPPORTED, "aggregate_combine: 2^32 or more groups are not supported");
+  ensure_device();
+  TFS_CHECK(comm.device() == dev_.device, TFS_ERR_INVALID,
+            "aggregate_combine: the communicator belongs to device " + std::to_string(comm.device()) + ", the session to device " +
+                std::to_string(dev_.device));
+  const int world = comm.world(), rank = comm.rank();
+  struct Col { int node; std::string feed; size_t row_bytes; Shape cell; };
+  std::vector<Col> cols;
+  for (size_t i = 0; i < partials.size(); ++i) {
+    const int idx = g_.find(partials[i].name);
+    TFS_CHECK(idx >= 0, TFS_ERR_INVALID, "fetch '" + partials[i].name + "' is not a node of the graph");
+    TFS_CHECK(merged[i].name == partials[i].name, TFS_ERR_INVALID, "aggregate_combine: partials and merged must name the same fetches in the same order");
+    const Node& n = g_.nodes[size_t(idx)];
+    const Shape& ps = partials[i].shape;
+    TFS_CHECK(ps.fully_known() && ps.rank >= 1 && ps.d[0] == n_groups, TFS_ERR_INVALID,
+              "aggregate_combine: partial column '" + n.name + "' must have " + std::to_string(n_groups) + " rows, got " + ps.str());
+    TFS_CHECK(partials[i].dtype == 0 || partials[i].dtype == n.dtype, TFS_ERR_INVALID, "aggregate_combine: fetch '" + n.name + "' is " + dtype_name(n.dtype));
+    if (n_groups > 0)
+      TFS_CHECK(on_device_or_refuse(partials[i].data, dev_.device, "partial column '" + n.name + "'"), TFS_ERR_INVALID,
+                "aggregate_combine: partial columns must be device memory");
+    Col c;
+    c.node = idx;
+    c.cell = drop_lead(ps);
+    c.row_bytes = size_t(c.cell.numel()) * size_t(dtype_size(n.dtype));
+    // the reduce contract: fetch X <- placeholder X_input (impl/DebugRowOps.scala:89-113)
+    c.feed = n.name + "_input";
+    if (g_.find(c.feed) < 0) {
+      TFS_CHECK(n.cls == OpClass::Reduce && g_.nodes[size_t(n.in[0])].cls == OpClass::Placeholder, TFS_ERR_INVALID,
+                "aggregate_combine: the graph has no placeholder '" + c.feed + "' for fetch '" + n.name + "'");
+      c.feed = g_.nodes[size_t(n.in[0])].name;
+    }
+    cols.push_back(c);
+  }
+  if (n_groups > 0)
+    TFS_CHECK(on_device_or_refuse(keys, dev_.device, "the partial key column"), TFS_ERR_INVALID, "aggregate_combine: keys must be device memory");
+
+  // ---- send side: owner of every group, stable partition by owner, keys and rows gathered in that order
+  const size_t ng = size_t(n_groups);
+  size_t off = 0;
+  const size_t off_counts = off; off += align_up(size_t(world) * 8);
+  const size_t off_owner = off; off += align_up(ng * 4);
+  const size_t off_perm = off; off += align_up(ng * 4);
+  const size_t off_radix = off; off += align_up(radix_scratch_bytes(dev_));
+  const size_t off_keys = off; off += align_up(ng * 8);
+  std::vector<size_t> off_rows(cols.size());
+  for (size_t i = 0; i < cols.size(); ++i) { off_rows[i] = off; off += align_up(ng * cols[i].row_bytes); }
+  char* sb = reserve_exchange(0, off);
+  unsigned long long* d_counts = reinterpret_cast<unsigned long long*>(sb + off_counts);
+  unsigned int* d_owner = reinterpret_cast<unsigned int*>(sb + off_owner);
+  unsigned int* d_perm = reinterpret_cast<unsigned int*>(sb + off_perm);
+  launches_ += launch_agg_owner(keys, n_groups, world, d_owner, d_counts, dev_, stream_);
+  if (n_groups > 0) {
+    int bits = 1;
+    while ((1 << bits) < world) ++bits;
+    launches_ += launch_radix_pass(4, 4, d_owner, nullptr, nullptr, d_perm, n_groups, 0, 0, bits, sb + off_radix, dev_, stream_);
+    launches_ += launch_gather_rows(keys, d_perm, n_groups, 8, sb + off_keys, dev_, stream_);
+    for (size_t i = 0; i < cols.size(); ++i)
+      launches_ += launch_gather_rows(partials[i].data, d_perm, n_groups, int64_t(cols[i].row_bytes), sb + off_rows[i], dev_, stream_);
+  }
+  // ---- every rank learns how much it receives from whom: all-gather of the count vectors, one small readback
+  comm.all_gather_bytes(d_counts, comm.counts_dev(), size_t(world) * 8, stream_);
+  TFS_CUDA(cudaMemcpyAsync(comm.counts_host(), comm.counts_dev(), size_t(world) * size_t(world) * 8, cudaMemcpyDeviceToHost, stream_));
+  TFS_CUDA(cudaStreamSynchronize(stream_));
+  const int64_t* all = comm.counts_host();          // all[src * world + dst]
+  std::vector<int64_t> send_off(size_t(world) + 1, 0), recv_off(size_t(world) + 1, 0);
+  for (int p = 0; p < world; ++p) {
+    send_off[size_t(p) + 1] = send_off[size_t(p)] + all[size_t(rank) * world + p];
+    recv_off[size_t(p) + 1] = recv_off[size_t(p)] + all[size_t(p) * world + rank];
+  }
+  TFS_CHECK(send_off[size_t(world)] == n_groups, TFS_ERR_RUNTIME, "aggregate_combine: owner counts do not add up");
+  const int64_t n_recv = recv_off[size_t(world)];
+  TFS_CHECK(n_recv < (int64_t(1) << 32), TFS_ERR_UNSUPPORTED, "aggregate_combine: 2^32 or more received groups");
+  size_t roff = 0;
+  const size_t roff_keys = roff; roff += align_up(size_t(n_recv) * 8);
+  std::vector<size_t> roff_rows(cols.size());
+  for (size_t i = 0; i < cols.size(); ++i) { roff_rows[i] = roff; roff += align_up(size_t(n_recv) * cols[i].row_bytes); }
+  char* rb = reserve_exchange(1, std::max<size_t>(roff, 256));
+  comm.group_start();
+  for (int p = 0; p < world; ++p) {
+    const size_t ns = size_t(send_off[size_t(p) + 1] - send_off[size_t(p)]), nr = size_t(recv_off[size_t(p) + 1] - recv_off[size_t(p)]);
+    if (ns > 0) comm.send_bytes(sb + off_keys + size_t(send_off[size_t(p)]) * 8, ns * 8, p, stream_);
+    if (nr > 0) comm.recv_bytes(rb + roff_keys + size_t(recv_off[size_t(p)]) * 8, nr * 8, p, stream_);
+    for (size_t i = 0; i < cols.size(); ++i) {
+      if (cols[i].row_bytes == 0) continue;
+      if (ns > 0) comm.send_bytes(sb + off_rows[i] + size_t(send_off[size_t(p)]) * cols[i].row_bytes, ns * cols[i].row_bytes, p, stream_);
+      if (nr > 0) comm.recv_bytes(rb + roff_rows[i] + size_t(recv_off[size_t(p)]) * cols[i].row_bytes, nr * cols[i].row_bytes, p, stream_);
+    }
+  }
+  comm.group_end();
+  // ---- merge: the keyed reduction once more, on what this rank owns (rows arrive ordered by source rank, each
+  // source's rows in ascending key order, so the merge order is reproducible)
+  std::vector<TensorArg> feeds(cols.size());
+  for (size_t i = 0; i < cols.size(); ++i) {
+    feeds[i].name = cols[i].feed;
+    feeds[i].dtype = g_.nodes[size_t(cols[i].node)].dtype;
+    feeds[i].shape = with_lead(n_recv, cols[i].cell);
+    feeds[i].data = rb + roff_rows[i];
+  }
+  *n_owned = 0;
+  if (n_recv == 0) { mark_work(); return; }
+  aggregate(n_recv, reinterpret_cast<const int64_t*>(rb + roff_keys), feeds, merged, max_groups, out_keys, n_owned);
 }
 
 }  // namespace tfs

@@ -9,6 +9,7 @@
 #include <unordered_map>
 #include <vector>
 
+#include "comm.h"
 #include "graph.h"
 #include "kernels.h"
 
@@ -41,6 +42,17 @@ class Session {
                  const std::vector<TensorArg>& fetches, int64_t max_groups, int64_t* out_keys,
                  int64_t* n_groups);
 
+  // ---- the exchange steps over a communicator (one rank per partition) ----------------------------------------
+  // reduceBlocks: merge this rank's partial result rows with every other rank's; every rank receives the merged
+  // row (RDD.reduce + reducePairBlock, impl/DebugRowOps.scala:524-525, 741-750).  partials / merged: device memory.
+  void reduce_combine(Comm& comm, const std::vector<TensorArg>& partials, const std::vector<TensorArg>& merged, bool overlap);
+  // the session's stream waits for the exchanges that were left running on the communicator's side stream
+  void combine_wait(Comm& comm);
+  // aggregate: every partial group travels to the rank that owns its key and is merged there
+  // (the UDAF's shuffle between partial and final aggregation, impl/DebugRowOps.scala:573-576)
+  void aggregate_combine(Comm& comm, int64_t n_groups, const int64_t* keys, const std::vector<TensorArg>& partials,
+                         const std::vector<TensorArg>& merged, int64_t max_groups, int64_t* out_keys, int64_t* n_owned);
+
  private:
   struct Plan;
   void ensure_device();
@@ -56,6 +68,7 @@ class Session {
   void reserve_workspace(size_t bytes);
   void check_device_error();
   void mark_work();
+  char* reserve_exchange(int which, size_t bytes);
 
   Graph g_;
   DeviceInfo dev_;
@@ -69,6 +82,8 @@ class Session {
   size_t ws_cap_ = 0;
   void* red_scratch_ = nullptr;
   size_t red_scratch_cap_ = 0;
+  char* xchg_[2] = {nullptr, nullptr};   // exchange staging ([0] gathered rows / send side, [1] receive side), grown on demand
+  size_t xchg_cap_[2] = {0, 0};
   char* seg_scratch_ = nullptr;        // UnsortedSegmentSum: keyed-reduction scratch, grown on demand
   size_t seg_scratch_cap_ = 0;
   int32_t* err_flag_ = nullptr;       // device

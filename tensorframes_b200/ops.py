@@ -44,26 +44,14 @@ def _strip0(name: str) -> str:
 def analyze_graph(graph: _native.Graph, hints: ShapeDescription) -> List[GraphNodeSummary]:
     """Inputs = zero-input Placeholders; outputs = requested fetches; dtype and shape from the
     library's static analysis, the hinted shape winning (impl/TensorFlowOps.scala:101-141)."""
-    outputs = {_strip0(f) for f in hints.requestedFetches}
-    res = []
-    for name, op in graph.nodes():
-        dtype, shape, is_ph, n_in = graph.node_info(name)
-        is_input = is_ph and n_in == 0
-        is_output = name in outputs
-        if not (is_input or is_output):
-            continue
-        hinted = hints.out.get(name, hints.out.get(name + ":0"))
-        s = hinted if hinted is not None else shape
-        if s is None:
-            # TF reports a scalar-attr Placeholder as "unknown shape"; Shape.from(tf.Shape) turns an unknown
-            # rank into the empty shape (Shape.scala:107-109), which is how the reference's scalar-placeholder
-            # tests pass without a hint.  Same here.
-            s = Shape.empty()
-        res.append(GraphNodeSummary(is_input, is_input, is_output, dtype, s, name))
-    missing = outputs - {r.name for r in res}
-    if missing:
-        raise Exception(f"Requested fetches are not in the graph: {', '.join(sorted(missing))}")
-    return res
+    try:
+        summaries = graph.analyze({name: list(shape.dims) for name, shape in hints.out.items()}, list(hints.requestedFetches))
+    except _native.NativeError as exc:
+        if "Requested fetches are not in the graph" in str(exc):
+            raise Exception(str(exc)) from None
+        raise
+    return [GraphNodeSummary(is_input, is_input, is_output, dtype, shape, name)
+            for name, dtype, shape, _is_ph, is_input, is_output in summaries]
 
 
 def infer_physical_shape(num_scalars: int, cell: Shape, expected_rows: Optional[int]) -> Tuple[int, Shape]:

@@ -33,6 +33,31 @@ def test_header_is_c99():
                     os.path.join(ROOT, "include", "tfs_b200.h")], check=True)
 
 
+def test_struct_layouts_a_binding_is_written_against(tmp_path):
+    """INTEGRATION.md's Panama MemoryLayouts (and jvm/.../Native.java) hard-code these sizes and offsets; the ctypes
+    binding must agree with the C compiler too."""
+    import ctypes
+    exe = tmp_path / "c_layout"
+    subprocess.run([GCC, "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"),
+                    os.path.join(ROOT, "tests", "c_layout.c"), "-o", str(exe)], check=True)
+    out = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.splitlines()
+    got = {}
+    for line in out:
+        w = line.split()
+        got[w[0]] = {"size": int(w[1]), **{w[i]: int(w[i + 1]) for i in range(2, len(w), 2)}}
+    assert got["tfs_tensor"] == {"size": 88, "name": 0, "dtype": 8, "rank": 12, "dims": 16, "data": 80}
+    assert got["tfs_node_info"] == {"size": 80, "dtype": 0, "rank": 4, "dims": 8, "is_placeholder": 72, "n_inputs": 76}
+    assert got["tfs_shape_hint"] == {"size": 80, "name": 0, "rank": 8, "dims": 16}
+    assert got["tfs_node_summary"] == {"size": 96, "name": 0, "dtype": 8, "rank": 12, "dims": 16, "is_placeholder": 80,
+                                       "is_input": 84, "is_output": 88}
+    for name, cls in (("tfs_tensor", _native.Tensor), ("tfs_node_info", _native.NodeInfo), ("tfs_shape_hint", _native.ShapeHint),
+                      ("tfs_node_summary", _native.NodeSummary)):
+        assert ctypes.sizeof(cls) == got[name]["size"], name
+        for field, _ in cls._fields_:
+            if field in got[name]:
+                assert getattr(cls, field).offset == got[name][field], (name, field)
+
+
 @pytest.mark.skipif(_native.device_count() > 0, reason="the GPU variant below covers the full program")
 def test_c_program_imports_and_analyses_without_a_gpu(tmp_path):
     exe, pb = _build(tmp_path)

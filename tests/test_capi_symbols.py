@@ -102,3 +102,60 @@ def test_resolve_rejects_sizes_that_are_not_numbers():
         assert s.resolve({"x": np.zeros((1,) * 6 + (2,))}, ["z"]) == [(tfs.DoubleType, (1,) * 7 + (2,))]
         with pytest.raises(_native.NativeError, match="rank above the supported maximum"):
             s.resolve({"x": np.zeros((5,) + (1,) * 6 + (2,))}, ["z"], rows=True)
+
+
+def test_graph_analyze_is_analyzeGraphTF_with_hints():
+    """tfs_graph_analyze = impl/TensorFlowOps.scala:101-141: inputs are zero-input Placeholders, outputs the requested
+    fetches (":0" accepted), a hinted shape overrides the inferred one, an unknown rank without a hint reads as a scalar."""
+    from tensorframes_b200.shape import Shape
+    with dsl.withGraph():
+        x = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 2).named("x_input")
+        s = dsl.placeholder(tfs.FloatType).named("scalar_in")
+        g = dsl.build_graph(dsl.reduce_sum(x, [0]).named("x"), dsl.cast(x, tfs.FloatType).named("c"), dsl.identity(s).named("t"))
+    with _native.Graph(g) as gr:
+        res = {r[0]: r for r in gr.analyze({"c": [7, 2], "x_input:0": [7, 2]}, ["x:0", "c", "t"])}
+        assert set(res) == {"x_input", "scalar_in", "x", "c", "t"}
+        name, dt, shape, is_ph, is_in, is_out = res["x_input"]
+        assert dt == tfs.DoubleType and shape == Shape([7, 2]) and is_ph and is_in and not is_out      # hinted under "name:0"
+        assert res["c"][2] == Shape([7, 2]) and res["c"][5] and not res["c"][4]                          # hint wins over [?, 2]
+        assert res["x"][2] == Shape([2]) and res["x"][1] == tfs.DoubleType                                # inferred
+        assert res["scalar_in"][2] == Shape([]) and res["t"][2] == Shape([])
+        with pytest.raises(_native.NativeError, match="Requested fetches are not in the graph: nope"):
+            gr.analyze({}, ["x", "nope"])
+        # capacity smaller than the result: the count is still reported
+        out = (_native.NodeSummary * 1)()
+        n = ctypes.c_int(0)
+        f = (ctypes.c_char_p * 1)(b"x")
+        assert _native.lib().tfs_graph_analyze(gr.handle, 0, None, 1, f, 1, out, ctypes.byref(n)) == 0
+        assert n.value == 3 and out[0].name in (b"x", b"x_input", b"scalar_in")
+
+
+def test_pack_and_unpack_rows():
+    """tfs_pack_rows / tfs_unpack_rows: one array per row <-> the dense [n, cell] block TFDataOps.convert builds."""
+    rng = np.random.default_rng(5)
+    for dt, n, cell in ((np.float64, 1000, 3), (np.float32, 7, 1), (np.int32, 50_000, 64), (np.int64, 0, 4)):
+        rows = [rng.integers(-100, 100, cell).astype(dt) for _ in range(n)]
+        block = np.empty((n, cell), dtype=dt)
+        _native.pack_rows(rows, block)
+        assert n == 0 or np.array_equal(block, np.stack(rows))
+        back = [np.zeros(cell, dtype=dt) for _ in range(n)]
+        _native.unpack_rows(block, back)
+        assert all(np.array_equal(a, b) for a, b in zip(rows, back))
+    lib = _native.lib()
+    bad = (ctypes.c_void_p * 2)(0, 0)
+    assert lib.tfs_pack_rows(tfs.DoubleType.tf_code, 2, 3, bad, ctypes.c_void_p(np.zeros(6).ctypes.data)) == _native.TFS_ERR_INVALID
+    assert b"row 0 is null" in lib.tfs_last_error()
+
+
+def test_comm_entry_points_fail_cleanly_without_a_clique():
+    """No GPU here: the communicator entry points must answer with a status, never crash (NCCL itself is only
+    loaded when one of them is called)."""
+    lib = _native.lib()
+    h = ctypes.c_void_p()
+    assert lib.tfs_comm_create(0, 2, 5, b"\0" * 128, ctypes.byref(h)) == _native.TFS_ERR_INVALID      # rank outside [0, world)
+    assert not h
+    assert lib.tfs_comm_world(None) == 0 and lib.tfs_comm_rank(None) == -1
+    lib.tfs_comm_free(None)
+    if _native.device_count() == 0:
+        st = lib.tfs_comm_create(0, 1, 0, b"\0" * 128, ctypes.byref(h))
+        assert st != 0 and lib.tfs_last_error()

@@ -1101,6 +1101,42 @@ def test_two_devices_in_one_process():
     assert np.all(np.abs(results[0][0] - exact) <= 1e-5 * (np.abs(x).astype(np.float64) @ np.abs(w).astype(np.float64)))
 
 
+@pytest.mark.skipif(_native.device_count() < 2, reason="needs two GPUs in one process")
+def test_memory_of_another_device_is_refused():
+    """Feeds, fetch buffers and keys must be host memory or memory of the session's own device (header: 'a CUDA device
+    pointer on the session's device'); a pointer into a peer GPU is TFS_ERR_INVALID, never dereferenced."""
+    torch = pytest.importorskip("torch")
+    DA = _native.DeviceArray.from_torch
+    x0 = torch.ones((1024, 64), dtype=torch.float32, device="cuda:0")
+    x1 = torch.ones((1024, 64), dtype=torch.float32, device="cuda:1")
+    y0 = torch.empty((1024, 64), dtype=torch.float32, device="cuda:0")
+    y1 = torch.empty((1024, 64), dtype=torch.float32, device="cuda:1")
+    k1 = torch.zeros(1024, dtype=torch.int64, device="cuda:1")
+    torch.cuda.synchronize(0)
+    torch.cuda.synchronize(1)
+    with dsl.withGraph():
+        px = dsl.placeholder(tfs.FloatType, dsl.Unknown, 64).named("x")
+        g = dsl.build_graph(dsl.matmul(px, dsl.constant(np.eye(64, dtype=np.float32))).named("y"))
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        with pytest.raises(_native.NativeError, match="lives on device 1"):
+            s.run_into({"x": DA(x1)}, {"y": DA(y0)})
+        with pytest.raises(_native.NativeError, match="lives on device 1"):
+            s.run_into({"x": DA(x0)}, {"y": DA(y1)})
+        s.run_into({"x": DA(x0)}, {"y": DA(y0)})
+        s.sync()
+    assert torch.equal(y0, x0)
+    with _native.Graph(aggregate_graph(tfs.FloatType, (64,), "sum")) as gr, _native.Session(gr, 0) as s:
+        ok = torch.empty(16, dtype=torch.int64, device="cuda:0")
+        out = torch.empty((16, 64), dtype=torch.float32, device="cuda:0")
+        with pytest.raises(_native.NativeError, match="lives on device 1"):
+            s.aggregate_into(DA(k1), {"v_input": DA(x0)}, {"v": DA(out)}, DA(ok))
+    import ctypes
+    lib = _native.lib()
+    status = lib.tfs_reduce_axis0_noalloc(0, None, tfs.FloatType.tf_code, 0, ctypes.c_void_p(x1.data_ptr()), 1024, 64,
+                                          ctypes.c_void_p(y0.data_ptr()))
+    assert status == _native.TFS_ERR_INVALID and b"lives on device 1" in lib.tfs_last_error()
+
+
 def test_blocks_beyond_2_31_elements():
     """int64 sizes end to end: the reference caps a block at Int.MaxValue scalars (impl/datatypes.scala:74-78);
     here a 2.2e9-element column is mapped and reduced in one block each (closed-form checks on the device)."""

@@ -4,9 +4,10 @@ Some callers of libtfsb200 cannot let the library allocate: an executor whose GP
 owned by a pool, a task that must not trigger the device-wide synchronisation of cudaMalloc /
 cudaFree, a process on a fixed memory budget.  For them the reduction's scratch is a fixed array
 inside the library.  This file checks that entry point against the regular one
-(tfs_session_run on `reduce_*(x_input, [0])`): same bits for integers and Min/Max, and float sums
-within the tolerance the other parity tests use (1e-12 f64 / 1e-5 f32 of sum|x|) -- on two calls
-in a row, because the array is shared and keeps the previous call's contents.
+(tfs_session_run on `reduce_*(x_input, [0])`) and, independently, against the oracle's evaluation
+of the same graph: same bits for integers and Min/Max, and float sums within the tolerance the
+other parity tests use (1e-12 f64 / 1e-5 f32 of sum|x|) -- on two calls in a row, because the
+array is shared and keeps the previous call's contents.
 
 The file sorts last on purpose: a run that stops at the first failure has then already run
 every other test.  It also passes on its own in a fresh process.
@@ -17,6 +18,7 @@ import numpy as np
 import pytest
 
 import tensorframes_b200 as tfs
+from oracle import tf_ops
 from tensorframes_b200 import _native, dsl
 
 pytestmark = pytest.mark.gpu
@@ -33,6 +35,15 @@ def regular_entry_point(st, x, op):
         g = dsl.build_graph(RED[op](p, [0]).named("x"))
     with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
         return s.run({"x_input": x}, ["x"])[0]
+
+
+def oracle_value(st, x, op):
+    """The oracle's numpy evaluation of the same reducer graph (oracle/tf_ops.py) -- a check that does not pass
+    through any code of the library."""
+    with dsl.withGraph():
+        p = dsl.placeholder(st, dsl.Unknown, *x.shape[1:]).named("x_input")
+        g = dsl.build_graph(RED[op](p, [0]).named("x"))
+    return tf_ops.evaluate(g, {"x_input": x}, ["x"])[0]
 
 
 def no_alloc_entry_point(torch, st, x, op, stream):
@@ -68,11 +79,14 @@ def test_no_alloc_matches_regular_entry_point_twice_in_a_row():
     for st, x, op in (first, second):
         got = no_alloc_entry_point(torch, st, x, op, stream)
         check(got, regular_entry_point(st, x, op), x, op)
+        check(got, oracle_value(st, x, op), x, op)
     # and once more around the size limit, every dtype
     for st, dt in ((tfs.IntegerType, np.int32), (tfs.LongType, np.int64), (tfs.DoubleType, np.float64)):
         for shape, op in (((5_001, 256), MAX), ((40_001, 3), SUM), ((7,), SUM)):
             x = rng.integers(-1000, 1000, shape).astype(dt)
-            check(no_alloc_entry_point(torch, st, x, op, stream), regular_entry_point(st, x, op), x, op)
+            got = no_alloc_entry_point(torch, st, x, op, stream)
+            check(got, regular_entry_point(st, x, op), x, op)
+            check(got, oracle_value(st, x, op), x, op)
 
 
 def test_no_alloc_rejects_cells_beyond_its_limit():
@@ -87,3 +101,15 @@ def test_no_alloc_rejects_cells_beyond_its_limit():
     assert "257" in msg and "256" in msg and "tfs_session_run" in msg
     assert lib.tfs_reduce_axis0_noalloc(0, None, 4, SUM, C.c_void_p(d.data_ptr()), 4, 2, C.c_void_p(out.data_ptr())) \
         == _native.TFS_ERR_UNSUPPORTED          # dtype code 4 (uint8) is not one of the four
+
+
+def test_no_alloc_takes_device_memory_only():
+    """`in` and `out` must already be on the device: a host pointer is turned down, not copied (copying would need a
+    staging allocation, which is what this entry point exists to avoid)."""
+    torch = pytest.importorskip("torch")
+    host = np.ones((8, 2))
+    out = torch.zeros(2, dtype=torch.float64, device="cuda")
+    lib = _native.lib()
+    status = lib.tfs_reduce_axis0_noalloc(0, None, tfs.DoubleType.tf_code, SUM, C.c_void_p(host.ctypes.data), 8, 2,
+                                          C.c_void_p(out.data_ptr()))
+    assert status == _native.TFS_ERR_INVALID and b"device pointer" in lib.tfs_last_error()
