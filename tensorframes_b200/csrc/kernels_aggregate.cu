@@ -452,8 +452,8 @@ AggLayout agg_layout(int64_t n_rows, int64_t max_groups, const DeviceInfo& dev) 
   const int passes = radix_passes(slot_bits(cap));
   L.off_row_slot[0] = off; off += up(size_t(n_rows) * 4);
   L.off_row_slot[1] = off; off += up(size_t(n_rows) * 4);
-  L.off_row_slot[2] = off; off += passes >= 3 ? up(size_t(n_rows) * 4) : 0;
   for (int b = 0; b < 2; ++b) { L.off_row_id[b] = off; off += up(size_t(n_rows) * 4); }
+  L.off_row_slot[2] = off; off += passes >= 3 ? up(size_t(n_rows) * 4) : 0;
   L.off_perm = L.off_row_id[0];   // set by launch_agg_segments to the buffer the partition finished in
   // group sort by key: one more (key, slot) column pair; then the histogram table of a pass
   L.off_group_tmp_keys = off; off += up(size_t(max_groups + 1) * 8);

@@ -5,17 +5,19 @@
 // low bits up (LSD).  What the callers need is narrow -- 32-bit slot numbers carrying a row index or a 4/8-byte value,
 // 64-bit group keys carrying a slot number -- so the pass is written for exactly that:
 //
-//   * every CTA owns one contiguous range of the input (grid = 2 CTAs per SM).  A histogram kernel counts the digits of
-//     each range, two small scan kernels turn the [bin][cta] table into global write positions, and the scatter kernel
-//     walks its range tile by tile with its bin cursors in shared memory.  No atomics decide an output position, so the
-//     pass is stable and its output is a pure function of its input: equal keys keep their input order, run after run.
-//   * 2048 bins instead of a library sort's 256: 22 slot bits are two passes instead of three (9 GB of traffic per
-//     2.5e8 rows where three 8-bit passes move 13 GB), the first pass takes its values from the element index (no
-//     row-id column is read), the last pass writes no keys.
+//   * every CTA owns one contiguous range of the input.  A histogram kernel counts the digits of each range, two small
+//     scan kernels turn the [bin][cta] table into global write positions, and the scatter kernel walks its range tile
+//     by tile with its bin cursors in shared memory.  No atomics decide an output position, so the pass is stable and
+//     its output is a pure function of its input: equal keys keep their input order, run after run.
+//   * the first pass takes its values from the element index (no row-id column is read), the last pass writes no keys.
 //   * inside a tile (4096 pairs) ranks come from __match_any_sync over the digit -- lanes with equal digits rank
-//     themselves by lane order -- on per-warp counters, then one pass over the 8 x 2048 counters gives every warp's
+//     themselves by lane order -- on per-warp counters, then one pass over the per-warp counters gives every warp's
 //     offset inside every bin.  Pairs are staged in shared memory in output order, so the global writes of a tile are
-//     runs of consecutive addresses.
+//     runs of consecutive addresses; the next tile's keys are loaded while the current one is written out.
+//   * passes are 8 bits wide by default (three for 22 slot bits): with 2048 bins a tile holds two pairs per bin, every
+//     write is a partial sector, and the open lines of 2 columns x 2048 bins x 296 CTAs do not fit L2 -- measured
+//     13 GB of DRAM traffic for 4 GB of data (profiles/r02_experiments.md).  Passes of 9 to 11 bits remain available
+//     (TFS_RADIX_BITS) and are used where a partition has that many bins by nature.
 #include <cstdlib>
 
 #include "kernels.h"
@@ -29,7 +31,10 @@ constexpr int kItems = 16;                       // pairs per thread per tile
 constexpr int kTile = kThreads * kItems;         // 4096
 constexpr int kMaxBits = 11;
 constexpr int kMaxBins = 1 << kMaxBits;
-constexpr int kCtasPerSm = 2;
+constexpr int kCtasPerSm = 2;          // passes of 9 to 11 bits
+constexpr int kSmallBits = 8;          // passes of at most 8 bits: 256 bins, small tables, three CTAs per SM
+constexpr int kCtasPerSmSmall = 3;
+constexpr int ctas_for(int mb) { return mb <= kSmallBits ? kCtasPerSmSmall : kCtasPerSm; }
 
 template <class K>
 __device__ __forceinline__ unsigned int digit_of(K key, K xor_mask, int shift, unsigned int mask) {
@@ -48,7 +53,15 @@ radix_hist_kernel(const K* __restrict__ keys, const int64_t n, const int64_t per
   __syncthreads();
   const int64_t lo = int64_t(blockIdx.x) * per_cta;
   const int64_t hi = lo + per_cta < n ? lo + per_cta : n;
-  for (int64_t i = lo + threadIdx.x; i < hi; i += kThreads) atomicAdd(&sm[digit_of<K>(__ldg(keys + i), xor_mask, shift, mask)], 1u);
+  int64_t i = lo + threadIdx.x;
+  for (; i + 7 * kThreads < hi; i += 8 * kThreads) {      // eight loads in flight per thread
+    K k[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) k[u] = __ldcs(keys + i + u * kThreads);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) atomicAdd(&sm[digit_of<K>(k[u], xor_mask, shift, mask)], 1u);
+  }
+  for (; i < hi; i += kThreads) atomicAdd(&sm[digit_of<K>(__ldcs(keys + i), xor_mask, shift, mask)], 1u);
   __syncthreads();
   for (int b = threadIdx.x; b < bins; b += kThreads) hist[int64_t(b) * gridDim.x + blockIdx.x] = sm[b];
 }
@@ -108,24 +121,31 @@ radix_scan_totals_kernel(unsigned int* __restrict__ bin_total, const int bins) {
 }
 
 // Dynamic shared memory of the scatter kernel:
-//   cursor[bins] u32 | bin_start[bins + 1] u32 | cnt[kWarps][bins] u16 | staged keys [kTile] | staged values [kTile]
-template <class K, class V>
+//   cursor[bins] u32 | bin_start[bins + 1] u32 | shift_of[bins] u32 | cnt[kWarps][bins] u16 | staged keys | staged values
+template <class K, class V, int MB>
 constexpr size_t scatter_smem_bytes() {
-  return size_t(kMaxBins) * 4 + size_t(kMaxBins + 8) * 4 + size_t(kWarps) * kMaxBins * 2 + size_t(kTile) * (sizeof(K) + sizeof(V));
+  return size_t(1 << MB) * 4 + size_t((1 << MB) + 8) * 4 + size_t(1 << MB) * 4 + size_t(kWarps) * (1 << MB) * 2 +
+         size_t(kTile) * (sizeof(K) + sizeof(V));
 }
 
-template <class K, class V, bool IOTA>
-__global__ void __launch_bounds__(kThreads, kCtasPerSm)
+// MODE: M_PLAIN = values loaded from vals_in; M_IOTA = the values are the element indices (4-byte values).
+enum : int { M_PLAIN = 0, M_IOTA = 1 };
+
+template <class K, class V, int MODE, int MB>
+__global__ void __launch_bounds__(kThreads, ctas_for(MB))
 radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_in, K* __restrict__ keys_out, V* __restrict__ vals_out,
                      const int64_t n, const int64_t per_cta, const K xor_mask, const int shift, const int bits,
                      const unsigned int* __restrict__ hist, const unsigned int* __restrict__ bin_base) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int bins = 1 << bits;
   const unsigned int mask = (unsigned int)bins - 1u;
+  constexpr int kMB = 1 << MB;                                        // bins this instantiation has room for
+  constexpr int kPT = kMB / kThreads >= 1 ? kMB / kThreads : 1;       // bins per thread in the per-bin phase
   unsigned int* cursor = reinterpret_cast<unsigned int*>(smem_raw);
-  unsigned int* bin_start = cursor + kMaxBins;
-  unsigned short* cnt = reinterpret_cast<unsigned short*>(bin_start + kMaxBins + 8);
-  K* st_keys = reinterpret_cast<K*>(cnt + kWarps * kMaxBins);
+  unsigned int* bin_start = cursor + kMB;
+  unsigned int* shift_of = bin_start + kMB + 8;
+  unsigned short* cnt = reinterpret_cast<unsigned short*>(shift_of + kMB);
+  K* st_keys = reinterpret_cast<K*>(cnt + kWarps * kMB);
   V* st_vals = reinterpret_cast<V*>(st_keys + kTile);
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -136,35 +156,58 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
   const int64_t hi = lo + per_cta < n ? lo + per_cta : n;
   unsigned short* my_cnt = cnt + warp * bins;
 
+  // Every phase below first issues all of its loads and only then its stores: with 8 warps per CTA the kernel lives on
+  // instruction-level parallelism, and a store between two loads of arrays the compiler cannot tell apart would chain
+  // them (measured: 30 000 cycles per tile before, latency-bound on shared memory and on the tile's global loads).
+  using Raw = K;
+  const Raw* raw_in = keys_in;
+  Raw raw[kItems];
+  auto load_raw = [&](int64_t tile_base) {
+    const int64_t wb = tile_base + int64_t(warp) * (32 * kItems) + lane;
+#pragma unroll
+    for (int r = 0; r < kItems; ++r) {
+      const int64_t i = wb + r * 32;
+      raw[r] = i < hi ? __ldcs(raw_in + i) : Raw(0);
+    }
+  };
+  if (lo < hi) load_raw(lo);
   for (int64_t tile = lo; tile < hi; tile += kTile) {
     // (a) counters to zero
     {
       unsigned int* z = reinterpret_cast<unsigned int*>(cnt);
       for (int i = threadIdx.x; i < kWarps * bins / 2; i += kThreads) z[i] = 0u;
     }
-    __syncthreads();       // also: the previous tile's write-out and cursor update are done
-    // (b) load, rank inside the warp.  Warp w owns items [w * 512, w * 512 + 512) of the tile, round r = 32 of them.
+    const int64_t wbase = tile + int64_t(warp) * (32 * kItems) + lane;
+    // the values are not needed before the staging phase: their loads travel while the tile is ranked
     K key[kItems];
     V val[kItems];
-    unsigned short lrank[kItems];
-    const int64_t wbase = tile + int64_t(warp) * (32 * kItems) + lane;
 #pragma unroll
     for (int r = 0; r < kItems; ++r) {
       const int64_t i = wbase + r * 32;
-      key[r] = i < hi ? __ldcs(keys_in + i) : K(0);
-      if constexpr (IOTA) val[r] = V(i);
-      else val[r] = i < hi ? __ldcs(vals_in + i) : V(0);
+      key[r] = raw[r];
+      if constexpr (MODE == M_PLAIN) val[r] = i < hi ? __ldcs(vals_in + i) : V(0);
+      else val[r] = V(i);
     }
+    __syncthreads();       // also: the previous tile's write-out and cursor update are done
+    // (b) rank inside the warp.  Warp w owns items [w * 512, w * 512 + 512) of the tile, round r = 32 of them.
+    unsigned short lrank[kItems];
+    unsigned int dig[kItems];
 #pragma unroll
     for (int r = 0; r < kItems; ++r) {
       const bool valid = wbase + r * 32 < hi;
-      const unsigned int d = valid ? digit_of<K>(key[r], xor_mask, shift, mask) : 0xffffffffu;
-      const unsigned int peers = __match_any_sync(0xffffffffu, d);
-      const unsigned int before = __popc(peers & lt_mask);
+      dig[r] = valid ? digit_of<K>(key[r], xor_mask, shift, mask) : 0xffffffffu;
+    }
+    unsigned int peers[kItems];
+#pragma unroll
+    for (int r = 0; r < kItems; ++r) peers[r] = __match_any_sync(0xffffffffu, dig[r]);
+#pragma unroll
+    for (int r = 0; r < kItems; ++r) {
+      const bool valid = dig[r] != 0xffffffffu;
+      const unsigned int before = __popc(peers[r] & lt_mask);
       unsigned int base = 0;
-      if (valid) base = my_cnt[d];
+      if (valid) base = my_cnt[dig[r]];
       __syncwarp();
-      if (valid && before == 0u) my_cnt[d] = (unsigned short)(base + __popc(peers));
+      if (valid && before == 0u) my_cnt[dig[r]] = (unsigned short)(base + __popc(peers[r]));
       __syncwarp();
       lrank[r] = (unsigned short)(base + before);
     }
@@ -173,22 +216,52 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
     {
       const int per_thread = (bins + kThreads - 1) / kThreads;       // 8 at 2048 bins
       const int b0 = threadIdx.x * per_thread;
-      unsigned int tot[kMaxBins / kThreads];
+      unsigned int tot[kPT];
       unsigned int mine = 0;
+      if (kPT == 8 && per_thread == 8) {
+        // 8 neighbouring 16-bit counters of one warp row are one 16-byte word: 8 vector loads, then 8 vector stores
+        uint4 c[kWarps];
 #pragma unroll
-      for (int j = 0; j < kMaxBins / kThreads; ++j) {
-        tot[j] = 0;
-        const int b = b0 + j;
-        if (j < per_thread && b < bins) {
-          unsigned int run = 0;
+        for (int w = 0; w < kWarps; ++w) c[w] = *reinterpret_cast<const uint4*>(cnt + w * bins + b0);
+        unsigned int run[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 #pragma unroll
-          for (int w = 0; w < kWarps; ++w) {
-            const unsigned int c = cnt[w * bins + b];
-            cnt[w * bins + b] = (unsigned short)run;
-            run += c;
+        for (int w = 0; w < kWarps; ++w) {
+          const unsigned int in[4] = {c[w].x, c[w].y, c[w].z, c[w].w};
+          unsigned int out[4];
+#pragma unroll
+          for (int h = 0; h < 4; ++h) {
+            const unsigned int lo16 = in[h] & 0xffffu, hi16 = in[h] >> 16;
+            out[h] = run[2 * h] | (run[2 * h + 1] << 16);
+            run[2 * h] += lo16;
+            run[2 * h + 1] += hi16;
           }
-          tot[j] = run;
-          mine += run;
+          c[w] = make_uint4(out[0], out[1], out[2], out[3]);
+        }
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) *reinterpret_cast<uint4*>(cnt + w * bins + b0) = c[w];
+#pragma unroll
+        for (int j = 0; j < kPT; ++j) { tot[j] = run[j % 8]; mine += run[j % 8]; }
+      } else {
+#pragma unroll
+        for (int j = 0; j < kPT; ++j) {
+          tot[j] = 0;
+          const int b = b0 + j;
+          if (j < per_thread && b < bins) {
+            unsigned int c[kWarps];
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) c[w] = cnt[w * bins + b];
+            unsigned int run = 0;
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) {
+              const unsigned int v = c[w];
+              c[w] = run;
+              run += v;
+            }
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) cnt[w * bins + b] = (unsigned short)c[w];
+            tot[j] = run;
+            mine += run;
+          }
         }
       }
       // exclusive scan of `mine` over the CTA
@@ -205,78 +278,112 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
 #pragma unroll
       for (int w = 0; w < kWarps; ++w) wofs += w < warp ? warp_tot[w] : 0u;
       unsigned int run = wofs + incl - mine;
+      // bin_start[b] = first position of bin b inside the tile; shift[b] = where that position goes in the output
+      unsigned int cur[kPT];
 #pragma unroll
-      for (int j = 0; j < kMaxBins / kThreads; ++j) {
+      for (int j = 0; j < kPT; ++j) cur[j] = (j < per_thread && b0 + j < bins) ? cursor[b0 + j] : 0u;
+#pragma unroll
+      for (int j = 0; j < kPT; ++j) {
         const int b = b0 + j;
         if (j < per_thread && b < bins) {
           bin_start[b] = run;
+          shift_of[b] = cur[j] - run;
+          cursor[b] = cur[j] + tot[j];      // (read again only in the next tile's phase (c))
           run += tot[j];
         }
       }
       if (threadIdx.x == kThreads - 1) bin_start[bins] = run;      // = pairs in this tile
     }
     __syncthreads();
-    // (d) stage the pairs in output order
+    // (d) stage the pairs in output order: all positions first, then the stores
+    {
+      unsigned int pos[kItems];
 #pragma unroll
-    for (int r = 0; r < kItems; ++r) {
-      if (wbase + r * 32 < hi) {
-        const unsigned int d = digit_of<K>(key[r], xor_mask, shift, mask);
-        const unsigned int pos = bin_start[d] + my_cnt[d] + lrank[r];
-        st_keys[pos] = key[r];
-        st_vals[pos] = val[r];
+      for (int r = 0; r < kItems; ++r) {
+        const unsigned int d = dig[r] != 0xffffffffu ? dig[r] : 0u;
+        pos[r] = bin_start[d] + my_cnt[d] + lrank[r];
+      }
+#pragma unroll
+      for (int r = 0; r < kItems; ++r) {
+        if (dig[r] != 0xffffffffu) {
+          st_keys[pos[r]] = key[r];
+          st_vals[pos[r]] = val[r];
+        }
       }
     }
+    // the next tile's keys start their trip now: the write-out below and the next tile's first phase cover the latency
+    if (tile + kTile < hi) load_raw(tile + kTile);
     __syncthreads();
-    // (e) write out: position p of the tile goes to cursor[digit] + (p - bin_start[digit])
-    const unsigned int in_tile = bin_start[bins];
-#pragma unroll 4
-    for (int j = 0; j < kItems; ++j) {
-      const unsigned int p = (unsigned int)(j * kThreads + threadIdx.x);
-      if (p < in_tile) {
-        const K k = st_keys[p];
-        const unsigned int d = digit_of<K>(k, xor_mask, shift, mask);
-        const unsigned int g = cursor[d] + (p - bin_start[d]);
-        if (keys_out != nullptr) keys_out[g] = k;
-        vals_out[g] = st_vals[p];
+    // (e) write out: position p of the tile goes to shift_of[digit] + p
+    {
+      const unsigned int in_tile = bin_start[bins];
+      K k[kItems];
+      V v[kItems];
+#pragma unroll
+      for (int j = 0; j < kItems; ++j) {
+        const unsigned int p = (unsigned int)(j * kThreads + threadIdx.x);
+        k[j] = p < in_tile ? st_keys[p] : K(0);
+        v[j] = p < in_tile ? st_vals[p] : V(0);
+      }
+      unsigned int g[kItems];
+#pragma unroll
+      for (int j = 0; j < kItems; ++j) {
+        const unsigned int p = (unsigned int)(j * kThreads + threadIdx.x);
+        g[j] = shift_of[digit_of<K>(k[j], xor_mask, shift, mask)] + p;
+      }
+#pragma unroll
+      for (int j = 0; j < kItems; ++j) {
+        const unsigned int p = (unsigned int)(j * kThreads + threadIdx.x);
+        if (p < in_tile) {
+          if (keys_out != nullptr) keys_out[g[j]] = k[j];
+          vals_out[g[j]] = v[j];
+        }
       }
     }
-    __syncthreads();
-    // (f) advance the cursors
-    for (int b = threadIdx.x; b < bins; b += kThreads) cursor[b] += bin_start[b + 1] - bin_start[b];
-    // (the next tile's first __syncthreads orders this against its use)
+    // (the next tile's first __syncthreads orders the staged pairs and shift_of against their next use)
   }
 }
 
 struct PassGeom { int grid; int64_t per_cta; };
-PassGeom pass_geometry(int64_t n, const DeviceInfo& dev) {
+PassGeom pass_geometry(int64_t n, int bits, const DeviceInfo& dev) {
   PassGeom g;
-  g.grid = dev.sm_count * kCtasPerSm;
+  g.grid = dev.sm_count * ctas_for(bits);
   int64_t per = (n + g.grid - 1) / g.grid;
   per = (per + kTile - 1) / kTile * kTile;
   g.per_cta = per < kTile ? kTile : per;
   return g;
 }
 
-template <class K, class V, bool IOTA>
+template <class K, class V, int MODE>
 int launch_pass_t(const K* keys_in, const V* vals_in, K* keys_out, V* vals_out, int64_t n, K xor_mask, int shift, int bits,
                   void* scratch, const DeviceInfo& dev, cudaStream_t stream) {
-  const PassGeom g = pass_geometry(n, dev);
+  const PassGeom g = pass_geometry(n, bits, dev);
   const int bins = 1 << bits;
   unsigned int* hist = static_cast<unsigned int*>(scratch);
-  unsigned int* bin_total = hist + size_t(kMaxBins) * size_t(g.grid);
+  unsigned int* bin_total = hist + size_t(bins) * size_t(g.grid);
   radix_hist_kernel<K><<<g.grid, kThreads, 0, stream>>>(keys_in, n, g.per_cta, xor_mask, shift, bits, hist);
   TFS_CUDA(cudaGetLastError());
   radix_scan_bins_kernel<<<(bins * 32 + kThreads - 1) / kThreads, kThreads, 0, stream>>>(hist, g.grid, bins, bin_total);
   TFS_CUDA(cudaGetLastError());
   radix_scan_totals_kernel<<<1, 1024, 0, stream>>>(bin_total, bins);
   TFS_CUDA(cudaGetLastError());
-  constexpr size_t smem = scatter_smem_bytes<K, V>();
-  static PerDeviceOnce attr;
-  attr.run(dev.device, [] {
-    TFS_CUDA(cudaFuncSetAttribute(radix_scatter_kernel<K, V, IOTA>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-  });
-  radix_scatter_kernel<K, V, IOTA><<<g.grid, kThreads, smem, stream>>>(keys_in, vals_in, keys_out, vals_out, n, g.per_cta, xor_mask,
-                                                                       shift, bits, hist, bin_total);
+  if (bits <= kSmallBits) {
+    constexpr size_t smem = scatter_smem_bytes<K, V, kSmallBits>();
+    static PerDeviceOnce attr;
+    attr.run(dev.device, [] {
+      TFS_CUDA(cudaFuncSetAttribute(radix_scatter_kernel<K, V, MODE, kSmallBits>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    });
+    radix_scatter_kernel<K, V, MODE, kSmallBits><<<g.grid, kThreads, smem, stream>>>(keys_in, vals_in, keys_out, vals_out, n, g.per_cta,
+                                                                                      xor_mask, shift, bits, hist, bin_total);
+  } else {
+    constexpr size_t smem = scatter_smem_bytes<K, V, kMaxBits>();
+    static PerDeviceOnce attr;
+    attr.run(dev.device, [] {
+      TFS_CUDA(cudaFuncSetAttribute(radix_scatter_kernel<K, V, MODE, kMaxBits>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    });
+    radix_scatter_kernel<K, V, MODE, kMaxBits><<<g.grid, kThreads, smem, stream>>>(keys_in, vals_in, keys_out, vals_out, n, g.per_cta,
+                                                                                    xor_mask, shift, bits, hist, bin_total);
+  }
   TFS_CUDA(cudaGetLastError());
   return 4;
 }
@@ -284,10 +391,25 @@ int launch_pass_t(const K* keys_in, const V* vals_in, K* keys_out, V* vals_out, 
 }  // namespace
 
 size_t radix_scratch_bytes(const DeviceInfo& dev) {
-  return (size_t(kMaxBins) * size_t(dev.sm_count * kCtasPerSm) + kMaxBins + 64) * sizeof(unsigned int);
+  return (size_t(kMaxBins) * size_t(dev.sm_count * kCtasPerSmSmall) + kMaxBins + 64) * sizeof(unsigned int);
 }
 
-int radix_passes(int bits) { return bits <= 0 ? 0 : (bits + kMaxBits - 1) / kMaxBits; }
+namespace {
+// Bits per pass of the generic (two-column) passes: 8 unless TFS_RADIX_BITS says otherwise.  Measured on 2.5e8
+// (slot, row) pairs: an 11-bit pass writing two columns moves 13 GB through DRAM for 4 GB of data (its 2 x 2048 x 296
+// open cache lines do not fit L2) and takes 8.8 ms; an 8-bit pass stays at its 4 GB and takes 2.1 ms.  The packed
+// two-pass path of launch_radix_rows_by_slot does not go through here.
+int pass_bits() {
+  static const int v = [] {
+    const char* e = std::getenv("TFS_RADIX_BITS");
+    const int b = e ? std::atoi(e) : kSmallBits;
+    return b >= 1 && b <= kMaxBits ? b : kSmallBits;
+  }();
+  return v;
+}
+}  // namespace
+
+int radix_passes(int bits) { return bits <= 0 ? 0 : (bits + pass_bits() - 1) / pass_bits(); }
 
 int launch_radix_pass(int key_bytes, int val_bytes, const void* keys_in, const void* vals_in, void* keys_out, void* vals_out,
                       int64_t n, uint64_t xor_mask, int shift, int bits, void* scratch, const DeviceInfo& dev, cudaStream_t stream) {
@@ -298,17 +420,17 @@ int launch_radix_pass(int key_bytes, int val_bytes, const void* keys_in, const v
   using u64 = unsigned long long;
   if (key_bytes == 4 && val_bytes == 4) {
     if (vals_in == nullptr)
-      return launch_pass_t<u32, u32, true>(static_cast<const u32*>(keys_in), nullptr, static_cast<u32*>(keys_out), static_cast<u32*>(vals_out),
+      return launch_pass_t<u32, u32, M_IOTA>(static_cast<const u32*>(keys_in), nullptr, static_cast<u32*>(keys_out), static_cast<u32*>(vals_out),
                                            n, u32(xor_mask), shift, bits, scratch, dev, stream);
-    return launch_pass_t<u32, u32, false>(static_cast<const u32*>(keys_in), static_cast<const u32*>(vals_in), static_cast<u32*>(keys_out),
+    return launch_pass_t<u32, u32, M_PLAIN>(static_cast<const u32*>(keys_in), static_cast<const u32*>(vals_in), static_cast<u32*>(keys_out),
                                           static_cast<u32*>(vals_out), n, u32(xor_mask), shift, bits, scratch, dev, stream);
   }
   TFS_CHECK(vals_in != nullptr, TFS_ERR_INVALID, "internal: index values are 4 bytes wide");
   if (key_bytes == 4 && val_bytes == 8)
-    return launch_pass_t<u32, u64, false>(static_cast<const u32*>(keys_in), static_cast<const u64*>(vals_in), static_cast<u32*>(keys_out),
+    return launch_pass_t<u32, u64, M_PLAIN>(static_cast<const u32*>(keys_in), static_cast<const u64*>(vals_in), static_cast<u32*>(keys_out),
                                           static_cast<u64*>(vals_out), n, u32(xor_mask), shift, bits, scratch, dev, stream);
   if (key_bytes == 8 && val_bytes == 4)
-    return launch_pass_t<u64, u32, false>(static_cast<const u64*>(keys_in), static_cast<const u32*>(vals_in), static_cast<u64*>(keys_out),
+    return launch_pass_t<u64, u32, M_PLAIN>(static_cast<const u64*>(keys_in), static_cast<const u32*>(vals_in), static_cast<u64*>(keys_out),
                                           static_cast<u32*>(vals_out), n, u64(xor_mask), shift, bits, scratch, dev, stream);
   fail(TFS_ERR_INVALID, "internal: radix pass for this key / value width is not built");
 }

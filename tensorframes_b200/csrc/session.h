@@ -40,7 +40,12 @@ class Session {
   void run(const std::vector<TensorArg>& feeds, const std::vector<TensorArg>& fetches, bool rows = false);
   void aggregate(int64_t n_rows, const int64_t* keys, const std::vector<TensorArg>& feeds,
                  const std::vector<TensorArg>& fetches, int64_t max_groups, int64_t* out_keys,
-                 int64_t* n_groups);
+                 int64_t* n_groups, const std::vector<int>* feed_of_fetch = nullptr);
+
+  // one block of at most ~64 GB of payload through the keyed-reduction passes (aggregate cuts larger blocks)
+  void aggregate_block(int64_t n_rows, const int64_t* keys, const std::vector<TensorArg>& feeds,
+                       const std::vector<TensorArg>& fetches, int64_t max_groups, int64_t* out_keys,
+                       int64_t* n_groups, const std::vector<int>* feed_of_fetch = nullptr);
 
   // ---- the exchange steps over a communicator (one rank per partition) ----------------------------------------
   // reduceBlocks: merge this rank's partial result rows with every other rank's; every rank receives the merged
@@ -82,8 +87,9 @@ class Session {
   size_t ws_cap_ = 0;
   void* red_scratch_ = nullptr;
   size_t red_scratch_cap_ = 0;
-  char* xchg_[2] = {nullptr, nullptr};   // exchange staging ([0] gathered rows / send side, [1] receive side), grown on demand
-  size_t xchg_cap_[2] = {0, 0};
+  // staging grown on demand: [0] gathered rows / send side of an exchange, [1] receive side, [2] per-chunk partial groups
+  char* xchg_[3] = {nullptr, nullptr, nullptr};
+  size_t xchg_cap_[3] = {0, 0, 0};
   char* seg_scratch_ = nullptr;        // UnsortedSegmentSum: keyed-reduction scratch, grown on demand
   size_t seg_scratch_cap_ = 0;
   int32_t* err_flag_ = nullptr;       // device

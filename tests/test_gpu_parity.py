@@ -563,7 +563,7 @@ def test_aggregate_far_more_keys_than_the_table_holds():
     """A block with far more distinct keys than max_groups fills the whole hash table (1024 slots for max_groups = 100):
     every warp then has a lane probing a full table.  The call must come back with the overflow error, not spin."""
     n = 1_000_000
-    keys = (np.arange(n, dtype=np.int64) * 0x9E3779B97F4A7C15 + 7).astype(np.int64)      # all distinct
+    keys = (np.arange(n, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15) + np.uint64(7)).view(np.int64)      # all distinct (odd multiplier)
     v = np.ones((n, 4), dtype=np.float32)
     g = aggregate_graph(tfs.FloatType, (4,), "sum")
     with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
@@ -572,6 +572,35 @@ def test_aggregate_far_more_keys_than_the_table_holds():
                 s.aggregate(keys, {"v_input": v}, ["v"], max_groups=mg)
         got_keys, (got,) = s.aggregate(keys[:5000], {"v_input": v[:5000]}, ["v"], max_groups=5000)    # session still usable
     assert np.array_equal(np.sort(got_keys), np.sort(keys[:5000])) and np.all(got == 1.0)
+
+
+def test_aggregate_cut_into_row_ranges_matches_one_pass(monkeypatch):
+    """Blocks whose payload spans more than 64 GB are reduced range by range and the partial groups merged (the gather
+    pass slows down past that span).  TFS_AGG_CHUNK_MB lowers the threshold so that a small block takes the same path:
+    keys and integer results must be identical, float sums within tolerance, also for two fetches of one placeholder."""
+    rng = np.random.default_rng(91)
+    n, n_keys = 300_007, 777
+    table = rng.integers(-2**62, 2**62, n_keys)
+    keys = table[rng.integers(0, n_keys, n)].astype(np.int64)
+    v = rng.uniform(0, 1, (n, 16)).astype(np.float32)
+    w = rng.integers(-1000, 1000, (n, 3)).astype(np.int64)
+    with dsl.withGraph():
+        pv = dsl.placeholder(tfs.FloatType, dsl.Unknown, 16).named("v_input")
+        pw = dsl.placeholder(tfs.LongType, dsl.Unknown, 3).named("w_input")
+        g = dsl.build_graph(dsl.reduce_sum(pv, [0]).named("v"), dsl.reduce_max(pw, [0]).named("w"),
+                            dsl.reduce_min(pw, [0]).named("w_lo"))
+    feeds, names = {"v_input": v, "w_input": w}, ["v", "w", "w_lo"]
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        k1, one = s.aggregate(keys, feeds, names, max_groups=1024)
+        monkeypatch.setenv("TFS_AGG_CHUNK_MB", "4")                 # 19 MB of float payload: five ranges
+        k2, cut = s.aggregate(keys, feeds, names, max_groups=1024)
+        with pytest.raises(_native.NativeError, match="more than max_groups"):
+            s.aggregate(keys, feeds, names, max_groups=500)
+    assert np.array_equal(k1, k2) and np.array_equal(k1, np.unique(keys))
+    assert_same(one[1], cut[1])
+    assert_same(one[2], cut[2])
+    want_keys, want, absum = numpy_group_reduce(keys, v, "sum")
+    assert np.all(np.abs(cut[0].astype(np.float64) - want.astype(np.float64)) <= 1e-5 * absum)
 
 
 def test_aggregate_rejects_non_reducer_graphs():
