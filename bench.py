@@ -492,7 +492,7 @@ def run_reduce(ctx, wl, rows, cols=None):
 
     def drain():
         if world > 1:
-            sess.combine_wait()          # launch stream waits for the side stream's last exchange
+            sess.combine_wait(ctx.comm)  # launch stream waits for the side stream's last exchange
 
     launches0 = sess.launch_count
     elapsed_ms, clocks, host_ms = ctx.timed(step, drain)
