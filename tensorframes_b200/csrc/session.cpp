@@ -4,6 +4,7 @@
 #include <mutex>
 
 #include <algorithm>
+#include <functional>
 #include <cstdio>
 #include <cstdlib>
 #include <map>
@@ -148,7 +149,7 @@ Session::~Session() {
   if (ws_) cudaFree(ws_);
   if (red_scratch_) cudaFree(red_scratch_);
   if (seg_scratch_) cudaFree(seg_scratch_);
-  for (int k = 0; k < 3; ++k)
+  for (int k = 0; k < 4; ++k)
     if (xchg_[k]) cudaFree(xchg_[k]);
   for (int k = 0; k < 2; ++k)
     if (pipe_stream_[k]) cudaStreamDestroy(pipe_stream_[k]);
@@ -308,7 +309,7 @@ void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<
     int idx = g_.find(feeds[i].name);
     TFS_CHECK(idx >= 0, TFS_ERR_INVALID, "feed '" + feeds[i].name + "' is not a node of the graph");
     const Node& n = g_.nodes[size_t(idx)];
-    TFS_CHECK(n.cls == OpClass::Placeholder, TFS_ERR_INVALID,
+    TFS_CHECK(n.cls == OpClass::Placeholder || allow_internal_feeds_, TFS_ERR_INVALID,
               "Invalid type for input node " + n.name + ". It has to be a placeholder");
     TFS_CHECK(plan.feed_of[size_t(idx)] < 0, TFS_ERR_INVALID, "placeholder '" + n.name + "' is fed twice");
     // No implicit casting (reference: impl/DebugRowOps.scala:328-333).
@@ -351,7 +352,7 @@ void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<
     while (!stack.empty()) {
       auto& [u, k] = stack.back();
       const Node& nu = g_.nodes[size_t(u)];
-      if (k < nu.in.size()) {
+      if (k < nu.in.size() && plan.feed_of[size_t(u)] < 0) {       // (a fed node is a leaf, whatever its op)
         int v = nu.in[k++];
         if (!state[size_t(v)]) { state[size_t(v)] = 1; stack.push_back({v, 0}); }
       } else {
@@ -365,7 +366,7 @@ void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<
   // depends on a placeholder)
   for (int idx : plan.needed) {
     const Node& n = g_.nodes[size_t(idx)];
-    if (n.cls == OpClass::Placeholder) {
+    if (n.cls == OpClass::Placeholder || plan.feed_of[size_t(idx)] >= 0) {
       int f = plan.feed_of[size_t(idx)];
       TFS_CHECK(f >= 0, TFS_ERR_INVALID, "placeholder '" + n.name + "' is needed by the fetches but was not fed");
       plan.cshape[size_t(idx)] = rows ? drop_lead(feeds[size_t(f)].shape) : feeds[size_t(f)].shape;
@@ -454,6 +455,7 @@ void Session::build_plan(const std::vector<TensorArg>& feeds, const std::vector<
   std::map<std::string, int> group_of_key;
   for (int idx : plan.needed) {
     const Node& n = g_.nodes[size_t(idx)];
+    if (plan.feed_of[size_t(idx)] >= 0) continue;        // fed: nothing to compute (a placeholder, or an internal node the caller supplies)
     if (fused_from[size_t(idx)] >= 0) {
       const int st = plan.step_of[size_t(fused_from[size_t(idx)])];
       plan.steps[size_t(st)].out_node = idx;
@@ -1419,7 +1421,7 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
   size_t red_bytes = 0;
   for (int idx : plan.needed) {
     const Node& n = g_.nodes[size_t(idx)];
-    if (n.cls == OpClass::Placeholder) {
+    if (plan.feed_of[size_t(idx)] >= 0) {
       int f = plan.feed_of[size_t(idx)];
       if (feed_dev[size_t(f)]) dev_ptr[size_t(idx)] = feeds[size_t(f)].data;
       else { ws_off[size_t(idx)] = ws_bytes; ws_bytes += align_up(nbytes(idx)); }
@@ -1460,8 +1462,7 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
 
   // host -> device
   for (int idx : plan.needed) {
-    const Node& n = g_.nodes[size_t(idx)];
-    if (n.cls != OpClass::Placeholder) continue;
+    if (plan.feed_of[size_t(idx)] < 0) continue;
     int f = plan.feed_of[size_t(idx)];
     if (!feed_dev[size_t(f)] && nbytes(idx) > 0)
       copy_in(dev_ptr[size_t(idx)], feeds[size_t(f)].data, nbytes(idx));
@@ -1595,6 +1596,23 @@ void Session::aggregate(int64_t n_rows, const int64_t* keys, const std::vector<T
   aggregate_block(total, reinterpret_cast<const int64_t*>(parts), mf, fetches, max_groups, out_keys, n_groups_out, &identity);
 }
 
+// What the keyed passes work on: one column of n_rows cells to be reduced per key into `out` (max_groups cells).
+struct Session::AggColumn {
+  std::string name;      // for messages
+  int dtype = 0, red_op = 0;
+  int64_t cell = 0;
+  const void* payload = nullptr;   // [n_rows, cell], host or device
+  void* out = nullptr;             // [max_groups, cell], host or device
+};
+
+// aggregate for one block.  The reference hands each key's buffered rows to the user's reducer graph
+// (TensorFlowUDAF.compact -> performReduceBlock, impl/DebugRowOps.scala:644-656), so any graph that keeps the X / X_input
+// contract works there.  Here a fetch is taken apart into
+//     fetch = post( Reduce_axis0( pre(placeholders) ) )
+// with `pre` and `post` element-wise (or empty): `pre` runs once over the whole block as an ordinary map, the keyed
+// passes reduce its result per key, and `post` runs once over the [n_groups, cell] table of reduced rows, every row being
+// one cell (row mode, with the Reduce node fed).  A bare Sum / Min / Max of a placeholder -- the usual case, and
+// BASELINE config 4 -- has neither and touches the payload exactly once.
 void Session::aggregate_block(int64_t n_rows, const int64_t* keys, const std::vector<TensorArg>& feeds,
                               const std::vector<TensorArg>& fetches, int64_t max_groups, int64_t* out_keys,
                               int64_t* n_groups_out, const std::vector<int>* feed_of_fetch) {
@@ -1602,45 +1620,147 @@ void Session::aggregate_block(int64_t n_rows, const int64_t* keys, const std::ve
   TFS_CHECK(n_rows < (int64_t(1) << 32), TFS_ERR_UNSUPPORTED, "aggregate: blocks of 2^32 rows or more are not supported");
   TFS_CHECK(n_rows == 0 || keys != nullptr, TFS_ERR_INVALID, "null key column");
   TFS_CHECK(max_groups == 0 || out_keys != nullptr, TFS_ERR_INVALID, "null out_keys");
-  // Every fetch must be Sum/Min/Max over axis 0 of a fed placeholder: the keyed form of the
-  // reduce contract (fetch X <- placeholder X_input, impl/DebugRowOps.scala:80-170).
-  struct Item { int node; int feed; int64_t cell; size_t fetch; };
+  TFS_CHECK(!fetches.empty(), TFS_ERR_INVALID, "Output cannot be empty: no fetch requested");
+  const size_t N = g_.nodes.size();
+  // which nodes depend on a placeholder
+  std::vector<signed char> dep(N, -1);
+  std::function<bool(int)> depends = [&](int u) -> bool {
+    if (dep[size_t(u)] >= 0) return dep[size_t(u)] != 0;
+    const Node& n = g_.nodes[size_t(u)];
+    bool d = n.cls == OpClass::Placeholder;
+    for (int k : n.in) d = depends(k) || d;
+    dep[size_t(u)] = d ? 1 : 0;
+    return d;
+  };
+  struct Item { int fetch_node, red_node, src_node, feed; bool pre, post; };
   std::vector<Item> items;
+  std::vector<AggColumn> cols;
+  std::vector<Shape> red_in_shape(fetches.size());     // [n_rows, cell...] shape of every reduction's input
+  bool any_pre = false, any_post = false;
   for (size_t i = 0; i < fetches.size(); ++i) {
-    int idx = g_.find(fetches[i].name);
-    TFS_CHECK(idx >= 0, TFS_ERR_INVALID, "fetch '" + fetches[i].name + "' is not a node of the graph");
-    const Node& n = g_.nodes[size_t(idx)];
-    TFS_CHECK(n.cls == OpClass::Reduce, TFS_ERR_UNSUPPORTED,
-              "aggregate: fetch '" + n.name + "' (" + n.op + ") must be a Sum, Min or Max over axis 0 of its placeholder");
-    const Node& src = g_.nodes[size_t(n.in[0])];
-    TFS_CHECK(src.cls == OpClass::Placeholder, TFS_ERR_UNSUPPORTED,
-              "aggregate: fetch '" + n.name + "' must reduce a placeholder directly, found '" + src.name + "' (" + src.op + ")");
-    int feed = -1;
-    if (feed_of_fetch != nullptr) feed = (*feed_of_fetch)[i];      // merge of partial rows: column i belongs to fetch i
-    else
-      for (size_t f = 0; f < feeds.size(); ++f)
-        if (g_.find(feeds[f].name) == n.in[0]) feed = int(f);
-    TFS_CHECK(feed >= 0, TFS_ERR_INVALID, "placeholder '" + src.name + "' is needed by the fetches but was not fed");
-    const TensorArg& fa = feeds[size_t(feed)];
-    TFS_CHECK(fa.dtype == src.dtype, TFS_ERR_INVALID,
-              "The type of node '" + src.name + "' (" + dtype_name(src.dtype) +
-                  ") is not compatible with the data type of the feed (" + dtype_name(fa.dtype) + ")");
-    TFS_CHECK(fa.shape.fully_known() && fa.shape.rank >= 1 && fa.shape.d[0] == n_rows, TFS_ERR_INVALID,
-              "feed '" + src.name + "' must have " + std::to_string(n_rows) + " rows, got shape " + fa.shape.str());
-    std::vector<int> axes = normalize_axes(n, fa.shape.rank);
-    TFS_CHECK(axes.size() == 1 && axes[0] == 0, TFS_ERR_UNSUPPORTED,
-              "aggregate: fetch '" + n.name + "' must reduce axis 0 only");
-    int64_t cell = 1;
-    for (int d = 1; d < fa.shape.rank; ++d) cell *= fa.shape.d[d];
-    TFS_CHECK(fetches[i].data != nullptr || max_groups * cell == 0, TFS_ERR_INVALID,
-              "fetch '" + n.name + "' has no output buffer");
-    items.push_back({idx, feed, cell, i});
+    const int f_idx = g_.find(fetches[i].name);
+    TFS_CHECK(f_idx >= 0, TFS_ERR_INVALID, "fetch '" + fetches[i].name + "' is not a node of the graph");
+    // walk down from the fetch through element-wise nodes to the one reduction
+    int cur = f_idx;
+    while (g_.nodes[size_t(cur)].cls != OpClass::Reduce) {
+      const Node& c = g_.nodes[size_t(cur)];
+      TFS_CHECK(c.cls == OpClass::Unary || c.cls == OpClass::Binary, TFS_ERR_UNSUPPORTED,
+                "aggregate: fetch '" + g_.nodes[size_t(f_idx)].name + "' must be a Sum, Min or Max over axis 0, optionally inside "
+                "element-wise operations; found '" + c.name + "' (" + c.op + ") on the way to the reduction");
+      int data = -1;
+      for (int k : c.in)
+        if (depends(k)) {
+          TFS_CHECK(data < 0 || data == k, TFS_ERR_UNSUPPORTED,
+                    "aggregate: '" + c.name + "' (" + c.op + ") combines two reduced values; one reduction per fetch is supported");
+          data = k;
+        }
+      TFS_CHECK(data >= 0, TFS_ERR_UNSUPPORTED,
+                "aggregate: fetch '" + g_.nodes[size_t(f_idx)].name + "' does not depend on any placeholder");
+      cur = data;
+    }
+    const Node& r = g_.nodes[size_t(cur)];
+    const Node& src = g_.nodes[size_t(r.in[0])];
+    Item it{f_idx, cur, r.in[0], -1, src.cls != OpClass::Placeholder, cur != f_idx};
+    AggColumn col;
+    col.name = g_.nodes[size_t(f_idx)].name;
+    col.dtype = r.dtype;
+    col.red_op = r.red_op;
+    if (!it.pre) {
+      if (feed_of_fetch != nullptr) it.feed = (*feed_of_fetch)[i];      // merge of partial rows: column i belongs to fetch i
+      else
+        for (size_t f = 0; f < feeds.size(); ++f)
+          if (g_.find(feeds[f].name) == r.in[0]) it.feed = int(f);
+      TFS_CHECK(it.feed >= 0, TFS_ERR_INVALID, "placeholder '" + src.name + "' is needed by the fetches but was not fed");
+      const TensorArg& fa = feeds[size_t(it.feed)];
+      TFS_CHECK(fa.dtype == src.dtype, TFS_ERR_INVALID,
+                "The type of node '" + src.name + "' (" + dtype_name(src.dtype) +
+                    ") is not compatible with the data type of the feed (" + dtype_name(fa.dtype) + ")");
+      TFS_CHECK(fa.shape.fully_known() && fa.shape.rank >= 1 && fa.shape.d[0] == n_rows, TFS_ERR_INVALID,
+                "feed '" + src.name + "' must have " + std::to_string(n_rows) + " rows, got shape " + fa.shape.str());
+      std::vector<int> axes = normalize_axes(r, fa.shape.rank);
+      TFS_CHECK(axes.size() == 1 && axes[0] == 0, TFS_ERR_UNSUPPORTED, "aggregate: fetch '" + col.name + "' must reduce axis 0 only");
+      col.cell = 1;
+      for (int d = 1; d < fa.shape.rank; ++d) col.cell *= fa.shape.d[d];
+      col.payload = fa.data;
+      red_in_shape[i] = fa.shape;
+    }
+    if (!it.post) {
+      col.out = fetches[i].data;
+      TFS_CHECK(col.out != nullptr || it.pre || max_groups * col.cell == 0, TFS_ERR_INVALID, "fetch '" + col.name + "' has no output buffer");
+    }
+    any_pre = any_pre || it.pre;
+    any_post = any_post || it.post;
+    items.push_back(it);
+    cols.push_back(col);
   }
-  TFS_CHECK(!items.empty(), TFS_ERR_INVALID, "Output cannot be empty: no fetch requested");
-
   ensure_device();
   *n_groups_out = 0;
   if (n_rows == 0) return;
+  if (!any_pre && !any_post) {
+    aggregate_columns(n_rows, keys, cols, max_groups, out_keys, n_groups_out);
+    return;
+  }
+  // ---- pre: one map run over the block for every reduction whose input is computed
+  std::vector<TensorArg> pre_fetch;
+  std::vector<size_t> pre_of;
+  for (size_t i = 0; i < items.size(); ++i)
+    if (items[i].pre) {
+      TensorArg a;
+      a.name = g_.nodes[size_t(items[i].src_node)].name;
+      pre_fetch.push_back(a);
+      pre_of.push_back(i);
+    }
+  if (!pre_fetch.empty()) resolve(feeds, pre_fetch, false);
+  size_t tmp = 0;
+  std::vector<size_t> off_pre(items.size(), SIZE_MAX), off_red(items.size(), SIZE_MAX);
+  for (size_t k = 0; k < pre_fetch.size(); ++k) {
+    const size_t i = pre_of[k];
+    const Shape& sh = pre_fetch[k].shape;
+    const Node& r = g_.nodes[size_t(items[i].red_node)];
+    TFS_CHECK(sh.rank >= 1 && sh.d[0] == n_rows, TFS_ERR_UNSUPPORTED,
+              "aggregate: the input of '" + r.name + "' has shape " + sh.str() + ", not one cell per row of the block");
+    std::vector<int> axes = normalize_axes(r, sh.rank);
+    TFS_CHECK(axes.size() == 1 && axes[0] == 0, TFS_ERR_UNSUPPORTED, "aggregate: fetch '" + cols[i].name + "' must reduce axis 0 only");
+    cols[i].cell = sh.numel() / n_rows;
+    red_in_shape[i] = sh;
+    off_pre[i] = tmp;
+    tmp += align_up(size_t(sh.numel()) * size_t(dtype_size(pre_fetch[k].dtype)));
+  }
+  for (size_t i = 0; i < items.size(); ++i)
+    if (items[i].post) { off_red[i] = tmp; tmp += align_up(size_t(max_groups) * size_t(cols[i].cell) * size_t(dtype_size(cols[i].dtype))); }
+  char* tbuf = reserve_exchange(3, std::max<size_t>(tmp, 256));
+  if (!pre_fetch.empty()) {
+    for (size_t k = 0; k < pre_fetch.size(); ++k) pre_fetch[k].data = tbuf + off_pre[pre_of[k]];
+    run(feeds, pre_fetch, false);
+    for (size_t k = 0; k < pre_fetch.size(); ++k) cols[pre_of[k]].payload = pre_fetch[k].data;
+  }
+  for (size_t i = 0; i < items.size(); ++i)
+    if (items[i].post) cols[i].out = tbuf + off_red[i];
+  int64_t n_groups = 0;
+  aggregate_columns(n_rows, keys, cols, max_groups, out_keys, &n_groups);
+  // ---- post: the element-wise tail of every fetch over the table of reduced rows, the Reduce node fed
+  for (size_t i = 0; i < items.size(); ++i) {
+    if (!items[i].post || n_groups == 0) continue;
+    const Node& r = g_.nodes[size_t(items[i].red_node)];
+    TensorArg feed;
+    feed.name = r.name;
+    feed.dtype = r.dtype;
+    const Shape cell_shape = drop_lead(red_in_shape[i]);
+    feed.shape = with_lead(n_groups, cell_shape);
+    feed.data = cols[i].out;
+    TensorArg out = fetches[i];
+    out.shape = Shape();                       // the caller's buffer holds max_groups rows; n_groups of them are written
+    out.dtype = 0;
+    struct Allow { bool& f; explicit Allow(bool& x) : f(x) { f = true; } ~Allow() { f = false; } } allow(allow_internal_feeds_);
+    run({feed}, {out}, true);
+  }
+  TFS_CUDA(cudaStreamSynchronize(stream_));
+  *n_groups_out = n_groups;
+}
+
+// The keyed passes (K3) over prepared columns.  Synchronous.
+void Session::aggregate_columns(int64_t n_rows, const int64_t* keys, const std::vector<AggColumn>& items, int64_t max_groups,
+                                int64_t* out_keys, int64_t* n_groups_out) {
   (void)on_device_or_refuse(out_keys, dev_.device, "out_keys");     // refused before any work, not at the final copy
   TFS_CHECK(max_groups > 0, TFS_ERR_INVALID, "aggregate: max_groups must be positive for a non-empty block");
 
@@ -1650,7 +1770,7 @@ void Session::aggregate_block(int64_t n_rows, const int64_t* keys, const std::ve
   size_t off = up(L.bytes);
   const size_t off_out_keys = off; off += up(size_t(max_groups) * 8);
   int64_t widest = 1;
-  for (const Item& it : items) widest = std::max(widest, it.cell);
+  for (const AggColumn& it : items) widest = std::max(widest, it.cell);
   const size_t split_bytes = agg_split_scratch_bytes(widest, dev_);
   const size_t off_split = off; off += up(split_bytes);
   // scalar payloads (at most two of them) ride through their own sort instead of being gathered
@@ -1658,8 +1778,8 @@ void Session::aggregate_block(int64_t n_rows, const int64_t* keys, const std::ve
   size_t carried_bytes = 0;
   {
     size_t n_scalar = 0;
-    auto row_bytes = [&](const Item& it) { return it.cell * int64_t(dtype_size(g_.nodes[size_t(it.node)].dtype)); };
-    for (const Item& it : items) n_scalar += row_bytes(it) <= 8 ? 1 : 0;
+    auto row_bytes = [&](const AggColumn& it) { return it.cell * int64_t(dtype_size(it.dtype)); };
+    for (const AggColumn& it : items) n_scalar += row_bytes(it) <= 8 ? 1 : 0;
     static const bool off_switch = [] { const char* e = std::getenv("TFS_AGG_CARRY"); return e && std::string(e) == "off"; }();
     if (n_scalar > 0 && n_scalar <= 2 && n_rows >= (int64_t(1) << 16) && !off_switch)
       for (size_t k = 0; k < items.size(); ++k)
@@ -1674,10 +1794,10 @@ void Session::aggregate_block(int64_t n_rows, const int64_t* keys, const std::ve
   if (!keys_dev) { off_keys = off; off += up(size_t(n_rows) * 8); }
   std::vector<size_t> off_feed(items.size(), SIZE_MAX), off_out(items.size(), SIZE_MAX);
   for (size_t k = 0; k < items.size(); ++k) {
-    const Node& n = g_.nodes[size_t(items[k].node)];
-    const size_t es = size_t(dtype_size(n.dtype));
-    if (!on_device_or_refuse(feeds[size_t(items[k].feed)].data, dev_.device, "feed '" + feeds[size_t(items[k].feed)].name + "'")) { off_feed[k] = off; off += up(size_t(n_rows) * items[k].cell * es); }
-    if (!on_device_or_refuse(fetches[items[k].fetch].data, dev_.device, "fetch buffer '" + fetches[items[k].fetch].name + "'")) { off_out[k] = off; off += up(size_t(max_groups) * items[k].cell * es); }
+    const size_t es = size_t(dtype_size(items[k].dtype));
+    TFS_CHECK(items[k].out != nullptr || max_groups * items[k].cell == 0, TFS_ERR_INVALID, "fetch '" + items[k].name + "' has no output buffer");
+    if (!on_device_or_refuse(items[k].payload, dev_.device, "the feed of '" + items[k].name + "'")) { off_feed[k] = off; off += up(size_t(n_rows) * items[k].cell * es); }
+    if (!on_device_or_refuse(items[k].out, dev_.device, "fetch buffer '" + items[k].name + "'")) { off_out[k] = off; off += up(size_t(max_groups) * items[k].cell * es); }
   }
   reserve_workspace(off);
   char* scratch = ws_;
@@ -1704,14 +1824,14 @@ void Session::aggregate_block(int64_t n_rows, const int64_t* keys, const std::ve
      launches_ += launch_agg_segments(d_keys, n_rows, n_groups, scratch, L, d_out_keys, false, true, dev_, stream_);  // rows by slot
    for (size_t k = 0; k < items.size(); ++k) {
     if ((pass == 0) != (carried[k] != 0)) continue;
-    const Node& n = g_.nodes[size_t(items[k].node)];
+    const AggColumn& n = items[k];
     const size_t es = size_t(dtype_size(n.dtype));
-    const void* payload = feeds[size_t(items[k].feed)].data;
+    const void* payload = items[k].payload;
     if (off_feed[k] != SIZE_MAX) {
       copy_in(ws_ + off_feed[k], payload, size_t(n_rows) * items[k].cell * es);
       payload = ws_ + off_feed[k];
     }
-    void* out = off_out[k] != SIZE_MAX ? static_cast<void*>(ws_ + off_out[k]) : fetches[items[k].fetch].data;
+    void* out = off_out[k] != SIZE_MAX ? static_cast<void*>(ws_ + off_out[k]) : items[k].out;
     if (carried[k])
       launches_ += launch_agg_reduce_carried(n.dtype, n.red_op, payload, items[k].cell, n_groups, n_rows, scratch, L, out, ws_ + off_carried,
                                              carried_bytes, ws_ + off_split, split_bytes, dev_, stream_);
@@ -1719,7 +1839,7 @@ void Session::aggregate_block(int64_t n_rows, const int64_t* keys, const std::ve
       launches_ += launch_agg_reduce(n.dtype, n.red_op, payload, items[k].cell, n_groups, n_rows, scratch, L, out, ws_ + off_split,
                                      split_bytes, dev_, stream_);
     if (off_out[k] != SIZE_MAX && n_groups * items[k].cell > 0)
-      TFS_CUDA(cudaMemcpyAsync(fetches[items[k].fetch].data, out, size_t(n_groups) * items[k].cell * es,
+      TFS_CUDA(cudaMemcpyAsync(items[k].out, out, size_t(n_groups) * items[k].cell * es,
                                cudaMemcpyDeviceToHost, stream_));
    }
   }

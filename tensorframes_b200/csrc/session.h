@@ -47,6 +47,10 @@ class Session {
                        const std::vector<TensorArg>& fetches, int64_t max_groups, int64_t* out_keys,
                        int64_t* n_groups, const std::vector<int>* feed_of_fetch = nullptr);
 
+  struct AggColumn;
+  void aggregate_columns(int64_t n_rows, const int64_t* keys, const std::vector<AggColumn>& cols, int64_t max_groups,
+                         int64_t* out_keys, int64_t* n_groups);
+
   // ---- the exchange steps over a communicator (one rank per partition) ----------------------------------------
   // reduceBlocks: merge this rank's partial result rows with every other rank's; every rank receives the merged
   // row (RDD.reduce + reducePairBlock, impl/DebugRowOps.scala:524-525, 741-750).  partials / merged: device memory.
@@ -88,8 +92,9 @@ class Session {
   void* red_scratch_ = nullptr;
   size_t red_scratch_cap_ = 0;
   // staging grown on demand: [0] gathered rows / send side of an exchange, [1] receive side, [2] per-chunk partial groups
-  char* xchg_[3] = {nullptr, nullptr, nullptr};
-  size_t xchg_cap_[3] = {0, 0, 0};
+  char* xchg_[4] = {nullptr, nullptr, nullptr, nullptr};      // ([3]: computed reduction inputs / reduced rows of general reducer graphs)
+  size_t xchg_cap_[4] = {0, 0, 0, 0};
+  bool allow_internal_feeds_ = false;   // the post-map of aggregate feeds the Reduce node itself
   char* seg_scratch_ = nullptr;        // UnsortedSegmentSum: keyed-reduction scratch, grown on demand
   size_t seg_scratch_cap_ = 0;
   int32_t* err_flag_ = nullptr;       // device

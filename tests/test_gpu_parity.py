@@ -603,6 +603,73 @@ def test_aggregate_cut_into_row_ranges_matches_one_pass(monkeypatch):
     assert np.all(np.abs(cut[0].astype(np.float64) - want.astype(np.float64)) <= 1e-5 * absum)
 
 
+def test_aggregate_general_reducer_graphs(monkeypatch):
+    """The reference hands each key's rows to the user's graph (TensorFlowUDAF.compact -> performReduceBlock,
+    impl/DebugRowOps.scala:644-656), so a reducer need not be a bare Sum / Min / Max of its placeholder.  Element-wise
+    operations before and after the one reduction are taken as a map over the block, the keyed reduction, and a map
+    over the reduced rows."""
+    rng = np.random.default_rng(123)
+    n, n_keys = 50_021, 301
+    table = rng.integers(-2**62, 2**62, n_keys)
+    keys = table[rng.integers(0, n_keys, n)].astype(np.int64)
+    x = rng.uniform(-3, 3, (n, 5))
+    y = rng.uniform(0, 1, (n, 7)).astype(np.float32)
+    z = rng.integers(-50, 50, n).astype(np.int32)
+    with dsl.withGraph():
+        px = dsl.placeholder(tfs.DoubleType, dsl.Unknown, 5).named("x_input")
+        py = dsl.placeholder(tfs.FloatType, dsl.Unknown, 7).named("y_input")
+        pz = dsl.placeholder(tfs.IntegerType, dsl.Unknown).named("z_input")
+        fx = dsl.neg(dsl.reduce_max(dsl.neg(px), [0])).named("x")                                   # min, the long way round
+        fy = dsl.cast(dsl.reduce_sum(dsl.cast(py, tfs.DoubleType), [0]), tfs.FloatType).named("y")  # float column summed in double
+        fz = dsl.reduce_sum(dsl._build("Abs", parents=[pz]), [0]).named("z")                        # pre-map only
+        g = dsl.build_graph(fx, fy, fz)
+    feeds, names = {"x_input": x, "y_input": y, "z_input": z}, ["x", "y", "z"]
+    uniq, inv = np.unique(keys, return_inverse=True)
+    want_x = np.full((len(uniq), 5), np.inf)
+    np.minimum.at(want_x, inv, x)
+    want_y = np.zeros((len(uniq), 7))
+    np.add.at(want_y, inv, y.astype(np.float64))
+    want_z = np.zeros(len(uniq), dtype=np.int64)
+    np.add.at(want_z, inv, np.abs(z).astype(np.int64))
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        for chunk_mb in (None, "1"):                # one pass, and cut into row ranges whose partial rows go through the graph again
+            if chunk_mb:
+                monkeypatch.setenv("TFS_AGG_CHUNK_MB", chunk_mb)
+            got_keys, (gx, gy, gz) = s.aggregate(keys, feeds, names, max_groups=512)
+            assert np.array_equal(got_keys, uniq)
+            assert gx.dtype == np.float64 and np.array_equal(gx, want_x)
+            assert gy.dtype == np.float32 and np.array_equal(gy, want_y.astype(np.float32)) or chunk_mb      # one pass: the double sum rounded once
+            assert np.all(np.abs(gy.astype(np.float64) - want_y) <= 1e-6 * want_y)
+            assert gz.dtype == np.int32 and np.array_equal(gz, want_z.astype(np.int32))
+        # what cannot be taken apart is named
+        with dsl.withGraph():
+            p = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("m_input")
+            bad = dsl.build_graph(dsl.div(dsl.reduce_sum(p, [0]), dsl.reduce_max(p, [0])).named("m"))
+    with _native.Graph(bad) as gr, _native.Session(gr, 0) as s:
+        with pytest.raises(_native.UnsupportedError, match="combines two reduced values"):
+            s.aggregate(keys, {"m_input": x[:, 0].copy()}, ["m"], max_groups=512)
+
+
+def test_aggregate_operator_with_a_general_reducer_matches_the_oracle_udaf():
+    """tfs.aggregate on a partitioned frame with a reducer that is not a bare reduction, against the oracle's
+    restatement of TensorFlowUDAF (10-row buffers, the graph re-applied to compacted rows)."""
+    from oracle import executors as ox
+    rng = np.random.default_rng(321)
+    n = 3000
+    key = rng.integers(0, 40, n).astype(np.int64)
+    x = rng.integers(-9, 9, (n, 3)).astype(np.float64)
+    rows = [(int(key[i]), x[i].tolist()) for i in range(n)]
+    df = tfs.analyze(TensorFrame.from_rows(rows, ["key", "x"], num_partitions=3))
+    with dsl.withGraph():
+        xi = tfs.block(df, "x", tf_name="x_input")
+        fetch = dsl.neg(dsl.reduce_max(dsl.neg(xi), [0])).named("x")
+        out = tfs.aggregate(fetch, df.groupBy("key"))
+        g = dsl.build_graph(fetch)
+    kparts, kcols = _golden.oracle_inputs(None, df)
+    want = ox.aggregate(kparts, kcols, [0], g, ["x"])
+    assert _golden.normalize(out.collect()) == _golden.normalize(want)
+
+
 def test_aggregate_rejects_non_reducer_graphs():
     with dsl.withGraph():
         p = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x_input")
