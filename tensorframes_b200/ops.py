@@ -186,13 +186,49 @@ def _as_feed(col):
 
 
 class B200Ops:
-    """OperationsInterface (Operations.scala:20-135) executed on a B200 through libtfsb200."""
+    """OperationsInterface (Operations.scala:20-135) executed on B200s through libtfsb200.
 
-    def __init__(self, device: int = 0):
-        self.device = device
+    `devices=[...]`: partition i of a frame runs on devices[i % len(devices)], every device driven by its own thread
+    (the reference runs one task thread per partition, impl/DebugRowOps.scala:377-391).  mapBlocks needs no exchange;
+    reduceBlocks and aggregate combine the per-device results through the library's communicators
+    (tfs_session_reduce_combine / tfs_session_aggregate_combine: NCCL over NVLink), which stand in for RDD.reduce and
+    the UDAF's shuffle (impl/DebugRowOps.scala:524-525, 573-576)."""
+
+    def __init__(self, device: int = 0, devices: Optional[List[int]] = None):
+        self.devices = list(devices) if devices else [device]
+        self.device = self.devices[0]
+        self._comms = None
 
     def __repr__(self) -> str:
-        return f"B200Ops(device={self.device})"
+        return f"B200Ops(devices={self.devices})"
+
+    def _communicators(self):
+        if self._comms is None:
+            self._comms = _native.Comm.create_all(self.devices)
+        return self._comms
+
+    def _per_device(self, work):
+        """Runs work(slot) for every device slot on its own thread; returns the results in slot order."""
+        n = len(self.devices)
+        if n == 1:
+            return [work(0)]
+        import threading
+        results, errors = [None] * n, []
+
+        def runner(slot):
+            try:
+                results[slot] = work(slot)
+            except BaseException as exc:      # surfaced in the caller's thread
+                errors.append(exc)
+
+        threads = [threading.Thread(target=runner, args=(slot,)) for slot in range(n)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        if errors:
+            raise errors[0]
+        return results
 
     # ---- helpers -------------------------------------------------------------------
     @staticmethod
@@ -270,34 +306,45 @@ class B200Ops:
             fetch_names = [f.name for f in tf_schema.fields]
             input_names = list(inputs.keys())
 
-            parts = []
-            with _native.Session(graph, self.device) as session:
-                for part in df.partitions:
-                    n = df._part_len(part)
-                    if n == 0:          # empty partitions never reach the runtime (:380-390, :777-779)
-                        continue
-                    feeds = {name: self._dense_block(df, part, name, n) for name in input_names}
-                    # blocks that live on the device stay there, and so do the columns computed from them
-                    on_device = any(is_device_column(v) for v in feeds.values())
-                    outs = session.run_torch(feeds, fetch_names, self.device) if on_device else session.run(feeds, fetch_names)
-                    new_part: Dict[str, object] = {}
-                    rows_seen = []
-                    for f, arr in zip(tf_schema.fields, outs):
-                        info = ColumnInformation.of(f).stf
-                        n_rows, cell = infer_physical_shape(_numel(arr), info.shape.tail, n if append_input else None)
-                        rows_seen.append(n_rows)
-                        if cell.numDims > 2:
-                            raise ValueError(f"Operations for tensors of order {cell.numDims + 1} are not supported")
-                        new_part[f.name] = arr.reshape((n_rows,) + cell.dims)
-                    if len(set(rows_seen)) != 1:
-                        raise Exception(f"Multiple number of rows detected. tf_struct={tf_schema}, tfSizes = {rows_seen}")
-                    assert (not append_input) or rows_seen[0] == n, \
-                        f"Incompatible sizes detected: appendInput={append_input}, tf num rows = {rows_seen[0]}, " \
-                        f"input num rows = {n}"
-                    if append_input:
-                        for name in df.schema.fieldNames:
-                            new_part[name] = part[name]
-                    parts.append(new_part)
+            def map_partition(session, device, part):
+                n = df._part_len(part)
+                feeds = {name: self._dense_block(df, part, name, n) for name in input_names}
+                # blocks that live on the device stay there, and so do the columns computed from them
+                on_device = any(is_device_column(v) for v in feeds.values())
+                outs = session.run_torch(feeds, fetch_names, device) if on_device else session.run(feeds, fetch_names)
+                new_part: Dict[str, object] = {}
+                rows_seen = []
+                for f, arr in zip(tf_schema.fields, outs):
+                    info = ColumnInformation.of(f).stf
+                    n_rows, cell = infer_physical_shape(_numel(arr), info.shape.tail, n if append_input else None)
+                    rows_seen.append(n_rows)
+                    if cell.numDims > 2:
+                        raise ValueError(f"Operations for tensors of order {cell.numDims + 1} are not supported")
+                    new_part[f.name] = arr.reshape((n_rows,) + cell.dims)
+                if len(set(rows_seen)) != 1:
+                    raise Exception(f"Multiple number of rows detected. tf_struct={tf_schema}, tfSizes = {rows_seen}")
+                assert (not append_input) or rows_seen[0] == n, \
+                    f"Incompatible sizes detected: appendInput={append_input}, tf num rows = {rows_seen[0]}, " \
+                    f"input num rows = {n}"
+                if append_input:
+                    for name in df.schema.fieldNames:
+                        new_part[name] = part[name]
+                return new_part
+
+            # empty partitions never reach the runtime (:380-390, :777-779)
+            live = [(i, part) for i, part in enumerate(df.partitions) if df._part_len(part) > 0]
+            done: Dict[int, Dict[str, object]] = {}
+
+            def work(slot):
+                mine = [(i, part) for k, (i, part) in enumerate(live) if k % len(self.devices) == slot]
+                if not mine:
+                    return
+                with _native.Session(graph, self.devices[slot]) as session:
+                    for i, part in mine:
+                        done[i] = map_partition(session, self.devices[slot], part)
+
+            self._per_device(work)
+            parts = [done[i] for i, _ in live]
         return TensorFrame(out_schema, parts)
 
     # ---- reduceBlocks (impl/DebugRowOps.scala:503-526, 872-895) -----------------------
@@ -306,23 +353,50 @@ class B200Ops:
         with _native.Graph(g) as graph:
             schemas = reduce_blocks_schema(df.schema, graph, h)
             out_names = [f.name for f in schemas.output.fields]
-            partials: List[List[np.ndarray]] = []
-            with _native.Session(graph, self.device) as session:
-                for part in df.partitions:
+            live = [part for part in df.partitions if df._part_len(part) > 0]
+            if not live:
+                raise ValueError("empty collection")  # RDD.reduce on an empty RDD (:524)
+            n_dev = min(len(self.devices), len(live))
+
+            def local_reduce(session, mine):
+                """The partial row of one device: its partitions one by one, then -- the reference merges partition
+                results pairwise by running the same graph on 2-row blocks (:741-750) -- one run over the stacked
+                [P, cell...] block, which is the same merge for the associative reducers the contract allows."""
+                partials = []
+                for part in mine:
                     n = df._part_len(part)
-                    if n == 0:
-                        continue
                     feeds = {name + "_input": _as_feed(self._dense_block(df, part, name, n)) for name in out_names}
                     partials.append(session.run(feeds, out_names))      # the partial row is small: it comes to the host
-                if not partials:
-                    raise ValueError("empty collection")  # RDD.reduce on an empty RDD (:524)
-                result = partials[0]
-                if len(partials) > 1:
-                    # The reference merges partition results pairwise by running the same graph on
-                    # 2-row blocks (:741-750); one run over the stacked [P, cell...] block is the same
-                    # merge for the associative reducers the contract allows.
-                    feeds = {name + "_input": np.stack([p[i] for p in partials]) for i, name in enumerate(out_names)}
-                    result = session.run(feeds, out_names)
+                if len(partials) == 1:
+                    return partials[0]
+                feeds = {name + "_input": np.stack([p[i] for p in partials]) for i, name in enumerate(out_names)}
+                return session.run(feeds, out_names)
+
+            if n_dev == 1:
+                with _native.Session(graph, self.device) as session:
+                    result = local_reduce(session, live)
+            else:
+                import torch
+                comms = self._communicators() if n_dev == len(self.devices) else _native.Comm.create_all(self.devices[:n_dev])
+                DA = _native.DeviceArray.from_torch
+
+                def work(slot):
+                    if slot >= n_dev:
+                        return None
+                    dev = self.devices[slot]
+                    with _native.Session(graph, dev) as session:
+                        rows = local_reduce(session, [p for k, p in enumerate(live) if k % n_dev == slot])
+                        part_t = {n_: torch.from_numpy(np.ascontiguousarray(r)).to(f"cuda:{dev}") for n_, r in zip(out_names, rows)}
+                        merged_t = {n_: torch.empty_like(t) for n_, t in part_t.items()}
+                        torch.cuda.synchronize(dev)
+                        session.reduce_combine(comms[slot], {k: DA(v) for k, v in part_t.items()}, {k: DA(v) for k, v in merged_t.items()})
+                        session.sync()
+                        return [merged_t[n_].cpu().numpy() for n_ in out_names]
+
+                result = self._per_device(work)[0]
+                if comms is not self._comms:
+                    for c in comms:
+                        c.close()
         for f, arr in zip(schemas.output.fields, result):
             cell = ColumnInformation.of(f).stf.shape.tail
             if cell.numElements is not None and int(arr.size) != cell.numElements:
@@ -331,6 +405,37 @@ class B200Ops:
         return Row.of(out_names, [_to_python(a) for a in result])
 
     # ---- aggregate (impl/DebugRowOps.scala:547-592, TensorFlowUDAF :601-695) ------------
+    @staticmethod
+    def _key_ids(df: TensorFrame, key_names: List[str], parts: List[Dict[str, object]]):
+        """The key columns of the given partitions as one int64 id per row, plus the way back from ids to key values.
+        A single integer key column is used as it is, bit for bit (no host pass over its values); anything else is
+        coded column by column with numpy (`np.unique(..., return_inverse=True)`) and the codes are combined --
+        the grouping itself is Spark's job in the reference."""
+        cols = {k: [p[k] for p in parts] for k in key_names}
+        if len(key_names) == 1 and all(isinstance(c, np.ndarray) and c.dtype.kind == "i" for c in cols[key_names[0]]):
+            ids = [c.astype(np.int64, copy=False) for c in cols[key_names[0]]]
+            return ids, None, None
+        codes, tables = [], []
+        for k in key_names:
+            flat = np.concatenate([np.asarray(c) if isinstance(c, np.ndarray) else np.asarray(list(c), dtype=object) for c in cols[k]])
+            if flat.dtype == object:
+                flat = flat.astype(str) if all(isinstance(v, str) for v in flat[:1]) else flat
+            values, inv = np.unique(flat, return_inverse=True)
+            codes.append(inv.astype(np.int64))
+            tables.append(values)
+        radix = [len(t) for t in tables]
+        span = 1
+        for r in radix:
+            span *= max(r, 1)
+        if span >= 2**62:
+            raise Exception("aggregate: the key columns have too many distinct value combinations to be coded in 64 bits")
+        ids_flat = np.zeros(len(codes[0]), dtype=np.int64)
+        for c, r in zip(codes, radix):
+            ids_flat = ids_flat * r + c
+        sizes = np.cumsum([0] + [df._part_len(p) for p in parts])
+        ids = [ids_flat[sizes[i]:sizes[i + 1]] for i in range(len(parts))]
+        return ids, tables, radix
+
     def aggregate(self, grouped: GroupedData, *fetches) -> TensorFrame:
         g, h = self._graph_args(fetches)
         # (grouping builds key ids on the host: device-resident frames come back for this operator)
@@ -339,52 +444,94 @@ class B200Ops:
             schemas = reduce_blocks_schema(df.schema, graph, h)
             out_names = [f.name for f in schemas.output.fields]
             key_names = list(grouped.keys)
-            # key columns -> dense int64 ids (the grouping itself is Spark's job in the reference);
-            # a single integer key column is used as is, bit for bit.
-            key_cols = {k: [] for k in key_names}
-            blocks = {n: [] for n in out_names}
-            for part in df.partitions:
-                n = df._part_len(part)
-                if n == 0:
-                    continue
-                for k in key_names:
-                    c = part[k]
-                    key_cols[k].extend(c.tolist() if isinstance(c, np.ndarray) else list(c))
+            out_schema = StructType(tuple(df.schema[k] for k in key_names) + schemas.output.fields)
+            live = [part for part in df.partitions if df._part_len(part) > 0]
+            if not live or not key_names:
+                return TensorFrame(out_schema, [])
+            ids, tables, radix = self._key_ids(df, key_names, live)
+            # a bound on the number of groups: every row its own group, or every combination of coded key values
+            total = int(sum(len(i) for i in ids))
+            bound = total
+            if radix is not None:
+                combos = 1
+                for r in radix:
+                    combos *= max(r, 1)
+                bound = min(total, combos)
+            n_dev = min(len(self.devices), len(live))
+
+            def local_aggregate(session, slot, capacity):
+                mine = [k for k in range(len(live)) if k % n_dev == slot]
+                keys = np.concatenate([ids[k] for k in mine])
+                feeds = {}
                 for name in out_names:
-                    blocks[name].append(self._dense_block(df, part, name, n))
-            total = len(key_cols[key_names[0]]) if key_names else 0
-            if total == 0:
-                return TensorFrame(StructType(tuple(df.schema[k] for k in key_names) + schemas.output.fields), [])
-            single_int = len(key_names) == 1 and all(isinstance(v, int) and not isinstance(v, bool)
-                                                      for v in key_cols[key_names[0]])
-            if single_int:
-                ids = np.asarray(key_cols[key_names[0]], dtype=np.int64)
-                decode = None
+                    blocks = [self._dense_block(df, live[k], name, df._part_len(live[k])) for k in mine]
+                    feeds[name + "_input"] = blocks[0] if len(blocks) == 1 else np.concatenate(blocks)
+                cap = min(len(keys), capacity)
+                while True:           # the capacity is a guess for raw integer keys: grow it when the block has more groups
+                    try:
+                        return session.aggregate(keys, feeds, out_names, cap)
+                    except _native.NativeError as exc:
+                        if "more than max_groups" not in str(exc) or cap >= len(keys):
+                            raise
+                        cap = min(len(keys), cap * 8)
+
+            first_guess = bound if radix is not None else min(bound, 1 << 20)
+            if n_dev == 1:
+                with _native.Session(graph, self.device) as session:
+                    shards = [local_aggregate(session, 0, first_guess)]
             else:
-                tuples = list(zip(*[key_cols[k] for k in key_names]))
-                table: Dict[tuple, int] = {}
-                ids = np.empty(total, dtype=np.int64)
-                for i, t in enumerate(tuples):
-                    ids[i] = table.setdefault(t, len(table))
-                decode = list(table.keys())
-            feeds = {name + "_input": np.concatenate(blocks[name]) for name in out_names}
-            with _native.Session(graph, self.device) as session:
-                # output capacity: every row its own group at worst; for big blocks size it exactly
-                max_groups = total if total <= (1 << 20) else int(np.unique(ids).size)
-                keys_out, outs = session.aggregate(ids, feeds, out_names, max_groups)
-        part: Dict[str, object] = {}
-        if decode is None:
-            kf = df.schema[key_names[0]]
-            part[key_names[0]] = keys_out.astype(kf.dataType.np_dtype) if isinstance(kf.dataType, ScalarType) else keys_out
-        else:
-            for ki, k in enumerate(key_names):
-                vals = [decode[int(i)][ki] for i in keys_out]
-                kf = df.schema[k]
-                part[k] = np.asarray(vals, dtype=kf.dataType.np_dtype) if isinstance(kf.dataType, ScalarType) else vals
-        for f, arr in zip(schemas.output.fields, outs):
-            part[f.name] = arr
-        schema = StructType(tuple(df.schema[k] for k in key_names) + schemas.output.fields)
-        return TensorFrame(schema, [part])
+                import torch
+                comms = self._communicators() if n_dev == len(self.devices) else _native.Comm.create_all(self.devices[:n_dev])
+                DA = _native.DeviceArray.from_torch
+                tdt = {"float64": torch.float64, "float32": torch.float32, "int32": torch.int32, "int64": torch.int64}
+
+                def work(slot):
+                    if slot >= n_dev:
+                        return None
+                    dev = self.devices[slot]
+                    with _native.Session(graph, dev) as session:
+                        keys_out, outs = local_aggregate(session, slot, first_guess)
+                        # the partial groups of this device go to the devices that own their keys and are merged there
+                        d_keys = torch.from_numpy(keys_out).to(f"cuda:{dev}")
+                        d_outs = {n_: torch.from_numpy(np.ascontiguousarray(o)).to(f"cuda:{dev}") for n_, o in zip(out_names, outs)}
+                        cap = max(1, bound)
+                        m_keys = torch.empty(cap, dtype=torch.int64, device=f"cuda:{dev}")
+                        m_outs = {n_: torch.empty((cap,) + tuple(o.shape[1:]), dtype=tdt[o.dtype.name], device=f"cuda:{dev}")
+                                  for n_, o in zip(out_names, outs)}
+                        torch.cuda.synchronize(dev)
+                        owned = session.aggregate_combine(comms[slot], len(keys_out), DA(d_keys), {k: DA(v) for k, v in d_outs.items()},
+                                                          {k: DA(v) for k, v in m_outs.items()}, DA(m_keys))
+                        return m_keys[:owned].cpu().numpy(), [m_outs[n_][:owned].cpu().numpy() for n_ in out_names]
+
+                shards = [r for r in self._per_device(work) if r is not None]
+                if comms is not self._comms:
+                    for c in comms:
+                        c.close()
+        # one output partition per device: the result stays sharded by key owner, as the reference's stays sharded by
+        # its shuffle (row order is unspecified there, T/TensorFlossTestSparkContext.scala:37-41)
+        parts_out = []
+        for keys_out, outs in shards:
+            if len(keys_out) == 0:
+                continue
+            part: Dict[str, object] = {}
+            if tables is None:
+                kf = df.schema[key_names[0]]
+                part[key_names[0]] = keys_out.astype(kf.dataType.np_dtype) if isinstance(kf.dataType, ScalarType) else keys_out
+            else:
+                rest = keys_out.copy()
+                decoded = {}
+                for k, t, r in reversed(list(zip(key_names, tables, radix))):
+                    decoded[k] = t[rest % r]
+                    rest //= r
+                for k in key_names:
+                    kf = df.schema[k]
+                    vals = decoded[k]
+                    part[k] = (np.asarray(vals, dtype=kf.dataType.np_dtype) if isinstance(kf.dataType, ScalarType)
+                               else [v.item() if hasattr(v, "item") else v for v in vals])
+            for f, arr in zip(schemas.output.fields, outs):
+                part[f.name] = arr
+            parts_out.append(part)
+        return TensorFrame(out_schema, parts_out)
 
     # ---- mapRows (impl/DebugRowOps.scala:396-477, 819-857) ------------------------------
     def mapRows(self, df: TensorFrame, *fetches, feed_dict: Optional[Dict[str, str]] = None) -> TensorFrame:
