@@ -373,8 +373,14 @@ def test_full_size_properties_on_device():
     exact = full * (1023 * 1024 // 2) + (rem - 1) * rem // 2     # integers: every partial sum is exact in f64
     assert ds.tolist() == [float(exact), float(-exact)]
     assert dm.tolist() == [0.0, -1023.0]
-    # map chain: linear in x, so z(x) on a known ramp has a closed form per element
-    x = u * (1.0 / 512.0) - 1.0
+    del y, u
+    torch.cuda.empty_cache()
+    # map chain at BASELINE config 2's size (1e9 rows): linear in x, so z(x) on a known ramp has a closed form per element
+    n = 1_000_000_000
+    x = torch.empty(n, dtype=torch.float64, device="cuda")
+    for a in range(0, n, 1 << 27):
+        b = min(n, a + (1 << 27))
+        x[a:b] = (torch.arange(a, b, dtype=torch.float64, device="cuda") % 1024.0) * (1.0 / 512.0) - 1.0
     dz = torch.empty(n, dtype=torch.float32, device="cuda")
     with dsl.withGraph():
         px = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("x")
@@ -384,19 +390,43 @@ def test_full_size_properties_on_device():
         s.set_stream(torch.cuda.current_stream().cuda_stream)
         s.run_into({"x": _native.DeviceArray.from_torch(x)}, {"z": _native.DeviceArray.from_torch(dz)})
         s.sync()
-    want = torch.clamp_min(x * 1.5 + 0.25, 0.0).to(torch.float32)
-    assert torch.equal(dz, want)
+    for a in range(0, n, 1 << 27):
+        b = min(n, a + (1 << 27))
+        assert torch.equal(dz[a:b], torch.clamp_min(x[a:b] * 1.5 + 0.25, 0.0).to(torch.float32))
+    # the ramp has period 1024: every period of the output must equal the first one
+    assert torch.equal(dz[:1024 * 976_562].view(-1, 1024), dz[:1024].expand(976_562, 1024))
+    # reduce_blocks on the same 1e9-row scalar column (the other half of the north-star target): exact in f64
+    with dsl.withGraph():
+        ps = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("s_input")
+        pm = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("m_input")
+        g = dsl.build_graph(dsl.reduce_sum(ps, [0]).named("s"), dsl.reduce_max(pm, [0]).named("m"))
+    ds1 = torch.empty((), dtype=torch.float64, device="cuda")
+    dm1 = torch.empty((), dtype=torch.float64, device="cuda")
+    k = (x + 1.0) * 512.0                      # back to the integers 0..1023: their sum is exact in f64
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        torch.cuda.synchronize()
+        s.set_stream(torch.cuda.current_stream().cuda_stream)
+        s.run_into({"s_input": _native.DeviceArray.from_torch(k), "m_input": _native.DeviceArray.from_torch(x)},
+                   {"s": _native.DeviceArray.from_torch(ds1), "m": _native.DeviceArray.from_torch(dm1)})
+        s.sync()
+    full, rem = divmod(n, 1024)
+    assert ds1.item() == float(full * (1023 * 1024 // 2) + (rem - 1) * rem // 2)
+    assert dm1.item() == 1023.0 / 512.0 - 1.0
 
 
 def test_full_size_aggregate_closed_form():
-    """BASELINE config 4 at the bench's block size (2.5e8 rows, 1e6 int64 keys, FloatType[?,64]): small-integer
-    payloads make every group sum exact in float32, so the result has a closed form that needs no CPU pass."""
+    """BASELINE config 4 at its configured size (5e8 rows, 1e6 int64 keys, FloatType[?,64]; 132 GB of input, reduced in
+    two 64 GB row ranges whose partial groups are merged): small-integer payloads make every group sum exact in
+    float32, so the result has a closed form that needs no CPU pass."""
     torch = pytest.importorskip("torch")
-    n, n_keys, cell = 250_000_000, 1_000_000, 64
+    torch.cuda.empty_cache()
+    n, n_keys, cell = 500_000_000, 1_000_000, 64
     i = torch.arange(n, dtype=torch.int64, device="cuda")
     gid = (i * 7919) % n_keys                                   # 7919 is coprime to 1e6: every key gets exactly n / n_keys rows
     keys = gid * 0x9E3779B97F4A7C15 + 12345                     # wrapping multiply by an odd constant: a bijection on int64
-    v = ((i % 5).to(torch.float32)[:, None] + torch.arange(cell, dtype=torch.float32, device="cuda")[None, :] % 3).contiguous()
+    v = torch.empty((n, cell), dtype=torch.float32, device="cuda")
+    for a in range(0, n, 1 << 25):                              # chunked: no second 128 GB temporary
+        v[a:a + (1 << 25)] = (i[a:a + (1 << 25)] % 5).to(torch.float32)[:, None] + torch.arange(cell, dtype=torch.float32, device="cuda")[None, :] % 3
     per = n // n_keys
     g = aggregate_graph(tfs.FloatType, (cell,), "sum")
     out = torch.empty((n_keys, cell), dtype=torch.float32, device="cuda")
