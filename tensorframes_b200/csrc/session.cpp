@@ -1193,7 +1193,11 @@ void Session::exec_step(const Plan& plan, size_t step_index, std::vector<void*>&
       void* out = dev_ptr[size_t(s.out_node >= 0 ? s.out_node : mm)];
       if (M * Nc == 0) break;
       const bool const_b = g_.nodes[size_t(n.in[1])].cls == OpClass::Const;
-      if (n.dtype == TFS_FLOAT && !matmul_force_simt() && const_b && matmul_tc_supported(a, out, M, Nc, K, n.transpose_a)) {
+      // The tensor-core kernel reads x and writes y through TMA tensor maps (its w loads use the cta_group::2 form):
+      // those maps cover memory of this GPU only, so anything else -- managed memory, whose pages may live elsewhere --
+      // takes the SIMT kernel.  (Memory of another device never gets here: the run refuses it.)
+      const bool local = pointer_location(a) == dev_.device && pointer_location(out) == dev_.device;
+      if (n.dtype == TFS_FLOAT && !matmul_force_simt() && const_b && local && matmul_tc_supported(a, out, M, Nc, K, n.transpose_a)) {
         auto it = ensure_tc_weights(n, static_cast<const float*>(b), Nc, K, stream);
         launches_ += launch_matmul_tc(static_cast<const float*>(a), it->second.first, it->second.second, static_cast<const float*>(bias),
                                       static_cast<float*>(out), M, Nc, K, dev_, stream);
