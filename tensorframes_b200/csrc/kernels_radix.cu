@@ -19,6 +19,7 @@
 //     13 GB of DRAM traffic for 4 GB of data (profiles/r02_experiments.md).  Passes of 9 to 11 bits remain available
 //     (TFS_RADIX_BITS) and are used where a partition has that many bins by nature.
 #include <cstdlib>
+#include <type_traits>
 
 #include "kernels.h"
 
@@ -162,31 +163,45 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
   using Raw = K;
   const Raw* raw_in = keys_in;
   Raw raw[kItems];
-  auto load_raw = [&](int64_t tile_base) {
-    const int64_t wb = tile_base + int64_t(warp) * (32 * kItems) + lane;
+  // a thread's items of a tile sit 32 apart from its first one: constant offsets from one pointer; `left` = items of
+  // the range from that first one on (only a range's last tile can be short)
+  auto load_raw = [&](int64_t tile_base, bool whole) {
+    const int64_t first = tile_base + warp * (32 * kItems) + lane;
+    const Raw* p = raw_in + first;
+    if (whole) {
 #pragma unroll
-    for (int r = 0; r < kItems; ++r) {
-      const int64_t i = wb + r * 32;
-      raw[r] = i < hi ? __ldcs(raw_in + i) : Raw(0);
+      for (int r = 0; r < kItems; ++r) raw[r] = __ldcs(p + r * 32);
+    } else {
+      const int64_t left64 = hi - first;
+      const int left = left64 > 32 * kItems ? 32 * kItems : (left64 < 0 ? 0 : int(left64));
+#pragma unroll
+      for (int r = 0; r < kItems; ++r) raw[r] = r * 32 < left ? __ldcs(p + r * 32) : Raw(0);
     }
   };
-  if (lo < hi) load_raw(lo);
-  for (int64_t tile = lo; tile < hi; tile += kTile) {
+  if (lo < hi) load_raw(lo, lo + kTile <= hi);
+  // The tile body exists twice: for whole tiles (all but possibly the last of a range) nothing is predicated.
+  auto tile_body = [&](const int64_t tile, auto whole_tag) {
+    constexpr bool WHOLE = decltype(whole_tag)::value;
     // (a) counters to zero
     {
       unsigned int* z = reinterpret_cast<unsigned int*>(cnt);
       for (int i = threadIdx.x; i < kWarps * bins / 2; i += kThreads) z[i] = 0u;
     }
-    const int64_t wbase = tile + int64_t(warp) * (32 * kItems) + lane;
+    const int64_t wbase = tile + warp * (32 * kItems) + lane;
+    int left = 32 * kItems;
+    if constexpr (!WHOLE) {
+      const int64_t left64 = hi - wbase;
+      left = left64 > 32 * kItems ? 32 * kItems : (left64 < 0 ? 0 : int(left64));
+    }
     // the values are not needed before the staging phase: their loads travel while the tile is ranked
     K key[kItems];
     V val[kItems];
+    const unsigned int iota0 = (unsigned int)wbase;
 #pragma unroll
     for (int r = 0; r < kItems; ++r) {
-      const int64_t i = wbase + r * 32;
       key[r] = raw[r];
-      if constexpr (MODE == M_PLAIN) val[r] = i < hi ? __ldcs(vals_in + i) : V(0);
-      else val[r] = V(i);
+      if constexpr (MODE == M_PLAIN) val[r] = (WHOLE || r * 32 < left) ? __ldcs(vals_in + wbase + r * 32) : V(0);
+      else val[r] = V(iota0 + (unsigned int)(r * 32));
     }
     __syncthreads();       // also: the previous tile's write-out and cursor update are done
     // (b) rank inside the warp.  Warp w owns items [w * 512, w * 512 + 512) of the tile, round r = 32 of them.
@@ -194,7 +209,7 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
     unsigned int dig[kItems];
 #pragma unroll
     for (int r = 0; r < kItems; ++r) {
-      const bool valid = wbase + r * 32 < hi;
+      const bool valid = WHOLE || r * 32 < left;
       dig[r] = valid ? digit_of<K>(key[r], xor_mask, shift, mask) : 0xffffffffu;
     }
     unsigned int peers[kItems];
@@ -202,7 +217,7 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
     for (int r = 0; r < kItems; ++r) peers[r] = __match_any_sync(0xffffffffu, dig[r]);
 #pragma unroll
     for (int r = 0; r < kItems; ++r) {
-      const bool valid = dig[r] != 0xffffffffu;
+      const bool valid = WHOLE || dig[r] != 0xffffffffu;
       const unsigned int before = __popc(peers[r] & lt_mask);
       unsigned int base = 0;
       if (valid) base = my_cnt[dig[r]];
@@ -300,19 +315,19 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
       unsigned int pos[kItems];
 #pragma unroll
       for (int r = 0; r < kItems; ++r) {
-        const unsigned int d = dig[r] != 0xffffffffu ? dig[r] : 0u;
+        const unsigned int d = (WHOLE || dig[r] != 0xffffffffu) ? dig[r] : 0u;
         pos[r] = bin_start[d] + my_cnt[d] + lrank[r];
       }
 #pragma unroll
       for (int r = 0; r < kItems; ++r) {
-        if (dig[r] != 0xffffffffu) {
+        if (WHOLE || dig[r] != 0xffffffffu) {
           st_keys[pos[r]] = key[r];
           st_vals[pos[r]] = val[r];
         }
       }
     }
     // the next tile's keys start their trip now: the write-out below and the next tile's first phase cover the latency
-    if (tile + kTile < hi) load_raw(tile + kTile);
+    if (tile + kTile < hi) load_raw(tile + kTile, tile + 2 * kTile <= hi);
     __syncthreads();
     // (e) write out: position p of the tile goes to shift_of[digit] + p
     {
@@ -322,8 +337,8 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
 #pragma unroll
       for (int j = 0; j < kItems; ++j) {
         const unsigned int p = (unsigned int)(j * kThreads + threadIdx.x);
-        k[j] = p < in_tile ? st_keys[p] : K(0);
-        v[j] = p < in_tile ? st_vals[p] : V(0);
+        k[j] = (WHOLE || p < in_tile) ? st_keys[p] : K(0);
+        v[j] = (WHOLE || p < in_tile) ? st_vals[p] : V(0);
       }
       unsigned int g[kItems];
 #pragma unroll
@@ -334,13 +349,17 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
 #pragma unroll
       for (int j = 0; j < kItems; ++j) {
         const unsigned int p = (unsigned int)(j * kThreads + threadIdx.x);
-        if (p < in_tile) {
+        if (WHOLE || p < in_tile) {
           if (keys_out != nullptr) keys_out[g[j]] = k[j];
           vals_out[g[j]] = v[j];
         }
       }
     }
     // (the next tile's first __syncthreads orders the staged pairs and shift_of against their next use)
+  };
+  for (int64_t tile = lo; tile < hi; tile += kTile) {
+    if (tile + kTile <= hi) tile_body(tile, std::true_type{});
+    else tile_body(tile, std::false_type{});
   }
 }
 
