@@ -115,7 +115,7 @@ int launch_matmul_tc(const float* x, const float* w_hi, const float* w_lo, const
 // radix_scratch_bytes().  launch_radix_sort chains ceil(bits / 11) passes from `keys_in / vals_in` through the two
 // buffer pairs and returns the index of the pair that holds the result (the last pass writes keys only if want_keys).
 size_t radix_scratch_bytes(const DeviceInfo& dev);
-int radix_passes(int bits);
+int radix_passes(int64_t n, int bits);
 int launch_radix_pass(int key_bytes, int val_bytes, const void* keys_in, const void* vals_in, void* keys_out, void* vals_out,
                       int64_t n, uint64_t xor_mask, int shift, int bits, void* scratch, const DeviceInfo& dev, cudaStream_t stream);
 int launch_radix_sort(int key_bytes, int val_bytes, const void* keys_in, const void* vals_in, void* keys_buf[2], void* vals_buf[2],

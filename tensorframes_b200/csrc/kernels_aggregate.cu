@@ -6,12 +6,11 @@
 // four passes, all HBM-bound:
 //
 //   1. insert   every key into an open-addressing table (64-bit CAS on the key slot); the row
-//               remembers its slot (u32) next to its own index (u32) and the slot counts its rows
-//                                                                         8 B read + 8 B written / row
+//               remembers its slot (u32) and the slot counts its rows       8 B read + 4 B written / row
 //   2. scan     one pass over the table: segment offset of every slot, dense group id of every
 //               occupied slot, out_keys                                   (table only)
-//   3. sort     rows by slot: a stable radix partition of the (slot, row) pairs on the slot bits, two 11-bit passes
-//               for tables of up to 2^22 slots (kernels_radix.cu); the first pass takes the row index from the
+//   3. sort     rows by slot: a stable radix partition of the (slot, row) pairs on the slot bits, three 8-bit passes
+//               for tables of up to 2^24 slots (kernels_radix.cu); the first pass takes the row index from the
 //               element's position, the last one writes row indices only
 //   4. gather-reduce  one warp per group walks its segment of the sorted row list and gathers
 //               the payload rows -- each a contiguous cell, read with coalesced vector loads --
@@ -449,7 +448,7 @@ AggLayout agg_layout(int64_t n_rows, int64_t max_groups, const DeviceInfo& dev) 
   L.off_tile_sums = off; off += up(size_t((cap + 1 + kScanTile) / kScanTile + 1) * 8);
   // row partition: the slot column the insert pass wrote (kept: every carried fetch sorts from it again), the slot
   // column between passes (a second one only when the table needs a third pass) and two row-index columns
-  const int passes = radix_passes(slot_bits(cap));
+  const int passes = radix_passes(n_rows, slot_bits(cap));
   L.off_row_slot[0] = off; off += up(size_t(n_rows) * 4);
   L.off_row_slot[1] = off; off += up(size_t(n_rows) * 4);
   for (int b = 0; b < 2; ++b) { L.off_row_id[b] = off; off += up(size_t(n_rows) * 4); }
@@ -513,11 +512,16 @@ int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, c
   // groups by key (signed order: the sign bit is flipped for the digit extraction): out_keys ascending, group_slot
   // permuted alongside.  64 key bits are six passes over a column that is small next to the rows.
   if (sort_groups && n_groups > 0) {
-    void* kbuf[2] = {scratch + L.off_group_tmp_keys, out_keys_dev};
-    void* vbuf[2] = {scratch + L.off_group_tmp_slot, scratch + L.off_group_slot};
+    // the passes alternate between two buffer pairs: order them so that the last pass lands in the output
+    const bool even = radix_passes(n_groups, 64) % 2 == 0;
+    void* tmp_k = scratch + L.off_group_tmp_keys;
+    void* tmp_v = scratch + L.off_group_tmp_slot;
+    void* out_v = scratch + L.off_group_slot;
+    void* kbuf[2] = {even ? tmp_k : static_cast<void*>(out_keys_dev), even ? static_cast<void*>(out_keys_dev) : tmp_k};
+    void* vbuf[2] = {even ? tmp_v : out_v, even ? out_v : tmp_v};
     const int at = launch_radix_sort(8, 4, scratch + L.off_keys_tab, scratch + L.off_group_slot_tab, kbuf, vbuf, n_groups,
                                      0x8000000000000000ULL, 64, true, temp, dev, stream, &launches);
-    TFS_CHECK(at == 1, TFS_ERR_INVALID, "internal: group sort ended in the wrong buffer");
+    TFS_CHECK(kbuf[at] == static_cast<void*>(out_keys_dev), TFS_ERR_INVALID, "internal: group sort ended in the wrong buffer");
   }
   if (!sort_rows) return launches;       // every fetch carries its values through its own sort (launch_agg_reduce_carried)
   // rows by slot, stable: values = row indices, read off the position in the first pass

@@ -428,7 +428,11 @@ int pass_bits() {
 }
 }  // namespace
 
-int radix_passes(int bits) { return bits <= 0 ? 0 : (bits + pass_bits() - 1) / pass_bits(); }
+// Small inputs (up to 4M pairs: the group sort of K3, the merge of partial groups) stay in L2 whatever the fan-out, so they
+// take 11-bit passes: six instead of eight for 64-bit keys, and their cost is launches, not bytes.
+int bits_per_pass(int64_t n) { return n <= (int64_t(1) << 22) ? kMaxBits : pass_bits(); }
+
+int radix_passes(int64_t n, int bits) { return bits <= 0 ? 0 : (bits + bits_per_pass(n) - 1) / bits_per_pass(n); }
 
 int launch_radix_pass(int key_bytes, int val_bytes, const void* keys_in, const void* vals_in, void* keys_out, void* vals_out,
                       int64_t n, uint64_t xor_mask, int shift, int bits, void* scratch, const DeviceInfo& dev, cudaStream_t stream) {
@@ -460,7 +464,7 @@ int launch_radix_pass(int key_bytes, int val_bytes, const void* keys_in, const v
 int launch_radix_sort(int key_bytes, int val_bytes, const void* keys_in, const void* vals_in, void* keys_buf[2], void* vals_buf[2],
                       int64_t n, uint64_t xor_mask, int bits, bool want_keys, void* scratch, const DeviceInfo& dev, cudaStream_t stream,
                       int* launches) {
-  const int passes = radix_passes(bits);
+  const int passes = radix_passes(n, bits);
   TFS_CHECK(passes >= 1, TFS_ERR_INVALID, "internal: radix sort over no bits");
   int shift = 0, into = 0;
   const void* kin = keys_in;

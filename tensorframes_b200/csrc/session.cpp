@@ -1062,7 +1062,9 @@ void Session::exec_step(const Plan& plan, size_t step_index, std::vector<void*>&
       gc.build(err_flag_);
       if (gc.prog.n_instr == 0) break;          // every member is needed for its shape only
       ChainProgram chain;
-      const bool straight = make_chain(gc.prog, chain);
+      // TFS_ELT_IMPL=interp sends every group to the interpreter (A/B measurements of the two kernels)
+      static const bool force_interp = [] { const char* e = std::getenv("TFS_ELT_IMPL"); return e && std::string(e) == "interp"; }();
+      const bool straight = !force_interp && make_chain(gc.prog, chain);
       static const bool trace = [] { const char* e = std::getenv("TFS_TRACE"); return e && *e && *e != '0'; }();
       if (trace)
         fprintf(stderr, "tfs: element-wise group of %zu nodes, %d instructions -> %s\n", s.nodes.size(), gc.prog.n_instr,
