@@ -122,6 +122,10 @@ int launch_radix_sort(int key_bytes, int val_bytes, const void* keys_in, const v
                       int64_t n, uint64_t xor_mask, int bits, bool want_keys, void* scratch, const DeviceInfo& dev, cudaStream_t stream,
                       int* launches);
 
+// rows ordered by slot (stable): slots[n] -> rows_out[n]; pairs_a / pairs_b are 8-byte-per-row scratch columns
+int launch_radix_rows_by_slot(const unsigned int* slots, int64_t n, int bits, unsigned long long* pairs_a, unsigned long long* pairs_b,
+                              unsigned int* rows_out, void* scratch, const DeviceInfo& dev, cudaStream_t stream);
+
 // K3: keyed block reduction. Scratch layout for n_rows rows and at most max_groups groups.
 struct AggLayout {
   uint64_t table_slots;
@@ -129,6 +133,7 @@ struct AggLayout {
   size_t off_group_slot_tab, off_keys_tab;   // groups in table order, before they are sorted by key
   size_t off_row_slot[3];   // [0] the slot column written by the insert pass, [1] / [2] the slot column between passes
   size_t off_row_id[2];     // row-index columns of the partition (ping-pong)
+  size_t off_pairs[2];      // packed (slot, row) columns between the passes of the row partition, 8 bytes per row
   size_t off_group_tmp_keys, off_group_tmp_slot;   // second (key, slot) column pair of the group sort
   size_t sort_temp_bytes;
   size_t bytes;

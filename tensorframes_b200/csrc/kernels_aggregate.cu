@@ -434,7 +434,14 @@ int slot_bits(uint64_t slots) {   // bits needed for slot indices 0..slots (incl
 AggLayout agg_layout(int64_t n_rows, int64_t max_groups, const DeviceInfo& dev) {
   AggLayout L{};
   uint64_t cap = 1024;
-  while (cap < 2 * uint64_t(std::max<int64_t>(max_groups, 1))) cap <<= 1;
+  // at least 2 slots per group; 4 while the table (key, count and offset per slot) stays well inside L2: fewer and
+  // shorter probe walks (insert 3.0 -> 2.65 ms per 2.5e8 rows at 1e6 groups; 8 buys nothing more)
+  uint64_t factor = uint64_t(std::max<int64_t>(max_groups, 1)) * 4 * 16 <= (uint64_t(96) << 20) ? 4 : 2;
+  if (const char* e = std::getenv("TFS_AGG_TABLE_FACTOR")) {     // (A/B measurements of the table's load factor)
+    const long v = std::atol(e);
+    if (v >= 2 && v <= 16) factor = uint64_t(v);
+  }
+  while (cap < factor * uint64_t(std::max<int64_t>(max_groups, 1))) cap <<= 1;
   L.table_slots = cap;
   auto up = [](size_t x) { return (x + 255) / 256 * 256; };
   size_t off = 0;
@@ -450,9 +457,14 @@ AggLayout agg_layout(int64_t n_rows, int64_t max_groups, const DeviceInfo& dev) 
   // column between passes (a second one only when the table needs a third pass) and two row-index columns
   const int passes = radix_passes(n_rows, slot_bits(cap));
   L.off_row_slot[0] = off; off += up(size_t(n_rows) * 4);
-  L.off_row_slot[1] = off; off += up(size_t(n_rows) * 4);
-  for (int b = 0; b < 2; ++b) { L.off_row_id[b] = off; off += up(size_t(n_rows) * 4); }
-  L.off_row_slot[2] = off; off += passes >= 3 ? up(size_t(n_rows) * 4) : 0;
+  // between passes: two packed (slot, row) columns of 8 bytes per row (the second only when there are three passes or
+  // more); the carried path of scalar payloads uses the same memory as 4-byte slot and value columns
+  L.off_pairs[0] = off; off += up(size_t(n_rows) * 8);
+  L.off_pairs[1] = off; off += passes >= 3 ? up(size_t(n_rows) * 8) : 0;
+  L.off_row_slot[1] = L.off_pairs[0];
+  L.off_row_slot[2] = passes >= 3 ? L.off_pairs[1] : L.off_pairs[0] + up(size_t(n_rows) * 4);
+  L.off_row_id[0] = off; off += up(size_t(n_rows) * 4);
+  L.off_row_id[1] = L.off_row_id[0];
   L.off_perm = L.off_row_id[0];   // set by launch_agg_segments to the buffer the partition finished in
   // group sort by key: one more (key, slot) column pair; then the histogram table of a pass
   L.off_group_tmp_keys = off; off += up(size_t(max_groups + 1) * 8);
@@ -525,11 +537,11 @@ int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, c
   }
   if (!sort_rows) return launches;       // every fetch carries its values through its own sort (launch_agg_reduce_carried)
   // rows by slot, stable: values = row indices, read off the position in the first pass
-  void* kbuf[2] = {scratch + L.off_row_slot[1], scratch + L.off_row_slot[2]};
-  void* vbuf[2] = {scratch + L.off_row_id[0], scratch + L.off_row_id[1]};
-  const int at = launch_radix_sort(4, 4, scratch + L.off_row_slot[0], nullptr, kbuf, vbuf, n_rows, 0, slot_bits(L.table_slots), false,
-                                   temp, dev, stream, &launches);
-  L.off_perm = L.off_row_id[at];
+  launches += launch_radix_rows_by_slot(reinterpret_cast<const unsigned int*>(scratch + L.off_row_slot[0]), n_rows, slot_bits(L.table_slots),
+                                        reinterpret_cast<unsigned long long*>(scratch + L.off_pairs[0]),
+                                        reinterpret_cast<unsigned long long*>(scratch + L.off_pairs[1]),
+                                        reinterpret_cast<unsigned int*>(scratch + L.off_row_id[0]), temp, dev, stream);
+  L.off_perm = L.off_row_id[0];
   return launches;
 }
 

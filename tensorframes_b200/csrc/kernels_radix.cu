@@ -33,8 +33,8 @@ constexpr int kTile = kThreads * kItems;         // 4096
 constexpr int kMaxBits = 11;
 constexpr int kMaxBins = 1 << kMaxBits;
 constexpr int kCtasPerSm = 2;          // passes of 9 to 11 bits
-constexpr int kSmallBits = 8;          // passes of at most 8 bits: 256 bins, small tables, three CTAs per SM
-constexpr int kCtasPerSmSmall = 3;
+constexpr int kSmallBits = 8;          // passes of at most 8 bits: 256 bins, small tables
+constexpr int kCtasPerSmSmall = 2;   // (three were measured: no faster, and the packed modes spill at 80 registers)
 constexpr int ctas_for(int mb) { return mb <= kSmallBits ? kCtasPerSmSmall : kCtasPerSm; }
 
 template <class K>
@@ -130,7 +130,11 @@ constexpr size_t scatter_smem_bytes() {
 }
 
 // MODE: M_PLAIN = values loaded from vals_in; M_IOTA = the values are the element indices (4-byte values).
-enum : int { M_PLAIN = 0, M_IOTA = 1 };
+// The packed modes (4-byte keys and values) keep a pair in ONE 8-byte word, key << 32 | value, between the passes of a
+// sort -- one load and one store per pair instead of two, and one write stream per bin instead of two:
+// M_IOTA_PACK = as M_IOTA, written packed through keys_out; M_PACKED = packed in (through keys_in), packed out;
+// M_UNPACK = packed in, values out.
+enum : int { M_PLAIN = 0, M_IOTA = 1, M_IOTA_PACK = 2, M_PACKED = 3, M_UNPACK = 4 };
 
 template <class K, class V, int MODE, int MB>
 __global__ void __launch_bounds__(kThreads, ctas_for(MB))
@@ -160,8 +164,10 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
   // Every phase below first issues all of its loads and only then its stores: with 8 warps per CTA the kernel lives on
   // instruction-level parallelism, and a store between two loads of arrays the compiler cannot tell apart would chain
   // them (measured: 30 000 cycles per tile before, latency-bound on shared memory and on the tile's global loads).
-  using Raw = K;
-  const Raw* raw_in = keys_in;
+  constexpr bool kPackedIn = MODE == M_PACKED || MODE == M_UNPACK;
+  constexpr bool kPackedOut = MODE == M_IOTA_PACK || MODE == M_PACKED;
+  using Raw = typename std::conditional<kPackedIn, unsigned long long, K>::type;
+  const Raw* raw_in = reinterpret_cast<const Raw*>(keys_in);
   Raw raw[kItems];
   // a thread's items of a tile sit 32 apart from its first one: constant offsets from one pointer; `left` = items of
   // the range from that first one on (only a range's last tile can be short)
@@ -199,9 +205,14 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
     const unsigned int iota0 = (unsigned int)wbase;
 #pragma unroll
     for (int r = 0; r < kItems; ++r) {
-      key[r] = raw[r];
-      if constexpr (MODE == M_PLAIN) val[r] = (WHOLE || r * 32 < left) ? __ldcs(vals_in + wbase + r * 32) : V(0);
-      else val[r] = V(iota0 + (unsigned int)(r * 32));
+      if constexpr (kPackedIn) {
+        key[r] = K(raw[r] >> 32);
+        val[r] = V(raw[r]);
+      } else {
+        key[r] = K(raw[r]);
+        if constexpr (MODE == M_PLAIN) val[r] = (WHOLE || r * 32 < left) ? __ldcs(vals_in + wbase + r * 32) : V(0);
+        else val[r] = V(iota0 + (unsigned int)(r * 32));
+      }
     }
     __syncthreads();       // also: the previous tile's write-out and cursor update are done
     // (b) rank inside the warp.  Warp w owns items [w * 512, w * 512 + 512) of the tile, round r = 32 of them.
@@ -350,8 +361,12 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
       for (int j = 0; j < kItems; ++j) {
         const unsigned int p = (unsigned int)(j * kThreads + threadIdx.x);
         if (WHOLE || p < in_tile) {
-          if (keys_out != nullptr) keys_out[g[j]] = k[j];
-          vals_out[g[j]] = v[j];
+          if constexpr (kPackedOut) {
+            reinterpret_cast<unsigned long long*>(keys_out)[g[j]] = ((unsigned long long)k[j] << 32) | (unsigned long long)v[j];
+          } else {
+            if (keys_out != nullptr) keys_out[g[j]] = k[j];
+            vals_out[g[j]] = v[j];
+          }
         }
       }
     }
@@ -380,7 +395,11 @@ int launch_pass_t(const K* keys_in, const V* vals_in, K* keys_out, V* vals_out, 
   const int bins = 1 << bits;
   unsigned int* hist = static_cast<unsigned int*>(scratch);
   unsigned int* bin_total = hist + size_t(bins) * size_t(g.grid);
-  radix_hist_kernel<K><<<g.grid, kThreads, 0, stream>>>(keys_in, n, g.per_cta, xor_mask, shift, bits, hist);
+  if constexpr (MODE == M_PACKED || MODE == M_UNPACK)
+    radix_hist_kernel<unsigned long long><<<g.grid, kThreads, 0, stream>>>(reinterpret_cast<const unsigned long long*>(keys_in), n, g.per_cta,
+                                                                          0ULL, shift + 32, bits, hist);
+  else
+    radix_hist_kernel<K><<<g.grid, kThreads, 0, stream>>>(keys_in, n, g.per_cta, xor_mask, shift, bits, hist);
   TFS_CUDA(cudaGetLastError());
   radix_scan_bins_kernel<<<(bins * 32 + kThreads - 1) / kThreads, kThreads, 0, stream>>>(hist, g.grid, bins, bin_total);
   TFS_CUDA(cudaGetLastError());
@@ -481,6 +500,36 @@ int launch_radix_sort(int key_bytes, int val_bytes, const void* keys_in, const v
     into ^= 1;
   }
   return into ^ 1;
+}
+
+// The row-by-slot ordering of K3: slots[n] -> rows_out[n] = row indices ordered by slot, stably.  Between the passes the
+// pairs travel packed (slot << 32 | row) through the two 8-byte scratch columns; the first pass reads the row index off
+// the element's position, the last one writes row indices only.
+int launch_radix_rows_by_slot(const unsigned int* slots, int64_t n, int bits, unsigned long long* pairs_a, unsigned long long* pairs_b,
+                              unsigned int* rows_out, void* scratch, const DeviceInfo& dev, cudaStream_t stream) {
+  if (n <= 0) return 0;
+  TFS_CHECK(n < (int64_t(1) << 32), TFS_ERR_UNSUPPORTED, "internal: radix pass over 2^32 or more pairs");
+  using u32 = unsigned int;
+  const int passes = radix_passes(n, bits);
+  int launches = 0, shift = 0;
+  if (passes == 1)
+    return launch_pass_t<u32, u32, M_IOTA>(slots, nullptr, nullptr, rows_out, n, 0u, 0, bits, scratch, dev, stream);
+  unsigned long long* cur = nullptr;
+  for (int p = 0; p < passes; ++p) {
+    const int b = (bits - shift + (passes - p) - 1) / (passes - p);
+    unsigned long long* dst = (cur == pairs_a) ? pairs_b : pairs_a;
+    if (p == 0)
+      launches += launch_pass_t<u32, u32, M_IOTA_PACK>(slots, nullptr, reinterpret_cast<u32*>(dst), nullptr, n, 0u, shift, b, scratch, dev, stream);
+    else if (p < passes - 1)
+      launches += launch_pass_t<u32, u32, M_PACKED>(reinterpret_cast<const u32*>(cur), nullptr, reinterpret_cast<u32*>(dst), nullptr, n, 0u,
+                                                    shift, b, scratch, dev, stream);
+    else
+      launches += launch_pass_t<u32, u32, M_UNPACK>(reinterpret_cast<const u32*>(cur), nullptr, nullptr, rows_out, n, 0u, shift, b, scratch,
+                                                    dev, stream);
+    cur = dst;
+    shift += b;
+  }
+  return launches;
 }
 
 }  // namespace tfs
