@@ -28,7 +28,11 @@ namespace tfs {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kJ = 4;
+// 8 vectors per thread and dispatch (was 4): the cost of decoding one instruction of the program is paid per tile, so a
+// wider tile halves it per element; together with a real jump table for the dispatch switch (built with
+// --jump-table-density, see __graft_entry__.py: nvcc's default lowers the ~150-case switch to a tree of 7-8
+// compare-and-branch pairs) the C3 chain forced through this kernel went from 2875 to 5243 GB/s.
+constexpr int kJ = 8;
 
 template <int ES> struct Slot;
 template <> struct Slot<8> { using type = unsigned long long; };
