@@ -146,8 +146,9 @@ int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, ch
                      const DeviceInfo& dev, cudaStream_t stream);
 // pass 3: groups sorted by key -> out_keys_dev[0..n_groups) ascending (the table order depends on probe races);
 // stable sort of the rows by slot -> row permutation (sets L.off_perm).
+constexpr int kGroupsKeep = 0, kGroupsByKey = 1, kGroupsTableOrder = 2;   // group_order: leave as is / sort by key / table order
 int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, char* scratch, AggLayout& L,
-                        int64_t* out_keys_dev, bool sort_groups, bool sort_rows, const DeviceInfo& dev, cudaStream_t stream);
+                        int64_t* out_keys_dev, int group_order, bool sort_rows, const DeviceInfo& dev, cudaStream_t stream);
 // pass 4: out[g, :] = reduce over the rows of group g of payload[row, :].
 // Scalar payloads: the values ride through their own stable slot sort and are reduced sequentially (no random gather).
 // Call after launch_agg_segments(..., sort_rows = false) or before a launch_agg_segments that sorts rows.

@@ -516,14 +516,19 @@ int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, ch
 }
 
 int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, char* scratch, AggLayout& L,
-                        int64_t* out_keys_dev, bool sort_groups, bool sort_rows, const DeviceInfo& dev, cudaStream_t stream) {
+                        int64_t* out_keys_dev, int group_order, bool sort_rows, const DeviceInfo& dev, cudaStream_t stream) {
   (void)keys;
   if (n_rows <= 0) return 0;
   int launches = 0;
   void* temp = scratch + L.off_sort_temp;
   // groups by key (signed order: the sign bit is flipped for the digit extraction): out_keys ascending, group_slot
   // permuted alongside.  64 key bits are six passes over a column that is small next to the rows.
-  if (sort_groups && n_groups > 0) {
+  if (group_order == kGroupsTableOrder && n_groups > 0) {
+    // groups stay in table order (not reproducible from run to run): for partial results that a merge will reorder
+    TFS_CUDA(cudaMemcpyAsync(out_keys_dev, scratch + L.off_keys_tab, size_t(n_groups) * 8, cudaMemcpyDeviceToDevice, stream));
+    TFS_CUDA(cudaMemcpyAsync(scratch + L.off_group_slot, scratch + L.off_group_slot_tab, size_t(n_groups) * 4, cudaMemcpyDeviceToDevice, stream));
+  }
+  if (group_order == kGroupsByKey && n_groups > 0) {
     // the passes alternate between two buffer pairs: order them so that the last pass lands in the output
     const bool even = radix_passes(n_groups, 64) % 2 == 0;
     void* tmp_k = scratch + L.off_group_tmp_keys;

@@ -1176,7 +1176,7 @@ void Session::exec_step(const Plan& plan, size_t step_index, std::vector<void*>&
       TFS_CHECK(header[1] == 0 && int64_t(header[2]) <= max_groups, TFS_ERR_RUNTIME,
                 "UnsortedSegmentSum: segment ids out of range [0, " + std::to_string(segments) + ")");
       const int64_t n_groups = header[2];
-      launches_ += launch_agg_segments(keys, n_rows, n_groups, scratch, L, d_out_keys, true, true, dev_, stream);
+      launches_ += launch_agg_segments(keys, n_rows, n_groups, scratch, L, d_out_keys, kGroupsByKey, true, dev_, stream);
       launches_ += launch_agg_reduce(n.dtype, R_SUM, dev_ptr[size_t(n.in[0])], cell, n_groups, n_rows, scratch, L, scratch + off_sums,
                                      scratch + off_split, split_bytes, dev_, stream);
       launches_ += launch_segment_scatter(n.dtype, scratch + off_sums, d_out_keys, n_groups, cell, segments, dev_ptr[size_t(idx)],
@@ -1585,7 +1585,12 @@ void Session::aggregate(int64_t n_rows, const int64_t* keys, const std::vector<T
       co[i].dtype = resolved[i].dtype;
     }
     int64_t g = 0;
-    aggregate_block(rows_here, keys + r0, cf, co, max_groups, reinterpret_cast<int64_t*>(parts) + total, &g, feed_of_fetch);
+    {
+      // the partial groups of a range need no order: the merge below sorts its own output, and the partial rows of a key
+      // are folded in range order whatever their position inside a range (the row partition is stable)
+      struct Flag { bool& f; explicit Flag(bool& x) : f(x) { f = true; } ~Flag() { f = false; } } table_order(agg_table_order_);
+      aggregate_block(rows_here, keys + r0, cf, co, max_groups, reinterpret_cast<int64_t*>(parts) + total, &g, feed_of_fetch);
+    }
     total += g;
   }
   // merge: the partial rows of a key, in chunk order, through the same graph
@@ -1823,11 +1828,12 @@ void Session::aggregate_columns(int64_t n_rows, const int64_t* keys, const std::
   const int64_t n_groups = header[2];
   bool any_gather = false;
   for (size_t k = 0; k < items.size(); ++k) any_gather = any_gather || !carried[k];
-  launches_ += launch_agg_segments(d_keys, n_rows, n_groups, scratch, L, d_out_keys, true, false, dev_, stream_);   // groups by key
+  launches_ += launch_agg_segments(d_keys, n_rows, n_groups, scratch, L, d_out_keys, agg_table_order_ ? kGroupsTableOrder : kGroupsByKey, false,
+                                   dev_, stream_);   // groups by key (partial results of a row range: table order)
   // carried fetches first: they read the unsorted slot column, which the row sort below recycles
   for (int pass = 0; pass < 2; ++pass) {
    if (pass == 1 && any_gather)
-     launches_ += launch_agg_segments(d_keys, n_rows, n_groups, scratch, L, d_out_keys, false, true, dev_, stream_);  // rows by slot
+     launches_ += launch_agg_segments(d_keys, n_rows, n_groups, scratch, L, d_out_keys, kGroupsKeep, true, dev_, stream_);  // rows by slot
    for (size_t k = 0; k < items.size(); ++k) {
     if ((pass == 0) != (carried[k] != 0)) continue;
     const AggColumn& n = items[k];

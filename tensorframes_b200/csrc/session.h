@@ -94,6 +94,7 @@ class Session {
   // staging grown on demand: [0] gathered rows / send side of an exchange, [1] receive side, [2] per-chunk partial groups
   char* xchg_[4] = {nullptr, nullptr, nullptr, nullptr};      // ([3]: computed reduction inputs / reduced rows of general reducer graphs)
   size_t xchg_cap_[4] = {0, 0, 0, 0};
+  bool agg_table_order_ = false;        // aggregate over row ranges: the partial groups of a range stay in table order
   bool allow_internal_feeds_ = false;   // the post-map of aggregate feeds the Reduce node itself
   char* seg_scratch_ = nullptr;        // UnsortedSegmentSum: keyed-reduction scratch, grown on demand
   size_t seg_scratch_cap_ = 0;
