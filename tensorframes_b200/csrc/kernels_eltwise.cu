@@ -22,6 +22,8 @@
 // Eigen's scalar (b < a ? b : a), Cast as C++ static_cast, integer arithmetic
 // wrapping, integer division truncating toward zero and flagged when the divisor
 // is zero (TF raises "Integer division by zero").
+#include <type_traits>
+
 #include "kernels.h"
 
 namespace tfs {
@@ -324,15 +326,22 @@ eltwise_kernel(const __grid_constant__ EltProgram prog, const int64_t n) {
   S x[kJ][P];
   S tmp[kMaxTmp][kJ][P];
 
-  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+  // The program is interpreted twice over in the source: for whole tiles (all but the block's last one) every vector is
+  // complete, nvalid is the constant P, and the tail tests inside the loads, stores and divisions fold away.
+  auto run_tile = [&](const int64_t tile, auto whole_tag) {
+    constexpr bool WHOLE = decltype(whole_tag)::value;
     int64_t elem[kJ];
     int nvalid[kJ];
 #pragma unroll
     for (int j = 0; j < kJ; ++j) {
       const int64_t v = tile * tile_vecs + int64_t(j) * kThreads + threadIdx.x;
       elem[j] = v * P;
-      const int64_t left = n - elem[j];
-      nvalid[j] = left >= P ? P : (left > 0 ? int(left) : 0);
+      if constexpr (WHOLE) {
+        nvalid[j] = P;
+      } else {
+        const int64_t left = n - elem[j];
+        nvalid[j] = left >= P ? P : (left > 0 ? int(left) : 0);
+      }
     }
     for (int pc = 0; pc < prog.n_instr; ++pc) {
       const Instr in = prog.ins[pc];
@@ -408,6 +417,10 @@ eltwise_kernel(const __grid_constant__ EltProgram prog, const int64_t n) {
         default: break;
       }
     }
+  };
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    if ((tile + 1) * tile_vecs * P <= n) run_tile(tile, std::true_type{});
+    else run_tile(tile, std::false_type{});
   }
 }
 
