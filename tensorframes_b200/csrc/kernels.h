@@ -123,13 +123,22 @@ int launch_radix_sort(int key_bytes, int val_bytes, const void* keys_in, const v
                       int* launches);
 
 // rows ordered by slot (stable): slots[n] -> rows_out[n]; pairs_a / pairs_b are 8-byte-per-row scratch columns
+// seg_lo / seg_hi (both or neither): per slot, the first position and one past the last position of its rows in rows_out
+// (pre-set to 0xffffffff / 0 by the caller, updated with atomicMin / atomicMax by the last pass)
 int launch_radix_rows_by_slot(const unsigned int* slots, int64_t n, int bits, unsigned long long* pairs_a, unsigned long long* pairs_b,
-                              unsigned int* rows_out, void* scratch, const DeviceInfo& dev, cudaStream_t stream);
+                              unsigned int* rows_out, unsigned int* seg_lo, unsigned int* seg_hi, void* scratch, const DeviceInfo& dev,
+                              cudaStream_t stream);
 
 // K3: keyed block reduction. Scratch layout for n_rows rows and at most max_groups groups.
 struct AggLayout {
   uint64_t table_slots;
   size_t off_header, off_slot_key, off_counts, off_offsets, off_group_slot, off_tile_sums, off_perm, off_sort_temp;
+  size_t off_ends;          // one past the last position of every slot's segment (rows_counted == false)
+  // true: the insert pass counts the rows of every slot (atomics) and the table scan turns the counts into segment
+  // offsets.  false (set by the caller before launch_agg_build; needs a row partition of two passes or more and no
+  // carried fetch): nothing is counted, the last partition pass records where every slot's segment begins and ends.
+  bool rows_counted;
+  bool bounds_eligible;     // the row partition has two passes or more (set by agg_layout)
   size_t off_group_slot_tab, off_keys_tab;   // groups in table order, before they are sorted by key
   size_t off_row_slot[3];   // [0] the slot column written by the insert pass, [1] / [2] the slot column between passes
   size_t off_row_id[2];     // row-index columns of the partition (ping-pong)

@@ -59,7 +59,7 @@ template <bool SMEM_COUNTS>
 __global__ void __launch_bounds__(kThreads)
 agg_insert_kernel(const long long* __restrict__ keys, const int64_t n, unsigned long long* __restrict__ slot_key,
                   unsigned int* __restrict__ counts, const unsigned long long slots, unsigned int* __restrict__ header,
-                  const unsigned int max_groups, unsigned int* __restrict__ row_slot) {
+                  const unsigned int max_groups, unsigned int* __restrict__ row_slot, const bool count_rows) {
   __shared__ unsigned int sm_counts[SMEM_COUNTS ? kSmemSlots + 1 : 1];
   if (SMEM_COUNTS) {
     for (unsigned int j = threadIdx.x; j <= (unsigned int)slots; j += kThreads) sm_counts[j] = 0u;
@@ -121,7 +121,7 @@ agg_insert_kernel(const long long* __restrict__ keys, const int64_t n, unsigned 
       if (i < n) {
         __stcs(row_slot + i, (unsigned int)h[u]);
         if (SMEM_COUNTS) atomicAdd(sm_counts + h[u], 1u);
-        else atomicAdd(counts + h[u], 1u);
+        else if (count_rows) atomicAdd(counts + h[u], 1u);
       }
     }
   }
@@ -130,6 +130,24 @@ agg_insert_kernel(const long long* __restrict__ keys, const int64_t n, unsigned 
     for (unsigned int j = threadIdx.x; j <= (unsigned int)slots; j += kThreads)
       if (sm_counts[j] != 0u) atomicAdd(counts + j, sm_counts[j]);
   }
+}
+
+// counts[i] = 1 for a taken slot, 0 for a free one (the marker-key slot, index `slots`, starts as 0 and holds the marker
+// once that key has been seen)
+__global__ void __launch_bounds__(kThreads)
+agg_mark_occupied_kernel(const unsigned long long* __restrict__ slot_key, const unsigned long long slots, unsigned int* __restrict__ counts) {
+  const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i <= slots; i += stride)
+    counts[i] = i < slots ? (slot_key[i] != kEmpty ? 1u : 0u) : (slot_key[i] == kEmpty ? 1u : 0u);
+}
+
+// counts[i] = rows of slot i, from the segment bounds the last partition pass recorded (lo = first position, hi = one past
+// the last; untouched slots have lo = 0xffffffff, hi = 0)
+__global__ void __launch_bounds__(kThreads)
+agg_counts_from_bounds_kernel(const unsigned int* __restrict__ lo, const unsigned int* __restrict__ hi, const uint64_t m,
+                              unsigned int* __restrict__ counts) {
+  const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < m; i += stride) counts[i] = hi[i] != 0u ? hi[i] - lo[i] : 0u;
 }
 
 __global__ void __launch_bounds__(kThreads)
@@ -449,6 +467,8 @@ AggLayout agg_layout(int64_t n_rows, int64_t max_groups, const DeviceInfo& dev) 
   L.off_slot_key = off; off += up((cap + 1) * 8);
   L.off_counts = off; off += up((cap + 1) * 4);
   L.off_offsets = off; off += up((cap + 2) * 4);
+  L.off_ends = off; off += up((cap + 2) * 4);
+  L.rows_counted = true;
   L.off_group_slot = off; off += up(size_t(max_groups + 1) * 4);
   L.off_group_slot_tab = off; off += up(size_t(max_groups + 1) * 4);     // table order, before the sort by key
   L.off_keys_tab = off; off += up(size_t(max_groups + 1) * 8);
@@ -456,6 +476,7 @@ AggLayout agg_layout(int64_t n_rows, int64_t max_groups, const DeviceInfo& dev) 
   // row partition: the slot column the insert pass wrote (kept: every carried fetch sorts from it again), the slot
   // column between passes (a second one only when the table needs a third pass) and two row-index columns
   const int passes = radix_passes(n_rows, slot_bits(cap));
+  L.bounds_eligible = passes >= 2 && cap > uint64_t(kSmemSlots);      // (small tables count in shared memory: cheap)
   L.off_row_slot[0] = off; off += up(size_t(n_rows) * 4);
   // between passes: two packed (slot, row) columns of 8 bytes per row (the second only when there are three passes or
   // more); the carried path of scalar payloads uses the same memory as 4-byte slot and value columns
@@ -486,6 +507,7 @@ int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, ch
   unsigned long long* tile_sums = reinterpret_cast<unsigned long long*>(scratch + L.off_tile_sums);
   unsigned int* row_slot = reinterpret_cast<unsigned int*>(scratch + L.off_row_slot[0]);
   const int64_t m = int64_t(L.table_slots) + 1;   // table + the marker-key slot
+  const bool count_rows = L.rows_counted;
   TFS_CUDA(cudaMemsetAsync(header, 0, 256, stream));
   TFS_CUDA(cudaMemsetAsync(counts, 0, size_t(m) * 4, stream));
   fill_u64_kernel<<<(unsigned)grid_for(int64_t(L.table_slots), dev), kThreads, 0, stream>>>(slot_key, L.table_slots, kEmpty);
@@ -497,10 +519,17 @@ int launch_agg_build(const int64_t* keys, int64_t n_rows, int64_t max_groups, ch
     const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>(tiles, int64_t(dev.sm_count) * 16));
     if (L.table_slots <= uint64_t(kSmemSlots))
       agg_insert_kernel<true><<<grid, kThreads, 0, stream>>>(reinterpret_cast<const long long*>(keys), n_rows, slot_key, counts,
-                                                             L.table_slots, header, (unsigned int)max_groups, row_slot);
+                                                             L.table_slots, header, (unsigned int)max_groups, row_slot, count_rows);
     else
       agg_insert_kernel<false><<<grid, kThreads, 0, stream>>>(reinterpret_cast<const long long*>(keys), n_rows, slot_key, counts,
-                                                              L.table_slots, header, (unsigned int)max_groups, row_slot);
+                                                              L.table_slots, header, (unsigned int)max_groups, row_slot, count_rows);
+    TFS_CUDA(cudaGetLastError());
+    ++launches;
+  }
+  if (!count_rows) {
+    // the rows are not counted while they are inserted (250 M scattered atomics): the table scan only needs to know
+    // which slots are taken, and the segment of every slot comes out of the last partition pass
+    agg_mark_occupied_kernel<<<(unsigned)grid_for(m, dev), kThreads, 0, stream>>>(slot_key, L.table_slots, counts);
     TFS_CUDA(cudaGetLastError());
     ++launches;
   }
@@ -542,10 +571,25 @@ int launch_agg_segments(const int64_t* keys, int64_t n_rows, int64_t n_groups, c
   }
   if (!sort_rows) return launches;       // every fetch carries its values through its own sort (launch_agg_reduce_carried)
   // rows by slot, stable: values = row indices, read off the position in the first pass
+  unsigned int* seg_lo = nullptr;
+  unsigned int* seg_hi = nullptr;
+  const uint64_t m = L.table_slots + 1;
+  if (!L.rows_counted) {
+    seg_lo = reinterpret_cast<unsigned int*>(scratch + L.off_offsets);
+    seg_hi = reinterpret_cast<unsigned int*>(scratch + L.off_ends);
+    TFS_CUDA(cudaMemsetAsync(seg_lo, 0xff, size_t(m) * 4, stream));
+    TFS_CUDA(cudaMemsetAsync(seg_hi, 0, size_t(m) * 4, stream));
+  }
   launches += launch_radix_rows_by_slot(reinterpret_cast<const unsigned int*>(scratch + L.off_row_slot[0]), n_rows, slot_bits(L.table_slots),
                                         reinterpret_cast<unsigned long long*>(scratch + L.off_pairs[0]),
                                         reinterpret_cast<unsigned long long*>(scratch + L.off_pairs[1]),
-                                        reinterpret_cast<unsigned int*>(scratch + L.off_row_id[0]), temp, dev, stream);
+                                        reinterpret_cast<unsigned int*>(scratch + L.off_row_id[0]), seg_lo, seg_hi, temp, dev, stream);
+  if (!L.rows_counted) {
+    agg_counts_from_bounds_kernel<<<(unsigned)grid_for(int64_t(m), dev), kThreads, 0, stream>>>(
+        seg_lo, seg_hi, m, reinterpret_cast<unsigned int*>(scratch + L.off_counts));
+    TFS_CUDA(cudaGetLastError());
+    ++launches;
+  }
   L.off_perm = L.off_row_id[0];
   return launches;
 }

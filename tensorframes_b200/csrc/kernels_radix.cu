@@ -133,14 +133,18 @@ constexpr size_t scatter_smem_bytes() {
 // The packed modes (4-byte keys and values) keep a pair in ONE 8-byte word, key << 32 | value, between the passes of a
 // sort -- one load and one store per pair instead of two, and one write stream per bin instead of two:
 // M_IOTA_PACK = as M_IOTA, written packed through keys_out; M_PACKED = packed in (through keys_in), packed out;
-// M_UNPACK = packed in, values out.
-enum : int { M_PLAIN = 0, M_IOTA = 1, M_IOTA_PACK = 2, M_PACKED = 3, M_UNPACK = 4 };
+// M_UNPACK = packed in, values out; M_UNPACK_BOUNDS = as M_UNPACK, and for a sort's LAST pass on whole keys: the first
+// and one-past-the-last output position of every key's run go to seg_lo[key] / seg_hi[key] (atomicMin / atomicMax at the
+// run boundaries of a tile: the pairs of a bin reach the last pass ordered by their low bits, so equal keys are
+// neighbours in the staged tile).
+enum : int { M_PLAIN = 0, M_IOTA = 1, M_IOTA_PACK = 2, M_PACKED = 3, M_UNPACK = 4, M_UNPACK_BOUNDS = 5 };
 
 template <class K, class V, int MODE, int MB>
 __global__ void __launch_bounds__(kThreads, ctas_for(MB))
 radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_in, K* __restrict__ keys_out, V* __restrict__ vals_out,
                      const int64_t n, const int64_t per_cta, const K xor_mask, const int shift, const int bits,
-                     const unsigned int* __restrict__ hist, const unsigned int* __restrict__ bin_base) {
+                     const unsigned int* __restrict__ hist, const unsigned int* __restrict__ bin_base,
+                     unsigned int* __restrict__ seg_lo, unsigned int* __restrict__ seg_hi) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int bins = 1 << bits;
   const unsigned int mask = (unsigned int)bins - 1u;
@@ -164,7 +168,7 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
   // Every phase below first issues all of its loads and only then its stores: with 8 warps per CTA the kernel lives on
   // instruction-level parallelism, and a store between two loads of arrays the compiler cannot tell apart would chain
   // them (measured: 30 000 cycles per tile before, latency-bound on shared memory and on the tile's global loads).
-  constexpr bool kPackedIn = MODE == M_PACKED || MODE == M_UNPACK;
+  constexpr bool kPackedIn = MODE == M_PACKED || MODE == M_UNPACK || MODE == M_UNPACK_BOUNDS;
   constexpr bool kPackedOut = MODE == M_IOTA_PACK || MODE == M_PACKED;
   using Raw = typename std::conditional<kPackedIn, unsigned long long, K>::type;
   const Raw* raw_in = reinterpret_cast<const Raw*>(keys_in);
@@ -202,7 +206,7 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
     // the values are not needed before the staging phase: their loads travel while the tile is ranked
     K key[kItems];
     V val[kItems];
-    const unsigned int iota0 = (unsigned int)wbase;
+    [[maybe_unused]] const unsigned int iota0 = (unsigned int)wbase;
 #pragma unroll
     for (int r = 0; r < kItems; ++r) {
       if constexpr (kPackedIn) {
@@ -357,6 +361,24 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
         const unsigned int p = (unsigned int)(j * kThreads + threadIdx.x);
         g[j] = shift_of[digit_of<K>(k[j], xor_mask, shift, mask)] + p;
       }
+      if constexpr (MODE == M_UNPACK_BOUNDS) {
+        // run boundaries inside the staged tile (a key whose run crosses tiles or CTAs gets several candidates)
+        K prev[kItems], next[kItems];
+#pragma unroll
+        for (int j = 0; j < kItems; ++j) {
+          const unsigned int p = (unsigned int)(j * kThreads + threadIdx.x);
+          prev[j] = (p > 0u && (WHOLE || p < in_tile)) ? st_keys[p - 1] : ~k[j];
+          next[j] = p + 1u < in_tile ? st_keys[p + 1] : ~k[j];
+        }
+#pragma unroll
+        for (int j = 0; j < kItems; ++j) {
+          const unsigned int p = (unsigned int)(j * kThreads + threadIdx.x);
+          if (WHOLE || p < in_tile) {
+            if (prev[j] != k[j]) atomicMin(seg_lo + k[j], g[j]);
+            if (next[j] != k[j]) atomicMax(seg_hi + k[j], g[j] + 1u);
+          }
+        }
+      }
 #pragma unroll
       for (int j = 0; j < kItems; ++j) {
         const unsigned int p = (unsigned int)(j * kThreads + threadIdx.x);
@@ -390,12 +412,12 @@ PassGeom pass_geometry(int64_t n, int bits, const DeviceInfo& dev) {
 
 template <class K, class V, int MODE>
 int launch_pass_t(const K* keys_in, const V* vals_in, K* keys_out, V* vals_out, int64_t n, K xor_mask, int shift, int bits,
-                  void* scratch, const DeviceInfo& dev, cudaStream_t stream) {
+                  void* scratch, const DeviceInfo& dev, cudaStream_t stream, unsigned int* seg_lo = nullptr, unsigned int* seg_hi = nullptr) {
   const PassGeom g = pass_geometry(n, bits, dev);
   const int bins = 1 << bits;
   unsigned int* hist = static_cast<unsigned int*>(scratch);
   unsigned int* bin_total = hist + size_t(bins) * size_t(g.grid);
-  if constexpr (MODE == M_PACKED || MODE == M_UNPACK)
+  if constexpr (MODE == M_PACKED || MODE == M_UNPACK || MODE == M_UNPACK_BOUNDS)
     radix_hist_kernel<unsigned long long><<<g.grid, kThreads, 0, stream>>>(reinterpret_cast<const unsigned long long*>(keys_in), n, g.per_cta,
                                                                           0ULL, shift + 32, bits, hist);
   else
@@ -412,7 +434,7 @@ int launch_pass_t(const K* keys_in, const V* vals_in, K* keys_out, V* vals_out, 
       TFS_CUDA(cudaFuncSetAttribute(radix_scatter_kernel<K, V, MODE, kSmallBits>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     });
     radix_scatter_kernel<K, V, MODE, kSmallBits><<<g.grid, kThreads, smem, stream>>>(keys_in, vals_in, keys_out, vals_out, n, g.per_cta,
-                                                                                      xor_mask, shift, bits, hist, bin_total);
+                                                                                      xor_mask, shift, bits, hist, bin_total, seg_lo, seg_hi);
   } else {
     constexpr size_t smem = scatter_smem_bytes<K, V, kMaxBits>();
     static PerDeviceOnce attr;
@@ -420,7 +442,7 @@ int launch_pass_t(const K* keys_in, const V* vals_in, K* keys_out, V* vals_out, 
       TFS_CUDA(cudaFuncSetAttribute(radix_scatter_kernel<K, V, MODE, kMaxBits>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     });
     radix_scatter_kernel<K, V, MODE, kMaxBits><<<g.grid, kThreads, smem, stream>>>(keys_in, vals_in, keys_out, vals_out, n, g.per_cta,
-                                                                                    xor_mask, shift, bits, hist, bin_total);
+                                                                                    xor_mask, shift, bits, hist, bin_total, seg_lo, seg_hi);
   }
   TFS_CUDA(cudaGetLastError());
   return 4;
@@ -506,12 +528,15 @@ int launch_radix_sort(int key_bytes, int val_bytes, const void* keys_in, const v
 // pairs travel packed (slot << 32 | row) through the two 8-byte scratch columns; the first pass reads the row index off
 // the element's position, the last one writes row indices only.
 int launch_radix_rows_by_slot(const unsigned int* slots, int64_t n, int bits, unsigned long long* pairs_a, unsigned long long* pairs_b,
-                              unsigned int* rows_out, void* scratch, const DeviceInfo& dev, cudaStream_t stream) {
+                              unsigned int* rows_out, unsigned int* seg_lo, unsigned int* seg_hi, void* scratch, const DeviceInfo& dev,
+                              cudaStream_t stream) {
   if (n <= 0) return 0;
+  TFS_CHECK((seg_lo == nullptr) == (seg_hi == nullptr), TFS_ERR_INVALID, "internal: segment bounds come as a pair");
   TFS_CHECK(n < (int64_t(1) << 32), TFS_ERR_UNSUPPORTED, "internal: radix pass over 2^32 or more pairs");
   using u32 = unsigned int;
   const int passes = radix_passes(n, bits);
   int launches = 0, shift = 0;
+  TFS_CHECK(seg_lo == nullptr || passes >= 2, TFS_ERR_INVALID, "internal: segment bounds need a partition of two passes or more");
   if (passes == 1)
     return launch_pass_t<u32, u32, M_IOTA>(slots, nullptr, nullptr, rows_out, n, 0u, 0, bits, scratch, dev, stream);
   unsigned long long* cur = nullptr;
@@ -523,9 +548,12 @@ int launch_radix_rows_by_slot(const unsigned int* slots, int64_t n, int bits, un
     else if (p < passes - 1)
       launches += launch_pass_t<u32, u32, M_PACKED>(reinterpret_cast<const u32*>(cur), nullptr, reinterpret_cast<u32*>(dst), nullptr, n, 0u,
                                                     shift, b, scratch, dev, stream);
-    else
+    else if (seg_lo == nullptr)
       launches += launch_pass_t<u32, u32, M_UNPACK>(reinterpret_cast<const u32*>(cur), nullptr, nullptr, rows_out, n, 0u, shift, b, scratch,
                                                     dev, stream);
+    else
+      launches += launch_pass_t<u32, u32, M_UNPACK_BOUNDS>(reinterpret_cast<const u32*>(cur), nullptr, nullptr, rows_out, n, 0u, shift, b,
+                                                           scratch, dev, stream, seg_lo, seg_hi);
     cur = dst;
     shift += b;
   }
