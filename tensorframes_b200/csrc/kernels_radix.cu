@@ -10,9 +10,9 @@
 //     by tile with its bin cursors in shared memory.  No atomics decide an output position, so the pass is stable and
 //     its output is a pure function of its input: equal keys keep their input order, run after run.
 //   * the first pass takes its values from the element index (no row-id column is read), the last pass writes no keys.
-//   * inside a tile (4096 pairs) ranks come from __match_any_sync over the digit -- lanes with equal digits rank
-//     themselves by lane order -- on per-warp counters, then one pass over the per-warp counters gives every warp's
-//     offset inside every bin.  Pairs are staged in shared memory in output order, so the global writes of a tile are
+//   * inside a tile (4096 pairs) ranks come from the set of lanes that hold the same digit (one ballot per digit bit)
+//     -- lanes with equal digits rank themselves by lane order -- on per-warp counters, then one pass over the per-warp
+//     counters gives every warp's offset inside every bin.  Pairs are staged in shared memory in output order, so the global writes of a tile are
 //     runs of consecutive addresses; the next tile's keys are loaded while the current one is written out.
 //   * passes are 8 bits wide by default (three for 22 slot bits): with 2048 bins a tile holds two pairs per bin, every
 //     write is a partial sector, and the open lines of 2 columns x 2048 bins x 296 CTAs do not fit L2 -- measured
@@ -227,9 +227,28 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
       const bool valid = WHOLE || r * 32 < left;
       dig[r] = valid ? digit_of<K>(key[r], xor_mask, shift, mask) : 0xffffffffu;
     }
+    // peers = the lanes that hold the same digit: one ballot per digit bit.  (__match_any_sync is one instruction, but
+    // MATCH.ANY retires once per 60 cycles per SM on this GPU whatever the occupancy -- 1.6 of the 1.9 ms of an 8-bit
+    // pass over 2.5e8 pairs; eight ballots and their masks take 29: profiles/experiments/match_rate.cu.)
     unsigned int peers[kItems];
 #pragma unroll
-    for (int r = 0; r < kItems; ++r) peers[r] = __match_any_sync(0xffffffffu, dig[r]);
+    for (int r = 0; r < kItems; ++r) {
+      unsigned int same = 0xffffffffu;
+#pragma unroll
+      for (int b = 0; b < MB; ++b) {
+        if (b < bits) {          // warp-uniform
+          const bool one = (dig[r] >> b) & 1u;
+          const unsigned int vote = __ballot_sync(0xffffffffu, one);
+          same &= one ? vote : ~vote;
+        }
+      }
+      if constexpr (!WHOLE) {      // items past the end of the range only match one another
+        const bool valid = dig[r] != 0xffffffffu;
+        const unsigned int vote = __ballot_sync(0xffffffffu, valid);
+        same &= valid ? vote : ~vote;
+      }
+      peers[r] = same;
+    }
 #pragma unroll
     for (int r = 0; r < kItems; ++r) {
       const bool valid = WHOLE || dig[r] != 0xffffffffu;

@@ -1803,7 +1803,8 @@ void Session::aggregate_columns(int64_t n_rows, const int64_t* keys, const std::
   // gather-only blocks whose table needs two partition passes or more: the rows of a slot are not counted at insert
   // (one scattered atomic per row), the last partition pass records where every slot's segment begins and ends
   {
-    static const bool count_at_insert = [] { const char* e = std::getenv("TFS_AGG_COUNT"); return e && std::string(e) == "insert"; }();
+    const char* e = std::getenv("TFS_AGG_COUNT");        // (A/B switch, read per call: "insert" counts the rows at insert)
+    const bool count_at_insert = e && std::string(e) == "insert";
     if (L.bounds_eligible && carried_bytes == 0 && !count_at_insert) L.rows_counted = false;
   }
   const bool keys_dev = on_device_or_refuse(keys, dev_.device, "the key column");

@@ -1385,6 +1385,33 @@ def test_aggregate_few_large_groups_split_across_warps(n_keys, cell):
         assert np.array_equal(o1.astype(np.float64), ref)
 
 
+@pytest.mark.parametrize("n,n_keys,max_groups", [(5_000_011, 1, 100_000), (5_000_011, 3, 100_000), (5_000_011, 70_000, 70_000),
+                                                 (6_000_001, 2_400_000, 2_400_000), (1_000_003, 40_000, 50_000),
+                                                 (300_007, 299_000, 300_000)])
+def test_aggregate_segments_from_the_partition(n, n_keys, max_groups, monkeypatch):
+    """Gather-only blocks with a table too large for shared-memory counters: the rows of a slot are not counted at
+    insert, the last partition pass records every slot's segment.  Group counts from 1 to 2.4e6, two and three passes;
+    the same call with the rows counted at insert must give the same bytes."""
+    rng = np.random.default_rng(n_keys)
+    universe = rng.integers(-2**62, 2**62, n_keys)
+    universe[0] = -1                                    # the table's empty marker is a legal key
+    keys = universe[rng.integers(0, n_keys, n)]
+    v = rng.integers(-8, 9, (n, 4)).astype(np.float32)
+    g = aggregate_graph(tfs.FloatType, (4,), "sum")
+    outs = []
+    for mode in ("bounds", "insert"):
+        monkeypatch.setenv("TFS_AGG_COUNT", mode)
+        with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+            k, (o,) = s.aggregate(keys, {"v_input": v}, ["v"], max_groups=max_groups)
+        outs.append((k, o))
+    present = np.unique(keys)
+    assert np.array_equal(outs[0][0], present)
+    order = np.argsort(keys, kind="stable")
+    ref = np.add.reduceat(v[order].astype(np.float64), np.searchsorted(keys[order], present), axis=0)
+    assert np.array_equal(outs[0][1].astype(np.float64), ref)
+    assert outs[0][1].tobytes() == outs[1][1].tobytes() and np.array_equal(outs[0][0], outs[1][0])
+
+
 def test_large_pageable_blocks_take_the_staged_copies():
     """numpy arrays (pageable memory) of 64 MiB and more go through the pinned staging ring in both directions;
     ragged sizes, two columns in, two out, plus the keyed path."""
