@@ -235,12 +235,14 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
     for (int r = 0; r < kItems; ++r) {
       unsigned int same = 0xffffffffu;
 #pragma unroll
-      for (int b = 0; b < MB; ++b) {
-        if (b < bits) {          // warp-uniform
-          const bool one = (dig[r] >> b) & 1u;
-          const unsigned int vote = __ballot_sync(0xffffffffu, one);
-          same &= one ? vote : ~vote;
-        }
+      for (int b = 0; b < MB; ++b) {      // (bits of the digit above `bits` are zero in every lane: their ballots change nothing)
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t.reg .b32 t, v;\n\t"
+            "and.b32 t, %1, %2;\n\tsetp.ne.u32 p, t, 0;\n\t"
+            "vote.sync.ballot.b32 v, p, 0xffffffff;\n\t"
+            "selp.b32 t, -1, 0, p;\n\tlop3.b32 %0, %0, v, t, 0x90;\n\t}"      // same &= ~(v ^ t)
+            : "+r"(same)
+            : "r"(dig[r]), "r"(1u << b));
       }
       if constexpr (!WHOLE) {      // items past the end of the range only match one another
         const bool valid = dig[r] != 0xffffffffu;
