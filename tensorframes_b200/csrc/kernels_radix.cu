@@ -123,10 +123,11 @@ radix_scan_totals_kernel(unsigned int* __restrict__ bin_total, const int bins) {
 
 // Dynamic shared memory of the scatter kernel:
 //   cursor[bins] u32 | bin_start[bins + 1] u32 | shift_of[bins] u32 | cnt[kWarps][bins] u16 | staged keys | staged values
+//   | (256-bin instantiation) lane-mask tables [2][kWarps][bins] u32
 template <class K, class V, int MB>
 constexpr size_t scatter_smem_bytes() {
   return size_t(1 << MB) * 4 + size_t((1 << MB) + 8) * 4 + size_t(1 << MB) * 4 + size_t(kWarps) * (1 << MB) * 2 +
-         size_t(kTile) * (sizeof(K) + sizeof(V));
+         size_t(kTile) * (sizeof(K) + sizeof(V)) + (MB <= kSmallBits ? size_t(2) * kWarps * (1 << MB) * 4 : 0);
 }
 
 // MODE: M_PLAIN = values loaded from vals_in; M_IOTA = the values are the element indices (4-byte values).
@@ -156,6 +157,12 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
   unsigned short* cnt = reinterpret_cast<unsigned short*>(shift_of + kMB);
   K* st_keys = reinterpret_cast<K*>(cnt + kWarps * kMB);
   V* st_vals = reinterpret_cast<V*>(st_keys + kTile);
+  constexpr bool kPair64 = sizeof(K) == 4 && sizeof(V) == 4;      // staged as one word: key << 32 | value
+  [[maybe_unused]] unsigned long long* st_pairs = reinterpret_cast<unsigned long long*>(st_keys);
+  [[maybe_unused]] unsigned int* peer_tab = reinterpret_cast<unsigned int*>(st_vals + kTile);
+  if constexpr (MB <= kSmallBits) {
+    for (int i = threadIdx.x; i < 2 * kWarps * kMB; i += kThreads) peer_tab[i] = 0u;      // (ordered by the first tile's barrier)
+  }
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned int lt_mask = (1u << lane) - 1u;
@@ -227,49 +234,95 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
       const bool valid = WHOLE || r * 32 < left;
       dig[r] = valid ? digit_of<K>(key[r], xor_mask, shift, mask) : 0xffffffffu;
     }
-    // peers = the lanes that hold the same digit: one ballot per digit bit.  (__match_any_sync is one instruction, but
-    // MATCH.ANY retires once per 60 cycles per SM on this GPU whatever the occupancy -- 1.6 of the 1.9 ms of an 8-bit
-    // pass over 2.5e8 pairs; eight ballots and their masks take 29: profiles/experiments/match_rate.cu.)
-    unsigned int peers[kItems];
+    // peers = the lanes that hold the same digit.  __match_any_sync is one instruction, but MATCH.ANY retires once per
+    // 60 cycles per SM on this GPU whatever the occupancy -- 1.6 of the 1.9 ms an 8-bit pass over 2.5e8 pairs took with
+    // it.  One ballot per digit bit with its mask: 29 cycles for 8 bits.  Lane masks collected in shared memory (every
+    // lane ORs its bit into its warp's word for the digit, then reads the word back): 10 cycles
+    // (profiles/experiments/match_rate.cu).  The 256-bin instantiation has room for the tables: two per warp, used in
+    // turn, so that clearing the words of a round waits one round and costs no extra warp barrier.
+    if constexpr (MB <= kSmallBits) {
+      unsigned int* const tab0 = peer_tab + warp * kMB;
+      unsigned int* const tab1 = peer_tab + (kWarps + warp) * kMB;
+      const unsigned int lane_bit = 1u << lane;
 #pragma unroll
-    for (int r = 0; r < kItems; ++r) {
-      unsigned int same = 0xffffffffu;
-#pragma unroll
-      for (int b = 0; b < MB; ++b) {      // (bits of the digit above `bits` are zero in every lane: their ballots change nothing)
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t.reg .b32 t, v;\n\t"
-            "and.b32 t, %1, %2;\n\tsetp.ne.u32 p, t, 0;\n\t"
-            "vote.sync.ballot.b32 v, p, 0xffffffff;\n\t"
-            "selp.b32 t, -1, 0, p;\n\tlop3.b32 %0, %0, v, t, 0x90;\n\t}"      // same &= ~(v ^ t)
-            : "+r"(same)
-            : "r"(dig[r]), "r"(1u << b));
+      for (int r = 0; r < kItems; ++r) {
+        unsigned int* const cur = (r & 1) ? tab1 : tab0;
+        unsigned int* const old = (r & 1) ? tab0 : tab1;
+        const bool valid = WHOLE || dig[r] != 0xffffffffu;
+        unsigned int base = 0;
+        if (valid) {
+          atomicOr(cur + dig[r], lane_bit);
+          base = my_cnt[dig[r]];
+        }
+        __syncwarp();
+        unsigned int peers = 0;
+        if (valid) peers = cur[dig[r]];
+        if (r > 0 && (WHOLE || dig[r > 0 ? r - 1 : 0] != 0xffffffffu)) old[dig[r > 0 ? r - 1 : 0]] = 0u;
+        const unsigned int before = __popc(peers & lt_mask);
+        if (valid && before == 0u) my_cnt[dig[r]] = (unsigned short)(base + __popc(peers));
+        __syncwarp();
+        lrank[r] = (unsigned short)(base + before);
       }
-      if constexpr (!WHOLE) {      // items past the end of the range only match one another
-        const bool valid = dig[r] != 0xffffffffu;
-        const unsigned int vote = __ballot_sync(0xffffffffu, valid);
-        same &= valid ? vote : ~vote;
-      }
-      peers[r] = same;
-    }
+      if (WHOLE || dig[kItems - 1] != 0xffffffffu) (((kItems - 1) & 1) ? tab1 : tab0)[dig[kItems - 1]] = 0u;
+    } else {
+      unsigned int peers[kItems];
 #pragma unroll
-    for (int r = 0; r < kItems; ++r) {
-      const bool valid = WHOLE || dig[r] != 0xffffffffu;
-      const unsigned int before = __popc(peers[r] & lt_mask);
-      unsigned int base = 0;
-      if (valid) base = my_cnt[dig[r]];
-      __syncwarp();
-      if (valid && before == 0u) my_cnt[dig[r]] = (unsigned short)(base + __popc(peers[r]));
-      __syncwarp();
-      lrank[r] = (unsigned short)(base + before);
+      for (int r = 0; r < kItems; ++r) {
+        unsigned int same = 0xffffffffu;
+#pragma unroll
+        for (int b = 0; b < MB; ++b) {      // (bits of the digit above `bits` are zero in every lane: their ballots change nothing)
+          asm volatile(
+              "{\n\t.reg .pred p;\n\t.reg .b32 t, v;\n\t"
+              "and.b32 t, %1, %2;\n\tsetp.ne.u32 p, t, 0;\n\t"
+              "vote.sync.ballot.b32 v, p, 0xffffffff;\n\t"
+              "selp.b32 t, -1, 0, p;\n\tlop3.b32 %0, %0, v, t, 0x90;\n\t}"      // same &= ~(v ^ t)
+              : "+r"(same)
+              : "r"(dig[r]), "r"(1u << b));
+        }
+        if constexpr (!WHOLE) {      // items past the end of the range only match one another
+          const bool valid = dig[r] != 0xffffffffu;
+          const unsigned int vote = __ballot_sync(0xffffffffu, valid);
+          same &= valid ? vote : ~vote;
+        }
+        peers[r] = same;
+      }
+#pragma unroll
+      for (int r = 0; r < kItems; ++r) {
+        const bool valid = WHOLE || dig[r] != 0xffffffffu;
+        const unsigned int before = __popc(peers[r] & lt_mask);
+        unsigned int base = 0;
+        if (valid) base = my_cnt[dig[r]];
+        __syncwarp();
+        if (valid && before == 0u) my_cnt[dig[r]] = (unsigned short)(base + __popc(peers[r]));
+        __syncwarp();
+        lrank[r] = (unsigned short)(base + before);
+      }
     }
     __syncthreads();
     // (c) per bin: each warp's offset inside the bin (in place) and the bin's start inside the tile
+    constexpr bool kFold = MB <= kSmallBits;      // one bin per thread
     {
       const int per_thread = (bins + kThreads - 1) / kThreads;       // 8 at 2048 bins
       const int b0 = threadIdx.x * per_thread;
       unsigned int tot[kPT];
       unsigned int mine = 0;
-      if (kPT == 8 && per_thread == 8) {
+      [[maybe_unused]] unsigned int within[kWarps];      // (256-bin instantiation) this thread's bin: every warp's offset in it
+      if constexpr (kFold) {
+        tot[0] = 0;
+        if (b0 < bins) {
+#pragma unroll
+          for (int w = 0; w < kWarps; ++w) within[w] = cnt[w * bins + b0];
+          unsigned int run = 0;
+#pragma unroll
+          for (int w = 0; w < kWarps; ++w) {
+            const unsigned int v = within[w];
+            within[w] = run;
+            run += v;
+          }
+          tot[0] = run;
+          mine = run;
+        }
+      } else if (kPT == 8 && per_thread == 8) {
         // 8 neighbouring 16-bit counters of one warp row are one 16-byte word: 8 vector loads, then 8 vector stores
         uint4 c[kWarps];
 #pragma unroll
@@ -337,7 +390,14 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
       for (int j = 0; j < kPT; ++j) {
         const int b = b0 + j;
         if (j < per_thread && b < bins) {
-          bin_start[b] = run;
+          if constexpr (kFold) {
+            // the bin's start goes into the per-warp offsets themselves (at most 4096: fits the 16-bit counters), so
+            // the staging phase looks up one word per pair instead of two
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) cnt[w * bins + b] = (unsigned short)(run + within[w]);
+          } else {
+            bin_start[b] = run;
+          }
           shift_of[b] = cur[j] - run;
           cursor[b] = cur[j] + tot[j];      // (read again only in the next tile's phase (c))
           run += tot[j];
@@ -352,13 +412,18 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
 #pragma unroll
       for (int r = 0; r < kItems; ++r) {
         const unsigned int d = (WHOLE || dig[r] != 0xffffffffu) ? dig[r] : 0u;
-        pos[r] = bin_start[d] + my_cnt[d] + lrank[r];
+        if constexpr (kFold) pos[r] = my_cnt[d] + lrank[r];
+        else pos[r] = bin_start[d] + my_cnt[d] + lrank[r];
       }
 #pragma unroll
       for (int r = 0; r < kItems; ++r) {
         if (WHOLE || dig[r] != 0xffffffffu) {
-          st_keys[pos[r]] = key[r];
-          st_vals[pos[r]] = val[r];
+          if constexpr (kPair64) {      // one 8-byte store per pair instead of two scattered 4-byte ones
+            st_pairs[pos[r]] = ((unsigned long long)key[r] << 32) | (unsigned long long)val[r];
+          } else {
+            st_keys[pos[r]] = key[r];
+            st_vals[pos[r]] = val[r];
+          }
         }
       }
     }
@@ -373,8 +438,14 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
 #pragma unroll
       for (int j = 0; j < kItems; ++j) {
         const unsigned int p = (unsigned int)(j * kThreads + threadIdx.x);
-        k[j] = (WHOLE || p < in_tile) ? st_keys[p] : K(0);
-        v[j] = (WHOLE || p < in_tile) ? st_vals[p] : V(0);
+        if constexpr (kPair64) {
+          const unsigned long long w = (WHOLE || p < in_tile) ? st_pairs[p] : 0ULL;
+          k[j] = K(w >> 32);
+          v[j] = V(w);
+        } else {
+          k[j] = (WHOLE || p < in_tile) ? st_keys[p] : K(0);
+          v[j] = (WHOLE || p < in_tile) ? st_vals[p] : V(0);
+        }
       }
       unsigned int g[kItems];
 #pragma unroll
@@ -388,8 +459,10 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const V* __restrict__ vals_i
 #pragma unroll
         for (int j = 0; j < kItems; ++j) {
           const unsigned int p = (unsigned int)(j * kThreads + threadIdx.x);
-          prev[j] = (p > 0u && (WHOLE || p < in_tile)) ? st_keys[p - 1] : ~k[j];
-          next[j] = p + 1u < in_tile ? st_keys[p + 1] : ~k[j];
+          // (M_UNPACK_BOUNDS is a mode of 4-byte keys and values: the staged key is the high half of the pair's word)
+          const unsigned int* st_hi = reinterpret_cast<const unsigned int*>(st_pairs) + 1;
+          prev[j] = (p > 0u && (WHOLE || p < in_tile)) ? K(st_hi[2 * (p - 1u)]) : ~k[j];
+          next[j] = p + 1u < in_tile ? K(st_hi[2 * (p + 1u)]) : ~k[j];
         }
 #pragma unroll
         for (int j = 0; j < kItems; ++j) {
