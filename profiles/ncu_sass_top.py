@@ -1,10 +1,11 @@
 """Top stall sites of one kernel from `ncu -i X.ncu-rep --page source --csv --print-source sass`, plus headline metrics
-from `--page raw --csv`.  usage: python profiles/ncu_sass_top.py X.ncu-rep [top_n]"""
+from `--page raw --csv`.  usage: python profiles/ncu_sass_top.py X.ncu-rep [top_n] [kernel-name regex]"""
 import csv, subprocess, sys, io
 
 rep = sys.argv[1]
 top_n = int(sys.argv[2]) if len(sys.argv) > 2 else 40
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+pick = ["-k", "regex:" + sys.argv[3], "-c", "1"] if len(sys.argv) > 3 else []
+raw = subprocess.run(["ncu", "-i", rep] + pick + ["--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 h, v = rows[0], rows[-1]
 d = dict(zip(h, v))
@@ -22,7 +23,7 @@ for k in ["gpu__time_duration.sum", "smsp__inst_executed.sum", "smsp__issue_acti
           "launch__registers_per_thread", "sm__warps_active.avg.pct_of_peak_sustained_active"]:
     if k in d:
         print(" ", k, d[k])
-src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "sass"], capture_output=True, text=True).stdout
+src = subprocess.run(["ncu", "-i", rep] + pick + ["--page", "source", "--csv", "--print-source", "sass"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(src)))
 h, body = rows[1], rows[2:]
 col = {n: h.index(n) for n in ["Source", "# Samples", "Instructions Executed", "stall_short_sb", "stall_barrier", "stall_mio", "stall_long_sb",

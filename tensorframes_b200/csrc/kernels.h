@@ -171,7 +171,7 @@ int launch_agg_reduce(int dtype, int red_op, const void* payload, int64_t cell, 
                       const AggLayout& L, void* out, void* split_scratch, size_t split_bytes, const DeviceInfo& dev,
                       cudaStream_t stream);
 
-// Exchange step of aggregate: owner[i] = mix64(key[i]) mod world and the number of groups per owner (counts[world],
+// Exchange step of aggregate: owner[i] = (mix64(key[i]) >> 32) mod world and the number of groups per owner (counts[world],
 // zeroed by the call); rows gathered through a permutation (row_bytes a multiple of 4).
 int launch_agg_owner(const int64_t* keys, int64_t n, int world, unsigned int* owner, unsigned long long* counts, const DeviceInfo& dev,
                      cudaStream_t stream);

@@ -656,7 +656,8 @@ int launch_agg_reduce(int dtype, int red_op, const void* payload, int64_t cell, 
 }
 
 // ---- the exchange step of aggregate over several GPUs ---------------------------------------------------------
-// owner[i] = mix64(key[i]) mod world -- the rank that merges group i -- and how many groups go to each rank.
+// owner[i] = (mix64(key[i]) >> 32) mod world -- the rank that merges group i -- and how many groups go to each rank.
+// (The high half: the low bits of the same mix pick the table slot of the merge on the owner.)
 namespace {
 __global__ void __launch_bounds__(kThreads)
 agg_owner_kernel(const long long* __restrict__ keys, const int64_t n, const unsigned int world, unsigned int* __restrict__ owner,
@@ -666,7 +667,7 @@ agg_owner_kernel(const long long* __restrict__ keys, const int64_t n, const unsi
   __syncthreads();
   const int64_t stride = int64_t(gridDim.x) * blockDim.x;
   for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const unsigned int o = (unsigned int)(mix64((unsigned long long)keys[i]) % world);
+    const unsigned int o = (unsigned int)((mix64((unsigned long long)keys[i]) >> 32) % world);
     owner[i] = o;
     atomicAdd(&sm[o], 1u);
   }

@@ -1991,7 +1991,7 @@ void Session::reduce_combine(Comm& comm, const std::vector<TensorArg>& partials,
 }
 
 // aggregate over several GPUs: after the per-GPU keyed reduction every rank holds partial groups; each group goes to the
-// rank that owns its key (owner = mix64(key) mod world) and is merged there by one more keyed reduction.  The reference
+// rank that owns its key (owner = (mix64(key) >> 32) mod world) and is merged there by one more keyed reduction.  The reference
 // does this with Spark's hash shuffle between the UDAF's partial and final aggregation (impl/DebugRowOps.scala:573-576).
 // Partition (stable, by owner), one grouped send / receive per peer, merge: all enqueued from here, no host work per
 // group; one small readback (the per-peer counts) sizes the receives.

@@ -59,7 +59,9 @@ def owner_of_key(keys: np.ndarray, world: int) -> np.ndarray:
     x ^= x >> np.uint64(27)
     x *= np.uint64(0x94D049BB133111EB)
     x ^= x >> np.uint64(31)
-    return (x % np.uint64(world)).astype(np.int64)
+    # the high half: the low bits of the same mix pick the hash-table slot of the merge on the owner, and a rank whose keys
+    # all agree in them modulo a power-of-two world would use one slot in `world` as home slot
+    return ((x >> np.uint64(32)) % np.uint64(world)).astype(np.int64)
 
 
 def owner_of_key_torch(keys, world: int):
@@ -79,15 +81,12 @@ def owner_of_key_torch(keys, world: int):
     x = x ^ lsr(x, 27)
     x = mul(x, 0x94D049BB133111EB)
     x = x ^ lsr(x, 31)
-    # unsigned modulo of a value held in int64: fold the top bit back in
-    hi = lsr(x, 1)
-    r = ((hi % world) * 2 + (x & 1)) % world
-    return r
+    return lsr(x, 32) % world      # (the high half: non-negative in int64)
 
 
 def exchange_groups(keys, values: Sequence, dist=None):
     """The exchange step of aggregate: every rank holds partial groups (keys [G], values[i] [G, cell...]);
-    afterwards every rank holds all partial rows of the keys it owns (owner = mix(key) mod world), ready
+    afterwards every rank holds all partial rows of the keys it owns (owner = high half of mix(key), mod world), ready
     for one more keyed reduction.  The reference does this with Spark's hash shuffle between the UDAF's
     partial and final aggregation (impl/DebugRowOps.scala:573-576).  Returns (keys, values) of the
     received rows; row order is by source rank."""
