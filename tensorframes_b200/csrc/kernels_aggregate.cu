@@ -6,12 +6,14 @@
 // four passes, all HBM-bound:
 //
 //   1. insert   every key into an open-addressing table (64-bit CAS on the key slot); the row
-//               remembers its slot (u32) and the slot counts its rows       8 B read + 4 B written / row
-//   2. scan     one pass over the table: segment offset of every slot, dense group id of every
-//               occupied slot, out_keys                                   (table only)
+//               remembers its slot (u32)                                    8 B read + 4 B written / row
+//               (small tables, and blocks with a carried scalar fetch, also count the rows of every slot here)
+//   2. scan     one pass over the table: dense group id of every occupied slot, out_keys (and the
+//               segment offset of every slot where rows were counted)      (table only)
 //   3. sort     rows by slot: a stable radix partition of the (slot, row) pairs on the slot bits, three 8-bit passes
 //               for tables of up to 2^24 slots (kernels_radix.cu); the first pass takes the row index from the
-//               element's position, the last one writes row indices only
+//               element's position, the last one writes row indices only and records where every slot's
+//               segment begins and ends
 //   4. gather-reduce  one warp per group walks its segment of the sorted row list and gathers
 //               the payload rows -- each a contiguous cell, read with coalesced vector loads --
 //               accumulating in registers; one coalesced store per group.      cell bytes / row

@@ -10,11 +10,14 @@
 //     by tile with its bin cursors in shared memory.  No atomics decide an output position, so the pass is stable and
 //     its output is a pure function of its input: equal keys keep their input order, run after run.
 //   * the first pass takes its values from the element index (no row-id column is read), the last pass writes no keys.
-//   * inside a tile (4096 pairs) ranks come from the set of lanes that hold the same digit (one ballot per digit bit)
-//     -- lanes with equal digits rank themselves by lane order -- on per-warp counters, then one pass over the per-warp
-//     counters gives every warp's offset inside every bin.  Pairs are staged in shared memory in output order, so the global writes of a tile are
-//     runs of consecutive addresses; the next tile's keys are loaded while the current one is written out.
-//   * passes are 8 bits wide by default (three for 22 slot bits): with 2048 bins a tile holds two pairs per bin, every
+//   * inside a tile (4096 pairs) a pair's rank is its warp's running count of the digit plus the number of lower lanes
+//     that hold the same digit in the same round.  That lane set is collected in shared memory in the 256-bin
+//     instantiation (every lane ORs its bit into its warp's word for the digit and reads the word back) and by one
+//     ballot per digit bit in the 2048-bin one; MATCH.ANY, the one-instruction way, retires once per 60 cycles per SM
+//     here.  One pass over the per-warp counters then gives every warp's offset inside every bin.  Pairs are staged in
+//     shared memory in output order, so the global writes of a tile are runs of consecutive addresses; the next tile's
+//     keys are loaded while the current one is written out.
+//   * passes are 8 bits wide by default (three for 23 slot bits): with 2048 bins a tile holds two pairs per bin, every
 //     write is a partial sector, and the open lines of 2 columns x 2048 bins x 296 CTAs do not fit L2 -- measured
 //     13 GB of DRAM traffic for 4 GB of data (profiles/r02_experiments.md).  Passes of 9 to 11 bits remain available
 //     (TFS_RADIX_BITS) and are used where a partition has that many bins by nature.
