@@ -17,7 +17,8 @@ environment, so the reference itself cannot be run.  The oracle is pinned agains
 every known-answer vector the reference's own tests and README hold for this path
 (tests/golden/reference_vectors.json, made by tests/golden/make_golden.py):
 Identity, Add, Const, Sum, the trimmed maps, reduce_blocks, aggregate, analyze, and
-the two GraphDef fixtures.  Ops with no reference test -- Sub, Mul, Div, Neg, Cast,
+the two GraphDef fixtures.  The graphs those cases run on are written by oracle/graph_writer.py
+(the reference's node layout restated, no product code); the product's DSL is checked against it.  Ops with no reference test -- Sub, Mul, Div, Neg, Cast,
 Minimum, Maximum, Relu, reduce_min (README only), reduce_max, MatMul, and the k-means /
 geometric-mean snippet vocabulary (Square, Inv, OnesLike, ZerosLike, Shape, StridedSlice,
 Pack, ExpandDims, Tile, ArgMin, ArgMax, UnsortedSegmentSum; the snippets print, they hold
