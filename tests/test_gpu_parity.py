@@ -44,6 +44,49 @@ def assert_same(got, want):
     assert got.tobytes() == want.tobytes(), np.argwhere(got != want)[:5]
 
 
+# ---- graphs the product did not write: the golden cases' graphs from the oracle's own writer, run as one block ------
+def _block_feeds(case, cols, parts, graph):
+    """Dense [n, cell...] arrays for the block placeholders of a case's graph, or None when a column is ragged."""
+    from oracle import graphdef
+    rows = [r for p in parts for r in p]
+    spec = case["graph"]
+    source = {name: name for name, _dt, _shape in spec.get("placeholders", [])}
+    source.update({tf_name: col for col, tf_name in spec.get("block_placeholders", [])})
+    names = [c.name for c in cols]
+    feeds = {}
+    for n in graphdef.parse_graph(graph):
+        if n.op != "Placeholder":
+            continue
+        col = source[n.name] if source[n.name] in names else source[n.name].replace("_input", "")
+        c = cols[names.index(col)]
+        try:
+            feeds[n.name] = np.asarray([r[names.index(col)] for r in rows], dtype=graphdef.DT[c.dtype])
+        except ValueError:
+            return None
+    return feeds
+
+
+@pytest.mark.parametrize("case", [c for c in G["cases"] if c["kind"] in ("map_blocks", "map_blocks_trimmed", "reduce_blocks", "aggregate")],
+                         ids=lambda c: c["id"])
+def test_library_runs_graphs_from_the_independent_writer(case):
+    """tfs_session_run on GraphDef bytes written by oracle/graph_writer.py (no product encoder involved), the whole
+    frame as one block, against the oracle's evaluator on the same bytes: bit-exact."""
+    from oracle import graph_writer, tf_ops
+    df = _golden.build_frame(case)
+    parts, cols = _golden.oracle_inputs(case, df)
+    columns = {c.name: (c.dtype, tuple(c.shape)) for c in cols if c.dtype is not None}
+    graph, _info = graph_writer.from_spec(case["graph"], columns)
+    feeds = _block_feeds(case, cols, parts, graph)
+    if feeds is None or any(v.size == 0 for v in feeds.values()):
+        pytest.skip("ragged or empty column: not one dense block")
+    fetches = list(case["graph"]["fetches"])
+    want = tf_ops.evaluate(graph, feeds, fetches)
+    with _native.Graph(graph) as gr, _native.Session(gr, 0) as s:
+        got = s.run(feeds, fetches)
+    for g_, w_ in zip(got, want):
+        assert_same(g_, np.asarray(w_))
+
+
 # ---- the reference's golden vectors through the product's operators --------------------------------
 @pytest.mark.parametrize("case", G["cases"], ids=[c["id"] for c in G["cases"]])
 def test_golden_through_operators(case):
