@@ -518,7 +518,8 @@ def run_reduce(ctx, wl, rows, cols=None):
     parity = {"full_block_vs_torch": "sum within 1e-12 of sum|x|, min bit-exact" + (", merged over all ranks" if world > 1 else "")}
 
     # ---- end to end: host (pinned) column buffers through the same C-ABI call -----------------
-    h2d = sum(v.numel() * v.element_size() for v in feeds_t.values())     # every fed placeholder is staged (reduce_1b feeds its column twice)
+    # one host buffer fed to two placeholders (reduce_1b: sum and min of the same column) is staged once by the library
+    h2d = sum(v.numel() * v.element_size() for v in {id(v): v for v in feeds_t.values()}.values())
     d2h = sum(v.numel() * v.element_size() for v in outs_t.values())
     e2e, pinned, host_in = None, [], {}
     if not args.no_e2e:

@@ -1423,6 +1423,7 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
   // workspace layout: staged host feeds, then every materialised node not bound to a caller buffer
   size_t ws_bytes = 0;
   std::vector<size_t> ws_off(N, SIZE_MAX);
+  std::vector<char> staged_twice(N, 0);      // a host feed that shares the staged copy of an earlier one
   bool needs_reduce_scratch = false;
   size_t red_bytes = 0;
   for (int idx : plan.needed) {
@@ -1430,7 +1431,21 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
     if (plan.feed_of[size_t(idx)] >= 0) {
       int f = plan.feed_of[size_t(idx)];
       if (feed_dev[size_t(f)]) dev_ptr[size_t(idx)] = feeds[size_t(f)].data;
-      else { ws_off[size_t(idx)] = ws_bytes; ws_bytes += align_up(nbytes(idx)); }
+      else {
+        // one host buffer fed to several placeholders (reduce_sum and reduce_min of the same column: the X / X_input
+        // contract gives every fetch its own placeholder) crosses PCIe once: placeholders are only ever read
+        for (int prev : plan.needed) {
+          if (prev == idx) break;
+          const int pf = plan.feed_of[size_t(prev)];
+          if (pf >= 0 && !feed_dev[size_t(pf)] && ws_off[size_t(prev)] != SIZE_MAX && feeds[size_t(pf)].data == feeds[size_t(f)].data &&
+              nbytes(prev) == nbytes(idx)) {
+            ws_off[size_t(idx)] = ws_off[size_t(prev)];
+            staged_twice[size_t(idx)] = 1;
+            break;
+          }
+        }
+        if (ws_off[size_t(idx)] == SIZE_MAX) { ws_off[size_t(idx)] = ws_bytes; ws_bytes += align_up(nbytes(idx)); }
+      }
     } else if (n.cls == OpClass::Const) {
       // uploaded lazily below
     } else if (plan.materialize[size_t(idx)]) {
@@ -1470,7 +1485,7 @@ void Session::run(const std::vector<TensorArg>& feeds, const std::vector<TensorA
   for (int idx : plan.needed) {
     if (plan.feed_of[size_t(idx)] < 0) continue;
     int f = plan.feed_of[size_t(idx)];
-    if (!feed_dev[size_t(f)] && nbytes(idx) > 0)
+    if (!feed_dev[size_t(f)] && nbytes(idx) > 0 && !staged_twice[size_t(idx)])
       copy_in(dev_ptr[size_t(idx)], feeds[size_t(f)].data, nbytes(idx));
   }
 

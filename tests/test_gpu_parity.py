@@ -1455,6 +1455,25 @@ def test_aggregate_segments_from_the_partition(n, n_keys, max_groups, monkeypatc
     assert outs[0][1].tobytes() == outs[1][1].tobytes() and np.array_equal(outs[0][0], outs[1][0])
 
 
+def test_one_host_column_fed_to_two_placeholders():
+    """reduce_sum and reduce_min of the same column: the X / X_input contract gives every fetch its own placeholder,
+    the caller feeds both from one host buffer, the library stages it once.  Same results as from two separate copies."""
+    rng = np.random.default_rng(5)
+    x = rng.integers(-1000, 1000, 3_000_001).astype(np.float64)
+    with dsl.withGraph():
+        a = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("s_input")
+        b = dsl.placeholder(tfs.DoubleType, dsl.Unknown).named("m_input")
+        g = dsl.build_graph(dsl.reduce_sum(a, [0]).named("s"), dsl.reduce_min(b, [0]).named("m"), (a + b).named("t"))
+    with _native.Graph(g) as gr, _native.Session(gr, 0) as s:
+        s1, m1, t1 = s.run({"s_input": x, "m_input": x}, ["s", "m", "t"])
+        s2, m2, t2 = s.run({"s_input": x, "m_input": x.copy()}, ["s", "m", "t"])
+        y = x[::-1].copy()
+        s3, m3, t3 = s.run({"s_input": x, "m_input": y}, ["s", "m", "t"])
+    assert s1 == x.sum() and m1 == x.min() and s1.tobytes() == s2.tobytes() and m1.tobytes() == m2.tobytes()
+    assert t1.tobytes() == (x + x).tobytes() == t2.tobytes() and t3.tobytes() == (x + y).tobytes()
+    assert s3 == x.sum() and m3 == y.min()
+
+
 def test_large_pageable_blocks_take_the_staged_copies():
     """numpy arrays (pageable memory) of 64 MiB and more go through the pinned staging ring in both directions;
     ragged sizes, two columns in, two out, plus the keyed path."""
