@@ -195,7 +195,11 @@ int tfs_session_resolve(tfs_session* s, int n_feeds, const tfs_tensor* feeds,
  *     declared shape (Shape.checkMorePreciseThan, Shape.scala:54-59).
  *   - if every feed and fetch pointer is a device pointer the call only
  *     enqueues work on the session stream and returns; otherwise it returns
- *     after the host buffers have been written. */
+ *     after the host buffers have been written.
+ *   - feeds are only read.  Several placeholders may be fed from one buffer
+ *     (reduce_sum and reduce_min of the same column: the X / X_input contract,
+ *     impl/DebugRowOps.scala:89-113, gives every fetch its own placeholder); a
+ *     host buffer fed more than once is copied to the device once. */
 int tfs_session_run(tfs_session* s, int n_feeds, const tfs_tensor* feeds,
                     int n_fetches, const tfs_tensor* fetches);
 
