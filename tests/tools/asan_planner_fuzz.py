@@ -3,7 +3,7 @@
 Build the instrumented host side next to the regular device objects and run:
 
     mkdir -p oracle/_build/asan
-    for f in graph capi session host_staging; do
+    for f in graph capi session host_staging comm; do
       nvcc -O1 -g -std=c++17 -gencode arch=compute_100a,code=sm_100a \
            -Xcompiler -fPIC,-fsanitize=address,-fno-omit-frame-pointer \
            -x cu -c tensorframes_b200/csrc/$f.cpp -o oracle/_build/asan/$f.o; done
@@ -16,7 +16,9 @@ Build the instrumented host side next to the regular device objects and run:
 Every mutated graph that still imports is planned for every node as a fetch, in block and in row mode, with
 placeholder dimensions drawn from {0, 1, 16, 2^40}.  Any outcome but a sanitizer report is fine.
 Round 1: 36000 mutations and the whole CPU suite ran clean against the instrumented build; 20000 more under
--fsanitize=undefined (same recipe, libubsan preloaded) reported nothing either.
+-fsanitize=undefined (same recipe, libubsan preloaded) reported nothing either.  Round 2 (comm.cpp added to the list of
+instrumented files; the library now also holds tfs_graph_analyze, the pack / unpack helpers and the exchange steps):
+12000 mutations and the 421 CPU tests, clean.
 """
 import os
 import sys
